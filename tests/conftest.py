@@ -1,0 +1,33 @@
+import importlib
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+REFERENCE = "/root/reference"
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
+    config.addinivalue_line("markers", "slow: multi-second CPU oracle runs")
+
+
+def pkg():
+    """The product package (its directory name carries a hyphen, so import by string)."""
+    return importlib.import_module("hunyuanworld-mirror_b200")
+
+
+@pytest.fixture(scope="session")
+def wmpkg():
+    return pkg()
+
+
+@pytest.fixture(scope="session")
+def state_dict_full():
+    w = importlib.import_module("hunyuanworld-mirror_b200.weights")
+    return w.synthetic_state_dict(seed=0)
