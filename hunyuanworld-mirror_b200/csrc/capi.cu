@@ -1,0 +1,647 @@
+// C ABI of libwm_b200 (include/wm_b200.h): handle, weight ingestion under the reference state_dict keys,
+// workspace carving, the forward pass of the aggregator as a stream-ordered launch sequence, and the NCCL
+// K|V all-gather used by sequence-parallel global attention.  No allocation, sync or host round-trip happens
+// inside wm_forward / wm_forward_tokens / wm_embed.
+#include <dlfcn.h>
+#include <math.h>
+
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "ops.cuh"
+
+namespace wm {
+
+char* error_buffer() {
+  static thread_local char buf[512] = {0};
+  return buf;
+}
+
+wm_status tmap_encode(CUtensorMap* out, CUtensorMapDataType dtype, int rank, const void* base, const uint64_t* dims,
+                      const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle sw) {
+  typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static encode_fn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    WM_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    if (!p || q != cudaDriverEntryPointSuccess) return fail(WM_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
+    fn = reinterpret_cast<encode_fn>(p);
+  }
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  cuuint64_t d[5], s[4];
+  cuuint32_t b[5];
+  for (int i = 0; i < rank; ++i) d[i] = dims[i], b[i] = box[i];
+  for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
+  const CUresult r = fn(out, dtype, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(WM_ERR_CUDA, "cuTensorMapEncodeTiled failed (CUresult %d): rank %d dims %llu,%llu,%llu stride0 %llu box %u,%u",
+                (int)r, rank, (unsigned long long)d[0], (unsigned long long)d[1], (unsigned long long)(rank > 2 ? d[2] : 0),
+                (unsigned long long)s[0], b[0], b[1]);
+  return WM_OK;
+}
+
+wm_status require_sm100(int* sm_count) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(WM_ERR_ARCH, "no CUDA device: %s (libwm_b200 has no CPU path)", cudaGetErrorString(e));
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, dev);
+  if (e != cudaSuccess) return fail(WM_ERR_ARCH, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+  if (prop.major != 10)
+    return fail(WM_ERR_ARCH, "device %d is sm_%d%d; libwm_b200 is built for sm_100a (B200) only", dev, prop.major, prop.minor);
+  *sm_count = prop.multiProcessorCount;
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ handle
+struct DevTensor {
+  float* f32 = nullptr;
+  __nv_bfloat16* b16 = nullptr;
+  std::vector<int64_t> shape;
+  int ld = 0;
+};
+
+struct BlockW {
+  const float *n1w, *n1b, *n2w, *n2b, *qkv_b, *qn_w, *qn_b, *kn_w, *kn_b, *proj_b, *ls1, *ls2, *fc1_b, *fc2_b;
+  const __nv_bfloat16 *qkv_w, *proj_w, *fc1_w, *fc2_w;
+};
+
+typedef struct ncclComm* nccl_comm_t;
+struct nccl_uid {
+  char internal[128];
+};
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(nccl_uid*) = nullptr;
+  int (*CommInitRank)(nccl_comm_t*, int, nccl_uid, int) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, nccl_comm_t, cudaStream_t) = nullptr;
+  int (*CommDestroy)(nccl_comm_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+
+static wm_status nccl_open(const char* path, NcclApi* api) {
+  WM_CHECK(path && *path, "nccl: library path is empty");
+  api->lib = dlopen(path, RTLD_NOW | RTLD_GLOBAL);
+  if (!api->lib) return fail(WM_ERR_NCCL, "dlopen(%s): %s", path, dlerror());
+  api->GetUniqueId = reinterpret_cast<int (*)(nccl_uid*)>(dlsym(api->lib, "ncclGetUniqueId"));
+  api->CommInitRank = reinterpret_cast<int (*)(nccl_comm_t*, int, nccl_uid, int)>(dlsym(api->lib, "ncclCommInitRank"));
+  api->AllGather = reinterpret_cast<int (*)(const void*, void*, size_t, int, nccl_comm_t, cudaStream_t)>(
+      dlsym(api->lib, "ncclAllGather"));
+  api->CommDestroy = reinterpret_cast<int (*)(nccl_comm_t)>(dlsym(api->lib, "ncclCommDestroy"));
+  api->GetErrorString = reinterpret_cast<const char* (*)(int)>(dlsym(api->lib, "ncclGetErrorString"));
+  if (!api->GetUniqueId || !api->CommInitRank || !api->AllGather || !api->CommDestroy || !api->GetErrorString)
+    return fail(WM_ERR_NCCL, "%s does not export the NCCL entry points", path);
+  return WM_OK;
+}
+
+}  // namespace wm
+
+struct wm_handle {
+  wm_config cfg{};
+  std::unordered_map<std::string, wm::DevTensor> w;
+  bool finalized = false;
+  std::vector<wm::BlockW> dino, frame, global;
+  float *rope_cos = nullptr, *rope_sin = nullptr;
+  int rope_max_pos = 0;
+  float* dino_table = nullptr;  // [5 + gh*gw, 1024]
+  int table_gh = 0, table_gw = 0;
+  wm::NcclApi nccl;
+  wm::nccl_comm_t comm = nullptr;
+  int rank = 0, world = 1;
+};
+
+namespace wm {
+
+static bool ends_with(const std::string& s, const char* suf) {
+  const size_t n = strlen(suf);
+  return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+
+// ------------------------------------------------------------------------------------------------ tables
+__global__ void dino_table_kernel(const float* __restrict__ cls, const float* __restrict__ reg,
+                                  const float* __restrict__ pos, const float* __restrict__ conv_bias, int rows,
+                                  float* __restrict__ table) {
+  // row 0: cls + pos[0]; rows 1-4: register tokens (no positional term); row 5+p: pos[1+p] + conv bias
+  // (vision_transformer.py:209-221; the conv bias is folded here so the GEMM epilogue has one addend).
+  const int r = blockIdx.x;
+  if (r >= rows) return;
+  for (int c = threadIdx.x; c < kEmbed; c += blockDim.x) {
+    float v;
+    if (r == 0)
+      v = cls[c] + pos[c];
+    else if (r < kDinoSpecial)
+      v = reg[(r - 1) * kEmbed + c];
+    else
+      v = pos[(size_t)(r - kDinoSpecial + 1) * kEmbed + c] + conv_bias[c];
+    table[(size_t)r * kEmbed + c] = v;
+  }
+}
+
+static wm_status build_dino_table(wm_handle* h, int gh, int gw, const float* pos_dev) {
+  const int rows = kDinoSpecial + gh * gw;
+  if (h->dino_table) cudaFree(h->dino_table);
+  h->dino_table = nullptr;
+  WM_CUDA(cudaMalloc(&h->dino_table, (size_t)rows * kEmbed * sizeof(float)));
+  dino_table_kernel<<<rows, 256>>>(h->w["patch_embed.cls_token"].f32, h->w["patch_embed.register_tokens"].f32, pos_dev,
+                                   h->w["patch_embed.patch_embed.proj.bias"].f32, rows, h->dino_table);
+  WM_LAUNCH_CHECK();
+  WM_CUDA(cudaDeviceSynchronize());
+  h->table_gh = gh, h->table_gw = gw;
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ workspace
+struct Workspace {
+  float *xd, *x;
+  __nv_bfloat16 *ln, *q, *kv, *att, *hid;
+  size_t bytes;
+};
+
+static size_t align_up(size_t v) { return (v + 1023) & ~(size_t)1023; }
+
+static Workspace carve(void* base, int n, int gh, int gw, int world) {
+  const size_t g = (size_t)gh * gw, Td = n * (kDinoSpecial + g), T = n * (kPatchStart + g);
+  uint8_t* p = static_cast<uint8_t*>(base);
+  size_t off = 0;
+  Workspace ws;
+  auto take = [&](size_t bytes) {
+    uint8_t* r = p ? p + off : nullptr;
+    off += align_up(bytes);
+    return r;
+  };
+  ws.xd = reinterpret_cast<float*>(take(Td * kEmbed * 4));
+  ws.x = reinterpret_cast<float*>(take(T * kEmbed * 4));
+  ws.ln = reinterpret_cast<__nv_bfloat16*>(take(T * kEmbed * 2));
+  ws.q = reinterpret_cast<__nv_bfloat16*>(take(T * kEmbed * 2));
+  ws.kv = reinterpret_cast<__nv_bfloat16*>(take(T * (size_t)world * 2 * kEmbed * 2));
+  ws.att = reinterpret_cast<__nv_bfloat16*>(take(T * kEmbed * 2));
+  ws.hid = reinterpret_cast<__nv_bfloat16*>(take(T * kMlp * 2));
+  ws.bytes = off + 1024;  // slack so the caller's base may be aligned up to 1024
+  return ws;
+}
+
+static void* align_base(void* p) { return reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~(uintptr_t)1023); }
+
+// ------------------------------------------------------------------------------------------------ blocks
+struct BlockShape {
+  int T;          // rows of the residual stream on this rank
+  int batch;      // attention batch (views for frame / DINOv2, 1 for global)
+  int Lq, Lkv;    // per batch entry
+  int kv_row0;    // row of this rank's first K|V row inside ws.kv (global blocks under SP)
+  int tokens_per_view, patch_start, grid_w;
+  bool rope;
+  float eps;
+};
+
+// Block.forward eval branch (block.py:91-92): x += ls1 * attn(norm1(x)); x += ls2 * mlp(norm2(x))
+static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const BlockShape& s, const Workspace& ws,
+                           float* x, float* out2, int out2_col, bool gather) {
+  WM_TRY(layernorm(st, x, w.n1w, w.n1b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
+  __nv_bfloat16* kv_local = ws.kv + (size_t)s.kv_row0 * 2 * kEmbed;
+  WM_TRY(gemm_qkv(st, ws.ln, kEmbed, w.qkv_w, w.qkv_b, w.qn_w, w.qn_b, w.kn_w, w.kn_b, 1e-5f,
+                  s.rope ? h->rope_cos : nullptr, s.rope ? h->rope_sin : nullptr, s.tokens_per_view, s.patch_start,
+                  s.grid_w, s.T, ws.q, kv_local));
+  if (gather) {
+    const size_t bytes = (size_t)s.T * 2 * kEmbed * 2;
+    const int r = h->nccl.AllGather(kv_local, ws.kv, bytes, /*ncclChar*/ 0, h->comm, st);
+    if (r != 0) return fail(WM_ERR_NCCL, "ncclAllGather: %s", h->nccl.GetErrorString(r));
+  }
+  const __nv_bfloat16* kbase = gather ? ws.kv : kv_local;
+  WM_TRY(flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv,
+                         kHeads, 0.125f, 0, 0, 0));
+  WM_TRY(gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x, kEmbed, nullptr,
+                          0, 0));
+  WM_TRY(layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
+  WM_TRY(gemm_bias_act(st, ws.ln, kEmbed, w.fc1_w, kEmbed, w.fc1_b, s.T, kMlp, kEmbed, ws.hid, kMlp, 1));
+  WM_TRY(gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed, out2,
+                          2 * kEmbed, out2_col));
+  return WM_OK;
+}
+
+static wm_status check_ready(const wm_handle* h, const void* workspace, size_t workspace_bytes, int n, int gh, int gw) {
+  WM_CHECK(h, "null handle");
+  if (!h->finalized) return fail(WM_ERR_STATE, "weights are not finalised (call wm_finalize_weights)");
+  WM_CHECK(n > 0 && gh > 0 && gw > 0, "n_views and the patch grid must be positive");
+  WM_CHECK(gh + 1 <= h->rope_max_pos && gw + 1 <= h->rope_max_pos, "patch grid %dx%d exceeds the RoPE table (%d)", gh, gw,
+           h->rope_max_pos);
+  const size_t need = carve(nullptr, n, gh, gw, h->world).bytes;
+  if (!workspace || workspace_bytes < need)
+    return fail(WM_ERR_STATE, "workspace too small: %zu bytes given, %zu needed", workspace_bytes, need);
+  return WM_OK;
+}
+
+static wm_status run_stack(wm_handle* h, cudaStream_t st, const Workspace& ws, int n, int gh, int gw, float* const* out) {
+  const int P = kPatchStart + gh * gw, T = n * P;
+  BlockShape fs{T, n, P, P, 0, P, kPatchStart, gw, true, 1e-5f};
+  BlockShape gs{T, 1, T, T * h->world, h->rank * T, P, kPatchStart, gw, true, 1e-5f};
+  int next_out = 0;
+  for (int i = 0; i < h->cfg.depth; ++i) {
+    float* o = nullptr;
+    if (next_out < h->cfg.n_intermediate && h->cfg.intermediate[next_out] == i) o = out[next_out++];
+    WM_TRY(run_block(h, st, h->frame[i], fs, ws, ws.x, o, 0, false));
+    WM_TRY(run_block(h, st, h->global[i], gs, ws, ws.x, o, kEmbed, h->world > 1));
+  }
+  return WM_OK;
+}
+
+static wm_status run_embed(wm_handle* h, cudaStream_t st, const Workspace& ws, const float* images, const float* depth,
+                           const float* rays, const float* poses, const int flags[3], int n, int H, int W,
+                           int first_view) {
+  const int gh = H / kPatch, gw = W / kPatch, g = gh * gw;
+  const int Pd = kDinoSpecial + g, P = kPatchStart + g, Td = n * Pd, T = n * P;
+  if (h->table_gh != gh || h->table_gw != gw) {
+    if (gh == 37 && gw == 37)
+      return fail(WM_ERR_STATE, "internal: native DINOv2 table missing");
+    return fail(WM_ERR_STATE, "no DINOv2 positional table for a %dx%d grid: call wm_set_dino_pos_table first", gh, gw);
+  }
+  // a1-a3: normalise + patch gather -> GEMM(588->1024) + pos/cls/reg table
+  const int ld_pe = 640;
+  __nv_bfloat16* a_pe = ws.hid;  // free until the first fc1
+  WM_CUDA(cudaMemsetAsync(a_pe, 0, (size_t)Td * ld_pe * 2, st));
+  WM_TRY(patch_gather(st, images, n, 3, H, W, Pd, kDinoSpecial, ld_pe, 1, a_pe));
+  const DevTensor& pew = h->w["patch_embed.patch_embed.proj.weight"];
+  WM_TRY(gemm_table(st, a_pe, ld_pe, pew.b16, pew.ld, h->dino_table, Pd, Td, kEmbed, ld_pe, ws.xd, kEmbed));
+  // a4: DINOv2 blocks (no rope, no qk-norm, eps 1e-6)
+  BlockShape ds{Td, n, Pd, Pd, 0, Pd, 0, gw, false, 1e-6f};
+  for (int i = 0; i < h->cfg.dino_depth; ++i) WM_TRY(run_block(h, st, h->dino[i], ds, ws, ws.xd, nullptr, 0, false));
+  // a6 (depth): pixel-unshuffle -> fc1+GELU -> fc2 written to the patch rows of x, then the final norm accumulates
+  const bool pose_on = flags[0] == 1 && poses, depth_on = flags[1] == 1 && depth, ray_on = flags[2] == 1 && rays;
+  if (depth_on) {
+    const int ld_d = 256;
+    __nv_bfloat16* a_d = ws.q;
+    WM_CUDA(cudaMemsetAsync(a_d, 0, (size_t)T * ld_d * 2, st));
+    WM_TRY(patch_gather(st, depth, n, 1, H, W, P, kPatchStart, ld_d, 0, a_d));
+    const DevTensor& f1 = h->w["depth_embed.proj.2.fc1.weight"];
+    const DevTensor& f2 = h->w["depth_embed.proj.2.fc2.weight"];
+    WM_TRY(gemm_bias_act(st, a_d, ld_d, f1.b16, f1.ld, h->w["depth_embed.proj.2.fc1.bias"].f32, T, kMlp, ld_d, ws.hid,
+                         kMlp, 1));
+    WM_TRY(gemm_ls_residual(st, ws.hid, kMlp, f2.b16, f2.ld, h->w["depth_embed.proj.2.fc2.bias"].f32, nullptr, T, kEmbed,
+                            kMlp, ws.x, kEmbed, nullptr, 0, 0));
+  }
+  // final DINOv2 norm of the patch rows -> rows [7, 7+g) of x  (vision_transformer.py:259-263)
+  WM_TRY(layernorm(st, ws.xd, h->w["patch_embed.norm.weight"].f32, h->w["patch_embed.norm.bias"].f32, 1e-6f, n * g, g, Pd,
+                   kDinoSpecial, P, kPatchStart, ws.x, 1, depth_on ? 1 : 0));
+  // a5-a7: special + prior tokens
+  WM_TRY(special_tokens(st, h->w["cam_token"].f32, h->w["reg_token"].f32, n, P, first_view, !pose_on, !ray_on, ws.x));
+  if (pose_on)
+    WM_TRY(prior_token(st, poses, n, 7, h->w["pose_embed.0.weight"].f32, h->w["pose_embed.0.bias"].f32,
+                       h->w["pose_embed.2.weight"].f32, h->w["pose_embed.2.bias"].f32, P, 5, ws.x));
+  if (ray_on)
+    WM_TRY(prior_token(st, rays, n, 4, h->w["ray_embed.0.weight"].f32, h->w["ray_embed.0.bias"].f32,
+                       h->w["ray_embed.2.weight"].f32, h->w["ray_embed.2.bias"].f32, P, 6, ws.x));
+  return WM_OK;
+}
+
+}  // namespace wm
+
+using namespace wm;
+
+// ================================================================================================ C ABI
+extern "C" {
+
+int wm_version(void) { return 100; }
+const char* wm_last_error(void) { return error_buffer(); }
+
+wm_status wm_create(const wm_config* cfg, wm_handle** out) {
+  WM_CHECK(cfg && out, "wm_create: null argument");
+  WM_CHECK(cfg->depth >= 0 && cfg->depth <= 64 && cfg->dino_depth >= 0 && cfg->dino_depth <= 64, "wm_create: bad depth");
+  WM_CHECK(cfg->n_intermediate >= 0 && cfg->n_intermediate <= 4, "wm_create: n_intermediate must be in [0,4]");
+  for (int i = 0; i < cfg->n_intermediate; ++i)
+    WM_CHECK(cfg->intermediate[i] >= 0 && cfg->intermediate[i] < cfg->depth &&
+                 (i == 0 || cfg->intermediate[i] > cfg->intermediate[i - 1]),
+             "wm_create: intermediate layers must be increasing and < depth");
+  int sms = 0;
+  WM_TRY(require_sm100(&sms));
+  wm_handle* h = new (std::nothrow) wm_handle();
+  WM_CHECK(h, "wm_create: out of host memory");
+  h->cfg = *cfg;
+  h->rope_max_pos = 512;
+  std::vector<float> c((h->rope_max_pos + 1) * 16), s((h->rope_max_pos + 1) * 16);
+  wm_rope_tables(h->rope_max_pos, c.data(), s.data());
+  cudaError_t e = cudaMalloc(&h->rope_cos, c.size() * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&h->rope_sin, s.size() * 4);
+  if (e == cudaSuccess) e = cudaMemcpy(h->rope_cos, c.data(), c.size() * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(h->rope_sin, s.data(), s.size() * 4, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    wm_destroy(h);
+    return fail(WM_ERR_CUDA, "wm_create: %s", cudaGetErrorString(e));
+  }
+  *out = h;
+  return WM_OK;
+}
+
+void wm_destroy(wm_handle* h) {
+  if (!h) return;
+  for (auto& kv : h->w) {
+    if (kv.second.f32) cudaFree(kv.second.f32);
+    if (kv.second.b16) cudaFree(kv.second.b16);
+  }
+  if (h->rope_cos) cudaFree(h->rope_cos);
+  if (h->rope_sin) cudaFree(h->rope_sin);
+  if (h->dino_table) cudaFree(h->dino_table);
+  if (h->comm && h->nccl.CommDestroy) h->nccl.CommDestroy(h->comm);
+  delete h;
+}
+
+wm_status wm_load_weight(wm_handle* h, const char* ref_key, const float* data, const int64_t* shape, int ndim) {
+  WM_CHECK(h && ref_key && data && shape && ndim >= 1 && ndim <= 4, "wm_load_weight: bad argument");
+  const std::string key(ref_key);
+  int64_t numel = 1;
+  for (int i = 0; i < ndim; ++i) {
+    WM_CHECK(shape[i] > 0, "wm_load_weight(%s): non-positive dimension", ref_key);
+    numel *= shape[i];
+  }
+  DevTensor t;
+  t.shape.assign(shape, shape + ndim);
+  float* tmp = nullptr;
+  WM_CUDA(cudaMalloc(&tmp, (size_t)numel * 4));
+  cudaError_t e = cudaMemcpy(tmp, data, (size_t)numel * 4, cudaMemcpyDefault);
+  if (e != cudaSuccess) {
+    cudaFree(tmp);
+    return fail(WM_ERR_CUDA, "wm_load_weight(%s): %s", ref_key, cudaGetErrorString(e));
+  }
+  const bool gemm_w = ends_with(key, "attn.qkv.weight") || ends_with(key, "attn.proj.weight") ||
+                      ends_with(key, "mlp.fc1.weight") || ends_with(key, "mlp.fc2.weight") ||
+                      key == "depth_embed.proj.2.fc1.weight" || key == "depth_embed.proj.2.fc2.weight" ||
+                      key == "patch_embed.patch_embed.proj.weight";
+  if (gemm_w) {
+    const int64_t rows = shape[0], cols = numel / rows;
+    const int ld = (int)((cols + 63) / 64 * 64);  // K padded to whole 64-element TMA boxes (588 -> 640, 196 -> 256)
+    e = cudaMalloc(&t.b16, (size_t)rows * ld * 2);
+    if (e != cudaSuccess) {
+      cudaFree(tmp);
+      return fail(WM_ERR_CUDA, "wm_load_weight(%s): %s", ref_key, cudaGetErrorString(e));
+    }
+    wm_status s = pack_bf16_rows(0, tmp, rows, (int)cols, ld, t.b16);
+    cudaError_t e2 = cudaDeviceSynchronize();
+    cudaFree(tmp);
+    if (s != WM_OK) return s;
+    if (e2 != cudaSuccess) return fail(WM_ERR_CUDA, "wm_load_weight(%s): %s", ref_key, cudaGetErrorString(e2));
+    t.ld = ld;
+  } else {
+    t.f32 = tmp;
+    t.ld = (int)shape[ndim - 1];
+  }
+  auto it = h->w.find(key);
+  if (it != h->w.end()) {
+    if (it->second.f32) cudaFree(it->second.f32);
+    if (it->second.b16) cudaFree(it->second.b16);
+  }
+  h->w[key] = t;
+  h->finalized = false;
+  return WM_OK;
+}
+
+static wm_status need(wm_handle* h, const std::string& key, int64_t numel, bool bf16, const void** out) {
+  auto it = h->w.find(key);
+  if (it == h->w.end()) return fail(WM_ERR_STATE, "missing weight: %s", key.c_str());
+  int64_t n = 1;
+  for (int64_t d : it->second.shape) n *= d;
+  if (n != numel) return fail(WM_ERR_STATE, "weight %s has %lld elements, expected %lld", key.c_str(), (long long)n, (long long)numel);
+  const void* p = bf16 ? (const void*)it->second.b16 : (const void*)it->second.f32;
+  if (!p) return fail(WM_ERR_STATE, "weight %s is stored in the wrong precision", key.c_str());
+  *out = p;
+  return WM_OK;
+}
+
+static wm_status resolve_block(wm_handle* h, const std::string& pre, bool qk_norm, BlockW* b) {
+  const int C = kEmbed, M = kMlp;
+#define NEEDF(field, name, n) WM_TRY(need(h, pre + name, n, false, reinterpret_cast<const void**>(&b->field)))
+#define NEEDB(field, name, n) WM_TRY(need(h, pre + name, n, true, reinterpret_cast<const void**>(&b->field)))
+  NEEDF(n1w, "norm1.weight", C);
+  NEEDF(n1b, "norm1.bias", C);
+  NEEDB(qkv_w, "attn.qkv.weight", 3LL * C * C);
+  NEEDF(qkv_b, "attn.qkv.bias", 3 * C);
+  b->qn_w = b->qn_b = b->kn_w = b->kn_b = nullptr;
+  if (qk_norm) {
+    NEEDF(qn_w, "attn.q_norm.weight", kHeadDim);
+    NEEDF(qn_b, "attn.q_norm.bias", kHeadDim);
+    NEEDF(kn_w, "attn.k_norm.weight", kHeadDim);
+    NEEDF(kn_b, "attn.k_norm.bias", kHeadDim);
+  }
+  NEEDB(proj_w, "attn.proj.weight", (int64_t)C * C);
+  NEEDF(proj_b, "attn.proj.bias", C);
+  NEEDF(ls1, "ls1.gamma", C);
+  NEEDF(n2w, "norm2.weight", C);
+  NEEDF(n2b, "norm2.bias", C);
+  NEEDB(fc1_w, "mlp.fc1.weight", (int64_t)M * C);
+  NEEDF(fc1_b, "mlp.fc1.bias", M);
+  NEEDB(fc2_w, "mlp.fc2.weight", (int64_t)C * M);
+  NEEDF(fc2_b, "mlp.fc2.bias", C);
+  NEEDF(ls2, "ls2.gamma", C);
+#undef NEEDF
+#undef NEEDB
+  return WM_OK;
+}
+
+wm_status wm_finalize_weights(wm_handle* h) {
+  WM_CHECK(h, "wm_finalize_weights: null handle");
+  h->dino.assign(h->cfg.dino_depth, BlockW{});
+  h->frame.assign(h->cfg.depth, BlockW{});
+  h->global.assign(h->cfg.depth, BlockW{});
+  for (int i = 0; i < h->cfg.dino_depth; ++i)
+    WM_TRY(resolve_block(h, "patch_embed.blocks." + std::to_string(i) + ".", false, &h->dino[i]));
+  for (int i = 0; i < h->cfg.depth; ++i) {
+    WM_TRY(resolve_block(h, "frame_blocks." + std::to_string(i) + ".", true, &h->frame[i]));
+    WM_TRY(resolve_block(h, "global_blocks." + std::to_string(i) + ".", true, &h->global[i]));
+  }
+  const void* p;
+  const int C = kEmbed;
+  WM_TRY(need(h, "cam_token", 2 * C, false, &p));
+  WM_TRY(need(h, "reg_token", 8 * C, false, &p));
+  WM_TRY(need(h, "patch_embed.cls_token", C, false, &p));
+  WM_TRY(need(h, "patch_embed.pos_embed", 1370LL * C, false, &p));
+  WM_TRY(need(h, "patch_embed.register_tokens", 4 * C, false, &p));
+  WM_TRY(need(h, "patch_embed.patch_embed.proj.weight", 588LL * C, true, &p));
+  WM_TRY(need(h, "patch_embed.patch_embed.proj.bias", C, false, &p));
+  WM_TRY(need(h, "patch_embed.norm.weight", C, false, &p));
+  WM_TRY(need(h, "patch_embed.norm.bias", C, false, &p));
+  WM_TRY(need(h, "pose_embed.0.weight", 7 * C, false, &p));
+  WM_TRY(need(h, "pose_embed.0.bias", C, false, &p));
+  WM_TRY(need(h, "pose_embed.2.weight", (int64_t)C * C, false, &p));
+  WM_TRY(need(h, "pose_embed.2.bias", C, false, &p));
+  WM_TRY(need(h, "ray_embed.0.weight", 4 * C, false, &p));
+  WM_TRY(need(h, "ray_embed.0.bias", C, false, &p));
+  WM_TRY(need(h, "ray_embed.2.weight", (int64_t)C * C, false, &p));
+  WM_TRY(need(h, "ray_embed.2.bias", C, false, &p));
+  WM_TRY(need(h, "depth_embed.proj.2.fc1.weight", 196LL * kMlp, true, &p));
+  WM_TRY(need(h, "depth_embed.proj.2.fc1.bias", kMlp, false, &p));
+  WM_TRY(need(h, "depth_embed.proj.2.fc2.weight", (int64_t)C * kMlp, true, &p));
+  WM_TRY(need(h, "depth_embed.proj.2.fc2.bias", C, false, &p));
+  WM_TRY(build_dino_table(h, 37, 37, h->w["patch_embed.pos_embed"].f32));
+  h->finalized = true;
+  return WM_OK;
+}
+
+wm_status wm_set_dino_pos_table(wm_handle* h, int gh, int gw, const float* pos) {
+  WM_CHECK(h && pos && gh > 0 && gw > 0, "wm_set_dino_pos_table: bad argument");
+  if (!h->finalized) return fail(WM_ERR_STATE, "wm_set_dino_pos_table: finalise the weights first");
+  const size_t bytes = (size_t)(1 + gh * gw) * kEmbed * 4;
+  float* tmp = nullptr;
+  WM_CUDA(cudaMalloc(&tmp, bytes));
+  cudaError_t e = cudaMemcpy(tmp, pos, bytes, cudaMemcpyDefault);
+  wm_status s = e == cudaSuccess ? build_dino_table(h, gh, gw, tmp) : fail(WM_ERR_CUDA, "wm_set_dino_pos_table: %s", cudaGetErrorString(e));
+  cudaFree(tmp);
+  return s;
+}
+
+size_t wm_workspace_bytes(const wm_handle* h, int n_views, int H, int W, int world) {
+  (void)h;
+  if (n_views <= 0 || H <= 0 || W <= 0 || world <= 0 || H % kPatch || W % kPatch) return 0;
+  return carve(nullptr, n_views, H / kPatch, W / kPatch, world).bytes;
+}
+
+wm_status wm_forward(wm_handle* h, wm_stream stream, const float* images, const float* depth, const float* rays,
+                     const float* poses, const int cond_flags[3], int n_views, int H, int W, int first_view,
+                     float* const* out, void* workspace, size_t workspace_bytes) {
+  WM_CHECK(images && cond_flags && out, "wm_forward: null argument");
+  WM_CHECK(H > 0 && W > 0 && H % kPatch == 0 && W % kPatch == 0, "wm_forward: H and W must be positive multiples of 14 (got %dx%d)", H, W);
+  const int gh = H / kPatch, gw = W / kPatch;
+  WM_TRY(check_ready(h, workspace, workspace_bytes, n_views, gh, gw));
+  for (int i = 0; i < h->cfg.n_intermediate; ++i) WM_CHECK(out[i], "wm_forward: out[%d] is null", i);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const Workspace ws = carve(align_base(workspace), n_views, gh, gw, h->world);
+  WM_TRY(run_embed(h, st, ws, images, depth, rays, poses, cond_flags, n_views, H, W, first_view));
+  return run_stack(h, st, ws, n_views, gh, gw, out);
+}
+
+wm_status wm_embed(wm_handle* h, wm_stream stream, const float* images, const float* depth, const float* rays,
+                   const float* poses, const int cond_flags[3], int n_views, int H, int W, int first_view, float* x,
+                   void* workspace, size_t workspace_bytes) {
+  WM_CHECK(images && cond_flags && x, "wm_embed: null argument");
+  WM_CHECK(H > 0 && W > 0 && H % kPatch == 0 && W % kPatch == 0, "wm_embed: H and W must be positive multiples of 14 (got %dx%d)", H, W);
+  const int gh = H / kPatch, gw = W / kPatch;
+  WM_TRY(check_ready(h, workspace, workspace_bytes, n_views, gh, gw));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const Workspace ws = carve(align_base(workspace), n_views, gh, gw, h->world);
+  WM_TRY(run_embed(h, st, ws, images, depth, rays, poses, cond_flags, n_views, H, W, first_view));
+  WM_CUDA(cudaMemcpyAsync(x, ws.x, (size_t)n_views * (kPatchStart + gh * gw) * kEmbed * 4, cudaMemcpyDeviceToDevice, st));
+  return WM_OK;
+}
+
+wm_status wm_forward_tokens(wm_handle* h, wm_stream stream, float* x, int n_views, int gh, int gw, float* const* out,
+                            void* workspace, size_t workspace_bytes) {
+  WM_CHECK(x && out, "wm_forward_tokens: null argument");
+  WM_TRY(check_ready(h, workspace, workspace_bytes, n_views, gh, gw));
+  for (int i = 0; i < h->cfg.n_intermediate; ++i) WM_CHECK(out[i], "wm_forward_tokens: out[%d] is null", i);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Workspace ws = carve(align_base(workspace), n_views, gh, gw, h->world);
+  ws.x = x;  // run in place on the caller's token buffer
+  return run_stack(h, st, ws, n_views, gh, gw, out);
+}
+
+// ---------------------------------------------------------------------------------------------- NCCL
+wm_status wm_nccl_unique_id(const char* nccl_lib, void* unique_id_128) {
+  WM_CHECK(unique_id_128, "wm_nccl_unique_id: null output");
+  NcclApi api;
+  WM_TRY(nccl_open(nccl_lib, &api));
+  nccl_uid id;
+  const int r = api.GetUniqueId(&id);
+  if (r != 0) return fail(WM_ERR_NCCL, "ncclGetUniqueId: %s", api.GetErrorString(r));
+  memcpy(unique_id_128, &id, sizeof(id));
+  return WM_OK;
+}
+
+wm_status wm_nccl_init(wm_handle* h, const char* nccl_lib, const void* unique_id_128, int rank, int world) {
+  WM_CHECK(h && unique_id_128 && world >= 1 && rank >= 0 && rank < world, "wm_nccl_init: bad argument");
+  WM_TRY(nccl_open(nccl_lib, &h->nccl));
+  nccl_uid id;
+  memcpy(&id, unique_id_128, sizeof(id));
+  const int r = h->nccl.CommInitRank(&h->comm, world, id, rank);
+  if (r != 0) return fail(WM_ERR_NCCL, "ncclCommInitRank: %s", h->nccl.GetErrorString(r));
+  h->rank = rank, h->world = world;
+  return WM_OK;
+}
+
+wm_status wm_nccl_allgather(wm_handle* h, wm_stream stream, void* buf, size_t bytes_per_rank) {
+  WM_CHECK(h && buf && bytes_per_rank > 0, "wm_nccl_allgather: bad argument");
+  if (!h->comm) return fail(WM_ERR_STATE, "wm_nccl_allgather: no communicator (call wm_nccl_init)");
+  const int r = h->nccl.AllGather(static_cast<uint8_t*>(buf) + (size_t)h->rank * bytes_per_rank, buf, bytes_per_rank, 0,
+                                  h->comm, static_cast<cudaStream_t>(stream));
+  if (r != 0) return fail(WM_ERR_NCCL, "ncclAllGather: %s", h->nccl.GetErrorString(r));
+  return WM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- micro-ops
+wm_status wm_layernorm(wm_stream stream, const float* x, const float* w, const float* b, float eps, int rows, void* y,
+                       int out_f32) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return layernorm(static_cast<cudaStream_t>(stream), x, w, b, eps, rows, rows > 0 ? rows : 1, 0, 0, 0, 0, y, out_f32, 0);
+}
+
+wm_status wm_gemm_bias_act(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias, int M,
+                           int N, int K, void* out, int ldo, int gelu) {
+  return gemm_bias_act(static_cast<cudaStream_t>(stream), A, lda, W, ldw, bias, M, N, K, out, ldo, gelu);
+}
+
+wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const float* bias, const float* qn_w,
+                      const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
+                      const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q, void* kv) {
+  return gemm_qkv(static_cast<cudaStream_t>(stream), A, kEmbed, W, bias, qn_w, qn_b, kn_w, kn_b, qk_eps, rope_cos,
+                  rope_sin, tokens_per_view, patch_start, grid_w, M, q, kv);
+}
+
+wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
+                              const float* gamma, int M, int N, int K, float* x, int ldx, float* out2, int ld2,
+                              int out2_col) {
+  return gemm_ls_residual(static_cast<cudaStream_t>(stream), A, lda, W, ldw, bias, gamma, M, N, K, x, ldx, out2, ld2,
+                          out2_col);
+}
+
+wm_status wm_gemm_table(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* table,
+                        int period, int M, int N, int K, float* out, int ldo) {
+  return gemm_table(static_cast<cudaStream_t>(stream), A, lda, W, ldw, table, period, M, N, K, out, ldo);
+}
+
+wm_status wm_flash_attn(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                        int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant) {
+  return flash_attention(static_cast<cudaStream_t>(stream), q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, heads, scale,
+                         variant, 0, 0);
+}
+
+wm_status wm_flash_attn_dbg(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                            int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, unsigned v_lbo,
+                            unsigned v_sbo) {
+  return flash_attention(static_cast<cudaStream_t>(stream), q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, heads, scale,
+                         variant, v_lbo, v_sbo);
+}
+
+wm_status wm_umma_probe(wm_stream stream, const void* p, const void* v, float* d, int mode, unsigned v_lbo,
+                        unsigned v_sbo) {
+  return umma_probe(static_cast<cudaStream_t>(stream), p, v, d, mode, v_lbo, v_sbo);
+}
+
+wm_status wm_patch_gather(wm_stream stream, const float* img, int n_views, int channels, int H, int W,
+                          int rows_per_view, int row_offset, int ld, int normalize, void* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return patch_gather(static_cast<cudaStream_t>(stream), img, n_views, channels, H, W, rows_per_view, row_offset, ld,
+                      normalize, out);
+}
+
+void wm_rope_tables(int max_pos, float* cos_host, float* sin_host) {
+  // rope.py:94-111: inv_freq_i = 1 / base^(2i/32) (fp32), angle = pos * inv_freq (fp32), table = cos/sin(angle)
+  for (int i = 0; i < 16; ++i) {
+    const float expo = (float)(2 * i) / 32.0f;
+    const float inv = 1.0f / powf(100.0f, expo);
+    for (int p = 0; p <= max_pos; ++p) {
+      const float ang = (float)p * inv;
+      cos_host[p * 16 + i] = (float)cos((double)ang);
+      sin_host[p * 16 + i] = (float)sin((double)ang);
+    }
+  }
+}
+
+wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return pack_bf16_rows(static_cast<cudaStream_t>(stream), src, rows, cols, ld, dst);
+}
+
+}  // extern "C"

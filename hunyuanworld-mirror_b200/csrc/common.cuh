@@ -1,0 +1,82 @@
+// Host-side plumbing shared by every translation unit of libwm_b200: status codes, the thread-local
+// error string behind wm_last_error(), CUDA error capture, and CUtensorMap construction through the
+// driver entry point (no link-time dependency on libcuda, so the library also loads on a GPU-less box).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/wm_b200.h"
+
+namespace wm {
+
+constexpr int kEmbed = 1024;
+constexpr int kHeads = 16;
+constexpr int kHeadDim = 64;
+constexpr int kMlp = 4096;
+constexpr int kPatch = 14;
+constexpr int kPatchStart = 7;   // cam + 4 reg + pose + ray (visual_transformer.py:99-101)
+constexpr int kDinoSpecial = 5;  // cls + 4 reg (vision_transformer.py:209-221)
+constexpr int kNumSms = 148;
+
+char* error_buffer();  // thread-local, 512 bytes (capi.cu)
+
+inline wm_status fail(wm_status code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(error_buffer(), 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define WM_CUDA(expr)                                                                                   \
+  do {                                                                                                  \
+    cudaError_t _e = (expr);                                                                            \
+    if (_e != cudaSuccess)                                                                              \
+      return ::wm::fail(WM_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                        __LINE__);                                                                      \
+  } while (0)
+
+#define WM_CHECK(cond, ...)                                    \
+  do {                                                         \
+    if (!(cond)) return ::wm::fail(WM_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+#define WM_TRY(expr)                 \
+  do {                               \
+    wm_status _s = (expr);           \
+    if (_s != WM_OK) return _s;      \
+  } while (0)
+
+// Launch-error check that is legal during stream capture (no sync).
+#define WM_LAUNCH_CHECK() WM_CUDA(cudaGetLastError())
+
+// ------------------------------------------------------------------ tensor maps
+wm_status tmap_encode(CUtensorMap* out, CUtensorMapDataType dtype, int rank, const void* base, const uint64_t* dims,
+                      const uint64_t* strides_bytes /* rank-1 entries */, const uint32_t* box, CUtensorMapSwizzle sw);
+
+// 2D row-major [rows, cols] with a row pitch in elements; box = [box_cols, box_rows]; SWIZZLE_128B
+inline wm_status tmap_2d(CUtensorMap* out, CUtensorMapDataType dtype, int elem_bytes, const void* base, uint64_t rows,
+                         uint64_t cols, uint64_t pitch_elems, uint32_t box_cols, uint32_t box_rows) {
+  uint64_t dims[2] = {cols, rows};
+  uint64_t strides[1] = {pitch_elems * (uint64_t)elem_bytes};
+  uint32_t box[2] = {box_cols, box_rows};
+  return tmap_encode(out, dtype, 2, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+// 3D [batch, rows, cols]: rows inside one batch entry are `pitch_elems` apart, batch entries `batch_pitch_elems`.
+inline wm_status tmap_3d(CUtensorMap* out, CUtensorMapDataType dtype, int elem_bytes, const void* base, uint64_t batch,
+                         uint64_t rows, uint64_t cols, uint64_t pitch_elems, uint64_t batch_pitch_elems,
+                         uint32_t box_cols, uint32_t box_rows) {
+  uint64_t dims[3] = {cols, rows, batch};
+  uint64_t strides[2] = {pitch_elems * (uint64_t)elem_bytes, batch_pitch_elems * (uint64_t)elem_bytes};
+  uint32_t box[3] = {box_cols, box_rows, 1};
+  return tmap_encode(out, dtype, 3, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+wm_status require_sm100(int* sm_count);
+
+}  // namespace wm

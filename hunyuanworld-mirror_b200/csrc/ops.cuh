@@ -1,0 +1,33 @@
+// Internal (C++) prototypes of the launchers defined in gemm.cu, attn.cu and rowops.cu.
+#pragma once
+#include "common.cuh"
+
+namespace wm {
+
+wm_status gemm_bias_act(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias, int M,
+                        int N, int K, void* out, int ldo, int gelu);
+wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const float* bias, const float* qn_w,
+                   const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
+                   const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q_out,
+                   void* kv_out);
+wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias,
+                           const float* gamma, int M, int N, int K, float* x, int ldx, float* out2, int ld2,
+                           int out2_col);
+wm_status gemm_table(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* table,
+                     int table_period, int M, int N, int K, float* out, int ldo);
+wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                          int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, uint32_t v_lbo,
+                          uint32_t v_sbo);
+wm_status umma_probe(cudaStream_t st, const void* p, const void* v, float* d, int mode, uint32_t v_lbo, uint32_t v_sbo);
+wm_status layernorm(cudaStream_t st, const float* x, const float* w, const float* b, float eps, int rows,
+                    int rows_per_group, int in_group_rows, int in_offset, int out_group_rows, int out_offset, void* y,
+                    int out_f32, int accumulate);
+wm_status patch_gather(cudaStream_t st, const float* img, int n_views, int channels, int H, int W, int rows_per_view,
+                       int row_offset, int ld, int normalize, void* out);
+wm_status prior_token(cudaStream_t st, const float* in, int n_views, int d_in, const float* w0, const float* b0,
+                      const float* w2, const float* b2, int rows_per_view, int row, float* x);
+wm_status special_tokens(cudaStream_t st, const float* cam, const float* reg, int n_views, int rows_per_view,
+                         int first_view_global, int zero_pose, int zero_ray, float* x);
+wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);
+
+}  // namespace wm

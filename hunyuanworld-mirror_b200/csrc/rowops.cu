@@ -1,0 +1,228 @@
+// HBM-bound row kernels around the GEMMs: LayerNorm over C = 1024,
+// image normalise + 14x14 patch gather, depth pixel-unshuffle, pose / ray prior-token MLPs, special-token
+// assembly and fp32 -> bf16 weight packing.  Vectorised 16-byte accesses, one warp per token row.
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace wm {
+
+// ------------------------------------------------------------------------------------------------
+// nn.LayerNorm(1024) (block.py:44,61 eps 1e-5; vision_transformer.py:89 eps 1e-6): biased variance around
+// the mean, fp32 statistics.  Row remap: logical row r -> group = r / rows_per_group, idx = r % rows_per_group;
+// input row = group * in_group_rows + in_offset + idx, output row likewise.  This lets the final DINOv2 norm
+// read patch rows [5, 5+g) of each view and write them to rows [7, 7+g) of the aggregator's token buffer
+// (vision_transformer.py:259-263 -> visual_transformer.py:293-295).
+template <typename OutT, bool ACCUM>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b, float eps,
+                 int rows, int rows_per_group, int in_group_rows, int in_offset, int out_group_rows, int out_offset,
+                 OutT* __restrict__ y) {
+  const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int grp = r / rows_per_group, idx = r % rows_per_group;
+  const float4* xr = reinterpret_cast<const float4*>(x + ((size_t)grp * in_group_rows + in_offset + idx) * kEmbed);
+  float4 v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = xr[i * 32 + lane];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mu = s * (1.0f / kEmbed);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float a = v[i].x - mu, bb = v[i].y - mu, c = v[i].z - mu, d = v[i].w - mu;
+    q += (a * a + bb * bb) + (c * c + d * d);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q * (1.0f / kEmbed) + eps);
+  const float4* w4 = reinterpret_cast<const float4*>(w);
+  const float4* b4 = reinterpret_cast<const float4*>(b);
+  const size_t orow = ((size_t)grp * out_group_rows + out_offset + idx) * kEmbed;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c4 = i * 32 + lane;
+    const float4 ww = __ldg(w4 + c4), bb = __ldg(b4 + c4);
+    float4 o;
+    o.x = (v[i].x - mu) * rstd * ww.x + bb.x;
+    o.y = (v[i].y - mu) * rstd * ww.y + bb.y;
+    o.z = (v[i].z - mu) * rstd * ww.z + bb.z;
+    o.w = (v[i].w - mu) * rstd * ww.w + bb.w;
+    if constexpr (sizeof(OutT) == 2) {
+      uint2 pk = make_uint2(pack_bf16(o.x, o.y), pack_bf16(o.z, o.w));
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(y) + orow + (size_t)c4 * 4) = pk;
+    } else {
+      float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(y) + orow) + c4;
+      if (ACCUM) {
+        const float4 old = *dst;
+        o.x += old.x, o.y += old.y, o.z += old.z, o.w += old.w;
+      }
+      *dst = o;
+    }
+  }
+}
+
+wm_status layernorm(cudaStream_t st, const float* x, const float* w, const float* b, float eps, int rows,
+                    int rows_per_group, int in_group_rows, int in_offset, int out_group_rows, int out_offset, void* y,
+                    int out_f32, int accumulate) {
+  WM_CHECK(x && w && b && y && rows > 0 && rows_per_group > 0, "layernorm: bad arguments");
+  const int grid = (rows + 7) / 8;
+  if (!out_f32) {
+    WM_CHECK(!accumulate, "layernorm: accumulate needs an fp32 output");
+    layernorm_kernel<__nv_bfloat16, false><<<grid, 256, 0, st>>>(x, w, b, eps, rows, rows_per_group, in_group_rows,
+                                                                  in_offset, out_group_rows, out_offset,
+                                                                  static_cast<__nv_bfloat16*>(y));
+  } else if (accumulate) {
+    layernorm_kernel<float, true><<<grid, 256, 0, st>>>(x, w, b, eps, rows, rows_per_group, in_group_rows, in_offset,
+                                                         out_group_rows, out_offset, static_cast<float*>(y));
+  } else {
+    layernorm_kernel<float, false><<<grid, 256, 0, st>>>(x, w, b, eps, rows, rows_per_group, in_group_rows, in_offset,
+                                                          out_group_rows, out_offset, static_cast<float*>(y));
+  }
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Patch gather.  One thread moves one 14-pixel row segment of one patch:
+//   images [N, C, H, W] fp32 -> A [N * rows_per_view, ld] bf16, row = n * rows_per_view + row_offset + patch,
+//   column = c * 196 + ky * 14 + kx  (the order of conv weight.flatten(1), patch_embed.py:63-76, and of
+//   pixel_unshuffle(14) for the depth prior, patch_embed.py:79-108).
+// With `normalize` the ImageNet mean/std of visual_transformer.py:16-17,276-277 is applied first.
+// Rows [0,row_offset) of every view and columns [C*196, ld) are zero-filled by the caller (memset).
+__global__ void __launch_bounds__(256)
+patch_gather_kernel(const float* __restrict__ img, int n_views, int channels, int H, int W, int rows_per_view,
+                    int row_offset, int ld, int normalize, __nv_bfloat16* __restrict__ out) {
+  const int gh = H / kPatch, gw = W / kPatch;
+  const long long total = (long long)n_views * channels * H * gw;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int px = (int)(t % gw);
+  long long r = t / gw;
+  const int y = (int)(r % H);
+  r /= H;
+  const int c = (int)(r % channels);
+  const int n = (int)(r / channels);
+  const int py = y / kPatch, ky = y % kPatch;
+  const float* src = img + (((size_t)n * channels + c) * H + y) * W + px * kPatch;
+  float mean = 0.f, inv = 1.f;
+  if (normalize) {
+    mean = c == 0 ? 0.485f : (c == 1 ? 0.456f : 0.406f);
+    inv = 1.0f / (c == 0 ? 0.229f : (c == 1 ? 0.224f : 0.225f));
+  }
+  __nv_bfloat16* dst = out + ((size_t)n * rows_per_view + row_offset + py * gw + px) * ld + c * 196 + ky * kPatch;
+  (void)gh;
+#pragma unroll
+  for (int i = 0; i < kPatch; i += 2) {
+    const float2 v = *reinterpret_cast<const float2*>(src + i);
+    *reinterpret_cast<uint32_t*>(dst + i) = pack_bf16((v.x - mean) * inv, (v.y - mean) * inv);
+  }
+}
+
+wm_status patch_gather(cudaStream_t st, const float* img, int n_views, int channels, int H, int W, int rows_per_view,
+                       int row_offset, int ld, int normalize, void* out) {
+  WM_CHECK(img && out && n_views > 0 && H % kPatch == 0 && W % kPatch == 0 && H > 0 && W > 0,
+           "patch_gather: H and W must be positive multiples of 14");
+  WM_CHECK(ld >= channels * 196 && ld % 8 == 0 && rows_per_view >= row_offset + (H / kPatch) * (W / kPatch),
+           "patch_gather: bad output geometry");
+  WM_CHECK((reinterpret_cast<uintptr_t>(img) & 7) == 0, "patch_gather: image pointer must be 8-byte aligned");
+  const long long total = (long long)n_views * channels * H * (W / kPatch);
+  const int grid = (int)((total + 255) / 256);
+  patch_gather_kernel<<<grid, 256, 0, st>>>(img, n_views, channels, H, W, rows_per_view, row_offset, ld, normalize,
+                                            static_cast<__nv_bfloat16*>(out));
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// pose_embed / ray_embed: Linear(d_in -> 1024) -> SiLU -> Linear(1024 -> 1024)  (visual_transformer.py:178-204),
+// one token per view, written to row (n * rows_per_view + row) of the fp32 token buffer.  fp32 weights.
+__global__ void __launch_bounds__(256)
+prior_token_kernel(const float* __restrict__ in, int d_in, const float* __restrict__ w0, const float* __restrict__ b0,
+                   const float* __restrict__ w2, const float* __restrict__ b2, int rows_per_view, int row,
+                   float* __restrict__ x) {
+  __shared__ float h[kEmbed];
+  const int n = blockIdx.x;
+  for (int o = threadIdx.x; o < kEmbed; o += blockDim.x) {
+    float acc = b0[o];
+    for (int k = 0; k < d_in; ++k) acc += w0[o * d_in + k] * in[n * d_in + k];
+    h[o] = acc / (1.0f + __expf(-acc));  // SiLU
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int o0 = blockIdx.y * 64 + warp * 8;
+  for (int o = o0; o < o0 + 8; ++o) {
+    const float4* wr = reinterpret_cast<const float4*>(w2 + (size_t)o * kEmbed);
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 ww = __ldg(wr + i * 32 + lane);
+      const float4 hh = *reinterpret_cast<const float4*>(h + (i * 32 + lane) * 4);
+      acc += (ww.x * hh.x + ww.y * hh.y) + (ww.z * hh.z + ww.w * hh.w);
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+    if (lane == 0) x[((size_t)n * rows_per_view + row) * kEmbed + o] = acc + b2[o];
+  }
+}
+
+wm_status prior_token(cudaStream_t st, const float* in, int n_views, int d_in, const float* w0, const float* b0,
+                      const float* w2, const float* b2, int rows_per_view, int row, float* x) {
+  WM_CHECK(in && w0 && b0 && w2 && b2 && x && n_views > 0 && d_in > 0, "prior_token: bad arguments");
+  prior_token_kernel<<<dim3(n_views, kEmbed / 64), 256, 0, st>>>(in, d_in, w0, b0, w2, b2, rows_per_view, row, x);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Special tokens (visual_transformer.py:285-295,397-416): rows 0..4 of each view = cam, reg x4 with variant 0
+// for the globally first view and variant 1 for every other; rows 5 (pose) and 6 (ray) are zeroed when their
+// prior is off (`zero_pose` / `zero_ray`), otherwise left to prior_token_kernel.
+__global__ void __launch_bounds__(256)
+special_tokens_kernel(const float* __restrict__ cam, const float* __restrict__ reg, int rows_per_view,
+                      int first_view_global, int zero_pose, int zero_ray, float* __restrict__ x) {
+  const int n = blockIdx.x, row = blockIdx.y;  // row in [0, 7)
+  const int variant = (first_view_global + n) == 0 ? 0 : 1;
+  float4* dst = reinterpret_cast<float4*>(x + ((size_t)n * rows_per_view + row) * kEmbed) + threadIdx.x;
+  if (row == 0) {
+    *dst = reinterpret_cast<const float4*>(cam + (size_t)variant * kEmbed)[threadIdx.x];
+  } else if (row < 5) {
+    *dst = reinterpret_cast<const float4*>(reg + ((size_t)variant * 4 + (row - 1)) * kEmbed)[threadIdx.x];
+  } else if ((row == 5 && zero_pose) || (row == 6 && zero_ray)) {
+    *dst = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+wm_status special_tokens(cudaStream_t st, const float* cam, const float* reg, int n_views, int rows_per_view,
+                         int first_view_global, int zero_pose, int zero_ray, float* x) {
+  WM_CHECK(cam && reg && x && n_views > 0 && rows_per_view >= kPatchStart, "special_tokens: bad arguments");
+  special_tokens_kernel<<<dim3(n_views, kPatchStart), 256, 0, st>>>(cam, reg, rows_per_view, first_view_global,
+                                                                     zero_pose, zero_ray, x);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp32 -> bf16 packing with optional row padding (weights: [rows, cols] -> [rows, ld], zero tail columns).
+__global__ void __launch_bounds__(256)
+pack_bf16_kernel(const float* __restrict__ src, long long rows, int cols, int ld, __nv_bfloat16* __restrict__ dst) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= rows * ld) return;
+  const long long r = t / ld;
+  const int c = (int)(t % ld);
+  dst[t] = __float2bfloat16_rn(c < cols ? src[r * cols + c] : 0.0f);
+}
+
+wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst) {
+  WM_CHECK(src && dst && rows > 0 && cols > 0 && ld >= cols, "pack_bf16_rows: bad arguments");
+  const long long total = rows * ld;
+  pack_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(src, rows, cols, ld, static_cast<__nv_bfloat16*>(dst));
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+}  // namespace wm

@@ -1,0 +1,138 @@
+/* libwm_b200 -- C ABI of the B200-native WorldMirror aggregator hot path.
+ *
+ * The reference (zubair-irshad/HunyuanWorld-Mirror) has no FFI: the path sits behind plain nn.Module calls.
+ * Each entry point below names the reference call it stands in for (paths relative to the reference root);
+ * hunyuanworld-mirror_b200/aggregator.py binds them with ctypes and mirrors the module interface
+ * (VisualGeometryTransformer.forward, src/models/models/visual_transformer.py:250-341).  INTEGRATION.md shows
+ * the stub a reference maintainer would add.
+ *
+ * Conventions
+ *  - Plain pointers and sizes only.  Device pointers unless a parameter says "host".  bf16 buffers are
+ *    passed as void* (uint16 storage).  All device buffers must be 16-byte aligned.
+ *  - Every call is stream-ordered on `stream` (a cudaStream_t), performs no host synchronisation and no
+ *    allocation (wm_load_weight / wm_finalize_weights / wm_set_dino_pos_table excepted), and is CUDA-graph
+ *    capturable.  One in-flight forward per handle.
+ *  - Return value: WM_OK or an error code; wm_last_error() gives the message of the calling thread's last
+ *    failure.  No C++ exception crosses this boundary.  There is no CPU path: on a device that is not
+ *    sm_100 every compute entry point returns WM_ERR_ARCH.
+ */
+#ifndef WM_B200_H
+#define WM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int wm_status;
+enum {
+  WM_OK = 0,
+  WM_ERR_INVALID = 1, /* bad shape / pointer / argument */
+  WM_ERR_ARCH = 2,    /* device is not sm_100 (B200) or no CUDA device */
+  WM_ERR_CUDA = 3,    /* CUDA runtime / driver error */
+  WM_ERR_NCCL = 4,    /* NCCL error */
+  WM_ERR_STATE = 5    /* weights missing / not finalised / workspace too small */
+};
+
+typedef struct wm_handle wm_handle;
+typedef void* wm_stream; /* cudaStream_t */
+
+typedef struct wm_config {
+  int depth;           /* aggregator depth: frame+global block pairs (reference: 24, visual_transformer.py:52) */
+  int dino_depth;      /* DINOv2 ViT-L blocks (reference: 24, vision_transformer.py:364) */
+  int intermediate[4]; /* layers whose outputs are returned (reference: 4,11,17,23, visual_transformer.py:69) */
+  int n_intermediate;  /* <= 4 */
+} wm_config;
+
+int wm_version(void);
+const char* wm_last_error(void);
+
+/* ---- lifetime and weights ------------------------------------------------------------------------------ */
+wm_status wm_create(const wm_config* cfg, wm_handle** out);
+void wm_destroy(wm_handle* h);
+
+/* One tensor of the reference state_dict under its reference key, fp32, host or device
+ * memory.  GEMM weights are packed to bf16 on the device; vectors stay fp32. */
+wm_status wm_load_weight(wm_handle* h, const char* ref_key, const float* data, const int64_t* shape, int ndim);
+/* Checks that every tensor of the schema arrived and resolves the per-block tables. */
+wm_status wm_finalize_weights(wm_handle* h);
+/* DINOv2 positional table for a (gh, gw) patch grid: pos [1 + gh*gw, 1024] fp32 host or device, i.e. the result
+ * of interpolate_pos_encoding (vision_transformer.py:175-207).  Not needed for the native 37 x 37 grid. */
+wm_status wm_set_dino_pos_table(wm_handle* h, int gh, int gw, const float* pos);
+
+/* ---- the hot path ---------------------------------------------------------------------------------------- */
+size_t wm_workspace_bytes(const wm_handle* h, int n_views, int H, int W, int world);
+
+/* VisualGeometryTransformer.forward (visual_transformer.py:250-341) for this rank's `n_views` views
+ * (global view indices first_view .. first_view + n_views - 1 of world * n_views).
+ *   images [n_views,3,H,W] fp32 in [0,1]; depth [n_views,H,W] | NULL; rays [n_views,4] | NULL;
+ *   poses [n_views,7] | NULL; cond_flags = {pose, depth, rays} as in the reference;
+ *   out[i] [n_views, P, 2048] fp32, i < n_intermediate, P = 7 + (H/14)(W/14):
+ *   [..., :1024] = frame-block output, [..., 1024:] = global-block output. */
+wm_status wm_forward(wm_handle* h, wm_stream stream, const float* images, const float* depth, const float* rays,
+                     const float* poses, const int cond_flags[3], int n_views, int H, int W, int first_view,
+                     float* const* out, void* workspace, size_t workspace_bytes);
+
+/* The alternating-attention stack alone (visual_transformer.py:309-339) on assembled tokens
+ * x [n_views, P, 1024] fp32 (updated in place); gh x gw is the patch grid (P = 7 + gh*gw). */
+wm_status wm_forward_tokens(wm_handle* h, wm_stream stream, float* x, int n_views, int gh, int gw, float* const* out,
+                            void* workspace, size_t workspace_bytes);
+
+/* DINOv2 front + token assembly only (visual_transformer.py:275-295): x [n_views, P, 1024] fp32 out. */
+wm_status wm_embed(wm_handle* h, wm_stream stream, const float* images, const float* depth, const float* rays,
+                   const float* poses, const int cond_flags[3], int n_views, int H, int W, int first_view, float* x,
+                   void* workspace, size_t workspace_bytes);
+
+/* ---- sequence parallelism: K|V all-gather of the global blocks through NCCL --------- */
+/* `nccl_lib` = path of libnccl.so.2 (the one torch loaded).  unique_id: 128 bytes. */
+wm_status wm_nccl_unique_id(const char* nccl_lib, void* unique_id_128);
+wm_status wm_nccl_init(wm_handle* h, const char* nccl_lib, const void* unique_id_128, int rank, int world);
+wm_status wm_nccl_allgather(wm_handle* h, wm_stream stream, void* buf, size_t bytes_per_rank); /* in place, test hook */
+
+/* ---- micro-ops (unit parity + microbenchmarks); C = 1024, head_dim = 64 ----------------------------------- */
+/* nn.LayerNorm(1024) (block.py:44,61): x [rows,1024] fp32 -> y [rows,1024] bf16 (or fp32 when out_f32). */
+wm_status wm_layernorm(wm_stream stream, const float* x, const float* w, const float* b, float eps, int rows, void* y,
+                       int out_f32);
+/* nn.Linear (+ nn.GELU when gelu != 0; mlp.py:30-31): A [M,K] bf16, W [N,K] bf16, bias [N] fp32 -> out [M,N] bf16. */
+wm_status wm_gemm_bias_act(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias, int M,
+                           int N, int K, void* out, int ldo, int gelu);
+/* Attention.qkv + q_norm/k_norm + rope (attention.py:50-56): A [M,1024] bf16, W [3072,1024] bf16 ->
+ * q [M,1024] bf16, kv [M,2048] bf16 (k | v).  Norm / rope pointers may be NULL (DINOv2 blocks).
+ * rope_cos/sin: [max_pos+1,16] fp32 from wm_rope_tables.  Token t sits at position
+ * (0,0) if t % tokens_per_view < patch_start else (1 + i / grid_w, 1 + i % grid_w), i = t % tokens_per_view - patch_start. */
+wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const float* bias, const float* qn_w,
+                      const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
+                      const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q, void* kv);
+/* Linear + LayerScale + residual (block.py:91-92): x [M,N] fp32 += gamma * (A W^T + bias); gamma NULL: x = A W^T + bias.
+ * out2 (optional) [M, ld2] fp32 receives a copy of the new x at column out2_col. */
+wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
+                              const float* gamma, int M, int N, int K, float* x, int ldx, float* out2, int ld2,
+                              int out2_col);
+/* out [M,N] fp32 = A W^T + table[row % period] (DINOv2 patch embed + pos_embed, vision_transformer.py:209-221). */
+wm_status wm_gemm_table(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* table,
+                        int period, int M, int N, int K, float* out, int ldo);
+/* F.scaled_dot_product_attention (attention.py:59), no mask: q [batch*Lq, ldq], k,v [batch*Lkv, ldkv],
+ * o [batch*Lq, ldo] bf16, head h in columns [64h, 64h+64).  variant 0: P through TMEM, 1: P through shared memory. */
+wm_status wm_flash_attn(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                        int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant);
+/* As wm_flash_attn with explicit V-descriptor strides (test hook). */
+wm_status wm_flash_attn_dbg(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                            int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, unsigned v_lbo,
+                            unsigned v_sbo);
+/* Single-tile probe: d [128,64] fp32 = p [128,128] bf16 x v [128,64] bf16; mode 0 = P in smem, 1 = P in TMEM. */
+wm_status wm_umma_probe(wm_stream stream, const void* p, const void* v, float* d, int mode, unsigned v_lbo,
+                        unsigned v_sbo);
+/* Image normalise + 14x14 patch gather / depth pixel-unshuffle (visual_transformer.py:276-277, patch_embed.py:63-108). */
+wm_status wm_patch_gather(wm_stream stream, const float* img, int n_views, int channels, int H, int W,
+                          int rows_per_view, int row_offset, int ld, int normalize, void* out);
+/* cos / sin of pos * 100^(-2i/32), i < 16 (rope.py:80-111): host arrays [(max_pos+1)*16]. */
+void wm_rope_tables(int max_pos, float* cos_host, float* sin_host);
+/* fp32 [rows, cols] -> bf16 [rows, ld] with zero tail columns. */
+wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WM_B200_H */

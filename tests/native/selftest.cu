@@ -1,0 +1,459 @@
+// Native self-test / micro-benchmark of libwm_b200 through its C ABI (no torch, fast start-up).
+// Each invocation runs ONE case so that a trap or time-out in a kernel cannot take the others down:
+//     selftest <case> [args...]
+// CPU references here are plain loops over the same bf16-rounded inputs (fp32/double accumulate); they are
+// test infrastructure only.  tests/native/run_selftest.sh drives the whole matrix on the GPU box.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/wm_b200.h"
+
+#define CK(x)                                                                   \
+  do {                                                                          \
+    cudaError_t e_ = (x);                                                       \
+    if (e_ != cudaSuccess) {                                                    \
+      printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); \
+      exit(2);                                                                  \
+    }                                                                           \
+  } while (0)
+#define WM(x)                                                      \
+  do {                                                             \
+    wm_status s_ = (x);                                            \
+    if (s_ != WM_OK) {                                             \
+      printf("wm error %d: %s (%s)\n", s_, wm_last_error(), #x);   \
+      exit(3);                                                     \
+    }                                                              \
+  } while (0)
+
+static uint32_t rng_state = 12345u;
+static float frand() {  // uniform (-1, 1)
+  rng_state = rng_state * 1664525u + 1013904223u;
+  return ((rng_state >> 8) & 0xFFFFFF) / 8388608.0f - 1.0f;
+}
+static uint16_t f2bf(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  u += 0x7FFFu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+static float bf2f(uint16_t h) {
+  uint32_t u = (uint32_t)h << 16;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+struct BF {  // host bf16 matrix with float mirror of the rounded values
+  std::vector<uint16_t> h;
+  std::vector<float> f;
+  void fill(size_t n, float scale) {
+    h.resize(n), f.resize(n);
+    for (size_t i = 0; i < n; ++i) {
+      h[i] = f2bf(frand() * scale);
+      f[i] = bf2f(h[i]);
+    }
+  }
+};
+template <typename T>
+static T* dev(const std::vector<T>& v) {
+  T* p;
+  CK(cudaMalloc(&p, v.size() * sizeof(T) + 16));
+  CK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return p;
+}
+template <typename T>
+static T* dev_alloc(size_t n, int fill_byte = 0xCD) {
+  T* p;
+  CK(cudaMalloc(&p, n * sizeof(T) + 16));
+  CK(cudaMemset(p, fill_byte, n * sizeof(T)));
+  return p;
+}
+template <typename T>
+static std::vector<T> host(const T* p, size_t n) {
+  std::vector<T> v(n);
+  CK(cudaMemcpy(v.data(), p, n * sizeof(T), cudaMemcpyDeviceToHost));
+  return v;
+}
+static std::vector<float> randf(size_t n, float scale, float mean = 0.f) {
+  std::vector<float> v(n);
+  for (auto& x : v) x = mean + frand() * scale;
+  return v;
+}
+
+struct Err {
+  double max_abs = 0, max_ref = 0;
+  long long bad = 0, n = 0;
+  void add(double got, double ref, double atol, double rtol) {
+    const double d = fabs(got - ref);
+    if (!(d <= atol + rtol * fabs(ref))) ++bad;  // also catches NaN
+    if (d > max_abs || d != d) max_abs = d != d ? 1e30 : d;
+    if (fabs(ref) > max_ref) max_ref = fabs(ref);
+    ++n;
+  }
+  int report(const char* name) const {
+    printf("%-44s n=%-9lld max_abs_err=%-11.4g max_ref=%-9.4g bad=%-8lld %s\n", name, n, max_abs, max_ref, bad,
+           bad == 0 ? "PASS" : "FAIL");
+    fflush(stdout);
+    return bad == 0 ? 0 : 1;
+  }
+};
+
+static double gelu_ref(double x) { return 0.5 * x * (1.0 + erf(x / sqrt(2.0))); }
+
+// ------------------------------------------------------------------------------------------------ probe
+static int case_probe(int mode, unsigned lbo, unsigned sbo) {
+  BF P, V;
+  P.fill(128 * 128, 1.0f);
+  V.fill(128 * 64, 1.0f);
+  uint16_t *dp = dev(P.h), *dv = dev(V.h);
+  float* dd = dev_alloc<float>(128 * 64);
+  WM(wm_umma_probe(0, dp, dv, dd, mode, lbo, sbo));
+  CK(cudaDeviceSynchronize());
+  auto d = host(dd, 128 * 64);
+  Err e;
+  for (int m = 0; m < 128; ++m)
+    for (int n = 0; n < 64; ++n) {
+      double acc = 0;
+      for (int k = 0; k < 128; ++k) acc += (double)P.f[m * 128 + k] * V.f[k * 64 + n];
+      e.add(d[m * 64 + n], acc, 1e-3, 1e-3);
+    }
+  char name[96];
+  snprintf(name, sizeof name, "probe mode=%d (P in %s) v_lbo=%u v_sbo=%u", mode, mode ? "TMEM" : "smem", lbo, sbo);
+  return e.report(name);
+}
+
+// ------------------------------------------------------------------------------------------------ layernorm
+static int case_layernorm(int rows) {
+  auto x = randf((size_t)rows * 1024, 2.0f, 0.3f), w = randf(1024, 0.2f, 1.0f), b = randf(1024, 0.1f);
+  float *dx = dev(x), *dw = dev(w), *db = dev(b);
+  uint16_t* dy = dev_alloc<uint16_t>((size_t)rows * 1024);
+  float* dyf = dev_alloc<float>((size_t)rows * 1024);
+  WM(wm_layernorm(0, dx, dw, db, 1e-5f, rows, dy, 0));
+  WM(wm_layernorm(0, dx, dw, db, 1e-5f, rows, dyf, 1));
+  CK(cudaDeviceSynchronize());
+  auto y = host(dy, (size_t)rows * 1024);
+  auto yf = host(dyf, (size_t)rows * 1024);
+  Err e, ef;
+  for (int r = 0; r < rows; ++r) {
+    double mu = 0, var = 0;
+    for (int c = 0; c < 1024; ++c) mu += x[(size_t)r * 1024 + c];
+    mu /= 1024;
+    for (int c = 0; c < 1024; ++c) var += (x[(size_t)r * 1024 + c] - mu) * (x[(size_t)r * 1024 + c] - mu);
+    var /= 1024;
+    const double rstd = 1.0 / sqrt(var + 1e-5);
+    for (int c = 0; c < 1024; ++c) {
+      const double ref = (x[(size_t)r * 1024 + c] - mu) * rstd * w[c] + b[c];
+      e.add(bf2f(y[(size_t)r * 1024 + c]), ref, 1e-3, 8e-3);
+      ef.add(yf[(size_t)r * 1024 + c], ref, 2e-5, 1e-5);
+    }
+  }
+  return e.report("layernorm bf16 out") | ef.report("layernorm fp32 out");
+}
+
+// ------------------------------------------------------------------------------------------------ GEMMs
+// ref[m][n] = sum_k A[m][k] W[n][k] for the sampled rows
+static void gemm_ref_row(const BF& A, int lda, const BF& W, int ldw, int m, int N, int K, std::vector<double>& out) {
+  out.assign(N, 0.0);
+  for (int n = 0; n < N; ++n) {
+    double acc = 0;
+    const float* a = &A.f[(size_t)m * lda];
+    const float* w = &W.f[(size_t)n * ldw];
+    for (int k = 0; k < K; ++k) acc += (double)a[k] * w[k];
+    out[n] = acc;
+  }
+}
+
+static int case_gemm_bias(int M, int N, int K, int gelu, int row_step) {
+  BF A, W;
+  A.fill((size_t)M * K, 1.0f);
+  W.fill((size_t)N * K, 1.0f / sqrtf((float)K) * 1.7f);
+  auto bias = randf(N, 0.5f);
+  uint16_t *da = dev(A.h), *dw = dev(W.h);
+  float* db = dev(bias);
+  uint16_t* dout = dev_alloc<uint16_t>((size_t)M * N);
+  WM(wm_gemm_bias_act(0, da, K, dw, K, db, M, N, K, dout, N, gelu));
+  CK(cudaDeviceSynchronize());
+  auto out = host(dout, (size_t)M * N);
+  Err e;
+  std::vector<double> ref;
+  for (int m = 0; m < M; m += row_step) {
+    gemm_ref_row(A, K, W, K, m, N, K, ref);
+    for (int n = 0; n < N; ++n) {
+      double r = ref[n] + bias[n];
+      if (gelu) r = gelu_ref(r);
+      e.add(bf2f(out[(size_t)m * N + n]), r, 4e-3, 8e-3);
+    }
+  }
+  char name[96];
+  snprintf(name, sizeof name, "gemm_bias_act M=%d N=%d K=%d gelu=%d", M, N, K, gelu);
+  return e.report(name);
+}
+
+static int case_gemm_resid(int M, int N, int K, int with_gamma, int with_out2, int row_step) {
+  BF A, W;
+  A.fill((size_t)M * K, 1.0f);
+  W.fill((size_t)N * K, 1.0f / sqrtf((float)K) * 1.7f);
+  auto bias = randf(N, 0.5f), gamma = randf(N, 0.3f, 0.5f), x0 = randf((size_t)M * N, 1.0f);
+  uint16_t *da = dev(A.h), *dw = dev(W.h);
+  float *db = dev(bias), *dg = dev(gamma), *dx = dev(x0);
+  const int ld2 = 2 * N, col2 = N;
+  float* d2 = dev_alloc<float>((size_t)M * ld2, 0);
+  WM(wm_gemm_ls_residual(0, da, K, dw, K, db, with_gamma ? dg : nullptr, M, N, K, dx, N, with_out2 ? d2 : nullptr, ld2, col2));
+  CK(cudaDeviceSynchronize());
+  auto x = host(dx, (size_t)M * N);
+  auto o2 = host(d2, (size_t)M * ld2);
+  Err e, e2;
+  std::vector<double> ref;
+  for (int m = 0; m < M; m += row_step) {
+    gemm_ref_row(A, K, W, K, m, N, K, ref);
+    for (int n = 0; n < N; ++n) {
+      const double r = with_gamma ? x0[(size_t)m * N + n] + gamma[n] * (ref[n] + bias[n]) : ref[n] + bias[n];
+      e.add(x[(size_t)m * N + n], r, 2e-4, 1e-4);
+      if (with_out2) {
+        e2.add(o2[(size_t)m * ld2 + col2 + n], r, 2e-4, 1e-4);
+        e2.add(o2[(size_t)m * ld2 + n], 0.0, 0, 0);  // the other half must stay untouched
+      }
+    }
+  }
+  char name[96];
+  snprintf(name, sizeof name, "gemm_ls_residual M=%d N=%d K=%d gamma=%d", M, N, K, with_gamma);
+  int rc = e.report(name);
+  if (with_out2) rc |= e2.report("  second (strided) output");
+  return rc;
+}
+
+static int case_gemm_table(int M, int N, int K, int ld, int period) {
+  BF A, W;
+  A.fill((size_t)M * ld, 1.0f);
+  W.fill((size_t)N * ld, 0.05f);
+  auto table = randf((size_t)period * N, 1.0f);
+  uint16_t *da = dev(A.h), *dw = dev(W.h);
+  float* dt = dev(table);
+  float* dout = dev_alloc<float>((size_t)M * N);
+  WM(wm_gemm_table(0, da, ld, dw, ld, dt, period, M, N, K, dout, N));
+  CK(cudaDeviceSynchronize());
+  auto out = host(dout, (size_t)M * N);
+  Err e;
+  std::vector<double> ref;
+  for (int m = 0; m < M; m += 3) {
+    gemm_ref_row(A, ld, W, ld, m, N, K, ref);
+    for (int n = 0; n < N; ++n) e.add(out[(size_t)m * N + n], ref[n] + table[(size_t)(m % period) * N + n], 2e-4, 1e-4);
+  }
+  char name[96];
+  snprintf(name, sizeof name, "gemm_table M=%d N=%d K=%d ld=%d period=%d", M, N, K, ld, period);
+  return e.report(name);
+}
+
+static int case_gemm_qkv(int M, int with_norm, int with_rope, int row_step) {
+  const int N = 3072, K = 1024, P = 37, ps = 7, gw = 6;  // tokens per view 37 = 7 + 5x6 grid
+  BF A, W;
+  A.fill((size_t)M * K, 1.0f);
+  W.fill((size_t)N * K, 1.0f / 32.0f * 1.7f);
+  auto bias = randf(N, 0.3f), qw = randf(64, 0.2f, 1.0f), qb = randf(64, 0.1f), kw = randf(64, 0.2f, 1.0f), kb = randf(64, 0.1f);
+  const int max_pos = 16;
+  std::vector<float> cs((max_pos + 1) * 16), sn((max_pos + 1) * 16);
+  wm_rope_tables(max_pos, cs.data(), sn.data());
+  uint16_t *da = dev(A.h), *dw = dev(W.h);
+  float *db = dev(bias), *dqw = dev(qw), *dqb = dev(qb), *dkw = dev(kw), *dkb = dev(kb), *dcs = dev(cs), *dsn = dev(sn);
+  uint16_t* dq = dev_alloc<uint16_t>((size_t)M * 1024);
+  uint16_t* dkv = dev_alloc<uint16_t>((size_t)M * 2048);
+  WM(wm_gemm_qkv(0, da, dw, db, with_norm ? dqw : nullptr, with_norm ? dqb : nullptr, with_norm ? dkw : nullptr,
+                 with_norm ? dkb : nullptr, 1e-5f, with_rope ? dcs : nullptr, with_rope ? dsn : nullptr, P, ps, gw, M, dq, dkv));
+  CK(cudaDeviceSynchronize());
+  auto q = host(dq, (size_t)M * 1024);
+  auto kv = host(dkv, (size_t)M * 2048);
+  Err e;
+  std::vector<double> ref;
+  for (int m = 0; m < M; m += row_step) {
+    gemm_ref_row(A, K, W, K, m, N, K, ref);
+    const int p = m % P;
+    int py = 0, px = 0;
+    if (p >= ps) py = (p - ps) / gw + 1, px = (p - ps) % gw + 1;
+    for (int hd = 0; hd < 48; ++hd) {
+      double x[64];
+      for (int i = 0; i < 64; ++i) x[i] = ref[hd * 64 + i] + bias[hd * 64 + i];
+      const int which = hd / 16;
+      if (which < 2 && with_norm) {
+        double mu = 0, var = 0;
+        for (int i = 0; i < 64; ++i) mu += x[i];
+        mu /= 64;
+        for (int i = 0; i < 64; ++i) var += (x[i] - mu) * (x[i] - mu);
+        var /= 64;
+        const double rstd = 1.0 / sqrt(var + 1e-5);
+        for (int i = 0; i < 64; ++i) x[i] = (x[i] - mu) * rstd * (which ? kw[i] : qw[i]) + (which ? kb[i] : qb[i]);
+      }
+      if (which < 2 && with_rope) {
+        for (int half = 0; half < 2; ++half) {
+          const int pos = half ? px : py;
+          for (int i = 0; i < 16; ++i) {
+            const double c = cs[pos * 16 + i], s = sn[pos * 16 + i];
+            const double a = x[half * 32 + i], b = x[half * 32 + 16 + i];
+            x[half * 32 + i] = a * c - b * s;
+            x[half * 32 + 16 + i] = b * c + a * s;
+          }
+        }
+      }
+      for (int i = 0; i < 64; ++i) {
+        const float got = which == 0 ? bf2f(q[(size_t)m * 1024 + hd * 64 + i]) : bf2f(kv[(size_t)m * 2048 + (hd - 16) * 64 + i]);
+        e.add(got, x[i], 6e-3, 8e-3);
+      }
+    }
+  }
+  char name[96];
+  snprintf(name, sizeof name, "gemm_qkv M=%d qk_norm=%d rope=%d", M, with_norm, with_rope);
+  return e.report(name);
+}
+
+// ------------------------------------------------------------------------------------------------ attention
+// q [batch*Lq, heads*64], kv [batch*Lkv, heads*128] (k | v); reference for every `row_step`-th query row.
+static int case_attn(int batch, int Lq, int Lkv, int heads, float qscale, int variant, unsigned lbo, unsigned sbo,
+                     int row_step) {
+  const int ldq = heads * 64, ldkv = heads * 128;
+  BF Q, KV;
+  Q.fill((size_t)batch * Lq * ldq, qscale);
+  KV.fill((size_t)batch * Lkv * ldkv, 1.0f);
+  uint16_t *dq = dev(Q.h), *dkv = dev(KV.h);
+  uint16_t* dout = dev_alloc<uint16_t>((size_t)batch * Lq * ldq);
+  WM(wm_flash_attn_dbg(0, dq, ldq, dkv, dkv + heads * 64, ldkv, dout, ldq, batch, Lq, Lkv, heads, 0.125f, variant, lbo, sbo));
+  CK(cudaDeviceSynchronize());
+  auto out = host(dout, (size_t)batch * Lq * ldq);
+  Err e;
+  std::vector<double> s(Lkv);
+  for (int b = 0; b < batch; ++b)
+    for (int h = 0; h < heads; ++h)
+      for (int i = (b * 7 + h * 3) % row_step; i < Lq; i += row_step) {
+        const float* qr = &Q.f[((size_t)b * Lq + i) * ldq + h * 64];
+        double mx = -1e300;
+        for (int j = 0; j < Lkv; ++j) {
+          const float* kr = &KV.f[((size_t)b * Lkv + j) * ldkv + h * 64];
+          double acc = 0;
+          for (int d = 0; d < 64; ++d) acc += (double)qr[d] * kr[d];
+          s[j] = acc * 0.125;
+          if (s[j] > mx) mx = s[j];
+        }
+        double l = 0, o[64] = {0};
+        for (int j = 0; j < Lkv; ++j) {
+          const double p = exp(s[j] - mx);
+          l += p;
+          const float* vr = &KV.f[((size_t)b * Lkv + j) * ldkv + heads * 64 + h * 64];
+          for (int d = 0; d < 64; ++d) o[d] += p * vr[d];
+        }
+        for (int d = 0; d < 64; ++d) e.add(bf2f(out[((size_t)b * Lq + i) * ldq + h * 64 + d]), o[d] / l, 6e-3, 2e-2);
+      }
+  char name[128];
+  snprintf(name, sizeof name, "attn b=%d Lq=%d Lkv=%d h=%d qs=%.0f var=%d lbo=%u sbo=%u", batch, Lq, Lkv, heads, qscale,
+           variant, lbo, sbo);
+  return e.report(name);
+}
+
+// ------------------------------------------------------------------------------------------------ timing
+static float time_ms(int iters, void (*fn)(void*), void* ctx) {
+  cudaEvent_t a, b;
+  CK(cudaEventCreate(&a));
+  CK(cudaEventCreate(&b));
+  for (int i = 0; i < 3; ++i) fn(ctx);
+  CK(cudaDeviceSynchronize());
+  CK(cudaEventRecord(a));
+  for (int i = 0; i < iters; ++i) fn(ctx);
+  CK(cudaEventRecord(b));
+  CK(cudaEventSynchronize(b));
+  float ms;
+  CK(cudaEventElapsedTime(&ms, a, b));
+  return ms / iters;
+}
+
+struct GemmCtx {
+  int kind, M, N, K;
+  uint16_t *a, *w, *out, *q, *kv;
+  float *bias, *gamma, *x, *qw, *cs;
+};
+static void gemm_run(void* p) {
+  GemmCtx* c = (GemmCtx*)p;
+  if (c->kind == 0) WM(wm_gemm_bias_act(0, c->a, c->K, c->w, c->K, c->bias, c->M, c->N, c->K, c->out, c->N, 0));
+  if (c->kind == 1) WM(wm_gemm_bias_act(0, c->a, c->K, c->w, c->K, c->bias, c->M, c->N, c->K, c->out, c->N, 1));
+  if (c->kind == 2)
+    WM(wm_gemm_qkv(0, c->a, c->w, c->bias, c->qw, c->qw, c->qw, c->qw, 1e-5f, c->cs, c->cs, 1376, 7, 37, c->M, c->q, c->kv));
+  if (c->kind == 3) WM(wm_gemm_ls_residual(0, c->a, c->K, c->w, c->K, c->bias, c->gamma, c->M, c->N, c->K, c->x, c->N, nullptr, 0, 0));
+}
+static int bench_gemm(int kind, int M, int N, int K) {
+  GemmCtx c{};
+  c.kind = kind, c.M = M, c.N = N, c.K = K;
+  BF A, W;
+  A.fill((size_t)M * K, 1.0f);
+  W.fill((size_t)N * K, 0.03f);
+  c.a = dev(A.h), c.w = dev(W.h);
+  c.out = dev_alloc<uint16_t>((size_t)M * N);
+  c.q = dev_alloc<uint16_t>((size_t)M * 1024), c.kv = dev_alloc<uint16_t>((size_t)M * 2048);
+  c.bias = dev(randf(N, 0.1f)), c.gamma = dev(randf(N, 0.01f)), c.x = dev(randf((size_t)M * N, 1.0f));
+  c.qw = dev(randf(64, 0.1f, 1.0f));
+  std::vector<float> cs(64 * 16), sn(64 * 16);
+  wm_rope_tables(63, cs.data(), sn.data());
+  c.cs = dev(cs);
+  const float ms = time_ms(20, gemm_run, &c);
+  const char* names[] = {"bias", "gelu", "qkv", "ls_residual"};
+  printf("BENCH gemm_%-12s M=%d N=%d K=%d  %.3f ms  %.1f TFLOP/s\n", names[kind], M, N, K, ms, 2.0 * M * N * K / ms * 1e-9);
+  return 0;
+}
+
+struct AttnCtx {
+  uint16_t *q, *kv, *o;
+  int batch, Lq, Lkv, heads, variant;
+};
+static void attn_run(void* p) {
+  AttnCtx* c = (AttnCtx*)p;
+  WM(wm_flash_attn(0, c->q, c->heads * 64, c->kv, c->kv + c->heads * 64, c->heads * 128, c->o, c->heads * 64, c->batch, c->Lq,
+                   c->Lkv, c->heads, 0.125f, c->variant));
+}
+static int bench_attn(int batch, int Lq, int Lkv, int heads, int variant) {
+  AttnCtx c{};
+  c.batch = batch, c.Lq = Lq, c.Lkv = Lkv, c.heads = heads, c.variant = variant;
+  BF Q, KV;
+  Q.fill((size_t)batch * Lq * heads * 64, 1.0f);
+  KV.fill((size_t)batch * Lkv * heads * 128, 1.0f);
+  c.q = dev(Q.h), c.kv = dev(KV.h), c.o = dev_alloc<uint16_t>((size_t)batch * Lq * heads * 64);
+  const float ms = time_ms(Lkv > 50000 ? 3 : 10, attn_run, &c);
+  printf("BENCH attn batch=%d Lq=%d Lkv=%d heads=%d variant=%d  %.3f ms  %.1f TFLOP/s\n", batch, Lq, Lkv, heads, variant, ms,
+         4.0 * batch * (double)Lq * Lkv * heads * 64 / ms * 1e-9);
+  return 0;
+}
+
+static int bench_ln(int rows) {
+  struct C {
+    float *x, *w;
+    uint16_t* y;
+    int rows;
+  } c;
+  c.rows = rows;
+  c.x = dev(randf((size_t)rows * 1024, 1.0f)), c.w = dev(randf(1024, 0.1f, 1.0f));
+  c.y = dev_alloc<uint16_t>((size_t)rows * 1024);
+  const float ms = time_ms(20, [](void* p) { C* c = (C*)p; WM(wm_layernorm(0, c->x, c->w, c->w, 1e-5f, c->rows, c->y, 0)); }, &c);
+  printf("BENCH layernorm rows=%d  %.4f ms  %.0f GB/s\n", rows, ms, rows * 6144.0 / ms * 1e-6);
+  return 0;
+}
+
+int main(int argc, char** argv) {
+  if (argc < 2) {
+    printf("usage: selftest <case> [args]\n");
+    return 64;
+  }
+  const std::string c = argv[1];
+  auto I = [&](int i, int def) { return argc > i ? atoi(argv[i]) : def; };
+  if (c == "probe") return case_probe(I(2, 0), I(3, 1024), I(4, 1024));
+  if (c == "layernorm") return case_layernorm(I(2, 333));
+  if (c == "gemm_bias") return case_gemm_bias(I(2, 300), I(3, 512), I(4, 192), I(5, 0), I(6, 1));
+  if (c == "gemm_resid") return case_gemm_resid(I(2, 300), I(3, 512), I(4, 192), I(5, 1), I(6, 1), I(7, 1));
+  if (c == "gemm_table") return case_gemm_table(I(2, 300), I(3, 1024), I(4, 588), I(5, 640), I(6, 77));
+  if (c == "gemm_qkv") return case_gemm_qkv(I(2, 300), I(3, 1), I(4, 1), I(5, 3));
+  if (c == "attn") return case_attn(I(2, 2), I(3, 331), I(4, 331), I(5, 2), (float)I(6, 1), I(7, 0), I(8, 0), I(9, 0), I(10, 5));
+  if (c == "bench_gemm") return bench_gemm(I(2, 0), I(3, 11008), I(4, 1024), I(5, 1024));
+  if (c == "bench_attn") return bench_attn(I(2, 1), I(3, 11008), I(4, 11008), I(5, 16), I(6, 0));
+  if (c == "bench_ln") return bench_ln(I(2, 11008));
+  printf("unknown case %s\n", c.c_str());
+  return 64;
+}
