@@ -1,0 +1,88 @@
+"""ctypes binding of libwm_b200.so (include/wm_b200.h).  There is no fallback: if the library has not been
+built (python hunyuanworld-mirror_b200/build.py) importing the symbols raises, and every compute entry point
+returns WM_ERR_ARCH on anything that is not a B200."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "lib", "libwm_b200.so")
+
+PROF_CLASSES = ("layernorm", "gemm_qkv", "attn_local", "attn_global", "gemm_proj", "gemm_fc1", "gemm_fc2", "embed", "allgather")
+WM_OK, WM_ERR_INVALID, WM_ERR_ARCH, WM_ERR_CUDA, WM_ERR_NCCL, WM_ERR_STATE = range(6)
+
+
+class WmConfig(C.Structure):
+    _fields_ = [("depth", C.c_int), ("dino_depth", C.c_int), ("intermediate", C.c_int * 4), ("n_intermediate", C.c_int)]
+
+
+class WmError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"libwm_b200 error {status}: {message}")
+        self.status = status
+
+
+_vp, _i, _f, _u = C.c_void_p, C.c_int, C.c_float, C.c_uint
+_fp = C.c_void_p  # float* passed as raw addresses (tensor.data_ptr())
+
+# name -> (restype, argtypes); every symbol include/wm_b200.h declares
+SIGNATURES = {
+    "wm_version": (C.c_int, []),
+    "wm_last_error": (C.c_char_p, []),
+    "wm_create": (C.c_int, [C.POINTER(WmConfig), C.POINTER(_vp)]),
+    "wm_destroy": (None, [_vp]),
+    "wm_load_weight": (C.c_int, [_vp, C.c_char_p, _fp, C.POINTER(C.c_int64), _i]),
+    "wm_finalize_weights": (C.c_int, [_vp]),
+    "wm_set_dino_pos_table": (C.c_int, [_vp, _i, _i, _fp]),
+    "wm_workspace_bytes": (C.c_size_t, [_vp, _i, _i, _i, _i]),
+    "wm_forward": (C.c_int, [_vp, _vp, _fp, _fp, _fp, _fp, C.POINTER(C.c_int), _i, _i, _i, _i, C.POINTER(_vp), _vp,
+                             C.c_size_t]),
+    "wm_forward_tokens": (C.c_int, [_vp, _vp, _fp, _i, _i, _i, C.POINTER(_vp), _vp, C.c_size_t]),
+    "wm_embed": (C.c_int, [_vp, _vp, _fp, _fp, _fp, _fp, C.POINTER(C.c_int), _i, _i, _i, _i, _fp, _vp, C.c_size_t]),
+    "wm_profile": (C.c_int, [_vp, _u]),
+    "wm_profile_read": (C.c_int, [_vp, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
+    "wm_launch_count": (C.c_longlong, [_vp]),
+    "wm_nccl_unique_id": (C.c_int, [C.c_char_p, _vp]),
+    "wm_nccl_init": (C.c_int, [_vp, C.c_char_p, _vp, _i, _i]),
+    "wm_nccl_allgather": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "wm_layernorm": (C.c_int, [_vp, _fp, _fp, _fp, _f, _i, _vp, _i]),
+    "wm_gemm_bias_act": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _i, _i, _i, _vp, _i, _i]),
+    "wm_gemm_qkv": (C.c_int, [_vp, _vp, _vp, _fp, _fp, _fp, _fp, _fp, _f, _fp, _fp, _i, _i, _i, _i, _vp, _vp]),
+    "wm_gemm_ls_residual": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _fp, _i, _i, _i, _fp, _i, _fp, _i, _i]),
+    "wm_gemm_table": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _i, _i, _i, _i, _fp, _i]),
+    "wm_flash_attn": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _i]),
+    "wm_flash_attn_dbg": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _i, _u, _u]),
+    "wm_umma_probe": (C.c_int, [_vp, _vp, _vp, _fp, _i, _u, _u]),
+    "wm_patch_gather": (C.c_int, [_vp, _fp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "wm_rope_tables": (None, [_i, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "wm_pack_bf16": (C.c_int, [_vp, _fp, C.c_longlong, _i, _i, _vp]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libwm_b200.so once and attach the prototypes.  Raises if it is missing (no CPU fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python hunyuanworld-mirror_b200/build.py` "
+                "(nvcc, sm_100a).  This package has no CPU or PyTorch fallback.")
+        handle = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError if the header and the library ever disagree
+            fn.restype, fn.argtypes = res, args
+        _lib = handle
+    return _lib
+
+
+def last_error() -> str:
+    msg = lib().wm_last_error()
+    return msg.decode("utf-8", "replace") if msg else ""
+
+
+def check(status: int) -> None:
+    if status != WM_OK:
+        raise WmError(status, last_error())

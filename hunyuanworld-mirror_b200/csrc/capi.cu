@@ -46,15 +46,22 @@ wm_status tmap_encode(CUtensorMap* out, CUtensorMapDataType dtype, int rank, con
 }
 
 wm_status require_sm100(int* sm_count) {
+  // cudaGetDeviceProperties costs milliseconds: remember the answer per device
+  static int cached_dev = -1, cached_sms = 0;
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return fail(WM_ERR_ARCH, "no CUDA device: %s (libwm_b200 has no CPU path)", cudaGetErrorString(e));
+  if (dev == cached_dev) {
+    *sm_count = cached_sms;
+    return WM_OK;
+  }
   cudaDeviceProp prop;
   e = cudaGetDeviceProperties(&prop, dev);
   if (e != cudaSuccess) return fail(WM_ERR_ARCH, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
   if (prop.major != 10)
     return fail(WM_ERR_ARCH, "device %d is sm_%d%d; libwm_b200 is built for sm_100a (B200) only", dev, prop.major, prop.minor);
   *sm_count = prop.multiProcessorCount;
+  cached_dev = dev, cached_sms = prop.multiProcessorCount;
   return WM_OK;
 }
 
@@ -113,6 +120,11 @@ struct wm_handle {
   wm::NcclApi nccl;
   wm::nccl_comm_t comm = nullptr;
   int rank = 0, world = 1;
+  // opt-in per-kernel-class timing (CUDA events on the forward's stream) and a launch counter
+  unsigned prof_mask = 0;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_ev[WM_PROF_CLASSES];
+  size_t prof_used[WM_PROF_CLASSES] = {0};
+  long long launches = 0;
 };
 
 namespace wm {
@@ -196,30 +208,60 @@ struct BlockShape {
   int tokens_per_view, patch_start, grid_w;
   bool rope;
   float eps;
+  bool global;
 };
+
+struct ProfScope {
+  wm_handle* h;
+  cudaStream_t st;
+  int cls;
+  bool on;
+  ProfScope(wm_handle* h_, cudaStream_t st_, int cls_) : h(h_), st(st_), cls(cls_), on((h_->prof_mask >> cls_) & 1u) {
+    ++h->launches;
+    if (!on) return;
+    auto& v = h->prof_ev[cls];
+    if (h->prof_used[cls] == v.size()) {
+      cudaEvent_t a, b;
+      cudaEventCreate(&a);
+      cudaEventCreate(&b);
+      v.emplace_back(a, b);
+    }
+    cudaEventRecord(v[h->prof_used[cls]].first, st);
+  }
+  ~ProfScope() {
+    if (on) cudaEventRecord(h->prof_ev[cls][h->prof_used[cls]++].second, st);
+  }
+};
+#define WM_OP(cls, expr)          \
+  do {                            \
+    ProfScope _ps(h, st, cls);    \
+    WM_TRY(expr);                 \
+  } while (0)
 
 // Block.forward eval branch (block.py:91-92): x += ls1 * attn(norm1(x)); x += ls2 * mlp(norm2(x))
 static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const BlockShape& s, const Workspace& ws,
                            float* x, float* out2, int out2_col, bool gather) {
-  WM_TRY(layernorm(st, x, w.n1w, w.n1b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
+  WM_OP(WM_PROF_LN, layernorm(st, x, w.n1w, w.n1b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
   __nv_bfloat16* kv_local = ws.kv + (size_t)s.kv_row0 * 2 * kEmbed;
-  WM_TRY(gemm_qkv(st, ws.ln, kEmbed, w.qkv_w, w.qkv_b, w.qn_w, w.qn_b, w.kn_w, w.kn_b, 1e-5f,
-                  s.rope ? h->rope_cos : nullptr, s.rope ? h->rope_sin : nullptr, s.tokens_per_view, s.patch_start,
-                  s.grid_w, s.T, ws.q, kv_local));
+  WM_OP(WM_PROF_QKV, gemm_qkv(st, ws.ln, kEmbed, w.qkv_w, w.qkv_b, w.qn_w, w.qn_b, w.kn_w, w.kn_b, 1e-5f,
+                              s.rope ? h->rope_cos : nullptr, s.rope ? h->rope_sin : nullptr, s.tokens_per_view,
+                              s.patch_start, s.grid_w, s.T, ws.q, kv_local));
   if (gather) {
+    ProfScope _ps(h, st, WM_PROF_ALLGATHER);
     const size_t bytes = (size_t)s.T * 2 * kEmbed * 2;
     const int r = h->nccl.AllGather(kv_local, ws.kv, bytes, /*ncclChar*/ 0, h->comm, st);
     if (r != 0) return fail(WM_ERR_NCCL, "ncclAllGather: %s", h->nccl.GetErrorString(r));
   }
   const __nv_bfloat16* kbase = gather ? ws.kv : kv_local;
-  WM_TRY(flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv,
-                         kHeads, 0.125f, 0, 0, 0));
-  WM_TRY(gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x, kEmbed, nullptr,
-                          0, 0));
-  WM_TRY(layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
-  WM_TRY(gemm_bias_act(st, ws.ln, kEmbed, w.fc1_w, kEmbed, w.fc1_b, s.T, kMlp, kEmbed, ws.hid, kMlp, 1));
-  WM_TRY(gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed, out2,
-                          2 * kEmbed, out2_col));
+  WM_OP(s.global ? WM_PROF_ATTN_GLOBAL : WM_PROF_ATTN_LOCAL,
+        flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
+                        0.125f, 0, 0, 0));
+  WM_OP(WM_PROF_PROJ, gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x,
+                                       kEmbed, nullptr, 0, 0));
+  WM_OP(WM_PROF_LN, layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
+  WM_OP(WM_PROF_FC1, gemm_bias_act(st, ws.ln, kEmbed, w.fc1_w, kEmbed, w.fc1_b, s.T, kMlp, kEmbed, ws.hid, kMlp, 1));
+  WM_OP(WM_PROF_FC2, gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed, out2,
+                                      2 * kEmbed, out2_col));
   return WM_OK;
 }
 
@@ -237,8 +279,8 @@ static wm_status check_ready(const wm_handle* h, const void* workspace, size_t w
 
 static wm_status run_stack(wm_handle* h, cudaStream_t st, const Workspace& ws, int n, int gh, int gw, float* const* out) {
   const int P = kPatchStart + gh * gw, T = n * P;
-  BlockShape fs{T, n, P, P, 0, P, kPatchStart, gw, true, 1e-5f};
-  BlockShape gs{T, 1, T, T * h->world, h->rank * T, P, kPatchStart, gw, true, 1e-5f};
+  BlockShape fs{T, n, P, P, 0, P, kPatchStart, gw, true, 1e-5f, false};
+  BlockShape gs{T, 1, T, T * h->world, h->rank * T, P, kPatchStart, gw, true, 1e-5f, true};
   int next_out = 0;
   for (int i = 0; i < h->cfg.depth; ++i) {
     float* o = nullptr;
@@ -263,11 +305,11 @@ static wm_status run_embed(wm_handle* h, cudaStream_t st, const Workspace& ws, c
   const int ld_pe = 640;
   __nv_bfloat16* a_pe = ws.hid;  // free until the first fc1
   WM_CUDA(cudaMemsetAsync(a_pe, 0, (size_t)Td * ld_pe * 2, st));
-  WM_TRY(patch_gather(st, images, n, 3, H, W, Pd, kDinoSpecial, ld_pe, 1, a_pe));
+  WM_OP(WM_PROF_EMBED, patch_gather(st, images, n, 3, H, W, Pd, kDinoSpecial, ld_pe, 1, a_pe));
   const DevTensor& pew = h->w["patch_embed.patch_embed.proj.weight"];
-  WM_TRY(gemm_table(st, a_pe, ld_pe, pew.b16, pew.ld, h->dino_table, Pd, Td, kEmbed, ld_pe, ws.xd, kEmbed));
+  WM_OP(WM_PROF_EMBED, gemm_table(st, a_pe, ld_pe, pew.b16, pew.ld, h->dino_table, Pd, Td, kEmbed, ld_pe, ws.xd, kEmbed));
   // a4: DINOv2 blocks (no rope, no qk-norm, eps 1e-6)
-  BlockShape ds{Td, n, Pd, Pd, 0, Pd, 0, gw, false, 1e-6f};
+  BlockShape ds{Td, n, Pd, Pd, 0, Pd, 0, gw, false, 1e-6f, false};
   for (int i = 0; i < h->cfg.dino_depth; ++i) WM_TRY(run_block(h, st, h->dino[i], ds, ws, ws.xd, nullptr, 0, false));
   // a6 (depth): pixel-unshuffle -> fc1+GELU -> fc2 written to the patch rows of x, then the final norm accumulates
   const bool pose_on = flags[0] == 1 && poses, depth_on = flags[1] == 1 && depth, ray_on = flags[2] == 1 && rays;
@@ -275,24 +317,24 @@ static wm_status run_embed(wm_handle* h, cudaStream_t st, const Workspace& ws, c
     const int ld_d = 256;
     __nv_bfloat16* a_d = ws.q;
     WM_CUDA(cudaMemsetAsync(a_d, 0, (size_t)T * ld_d * 2, st));
-    WM_TRY(patch_gather(st, depth, n, 1, H, W, P, kPatchStart, ld_d, 0, a_d));
+    WM_OP(WM_PROF_EMBED, patch_gather(st, depth, n, 1, H, W, P, kPatchStart, ld_d, 0, a_d));
     const DevTensor& f1 = h->w["depth_embed.proj.2.fc1.weight"];
     const DevTensor& f2 = h->w["depth_embed.proj.2.fc2.weight"];
-    WM_TRY(gemm_bias_act(st, a_d, ld_d, f1.b16, f1.ld, h->w["depth_embed.proj.2.fc1.bias"].f32, T, kMlp, ld_d, ws.hid,
+    WM_OP(WM_PROF_EMBED, gemm_bias_act(st, a_d, ld_d, f1.b16, f1.ld, h->w["depth_embed.proj.2.fc1.bias"].f32, T, kMlp, ld_d, ws.hid,
                          kMlp, 1));
-    WM_TRY(gemm_ls_residual(st, ws.hid, kMlp, f2.b16, f2.ld, h->w["depth_embed.proj.2.fc2.bias"].f32, nullptr, T, kEmbed,
+    WM_OP(WM_PROF_EMBED, gemm_ls_residual(st, ws.hid, kMlp, f2.b16, f2.ld, h->w["depth_embed.proj.2.fc2.bias"].f32, nullptr, T, kEmbed,
                             kMlp, ws.x, kEmbed, nullptr, 0, 0));
   }
   // final DINOv2 norm of the patch rows -> rows [7, 7+g) of x  (vision_transformer.py:259-263)
-  WM_TRY(layernorm(st, ws.xd, h->w["patch_embed.norm.weight"].f32, h->w["patch_embed.norm.bias"].f32, 1e-6f, n * g, g, Pd,
+  WM_OP(WM_PROF_EMBED, layernorm(st, ws.xd, h->w["patch_embed.norm.weight"].f32, h->w["patch_embed.norm.bias"].f32, 1e-6f, n * g, g, Pd,
                    kDinoSpecial, P, kPatchStart, ws.x, 1, depth_on ? 1 : 0));
   // a5-a7: special + prior tokens
-  WM_TRY(special_tokens(st, h->w["cam_token"].f32, h->w["reg_token"].f32, n, P, first_view, !pose_on, !ray_on, ws.x));
+  WM_OP(WM_PROF_EMBED, special_tokens(st, h->w["cam_token"].f32, h->w["reg_token"].f32, n, P, first_view, !pose_on, !ray_on, ws.x));
   if (pose_on)
-    WM_TRY(prior_token(st, poses, n, 7, h->w["pose_embed.0.weight"].f32, h->w["pose_embed.0.bias"].f32,
+    WM_OP(WM_PROF_EMBED, prior_token(st, poses, n, 7, h->w["pose_embed.0.weight"].f32, h->w["pose_embed.0.bias"].f32,
                        h->w["pose_embed.2.weight"].f32, h->w["pose_embed.2.bias"].f32, P, 5, ws.x));
   if (ray_on)
-    WM_TRY(prior_token(st, rays, n, 4, h->w["ray_embed.0.weight"].f32, h->w["ray_embed.0.bias"].f32,
+    WM_OP(WM_PROF_EMBED, prior_token(st, rays, n, 4, h->w["ray_embed.0.weight"].f32, h->w["ray_embed.0.bias"].f32,
                        h->w["ray_embed.2.weight"].f32, h->w["ray_embed.2.bias"].f32, P, 6, ws.x));
   return WM_OK;
 }
@@ -345,6 +387,11 @@ void wm_destroy(wm_handle* h) {
   if (h->rope_sin) cudaFree(h->rope_sin);
   if (h->dino_table) cudaFree(h->dino_table);
   if (h->comm && h->nccl.CommDestroy) h->nccl.CommDestroy(h->comm);
+  for (auto& v : h->prof_ev)
+    for (auto& e : v) {
+      cudaEventDestroy(e.first);
+      cudaEventDestroy(e.second);
+    }
   delete h;
 }
 
@@ -534,6 +581,31 @@ wm_status wm_forward_tokens(wm_handle* h, wm_stream stream, float* x, int n_view
   ws.x = x;  // run in place on the caller's token buffer
   return run_stack(h, st, ws, n_views, gh, gw, out);
 }
+
+// ---------------------------------------------------------------------------------------------- profiling
+wm_status wm_profile(wm_handle* h, unsigned class_mask) {
+  WM_CHECK(h, "wm_profile: null handle");
+  h->prof_mask = class_mask;
+  for (int c = 0; c < WM_PROF_CLASSES; ++c) h->prof_used[c] = 0;
+  h->launches = 0;
+  return WM_OK;
+}
+
+wm_status wm_profile_read(wm_handle* h, int cls, float* total_ms, int* count) {
+  WM_CHECK(h && total_ms && count && cls >= 0 && cls < WM_PROF_CLASSES, "wm_profile_read: bad argument");
+  float sum = 0.f;
+  for (size_t i = 0; i < h->prof_used[cls]; ++i) {
+    WM_CUDA(cudaEventSynchronize(h->prof_ev[cls][i].second));
+    float ms = 0.f;
+    WM_CUDA(cudaEventElapsedTime(&ms, h->prof_ev[cls][i].first, h->prof_ev[cls][i].second));
+    sum += ms;
+  }
+  *total_ms = sum;
+  *count = (int)h->prof_used[cls];
+  return WM_OK;
+}
+
+long long wm_launch_count(const wm_handle* h) { return h ? h->launches : 0; }
 
 // ---------------------------------------------------------------------------------------------- NCCL
 wm_status wm_nccl_unique_id(const char* nccl_lib, void* unique_id_128) {

@@ -85,6 +85,26 @@ wm_status wm_embed(wm_handle* h, wm_stream stream, const float* images, const fl
                    const float* poses, const int cond_flags[3], int n_views, int H, int W, int first_view, float* x,
                    void* workspace, size_t workspace_bytes);
 
+/* ---- measurement hooks (bench.py): CUDA-event timing of kernel classes on the forward's own stream -------- */
+enum {
+  WM_PROF_LN = 0,          /* layernorm_kernel */
+  WM_PROF_QKV = 1,         /* gemm_kernel<EPI_QKV> */
+  WM_PROF_ATTN_LOCAL = 2,  /* attn_kernel, per-view (frame blocks and DINOv2) */
+  WM_PROF_ATTN_GLOBAL = 3, /* attn_kernel over all views' tokens */
+  WM_PROF_PROJ = 4,        /* gemm_kernel<EPI_RESID>, K = 1024 */
+  WM_PROF_FC1 = 5,         /* gemm_kernel<EPI_GELU> */
+  WM_PROF_FC2 = 6,         /* gemm_kernel<EPI_RESID>, K = 4096 */
+  WM_PROF_EMBED = 7,       /* patch gather / patch-embed GEMM / prior tokens / assembly */
+  WM_PROF_ALLGATHER = 8,   /* ncclAllGather of K|V */
+  WM_PROF_CLASSES = 9
+};
+/* Select the classes to time (bit i = class i; 0 switches timing off) and reset the records and launch counter. */
+wm_status wm_profile(wm_handle* h, unsigned class_mask);
+/* Synchronises on the recorded events; total_ms = sum over the launches of class `cls` since wm_profile(). */
+wm_status wm_profile_read(wm_handle* h, int cls, float* total_ms, int* count);
+/* Kernel (and collective) launches issued by forwards since the last wm_profile() call. */
+long long wm_launch_count(const wm_handle* h);
+
 /* ---- sequence parallelism: K|V all-gather of the global blocks through NCCL --------- */
 /* `nccl_lib` = path of libnccl.so.2 (the one torch loaded).  unique_id: 128 bytes. */
 wm_status wm_nccl_unique_id(const char* nccl_lib, void* unique_id_128);
