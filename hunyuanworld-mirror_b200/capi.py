@@ -49,7 +49,8 @@ SIGNATURES = {
     "wm_layernorm": (C.c_int, [_vp, _fp, _fp, _fp, _f, _i, _vp, _i]),
     "wm_gemm_bias_act": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _i, _i, _i, _vp, _i, _i]),
     "wm_gemm_qkv": (C.c_int, [_vp, _vp, _vp, _fp, _fp, _fp, _fp, _fp, _f, _fp, _fp, _i, _i, _i, _i, _vp, _vp]),
-    "wm_gemm_ls_residual": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _fp, _i, _i, _i, _fp, _i, _fp, _i, _i]),
+    "wm_gemm_ls_residual": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _fp, _i, _i, _i, _fp, _i]),
+    "wm_copy_cols": (C.c_int, [_vp, _fp, C.c_longlong, _fp, _i, _i]),
     "wm_gemm_table": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _i, _i, _i, _i, _fp, _i]),
     "wm_flash_attn": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _i]),
     "wm_flash_attn_dbg": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _i, _u, _u]),

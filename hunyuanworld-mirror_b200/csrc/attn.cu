@@ -7,14 +7,20 @@
 // exactly what the QKV GEMM writes and the proj GEMM reads, so no permute/transposed copy exists.
 //
 // Persistent CTAs (one per SM, 384 threads).  A work item is (head, batch, 256 query rows):
-//   warp 0      TMA producer: Q pair once per item, K/V tiles through a KV_STAGES ring
-//   warp 1      MMA issuer (one lane): S_w = Q_w K^T (128x128x64), O_w += P_w V (128x64x128)
+//   warp 0      TMA producer: Q pair (double-buffered across items), K/V tiles through a 3-stage ring
+//   warp 1      MMA issuer (one lane): S_w = Q_w K^T (128x128x64), O_w += P_w V (128x64x128, P from TMEM)
 //   warp 2      TMEM allocator
 //   warps 4-7   softmax / correction / epilogue for query tile 0 (thread == query row)
-//   warps 8-11  the same for query tile 1 (ping-pong: tensor core works on one tile while the other is in softmax)
-// TMEM: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384); P (bf16) overwrites the first 64 columns of its S.
+//   warps 8-11  the same for query tile 1
+// TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384) P0 [384,448) P1 [448,512).
+// P has its own columns, so the softmax warps release S as soon as it is in registers (s_free) and the MMA
+// warp issues S(j+1) while softmax(j) is still running: a warpgroup goes from one tile's softmax straight
+// into the next, and the next work item's first S overlaps the current item's epilogue.
 // Online softmax keeps a running max that is only advanced (and O rescaled) when it grew by more than 2^8,
-// so the O correction is rare; the row sum and the final 1/l normalisation stay in fp32.
+// so the O correction is rare; row sum and the final 1/l normalisation stay in fp32.  exp2 runs on the MUFU
+// pipe for most elements and, for NPOLY of every 32, as a Cody-Waite split + degree-3 polynomial on the FMA
+// pipe (max relative error 7.6e-5, far below the bf16 rounding of P): at head_dim 64 the kernel is bound by
+// exponentials, not by the tensor core (SURVEY.md section 7 "hard parts").
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -22,48 +28,61 @@ namespace wm {
 
 constexpr int ATT_THREADS = 384;
 constexpr int ATT_TILE = 128 * 64 * 2;  // one 128 x 64 bf16 tile, 16 KB
+constexpr int KV_ST = 3;
+constexpr int ATT_SMEM = (4 + 2 * KV_ST + 2) * ATT_TILE + 512 + 1024;
 
 struct AttnArgs {
   int Lq, Lkv, batch;
   int n_qpairs, n_kv, total_items;
   float scale_log2;
-  uint32_t v_lbo, v_sbo;  // V (MN-major B operand) descriptor strides in bytes
 };
 
-template <bool P_TMEM>
-struct AttnCfg {
-  static constexpr int KV_STAGES = P_TMEM ? 4 : 2;
-  static constexpr int P_TILES = P_TMEM ? 0 : 4;  // two 64-wide K halves per query tile
-  static constexpr int SMEM = (2 + 2 * KV_STAGES + 2 + P_TILES) * ATT_TILE + 512 + 1024;
-};
-
-__host__ __device__ constexpr uint32_t s_col(int w) { return 128u * w; }        // S0 / S1
+__host__ __device__ constexpr uint32_t s_col(int w) { return 128u * w; }         // S0 / S1
 __host__ __device__ constexpr uint32_t o_col(int w) { return 256u + 64u * w; }   // O0 / O1
+__host__ __device__ constexpr uint32_t p_col(int w) { return 384u + 64u * w; }   // P0 / P1 (bf16 pairs)
 
-template <bool P_TMEM>
+// 2^x for x <= 0 on the FMA pipe, two lanes at a time: x = n + f with n = round(x), f in [-0.5, 0.5];
+// 2^f by a degree-3 minimax polynomial, 2^n by adding n to the exponent field.
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+  const float2 magic = make_float2(12582912.0f, 12582912.0f);  // 1.5 * 2^23: the add rounds x to an integer
+  x.x = fmaxf(x.x, -126.0f);
+  x.y = fmaxf(x.y, -126.0f);
+  const float2 xr = fadd2(x, magic);
+  const float2 n = fadd2(xr, make_float2(-12582912.0f, -12582912.0f));
+  const float2 f = ffma2(n, make_float2(-1.0f, -1.0f), x);
+  float2 p = ffma2(make_float2(0.05520551f, 0.05520551f), f, make_float2(0.24261397f, 0.24261397f));
+  p = ffma2(p, f, make_float2(0.69325477f, 0.69325477f));
+  p = ffma2(p, f, make_float2(0.9999277f, 0.9999277f));
+  float2 r;
+  r.x = __uint_as_float(__float_as_uint(p.x) + (__float_as_uint(xr.x) << 23));
+  r.y = __uint_as_float(__float_as_uint(p.y) + (__float_as_uint(xr.y) << 23));
+  return r;
+}
+
+template <int NPOLY>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO, const AttnArgs a) {
-  using Cfg = AttnCfg<P_TMEM>;
-  constexpr int ST = Cfg::KV_STAGES;
+  constexpr int ST = KV_ST;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  uint8_t* sQ = smem;                       // 2 tiles
-  uint8_t* sK = sQ + 2 * ATT_TILE;          // ST tiles
+  uint8_t* sQ = smem;                       // 2 buffers x 2 tiles
+  uint8_t* sK = sQ + 4 * ATT_TILE;          // ST tiles
   uint8_t* sV = sK + ST * ATT_TILE;         // ST tiles
   uint8_t* sO = sV + ST * ATT_TILE;         // 2 tiles (epilogue staging, one per query tile)
-  uint8_t* sP = sO + 2 * ATT_TILE;          // 4 tiles when P goes through shared memory
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + Cfg::P_TILES * ATT_TILE);
-  uint64_t* q_full = bars;            // 1
-  uint64_t* q_empty = bars + 1;       // 1
-  uint64_t* k_full = bars + 2;        // ST
-  uint64_t* k_empty = k_full + ST;    // ST
-  uint64_t* v_full = k_empty + ST;    // ST
-  uint64_t* v_empty = v_full + ST;    // ST
-  uint64_t* s_full = v_empty + ST;    // 2
-  uint64_t* p_full = s_full + 2;      // 2
-  uint64_t* o_done = p_full + 2;      // 2
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_done + 2);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sO + 2 * ATT_TILE);
+  uint64_t* q_full = bars;             // 2
+  uint64_t* q_empty = q_full + 2;      // 2
+  uint64_t* k_full = q_empty + 2;      // ST
+  uint64_t* k_empty = k_full + ST;     // ST
+  uint64_t* v_full = k_empty + ST;     // ST
+  uint64_t* v_empty = v_full + ST;     // ST
+  uint64_t* s_full = v_empty + ST;     // 2  MMA -> softmax: S_w written
+  uint64_t* s_free = s_full + 2;       // 2  softmax -> MMA: S_w is in registers
+  uint64_t* p_full = s_free + 2;       // 2  softmax -> MMA: P_w written
+  uint64_t* pv_done = p_full + 2;      // 2  MMA -> softmax: O_w += P_w V complete (P_w reusable, O_w readable)
+  uint64_t* o_free = pv_done + 2;      // 2  epilogue -> MMA: O_w has been read out
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 2);
 
   const int warp = threadIdx.x >> 5;
 
@@ -74,18 +93,20 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     tma_prefetch_desc(&tmO);
   }
   if (warp == 1 && elect_one()) {
-    mbar_init(q_full, 1);
-    mbar_init(q_empty, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&s_free[i], 128);
+      mbar_init(&p_full[i], 128);
+      mbar_init(&pv_done[i], 1);
+      mbar_init(&o_free[i], 128);
+    }
     for (int i = 0; i < ST; ++i) {
       mbar_init(&k_full[i], 1);
       mbar_init(&k_empty[i], 1);
       mbar_init(&v_full[i], 1);
       mbar_init(&v_empty[i], 1);
-    }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&s_full[i], 1);
-      mbar_init(&p_full[i], 128);
-      mbar_init(&o_done[i], 1);
     }
     fence_barrier_init();
   }
@@ -108,10 +129,11 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
           const int per_head = a.batch * a.n_qpairs;
           const int h = item / per_head, rem = item % per_head;
           const int b = rem / a.n_qpairs, q0 = (rem % a.n_qpairs) * 256;
-          mbar_wait(q_empty, (icount & 1) ^ 1);
-          mbar_arrive_expect_tx(q_full, 2 * ATT_TILE);
-          tma_load_3d(sQ, &tmQ, q_full, h * 64, q0, b, kEvictFirst);
-          tma_load_3d(sQ + ATT_TILE, &tmQ, q_full, h * 64, q0 + 128, b, kEvictFirst);
+          const uint32_t qb = icount & 1, qph = (icount >> 1) & 1;
+          mbar_wait(&q_empty[qb], qph ^ 1);
+          mbar_arrive_expect_tx(&q_full[qb], 2 * ATT_TILE);
+          tma_load_3d(sQ + (2 * qb) * ATT_TILE, &tmQ, &q_full[qb], h * 64, q0, b, kEvictFirst);
+          tma_load_3d(sQ + (2 * qb + 1) * ATT_TILE, &tmQ, &q_full[qb], h * 64, q0 + 128, b, kEvictFirst);
           for (int j = 0; j < a.n_kv; ++j, ++kvit) {
             const uint32_t s = kvit % ST, ph = (kvit / ST) & 1;
             mbar_wait(&k_empty[s], ph ^ 1);
@@ -130,14 +152,21 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);
         constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);  // B = V is MN-major (dims contiguous)
         uint32_t kvit = 0, icount = 0;
-        uint32_t pcount[2] = {0, 0};
+        uint32_t tiles0 = 0, tiles1 = 0;  // S tiles issued per warpgroup (s_free phase bookkeeping)
+        uint32_t pvs0 = 0, pvs1 = 0;      // PVs issued per warpgroup (p_full phases consumed)
+        uint32_t items0 = 0, items1 = 0;  // work items started per warpgroup (o_free phases)
         for (int item = blockIdx.x; item < a.total_items; item += gridDim.x, ++icount) {
           const int q0 = (item % a.n_qpairs) * 256;
           const int nw = (q0 + 128 < a.Lq) ? 2 : 1;  // second query tile entirely out of range: skip it
-          mbar_wait(q_full, icount & 1);
+          const uint32_t qb = icount & 1, qph = (icount >> 1) & 1;
+          mbar_wait(&q_full[qb], qph);
           tcgen05_fence_after();
           auto issue_s = [&](int w, uint32_t stage) {
-            const uint64_t qd = umma_desc_sw128(smem_u32(sQ + w * ATT_TILE), 16, 1024);
+            uint32_t& tiles = w == 0 ? tiles0 : tiles1;
+            mbar_wait(&s_free[w], (tiles & 1) ^ 1);  // softmax has read the previous S_w into registers
+            ++tiles;
+            tcgen05_fence_after();
+            const uint64_t qd = umma_desc_sw128(smem_u32(sQ + (2 * qb + w) * ATT_TILE), 16, 1024);
             const uint64_t kd = umma_desc_sw128(smem_u32(sK + stage * ATT_TILE), 16, 1024);
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_ss(tmem_base + s_col(w), qd + 2 * k, kd + 2 * k, idesc_s, k != 0);
@@ -152,39 +181,34 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
           }
           for (int j = 0; j < a.n_kv; ++j, ++kvit) {
             const uint32_t sj = kvit % ST, phj = (kvit / ST) & 1;
-            const uint32_t sn = (kvit + 1) % ST, phn = ((kvit + 1) / ST) & 1;
-            const bool more = j + 1 < a.n_kv;
+            if (j + 1 < a.n_kv) {
+              const uint32_t sn = (kvit + 1) % ST, phn = ((kvit + 1) / ST) & 1;
+              mbar_wait(&k_full[sn], phn);
+              tcgen05_fence_after();
+              for (int w = 0; w < nw; ++w) issue_s(w, sn);
+              umma_commit(&k_empty[sn]);
+            }
             mbar_wait(&v_full[sj], phj);
             tcgen05_fence_after();
             for (int w = 0; w < nw; ++w) {
-              mbar_wait(&p_full[w], pcount[w] & 1);
-              ++pcount[w];
+              uint32_t& pvs = w == 0 ? pvs0 : pvs1;
+              mbar_wait(&p_full[w], pvs & 1);
+              ++pvs;
+              if (j == 0) mbar_wait(&o_free[w], ((w == 0 ? items0 : items1) & 1) ^ 1);  // previous item's O_w read out
               tcgen05_fence_after();
               const uint32_t vbase = smem_u32(sV + sj * ATT_TILE);
 #pragma unroll
-              for (int k = 0; k < 8; ++k) {  // 16 kv rows (2048 B of the V tile) per step
-                const uint64_t vd = umma_desc_sw128(vbase + k * 2048, a.v_lbo, a.v_sbo);
-                if (P_TMEM) {
-                  umma_ts(tmem_base + o_col(w), tmem_base + s_col(w) + k * 8, vd, idesc_pv, (j | k) != 0);
-                } else {
-                  const uint64_t pd =
-                      umma_desc_sw128(smem_u32(sP + (2 * w + (k >> 2)) * ATT_TILE), 16, 1024) + 2 * (k & 3);
-                  umma_ss(tmem_base + o_col(w), pd, vd, idesc_pv, (j | k) != 0);
-                }
+              for (int k = 0; k < 8; ++k) {  // 16 kv rows (2048 B of the V tile) per step; P: 8 TMEM columns per step
+                const uint64_t vd = umma_desc_sw128(vbase + k * 2048, 1024, 1024);
+                umma_ts(tmem_base + o_col(w), tmem_base + p_col(w) + k * 8, vd, idesc_pv, (j | k) != 0);
               }
-              umma_commit(&o_done[w]);
-              if (more) {
-                if (w == 0) {
-                  mbar_wait(&k_full[sn], phn);
-                  tcgen05_fence_after();
-                }
-                issue_s(w, sn);
-              }
+              umma_commit(&pv_done[w]);
             }
             umma_commit(&v_empty[sj]);
-            if (more) umma_commit(&k_empty[sn]);
           }
-          umma_commit(q_empty);
+          umma_commit(&q_empty[qb]);
+          ++items0;
+          if (nw == 2) ++items1;
         }
       }
       __syncwarp();
@@ -192,14 +216,16 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   } else {
     // ---------------------------------------------------------------- softmax / correction / epilogue
     setmaxnreg_inc<208>();
-    const int w = (warp - 4) >> 2;              // query tile of this warpgroup
-    const int wt = threadIdx.x - 128 - w * 128;  // row inside the tile
+    const int w = (warp - 4) >> 2;               // query tile of this warpgroup
+    const int wt = (threadIdx.x - 128) & 127;    // row inside the tile
     const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const uint32_t s_addr = tmem_base + s_col(w) + lane_base;
     const uint32_t o_addr = tmem_base + o_col(w) + lane_base;
+    const uint32_t p_addr = tmem_base + p_col(w) + lane_base;
     const uint32_t stg = smem_u32(sO + w * ATT_TILE);
     const bool ragged = (a.Lkv & 127) != 0;
-    uint32_t scount = 0, ocount = 0;  // completed phases of s_full[w] / o_done[w] consumed so far
+    const float2 scale2 = make_float2(a.scale_log2, a.scale_log2);
+    uint32_t scount = 0, pvbase = 0;  // s_full[w] phases consumed / pv_done[w] phases of finished items
 
     for (int item = blockIdx.x; item < a.total_items; item += gridDim.x) {
       const int per_head = a.batch * a.n_qpairs;
@@ -215,6 +241,8 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
 #pragma unroll
         for (int i = 0; i < 4; ++i) tmem_ld_x32(s_addr + 32 * i, v[i]);
         tmem_wait_ld();
+        tcgen05_fence_before();
+        mbar_arrive(&s_free[w]);  // the MMA warp may overwrite S_w with the next tile's scores
         if (ragged && j == a.n_kv - 1) {
           const int valid = a.Lkv - j * 128;
 #pragma unroll
@@ -229,13 +257,15 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
 #pragma unroll
           for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(v[i][c]));
         const float m_new = fmaxf(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])), m);
+        bool pv_waited = false;
         if (j == 0) {
           m = m_new;
         } else {
           const bool need = (m_new - m) * a.scale_log2 > 8.0f;
           if (__any_sync(0xffffffffu, need)) {
             // O correction: wait for PV(j-1), then scale this row of O and l by 2^((m_old - m_new) * scale)
-            mbar_wait(&o_done[w], (ocount + j - 1) & 1);
+            mbar_wait(&pv_done[w], (pvbase + j - 1) & 1);
+            pv_waited = true;
             tcgen05_fence_after();
             const float alpha = need ? ex2_approx((m - m_new) * a.scale_log2) : 1.0f;
             if (need) m = m_new;
@@ -254,59 +284,58 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
           }
         }
         const float ms = m * a.scale_log2;
-        float sum[4] = {0.f, 0.f, 0.f, 0.f};
+        const float2 nms2 = make_float2(-ms, -ms);
+        float2 sum2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+        uint32_t pk[2][32];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          uint32_t pk[16];
 #pragma unroll
           for (int c = 0; c < 32; c += 2) {
-            const float p0 = ex2_approx(fmaf(__uint_as_float(v[i][c]), a.scale_log2, -ms));
-            const float p1 = ex2_approx(fmaf(__uint_as_float(v[i][c + 1]), a.scale_log2, -ms));
-            sum[(c >> 1) & 3] += p0 + p1;
-            pk[c >> 1] = pack_bf16(p0, p1);
-          }
-          if (P_TMEM) {
-            tmem_st_x16(s_addr + 16 * i, pk);
-          } else {
-            // K-major SW128 tile pair: columns [64*half, 64*half+64) of row wt; chunk = 8 bf16 = 16 bytes
-            const uint32_t pbase = smem_u32(sP + (2 * w + (i >> 1)) * ATT_TILE);
-#pragma unroll
-            for (int c = 0; c < 4; ++c)
-              st_shared_v4(pbase + sw128_offset(wt, (i & 1) * 4 + c), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2],
-                           pk[4 * c + 3]);
+            const float2 xs = ffma2(make_float2(__uint_as_float(v[i][c]), __uint_as_float(v[i][c + 1])), scale2, nms2);
+            float2 p;
+            if (c >= 32 - NPOLY) {
+              p = exp2_poly2(xs);
+            } else {
+              p.x = ex2_approx(xs.x);
+              p.y = ex2_approx(xs.y);
+            }
+            sum2[(c >> 1) & 1] = fadd2(sum2[(c >> 1) & 1], p);
+            pk[i >> 1][(i & 1) * 16 + (c >> 1)] = pack_bf16(p.x, p.y);
           }
         }
-        l += (sum[0] + sum[1]) + (sum[2] + sum[3]);
-        if (P_TMEM) {
-          tmem_wait_st();
-          tcgen05_fence_before();
-        } else {
-          fence_proxy_async_smem();
-          tcgen05_fence_before();
+        l += (sum2[0].x + sum2[0].y) + (sum2[1].x + sum2[1].y);
+        if (j > 0 && !pv_waited) {  // P_w is still being read by PV(j-1) until this completes (normally long done)
+          mbar_wait(&pv_done[w], (pvbase + j - 1) & 1);
+          tcgen05_fence_after();
         }
+        tmem_st_x32(p_addr, pk[0]);
+        tmem_st_x32(p_addr + 32, pk[1]);
+        tmem_wait_st();
+        tcgen05_fence_before();
         mbar_arrive(&p_full[w]);
       }
       // ---- epilogue: O / l -> bf16 -> swizzled staging tile -> TMA store
-      ocount += a.n_kv;
-      mbar_wait(&o_done[w], (ocount - 1) & 1);
+      pvbase += a.n_kv;
+      mbar_wait(&pv_done[w], (pvbase - 1) & 1);
       tcgen05_fence_after();
       uint32_t o[2][32];
       tmem_ld_x32(o_addr, o[0]);
       tmem_ld_x32(o_addr + 32, o[1]);
       tmem_wait_ld();
       tcgen05_fence_before();
+      mbar_arrive(&o_free[w]);  // the next item's first PV may overwrite O_w
       if (wt == 0) tma_store_wait_read<0>();
       named_bar_sync(1 + w, 128);
       const float inv = 1.0f / l;
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
-        uint32_t pk[4];
+        uint32_t pk4[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int e = 8 * c + 2 * i;
-          pk[i] = pack_bf16(__uint_as_float(o[e >> 5][e & 31]) * inv, __uint_as_float(o[e >> 5][(e & 31) + 1]) * inv);
+          pk4[i] = pack_bf16(__uint_as_float(o[e >> 5][e & 31]) * inv, __uint_as_float(o[e >> 5][(e & 31) + 1]) * inv);
         }
-        st_shared_v4(stg + sw128_offset(wt, c), pk[0], pk[1], pk[2], pk[3]);
+        st_shared_v4(stg + sw128_offset(wt, c), pk4[0], pk4[1], pk4[2], pk4[3]);
       }
       fence_proxy_async_smem();
       named_bar_sync(1 + w, 128);
@@ -411,9 +440,27 @@ umma_probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
 }
 
 // ------------------------------------------------------------------------------------------------ host
+template <int NPOLY>
+static wm_status launch_attn(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
+                             const CUtensorMap& to, const AttnArgs& a) {
+  static bool cfg = false;
+  if (!cfg) {
+    WM_CUDA(cudaFuncSetAttribute(attn_kernel<NPOLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    cfg = true;
+  }
+  attn_kernel<NPOLY><<<grid, ATT_THREADS, ATT_SMEM, st>>>(tq, tk, tv, to, a);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// variant: how many of every 32 exponentials run as a polynomial on the FMA pipe (0 -> 0, 1 -> 8, 2 -> 12, 3 -> 16);
+// kDefaultVariant is what the forward pass uses.
+constexpr int kDefaultVariant = 2;
+
 wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
                           int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, uint32_t v_lbo,
                           uint32_t v_sbo) {
+  (void)v_lbo, (void)v_sbo;
   static int sm_count = 0;
   if (sm_count == 0) WM_TRY(require_sm100(&sm_count));
   WM_CHECK(q && k && v && o, "flash_attention: null pointer");
@@ -432,26 +479,15 @@ wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k
   a.n_kv = (Lkv + 127) / 128;
   a.total_items = heads * batch * a.n_qpairs;
   a.scale_log2 = scale * 1.4426950408889634f;
-  a.v_lbo = v_lbo ? v_lbo : 1024;
-  a.v_sbo = v_sbo ? v_sbo : 1024;
   const int grid = a.total_items < sm_count ? a.total_items : sm_count;
-  if (variant == 0) {
-    static bool cfg = false;
-    if (!cfg) {
-      WM_CUDA(cudaFuncSetAttribute(attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<true>::SMEM));
-      cfg = true;
-    }
-    attn_kernel<true><<<grid, ATT_THREADS, AttnCfg<true>::SMEM, st>>>(tq, tk, tv, to, a);
-  } else {
-    static bool cfg = false;
-    if (!cfg) {
-      WM_CUDA(cudaFuncSetAttribute(attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnCfg<false>::SMEM));
-      cfg = true;
-    }
-    attn_kernel<false><<<grid, ATT_THREADS, AttnCfg<false>::SMEM, st>>>(tq, tk, tv, to, a);
+  if (variant < 0) variant = kDefaultVariant;
+  switch (variant) {
+    case 0: return launch_attn<0>(st, grid, tq, tk, tv, to, a);
+    case 1: return launch_attn<8>(st, grid, tq, tk, tv, to, a);
+    case 2: return launch_attn<12>(st, grid, tq, tk, tv, to, a);
+    case 3: return launch_attn<16>(st, grid, tq, tk, tv, to, a);
+    default: return fail(WM_ERR_INVALID, "flash_attention: variant must be -1 (default) or 0..3");
   }
-  WM_LAUNCH_CHECK();
-  return WM_OK;
 }
 
 wm_status umma_probe(cudaStream_t st, const void* p, const void* v, float* d, int mode, uint32_t v_lbo, uint32_t v_sbo) {

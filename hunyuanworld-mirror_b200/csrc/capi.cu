@@ -255,13 +255,13 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
   const __nv_bfloat16* kbase = gather ? ws.kv : kv_local;
   WM_OP(s.global ? WM_PROF_ATTN_GLOBAL : WM_PROF_ATTN_LOCAL,
         flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
-                        0.125f, 0, 0, 0));
+                        0.125f, -1, 0, 0));
   WM_OP(WM_PROF_PROJ, gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x,
-                                       kEmbed, nullptr, 0, 0));
+                                       kEmbed));
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
   WM_OP(WM_PROF_FC1, gemm_bias_act(st, ws.ln, kEmbed, w.fc1_w, kEmbed, w.fc1_b, s.T, kMlp, kEmbed, ws.hid, kMlp, 1));
-  WM_OP(WM_PROF_FC2, gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed, out2,
-                                      2 * kEmbed, out2_col));
+  WM_OP(WM_PROF_FC2, gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed));
+  if (out2) WM_OP(WM_PROF_EMBED, copy_cols(st, x, s.T, out2, 2 * kEmbed, out2_col));
   return WM_OK;
 }
 
@@ -323,7 +323,7 @@ static wm_status run_embed(wm_handle* h, cudaStream_t st, const Workspace& ws, c
     WM_OP(WM_PROF_EMBED, gemm_bias_act(st, a_d, ld_d, f1.b16, f1.ld, h->w["depth_embed.proj.2.fc1.bias"].f32, T, kMlp, ld_d, ws.hid,
                          kMlp, 1));
     WM_OP(WM_PROF_EMBED, gemm_ls_residual(st, ws.hid, kMlp, f2.b16, f2.ld, h->w["depth_embed.proj.2.fc2.bias"].f32, nullptr, T, kEmbed,
-                            kMlp, ws.x, kEmbed, nullptr, 0, 0));
+                            kMlp, ws.x, kEmbed));
   }
   // final DINOv2 norm of the patch rows -> rows [7, 7+g) of x  (vision_transformer.py:259-263)
   WM_OP(WM_PROF_EMBED, layernorm(st, ws.xd, h->w["patch_embed.norm.weight"].f32, h->w["patch_embed.norm.bias"].f32, 1e-6f, n * g, g, Pd,
@@ -660,10 +660,14 @@ wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const floa
 }
 
 wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
-                              const float* gamma, int M, int N, int K, float* x, int ldx, float* out2, int ld2,
-                              int out2_col) {
-  return gemm_ls_residual(static_cast<cudaStream_t>(stream), A, lda, W, ldw, bias, gamma, M, N, K, x, ldx, out2, ld2,
-                          out2_col);
+                              const float* gamma, int M, int N, int K, float* x, int ldx) {
+  return gemm_ls_residual(static_cast<cudaStream_t>(stream), A, lda, W, ldw, bias, gamma, M, N, K, x, ldx);
+}
+
+wm_status wm_copy_cols(wm_stream stream, const float* x, long long rows, float* out, int ld_out, int col0) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return copy_cols(static_cast<cudaStream_t>(stream), x, rows, out, ld_out, col0);
 }
 
 wm_status wm_gemm_table(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* table,

@@ -5,17 +5,16 @@
 //   EPI_GELU   out bf16 = gelu_erf(acc + b)                         Mlp.fc1 + nn.GELU   (mlp.py:30-31)
 //   EPI_QKV    per 64-wide head: + b, QK-LayerNorm(64), 2D RoPE     attention.py:50-56, rope.py:148-181
 //              q -> out0[M,1024], k|v -> out1[M,2048]  (both bf16)
-//   EPI_RESID  x fp32 (in place) = x + gamma * (acc + b), optional second strided copy of the result
-//              (attn.proj / Mlp.fc2 + LayerScale + residual: block.py:91-92, layer_scale.py:17, and the
-//              `cat([frame, global], -1)` intermediates of visual_transformer.py:337-339)
+//   EPI_RESID  x fp32 += gamma * (acc + b) as a TMA reduce-add (the residual is never read by the SM);
+//              gamma null: x = acc + b   (attn.proj / Mlp.fc2 + LayerScale + residual: block.py:91-92)
 //   EPI_TABLE  out fp32 = acc + table[row % period][col]            DINOv2 patch embed + pos_embed / cls / reg
 //
-// One CTA per SM, 256 threads: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
-// warp 2 = TMEM allocator, warps 4-7 = epilogue (thread == accumulator row; TMEM lane quarter = warp % 4).
+// One CTA per SM, 384 threads: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
+// warp 2 = TMEM allocator, warps 4-11 = epilogue in two teams of four warps (team t owns accumulator columns
+// [128 t, 128 t + 128); thread == accumulator row; TMEM lane quarter = warp % 4).
 // Tile 128 x 256 x 64, 4-stage smem ring (SWIZZLE_128B, K-major for both operands), two 256-column TMEM
-// accumulators so the epilogue of tile i overlaps the main loop of tile i+1.  Outputs leave through a
-// swizzled staging tile and TMA stores (row clipping for the M tail comes for free); the fp32 residual is
-// TMA-loaded into that same staging tile, updated in place and stored back.
+// accumulators so the epilogue of tile i overlaps the main loop of tile i+1.  Outputs leave through one
+// swizzled staging tile per team and TMA stores / reduce-adds (row clipping for the M tail comes for free).
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -26,8 +25,8 @@ enum : int { EPI_BIAS = 0, EPI_GELU = 1, EPI_QKV = 2, EPI_RESID = 3, EPI_TABLE =
 constexpr int BM = 128, BN = 256, BK = 64, STAGES = 4;
 constexpr int A_BYTES = BM * BK * 2;        // 16 KB
 constexpr int B_BYTES = BN * BK * 2;        // 32 KB
-constexpr int STG_BYTES = 128 * 128;        // 128 rows x 128 B
-constexpr int GEMM_THREADS = 256;
+constexpr int STG_BYTES = 128 * 128;        // 128 rows x 128 B, one per epilogue team
+constexpr int GEMM_THREADS = 384;           // 4 control warps + 2 epilogue teams of 4 warps
 constexpr int GEMM_SMEM = STAGES * (A_BYTES + B_BYTES) + 2 * STG_BYTES + 256 + 1024;
 
 struct GemmArgs {
@@ -40,31 +39,59 @@ struct GemmArgs {
   int tokens_per_view, patch_start, grid_w;
   float qk_eps;
   // EPI_RESID
-  const float* gamma;  // null: out = acc + b (no residual read)
-  int has_out2, out2_col;
+  const float* gamma;  // null: out = acc + b (plain store); else out += gamma * (acc + b) (TMA reduce-add)
   // EPI_TABLE
   const float* table;
   int table_period;
 };
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// Exact-erf GELU (nn.GELU() default, mlp.py:16,25) with erf from Abramowitz-Stegun 7.1.26 (|err| <= 1.5e-7,
+// far below the bf16 rounding of the output): Phi(x) = 1 - h for x >= 0, h for x < 0,
+// h = 0.5 * (a1 t + ... + a5 t^5) * exp(-x^2 / 2), t = 1 / (1 + p |x| / sqrt(2)).
+__device__ __forceinline__ float gelu_erf(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = rcp_approx(fmaf(z, 0.3275911f, 1.0f));
+  float poly = fmaf(t, 1.061405429f, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float h = 0.5f * poly * t * ex2_approx(z * z * -1.4426950408889634f);
+  return x * (x >= 0.f ? 1.0f - h : h);
+}
+
+__device__ __forceinline__ void add_vec64(float (&x)[64], const float* __restrict__ b) {
+  const float4* b4 = reinterpret_cast<const float4*>(b);
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float4 v = __ldg(b4 + i);
+    x[4 * i] += v.x, x[4 * i + 1] += v.y, x[4 * i + 2] += v.z, x[4 * i + 3] += v.w;
+  }
+}
 
 // LayerNorm over the 64 values of one head held by one thread (attention.py:41-42,52; eps 1e-5, affine).
 __device__ __forceinline__ void head_layernorm(float (&x)[64], const float* __restrict__ w,
                                                const float* __restrict__ b, float eps) {
-  float s = 0.f;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-  for (int i = 0; i < 64; ++i) s += x[i];
-  const float mu = s * (1.0f / 64.0f);
-  float v = 0.f;
+  for (int i = 0; i < 64; i += 4) s0 += x[i], s1 += x[i + 1], s2 += x[i + 2], s3 += x[i + 3];
+  const float mu = ((s0 + s1) + (s2 + s3)) * (1.0f / 64.0f);
+  float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
 #pragma unroll
-  for (int i = 0; i < 64; ++i) {
-    const float d = x[i] - mu;
-    v += d * d;
+  for (int i = 0; i < 64; i += 4) {
+    const float d0 = x[i] - mu, d1 = x[i + 1] - mu, d2 = x[i + 2] - mu, d3 = x[i + 3] - mu;
+    v0 = fmaf(d0, d0, v0), v1 = fmaf(d1, d1, v1), v2 = fmaf(d2, d2, v2), v3 = fmaf(d3, d3, v3);
   }
-  const float rstd = rsqrtf(v * (1.0f / 64.0f) + eps);
+  const float rstd = rsqrtf(((v0 + v1) + (v2 + v3)) * (1.0f / 64.0f) + eps);
+  const float4* w4 = reinterpret_cast<const float4*>(w);
+  const float4* b4 = reinterpret_cast<const float4*>(b);
 #pragma unroll
-  for (int i = 0; i < 64; ++i) x[i] = (x[i] - mu) * rstd * __ldg(w + i) + __ldg(b + i);
+  for (int i = 0; i < 16; ++i) {
+    const float4 ww = __ldg(w4 + i), bb = __ldg(b4 + i);
+    x[4 * i] = (x[4 * i] - mu) * rstd * ww.x + bb.x;
+    x[4 * i + 1] = (x[4 * i + 1] - mu) * rstd * ww.y + bb.y;
+    x[4 * i + 2] = (x[4 * i + 2] - mu) * rstd * ww.z + bb.z;
+    x[4 * i + 3] = (x[4 * i + 3] - mu) * rstd * ww.w + bb.w;
+  }
 }
 
 // 2D RoPE (rope.py:148-181): dims [0,32) rotate by y, [32,64) by x; inside each half the pair is (i, i+16).
@@ -73,14 +100,19 @@ __device__ __forceinline__ void head_rope(float (&x)[64], const float* __restric
 #pragma unroll
   for (int half = 0; half < 2; ++half) {
     const int p = half == 0 ? py : px;
-    const float* c = cs + p * 16;
-    const float* s = sn + p * 16;
+    const float4* c4 = reinterpret_cast<const float4*>(cs + p * 16);
+    const float4* s4 = reinterpret_cast<const float4*>(sn + p * 16);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const float co = __ldg(c + i), si = __ldg(s + i);
-      const float a = x[half * 32 + i], bb = x[half * 32 + 16 + i];
-      x[half * 32 + i] = a * co - bb * si;
-      x[half * 32 + 16 + i] = bb * co + a * si;
+    for (int i4 = 0; i4 < 4; ++i4) {
+      const float4 co = __ldg(c4 + i4), si = __ldg(s4 + i4);
+      const float cc[4] = {co.x, co.y, co.z, co.w}, ss[4] = {si.x, si.y, si.z, si.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int i = 4 * i4 + k;
+        const float a = x[half * 32 + i], bb = x[half * 32 + 16 + i];
+        x[half * 32 + i] = a * cc[k] - bb * ss[k];
+        x[half * 32 + 16 + i] = bb * cc[k] + a * ss[k];
+      }
     }
   }
 }
@@ -98,8 +130,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* empty = full + STAGES;
   uint64_t* tfull = empty + STAGES;
   uint64_t* tempty = tfull + 2;
-  uint64_t* ldbar = tempty + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(ldbar + 2);
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int total_tiles = g.num_m_tiles * g.num_n_tiles;
@@ -108,7 +139,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC0);
-    if (EPI == EPI_QKV || EPI == EPI_RESID) tma_prefetch_desc(&tmC1);
+    if (EPI == EPI_QKV) tma_prefetch_desc(&tmC1);
   }
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < STAGES; ++i) {
@@ -117,8 +148,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 128);
-      mbar_init(&ldbar[i], 1);
+      mbar_init(&tempty[i], 256);
     }
     fence_barrier_init();
   }
@@ -174,32 +204,27 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     __syncwarp();
   } else if (warp >= 4) {
-    // ------------------------------------------------------------ epilogue (128 threads, thread == row)
-    const int et = threadIdx.x - 128;
+    // ------------------------------------------------------------ epilogue: two teams of 128 threads, team t owns
+    // accumulator columns [128 t, 128 t + 128); thread == accumulator row; one staging tile per team
+    const int team = (warp - 4) >> 2;
+    const int et = (threadIdx.x - 128) & 127;
     const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const uint32_t stg0 = smem_u32(sC);
-    uint32_t tcount = 0, ccount = 0;
-
-    if (EPI == EPI_RESID) {
-      // prologue: residual chunk 0 of this CTA's first tile -> staging buffer 0
-      if (et == 0 && g.gamma != nullptr && (int)blockIdx.x < total_tiles) {
-        const int m0 = (blockIdx.x / g.num_n_tiles) * BM, n0 = (blockIdx.x % g.num_n_tiles) * BN;
-        mbar_arrive_expect_tx(&ldbar[0], STG_BYTES);
-        tma_load_2d(sC, &tmC0, &ldbar[0], n0, m0, kEvictNormal);
-      }
-    }
+    uint8_t* stg_ptr = sC + team * STG_BYTES;
+    const uint32_t stg = smem_u32(stg_ptr);
+    const uint32_t bar_id = 1 + team;
+    uint32_t tcount = 0;
 
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       const int m0 = (tile / g.num_n_tiles) * BM;
-      const int n0 = (tile % g.num_n_tiles) * BN;
+      const int n0 = (tile % g.num_n_tiles) * BN + team * 128;
       const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
       mbar_wait(&tfull[acc], aph);
       tcgen05_fence_after();
-      const uint32_t taddr = tmem_base + acc * BN + lane_base;
+      const uint32_t taddr = tmem_base + acc * BN + team * 128 + lane_base;
       const int row = m0 + et;
 
       if (EPI == EPI_BIAS || EPI == EPI_GELU || EPI == EPI_QKV) {
-        // ---- bf16 outputs: four 64-column groups (one attention head each for EPI_QKV)
+        // ---- bf16 outputs: two 64-column groups per team (one attention head each for EPI_QKV)
         int py = 0, px = 0;
         if (EPI == EPI_QKV && g.rope_cos != nullptr) {
           const int p = row % g.tokens_per_view;
@@ -210,10 +235,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
         }
 #pragma unroll 1
-        for (int grp = 0; grp < BN / 64; ++grp, ++ccount) {
-          const uint32_t stg = stg0 + (ccount & 1) * STG_BYTES;
-          if (et == 0) tma_store_wait_read<1>();  // the store that last used this buffer has drained it
-          named_bar_sync(1, 128);
+        for (int grp = 0; grp < 2; ++grp) {
           float x[64];
           {
             uint32_t v0[32], v1[32];
@@ -226,14 +248,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               x[32 + i] = __uint_as_float(v1[i]);
             }
           }
-          if (grp == BN / 64 - 1) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
+          if (grp == 1) {  // this thread's share of the accumulator is in registers: hand TMEM back to the MMA warp
             tcgen05_fence_before();
             mbar_arrive(&tempty[acc]);
           }
           const int col0 = n0 + grp * 64;
-          const float* bias = g.bias + col0;
-#pragma unroll
-          for (int i = 0; i < 64; ++i) x[i] += __ldg(bias + i);
+          add_vec64(x, g.bias + col0);
           if (EPI == EPI_GELU) {
 #pragma unroll
             for (int i = 0; i < 64; ++i) x[i] = gelu_erf(x[i]);
@@ -246,93 +266,69 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               if (g.rope_cos != nullptr) head_rope(x, g.rope_cos, g.rope_sin, py, px);
             }
           }
+          if (et == 0) tma_store_wait_read<0>();  // the team's previous store has drained the staging tile
+          named_bar_sync(bar_id, 128);
 #pragma unroll
           for (int c = 0; c < 8; ++c)
             st_shared_v4(stg + sw128_offset(et, c), pack_bf16(x[8 * c], x[8 * c + 1]),
                          pack_bf16(x[8 * c + 2], x[8 * c + 3]), pack_bf16(x[8 * c + 4], x[8 * c + 5]),
                          pack_bf16(x[8 * c + 6], x[8 * c + 7]));
           fence_proxy_async_smem();
-          named_bar_sync(1, 128);
+          named_bar_sync(bar_id, 128);
           if (et == 0) {
-            const void* src = sC + (ccount & 1) * STG_BYTES;
             if (EPI == EPI_QKV && col0 >= kEmbed)
-              tma_store_2d(&tmC1, src, col0 - kEmbed, m0);
+              tma_store_2d(&tmC1, stg_ptr, col0 - kEmbed, m0);
             else
-              tma_store_2d(&tmC0, src, col0, m0);
+              tma_store_2d(&tmC0, stg_ptr, col0, m0);
             tma_store_commit();
           }
         }
       } else {
-        // ---- fp32 outputs: eight 32-column chunks
+        // ---- fp32 outputs: four 32-column chunks per team
 #pragma unroll 1
-        for (int ch = 0; ch < BN / 32; ++ch, ++ccount) {
-          const uint32_t buf = ccount & 1;
-          const uint32_t stg = stg0 + buf * STG_BYTES;
+        for (int ch = 0; ch < 4; ++ch) {
           const int col0 = n0 + ch * 32;
-          const bool resid = (EPI == EPI_RESID) && g.gamma != nullptr;
-          if (et == 0) {
-            if (resid) {
-              // prefetch the next residual chunk (possibly of this CTA's next tile) into the other buffer
-              int nt = tile, nch = ch + 1;
-              if (nch == BN / 32) {
-                nch = 0;
-                nt = tile + gridDim.x;
-              }
-              tma_store_wait_read<0>();
-              if (nt < total_tiles) {
-                mbar_arrive_expect_tx(&ldbar[buf ^ 1], STG_BYTES);
-                tma_load_2d(sC + (buf ^ 1) * STG_BYTES, &tmC0, &ldbar[buf ^ 1], (nt % g.num_n_tiles) * BN + nch * 32,
-                            (nt / g.num_n_tiles) * BM, kEvictNormal);
-              }
-            } else {
-              tma_store_wait_read<1>();
-            }
-          }
-          if (resid)
-            mbar_wait(&ldbar[buf], (ccount >> 1) & 1);
-          else
-            named_bar_sync(1, 128);
           uint32_t v[32];
           tmem_ld_x32(taddr + ch * 32, v);
           tmem_wait_ld();
-          if (ch == BN / 32 - 1) {
+          if (ch == 3) {
             tcgen05_fence_before();
             mbar_arrive(&tempty[acc]);
           }
-          const float* bias = g.bias + col0;
-          const float* tab = nullptr;
-          if (EPI == EPI_TABLE) tab = g.table + (size_t)(row % g.table_period) * g.N + col0;
+          float o[32];
+          if (EPI == EPI_TABLE) {
+            const float4* t4 = reinterpret_cast<const float4*>(g.table + (size_t)(row % g.table_period) * g.N + col0);
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            float o[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) o[i] = __uint_as_float(v[4 * c + i]);
-            const uint32_t addr = stg + sw128_offset(et, c);
-            if (EPI == EPI_TABLE) {
-              const float4 t = __ldg(reinterpret_cast<const float4*>(tab + 4 * c));
-              o[0] += t.x, o[1] += t.y, o[2] += t.z, o[3] += t.w;
-            } else {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) o[i] += __ldg(bias + 4 * c + i);
-              if (resid) {
-                uint32_t r0, r1, r2, r3;
-                ld_shared_v4(addr, r0, r1, r2, r3);
-                const float* gm = g.gamma + col0 + 4 * c;
-                o[0] = __uint_as_float(r0) + __ldg(gm + 0) * o[0];
-                o[1] = __uint_as_float(r1) + __ldg(gm + 1) * o[1];
-                o[2] = __uint_as_float(r2) + __ldg(gm + 2) * o[2];
-                o[3] = __uint_as_float(r3) + __ldg(gm + 3) * o[3];
-              }
+            for (int c = 0; c < 8; ++c) {
+              const float4 t = __ldg(t4 + c);
+              o[4 * c] = __uint_as_float(v[4 * c]) + t.x, o[4 * c + 1] = __uint_as_float(v[4 * c + 1]) + t.y;
+              o[4 * c + 2] = __uint_as_float(v[4 * c + 2]) + t.z, o[4 * c + 3] = __uint_as_float(v[4 * c + 3]) + t.w;
             }
-            st_shared_v4(addr, __float_as_uint(o[0]), __float_as_uint(o[1]), __float_as_uint(o[2]),
-                         __float_as_uint(o[3]));
+          } else {
+            const float4* b4 = reinterpret_cast<const float4*>(g.bias + col0);
+            const float4* g4 = reinterpret_cast<const float4*>(g.gamma + col0);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              const float4 b = __ldg(b4 + c);
+              float4 gm = make_float4(1.f, 1.f, 1.f, 1.f);
+              if (g.gamma != nullptr) gm = __ldg(g4 + c);
+              o[4 * c] = gm.x * (__uint_as_float(v[4 * c]) + b.x), o[4 * c + 1] = gm.y * (__uint_as_float(v[4 * c + 1]) + b.y);
+              o[4 * c + 2] = gm.z * (__uint_as_float(v[4 * c + 2]) + b.z), o[4 * c + 3] = gm.w * (__uint_as_float(v[4 * c + 3]) + b.w);
+            }
           }
+          if (et == 0) tma_store_wait_read<0>();
+          named_bar_sync(bar_id, 128);
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            st_shared_v4(stg + sw128_offset(et, c), __float_as_uint(o[4 * c]), __float_as_uint(o[4 * c + 1]),
+                         __float_as_uint(o[4 * c + 2]), __float_as_uint(o[4 * c + 3]));
           fence_proxy_async_smem();
-          named_bar_sync(1, 128);
+          named_bar_sync(bar_id, 128);
           if (et == 0) {
-            const void* src = sC + buf * STG_BYTES;
-            tma_store_2d(&tmC0, src, col0, m0);
-            if (EPI == EPI_RESID && g.has_out2) tma_store_2d(&tmC1, src, g.out2_col + col0, m0);
+            if (EPI == EPI_RESID && g.gamma != nullptr)
+              tma_reduce_add_2d(&tmC0, stg_ptr, col0, m0);  // x += gamma * (acc + b), added at L2
+            else
+              tma_store_2d(&tmC0, stg_ptr, col0, m0);
             tma_store_commit();
           }
         }
@@ -426,21 +422,15 @@ wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const
 }
 
 wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias,
-                           const float* gamma, int M, int N, int K, float* x, int ldx, float* out2, int ld2,
-                           int out2_col) {
+                           const float* gamma, int M, int N, int K, float* x, int ldx) {
   WM_TRY(check_common(A, W, M, N, K, lda, ldw));
   WM_CHECK(x && bias && ldx % 4 == 0 && ldx >= N, "gemm_ls_residual: bad x");
-  CUtensorMap ta, tb, tx, t2;
+  CUtensorMap ta, tb, tx;
   WM_TRY(operand_maps(&ta, &tb, A, lda, W, ldw, M, N, K));
   WM_TRY(tmap_2d(&tx, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, x, M, N, ldx, 32, 128));
-  t2 = tx;
-  if (out2) {
-    WM_CHECK(ld2 % 4 == 0 && out2_col >= 0 && out2_col + N <= ld2, "gemm_ls_residual: bad out2 geometry");
-    WM_TRY(tmap_2d(&t2, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out2, M, ld2, ld2, 32, 128));
-  }
   GemmArgs g{};
-  g.M = M, g.N = N, g.K = K, g.bias = bias, g.gamma = gamma, g.has_out2 = out2 != nullptr, g.out2_col = out2_col;
-  return launch<EPI_RESID>(st, ta, tb, tx, t2, g);
+  g.M = M, g.N = N, g.K = K, g.bias = bias, g.gamma = gamma;
+  return launch<EPI_RESID>(st, ta, tb, tx, tx, g);
 }
 
 wm_status gemm_table(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* table,

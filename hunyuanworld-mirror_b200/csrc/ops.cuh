@@ -11,8 +11,8 @@ wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const
                    const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q_out,
                    void* kv_out);
 wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias,
-                           const float* gamma, int M, int N, int K, float* x, int ldx, float* out2, int ld2,
-                           int out2_col);
+                           const float* gamma, int M, int N, int K, float* x, int ldx);
+wm_status copy_cols(cudaStream_t st, const float* x, long long rows, float* out, int ld_out, int col0);
 wm_status gemm_table(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* table,
                      int table_period, int M, int N, int K, float* out, int ldo);
 wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,

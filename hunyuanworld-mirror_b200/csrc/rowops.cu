@@ -207,6 +207,27 @@ wm_status special_tokens(cudaStream_t st, const float* cam, const float* reg, in
 }
 
 // ------------------------------------------------------------------------------------------------
+// Intermediate outputs (visual_transformer.py:337-339): out[:, col0 : col0 + 1024] = x, the two halves of the
+// reference's `cat([frame, global], -1)` written in place, one float4 per thread.
+__global__ void __launch_bounds__(256)
+copy_cols_kernel(const float4* __restrict__ x, long long rows, int ld_out4, int col4, float4* __restrict__ out) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= rows * (kEmbed / 4)) return;
+  const long long r = t / (kEmbed / 4);
+  const int c = (int)(t % (kEmbed / 4));
+  out[r * ld_out4 + col4 + c] = x[t];
+}
+
+wm_status copy_cols(cudaStream_t st, const float* x, long long rows, float* out, int ld_out, int col0) {
+  WM_CHECK(x && out && rows > 0 && ld_out % 4 == 0 && col0 % 4 == 0 && col0 + kEmbed <= ld_out, "copy_cols: bad arguments");
+  const long long total = rows * (kEmbed / 4);
+  copy_cols_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(x), rows, ld_out / 4,
+                                                                    col0 / 4, reinterpret_cast<float4*>(out));
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // fp32 -> bf16 packing with optional row padding (weights: [rows, cols] -> [rows, ld], zero tail columns).
 __global__ void __launch_bounds__(256)
 pack_bf16_kernel(const float* __restrict__ src, long long rows, int cols, int ld, __nv_bfloat16* __restrict__ dst) {

@@ -125,11 +125,12 @@ wm_status wm_gemm_bias_act(wm_stream stream, const void* A, int lda, const void*
 wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const float* bias, const float* qn_w,
                       const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
                       const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q, void* kv);
-/* Linear + LayerScale + residual (block.py:91-92): x [M,N] fp32 += gamma * (A W^T + bias); gamma NULL: x = A W^T + bias.
- * out2 (optional) [M, ld2] fp32 receives a copy of the new x at column out2_col. */
+/* Linear + LayerScale + residual (block.py:91-92): x [M,N] fp32 += gamma * (A W^T + bias), the addition done by a
+ * TMA reduce-add (each element is added exactly once: deterministic); gamma NULL: x = A W^T + bias. */
 wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
-                              const float* gamma, int M, int N, int K, float* x, int ldx, float* out2, int ld2,
-                              int out2_col);
+                              const float* gamma, int M, int N, int K, float* x, int ldx);
+/* out[:, col0 : col0+1024] = x [rows,1024] fp32: one half of `cat([frame, global], -1)` (visual_transformer.py:337-339). */
+wm_status wm_copy_cols(wm_stream stream, const float* x, long long rows, float* out, int ld_out, int col0);
 /* out [M,N] fp32 = A W^T + table[row % period] (DINOv2 patch embed + pos_embed, vision_transformer.py:209-221). */
 wm_status wm_gemm_table(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* table,
                         int period, int M, int N, int K, float* out, int ldo);

@@ -14,7 +14,7 @@ run() {
 }
 echo "== selftest $(date -u) $(nvidia-smi --query-gpu=name --format=csv,noheader | head -1)" >> $LOG
 if [ "$what" = probe ] || [ "$what" = all ]; then
-  for mode in 0 1; do for lbo in 16 128 1024 2048; do for sbo in 128 1024 2048; do run probe $mode $lbo $sbo; done; done; done
+  for mode in 0 1; do run probe $mode 1024 1024; done
 fi
 if [ "$what" = correct ] || [ "$what" = all ]; then
   run layernorm 333
@@ -22,14 +22,14 @@ if [ "$what" = correct ] || [ "$what" = all ]; then
   run gemm_bias 300 512 192 1 1
   run gemm_bias 5137 1024 256 0 37
   run gemm_bias 700 256 4096 1 7
-  run gemm_resid 300 512 192 1 1 1
-  run gemm_resid 300 512 192 0 0 1
+  run gemm_resid 300 512 192 1 0 1
+  run gemm_resid 300 1024 192 0 1 1
   run gemm_resid 5137 1024 1024 1 1 41
   run gemm_table 300 1024 588 640 77
   run gemm_qkv 300 1 1 3
   run gemm_qkv 300 0 0 3
   run gemm_qkv 2500 1 1 29
-  for var in 0 1; do
+  for var in 0 1 2 3; do
     run attn 2 331 331 2 1 $var 0 0 5
     run attn 1 128 128 1 1 $var 0 0 1
     run attn 1 1376 1376 16 1 $var 0 0 97
@@ -46,7 +46,7 @@ if [ "$what" = bench ] || [ "$what" = all ]; then
   run bench_gemm 3 11008 1024 1024
   run bench_gemm 3 11008 1024 4096
   run bench_gemm 0 11008 4096 4096
-  for var in 0 1; do
+  for var in 0 1 2 3; do
     run bench_attn 8 1376 1376 16 $var
     run bench_attn 1 11008 11008 16 $var
     run bench_attn 1 22016 44032 16 $var

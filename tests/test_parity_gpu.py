@@ -248,7 +248,7 @@ def test_micro_ops_match_oracle():
     wp, bp, gm = bf(sd[pre + "attn.proj.weight"]), dev(sd[pre + "attn.proj.bias"]), dev(sd[pre + "ls1.gamma"])
     x2 = xd.clone()
     capi.check(lib.wm_gemm_ls_residual(st, o.data_ptr(), 1024, wp.data_ptr(), 1024, bp.data_ptr(), gm.data_ptr(), T, 1024,
-                                       1024, x2.data_ptr(), 1024, None, 0, 0))
+                                       1024, x2.data_ptr(), 1024))
     ref_x = x.reshape(T, 1024) + sd[pre + "ls1.gamma"] * (
         o.float().cpu() @ sd[pre + "attn.proj.weight"].to(torch.bfloat16).float().t() + sd[pre + "attn.proj.bias"])
     torch.cuda.synchronize()
