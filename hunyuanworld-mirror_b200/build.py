@@ -18,8 +18,8 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIBDIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIBDIR, "libwm_b200.so")
-SOURCES = ["gemm.cu", "attn.cu", "rowops.cu", "capi.cu"]
-HEADERS = ["common.cuh", "ptx.cuh", "ops.cuh", os.path.join(ROOT, "include", "wm_b200.h")]
+SOURCES = ["gemm.cu", "attn.cu", "attn_split.cu", "rowops.cu", "capi.cu"]
+HEADERS = ["common.cuh", "ptx.cuh", "ops.cuh", "attn_common.cuh", os.path.join(ROOT, "include", "wm_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--shared",
               "-Xcompiler", "-fPIC"]
 SELFTEST_SRC = os.path.join(ROOT, "tests", "native", "selftest.cu")

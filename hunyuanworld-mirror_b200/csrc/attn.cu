@@ -21,43 +21,9 @@
 // pipe for most elements and, for NPOLY of every 32, as a Cody-Waite split + degree-3 polynomial on the FMA
 // pipe (max relative error 7.6e-5, far below the bf16 rounding of P): at head_dim 64 the kernel is bound by
 // exponentials, not by the tensor core (SURVEY.md section 7 "hard parts").
-#include "common.cuh"
-#include "ptx.cuh"
+#include "attn_common.cuh"
 
 namespace wm {
-
-constexpr int ATT_THREADS = 384;
-constexpr int ATT_TILE = 128 * 64 * 2;  // one 128 x 64 bf16 tile, 16 KB
-constexpr int KV_ST = 3;
-constexpr int ATT_SMEM = (4 + 2 * KV_ST + 2) * ATT_TILE + 512 + 1024;
-
-struct AttnArgs {
-  int Lq, Lkv, batch;
-  int n_qpairs, n_kv, total_items;
-  float scale_log2;
-};
-
-__host__ __device__ constexpr uint32_t s_col(int w) { return 128u * w; }         // S0 / S1
-__host__ __device__ constexpr uint32_t o_col(int w) { return 256u + 64u * w; }   // O0 / O1
-__host__ __device__ constexpr uint32_t p_col(int w) { return 384u + 64u * w; }   // P0 / P1 (bf16 pairs)
-
-// 2^x for x <= 0 on the FMA pipe, two lanes at a time: x = n + f with n = round(x), f in [-0.5, 0.5];
-// 2^f by a degree-3 minimax polynomial, 2^n by adding n to the exponent field.
-__device__ __forceinline__ float2 exp2_poly2(float2 x) {
-  const float2 magic = make_float2(12582912.0f, 12582912.0f);  // 1.5 * 2^23: the add rounds x to an integer
-  x.x = fmaxf(x.x, -126.0f);
-  x.y = fmaxf(x.y, -126.0f);
-  const float2 xr = fadd2(x, magic);
-  const float2 n = fadd2(xr, make_float2(-12582912.0f, -12582912.0f));
-  const float2 f = ffma2(n, make_float2(-1.0f, -1.0f), x);
-  float2 p = ffma2(make_float2(0.05520551f, 0.05520551f), f, make_float2(0.24261397f, 0.24261397f));
-  p = ffma2(p, f, make_float2(0.69325477f, 0.69325477f));
-  p = ffma2(p, f, make_float2(0.9999277f, 0.9999277f));
-  float2 r;
-  r.x = __uint_as_float(__float_as_uint(p.x) + (__float_as_uint(xr.x) << 23));
-  r.y = __uint_as_float(__float_as_uint(p.y) + (__float_as_uint(xr.y) << 23));
-  return r;
-}
 
 template <int NPOLY>
 __global__ void __launch_bounds__(ATT_THREADS, 1)
@@ -440,6 +406,9 @@ umma_probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
 }
 
 // ------------------------------------------------------------------------------------------------ host
+wm_status flash_attention_split(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk,
+                                const CUtensorMap& tv, const CUtensorMap& to, const AttnArgs& a, int variant);  // attn_split.cu
+
 template <int NPOLY>
 static wm_status launch_attn(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
                              const CUtensorMap& to, const AttnArgs& a) {
@@ -481,12 +450,13 @@ wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k
   a.scale_log2 = scale * 1.4426950408889634f;
   const int grid = a.total_items < sm_count ? a.total_items : sm_count;
   if (variant < 0) variant = kDefaultVariant;
+  if (variant >= 4) return flash_attention_split(st, grid, tq, tk, tv, to, a, variant);
   switch (variant) {
     case 0: return launch_attn<0>(st, grid, tq, tk, tv, to, a);
     case 1: return launch_attn<8>(st, grid, tq, tk, tv, to, a);
     case 2: return launch_attn<12>(st, grid, tq, tk, tv, to, a);
     case 3: return launch_attn<16>(st, grid, tq, tk, tv, to, a);
-    default: return fail(WM_ERR_INVALID, "flash_attention: variant must be -1 (default) or 0..3");
+    default: return fail(WM_ERR_INVALID, "flash_attention: variant must be -1 (default) or 0..7");
   }
 }
 

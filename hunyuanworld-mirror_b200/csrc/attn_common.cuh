@@ -1,0 +1,58 @@
+// Shared pieces of the two flash-attention kernels (attn.cu: thread == query row, 8 softmax warps;
+// attn_split.cu: thread == half a query row, 16 softmax warps): tile constants, TMEM column map, launch
+// arguments and the FMA-pipe exp2.
+#pragma once
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace wm {
+
+constexpr int ATT_THREADS = 384;
+constexpr int ATT_TILE = 128 * 64 * 2;  // one 128 x 64 bf16 tile, 16 KB
+constexpr int KV_ST = 3;
+constexpr int ATT_SMEM = (4 + 2 * KV_ST + 2) * ATT_TILE + 512 + 1024;
+
+struct AttnArgs {
+  int Lq, Lkv, batch;
+  int n_qpairs, n_kv, total_items;
+  float scale_log2;
+};
+
+__host__ __device__ constexpr uint32_t s_col(int w) { return 128u * w; }         // S0 / S1
+__host__ __device__ constexpr uint32_t o_col(int w) { return 256u + 64u * w; }   // O0 / O1
+__host__ __device__ constexpr uint32_t p_col(int w) { return 384u + 64u * w; }   // P0 / P1 (bf16 pairs)
+
+// 2^x for x <= 0 on the FMA pipe, two lanes at a time: x = n + f with n = round(x), f in [-0.5, 0.5];
+// 2^f by a degree-3 minimax polynomial, 2^n by adding n to the exponent field.
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+  const float2 magic = make_float2(12582912.0f, 12582912.0f);  // 1.5 * 2^23: the add rounds x to an integer
+  x.x = fmaxf(x.x, -126.0f);
+  x.y = fmaxf(x.y, -126.0f);
+  const float2 xr = fadd2(x, magic);
+  const float2 n = fadd2(xr, make_float2(-12582912.0f, -12582912.0f));
+  const float2 f = ffma2(n, make_float2(-1.0f, -1.0f), x);
+  float2 p = ffma2(make_float2(0.05520551f, 0.05520551f), f, make_float2(0.24261397f, 0.24261397f));
+  p = ffma2(p, f, make_float2(0.69325477f, 0.69325477f));
+  p = ffma2(p, f, make_float2(0.9999277f, 0.9999277f));
+  float2 r;
+  r.x = __uint_as_float(__float_as_uint(p.x) + (__float_as_uint(xr.x) << 23));
+  r.y = __uint_as_float(__float_as_uint(p.y) + (__float_as_uint(xr.y) << 23));
+  return r;
+}
+
+// The same without the clamp, for arguments known to lie in [-126, 126] (bounded-logit mode).
+__device__ __forceinline__ float2 exp2_poly2_bounded(float2 x) {
+  const float2 magic = make_float2(12582912.0f, 12582912.0f);
+  const float2 xr = fadd2(x, magic);
+  const float2 n = fadd2(xr, make_float2(-12582912.0f, -12582912.0f));
+  const float2 f = ffma2(n, make_float2(-1.0f, -1.0f), x);
+  float2 p = ffma2(make_float2(0.05520551f, 0.05520551f), f, make_float2(0.24261397f, 0.24261397f));
+  p = ffma2(p, f, make_float2(0.69325477f, 0.69325477f));
+  p = ffma2(p, f, make_float2(0.9999277f, 0.9999277f));
+  float2 r;
+  r.x = __uint_as_float(__float_as_uint(p.x) + (__float_as_uint(xr.x) << 23));
+  r.y = __uint_as_float(__float_as_uint(p.y) + (__float_as_uint(xr.y) << 23));
+  return r;
+}
+
+}  // namespace wm

@@ -1,0 +1,392 @@
+// Flash attention, head_dim 64, "split-row" variant: the same tile pipeline as attn.cu (TMA-fed K/V ring,
+// tcgen05.mma with S, O and P in TMEM, two 128-row query tiles per CTA) but every 128 x 128 score tile is
+// shared by TWO softmax warpgroups -- thread == (query row, 64-key half) -- so 16 softmax warps (4 per SM
+// sub-partition) are in flight instead of 8.  ncu on attn.cu showed no saturated pipe (tensor 35 %, MUFU 43 %,
+// FMA 43 %, issue 52 %): two warps per scheduler cannot hide MUFU / FMA / TMEM latencies; four can.
+//
+// 640 threads: warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warp 3 idle (setmaxnreg acts on
+// whole warpgroups, so the control roles fill one), warps 4-19 softmax:
+//   group g = (warp - 4) / 4, query tile qt = g / 2, key half hf = g % 2, TMEM lane quarter = warp % 4.
+// Per tile the two halves of a row exchange their half-row maxima through shared memory (one named barrier of
+// 256 threads per query tile) so both use the same reference maximum; row sums stay partial per half and are
+// merged once per work item in the epilogue.  Everything else (lazy rescale, polynomial exp2 share, ragged
+// last tile) follows attn.cu.
+#include "attn_common.cuh"
+
+namespace wm {
+
+constexpr int ATS_THREADS = 640;
+constexpr int ATS_XCH = 2 * 2 * 2 * 128 * 4 + 2 * 2 * 128 * 4;  // half-row maxima (double-buffered) + partial row sums
+constexpr int ATS_SMEM = (4 + 2 * KV_ST + 2) * ATT_TILE + 512 + ATS_XCH + 1024;
+
+// BOUNDED: the caller guarantees |q . k| <= ~96 with q pre-multiplied by scale * log2(e) (QK-LayerNorm bounds the
+// logits; the bound is computed from the norm weights at load time, capi.cu).  softmax is shift-invariant, so the
+// reference maximum is fixed at 0: P = 2^s needs no running max, no exchange between the halves, no rescale
+// and no clamp -- exact up to the same bf16 rounding of P, because bf16 keeps 8 exponent bits.
+template <int NPOLY, bool BOUNDED>
+__global__ void __launch_bounds__(ATS_THREADS, 1)
+attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO, const AttnArgs a) {
+  constexpr int ST = KV_ST;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sQ = smem;                       // 2 buffers x 2 tiles
+  uint8_t* sK = sQ + 4 * ATT_TILE;          // ST tiles
+  uint8_t* sV = sK + ST * ATT_TILE;         // ST tiles
+  uint8_t* sO = sV + ST * ATT_TILE;         // 2 tiles (epilogue staging, one per query tile)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sO + 2 * ATT_TILE);
+  uint64_t* q_full = bars;             // 2
+  uint64_t* q_empty = q_full + 2;      // 2
+  uint64_t* k_full = q_empty + 2;      // ST
+  uint64_t* k_empty = k_full + ST;     // ST
+  uint64_t* v_full = k_empty + ST;     // ST
+  uint64_t* v_empty = v_full + ST;     // ST
+  uint64_t* s_full = v_empty + ST;     // 2  MMA -> softmax: S_qt written
+  uint64_t* s_free = s_full + 2;       // 2  softmax -> MMA: S_qt is in registers (256 arrivals)
+  uint64_t* p_full = s_free + 2;       // 2  softmax -> MMA: P_qt written (256 arrivals)
+  uint64_t* pv_done = p_full + 2;      // 2  MMA -> softmax: O_qt += P_qt V complete
+  uint64_t* o_free = pv_done + 2;      // 2  epilogue -> MMA: O_qt has been read out (256 arrivals)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 2);
+  float* xmax = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);  // [qt][parity][half][128]
+  float* xsum = xmax + 2 * 2 * 2 * 128;                                            // [qt][half][128]
+
+  const int warp = threadIdx.x >> 5;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmO);
+  }
+  if (warp == 1 && elect_one()) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&s_free[i], 256);
+      mbar_init(&p_full[i], 256);
+      mbar_init(&pv_done[i], 1);
+      mbar_init(&o_free[i], 256);
+    }
+    for (int i = 0; i < ST; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, 512);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp < 4) {
+    setmaxnreg_dec<56>();
+    if (warp == 0) {
+      // -------------------------------------------------------------- TMA producer
+      if (elect_one()) {
+        uint32_t kvit = 0, icount = 0;
+        for (int item = blockIdx.x; item < a.total_items; item += gridDim.x, ++icount) {
+          const int per_head = a.batch * a.n_qpairs;
+          const int h = item / per_head, rem = item % per_head;
+          const int b = rem / a.n_qpairs, q0 = (rem % a.n_qpairs) * 256;
+          const uint32_t qb = icount & 1, qph = (icount >> 1) & 1;
+          mbar_wait(&q_empty[qb], qph ^ 1);
+          mbar_arrive_expect_tx(&q_full[qb], 2 * ATT_TILE);
+          tma_load_3d(sQ + (2 * qb) * ATT_TILE, &tmQ, &q_full[qb], h * 64, q0, b, kEvictFirst);
+          tma_load_3d(sQ + (2 * qb + 1) * ATT_TILE, &tmQ, &q_full[qb], h * 64, q0 + 128, b, kEvictFirst);
+          for (int j = 0; j < a.n_kv; ++j, ++kvit) {
+            const uint32_t s = kvit % ST, ph = (kvit / ST) & 1;
+            mbar_wait(&k_empty[s], ph ^ 1);
+            mbar_arrive_expect_tx(&k_full[s], ATT_TILE);
+            tma_load_3d(sK + s * ATT_TILE, &tmK, &k_full[s], h * 64, j * 128, b, kEvictLast);
+            mbar_wait(&v_empty[s], ph ^ 1);
+            mbar_arrive_expect_tx(&v_full[s], ATT_TILE);
+            tma_load_3d(sV + s * ATT_TILE, &tmV, &v_full[s], h * 64, j * 128, b, kEvictLast);
+          }
+        }
+      }
+      __syncwarp();
+    } else if (warp == 1) {
+      // -------------------------------------------------------------- MMA issuer
+      if (elect_one()) {
+        constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);
+        constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);  // B = V is MN-major (dims contiguous)
+        uint32_t kvit = 0, icount = 0;
+        uint32_t tiles0 = 0, tiles1 = 0;  // S tiles issued per query tile (s_free phase bookkeeping)
+        uint32_t pvs0 = 0, pvs1 = 0;      // PVs issued per query tile (p_full phases consumed)
+        uint32_t items0 = 0, items1 = 0;  // work items started per query tile (o_free phases)
+        for (int item = blockIdx.x; item < a.total_items; item += gridDim.x, ++icount) {
+          const int q0 = (item % a.n_qpairs) * 256;
+          const int nw = (q0 + 128 < a.Lq) ? 2 : 1;  // second query tile entirely out of range: skip it
+          const uint32_t qb = icount & 1, qph = (icount >> 1) & 1;
+          mbar_wait(&q_full[qb], qph);
+          tcgen05_fence_after();
+          auto issue_s = [&](int w, uint32_t stage) {
+            uint32_t& tiles = w == 0 ? tiles0 : tiles1;
+            mbar_wait(&s_free[w], (tiles & 1) ^ 1);  // both halves have read the previous S_w into registers
+            ++tiles;
+            tcgen05_fence_after();
+            const uint64_t qd = umma_desc_sw128(smem_u32(sQ + (2 * qb + w) * ATT_TILE), 16, 1024);
+            const uint64_t kd = umma_desc_sw128(smem_u32(sK + stage * ATT_TILE), 16, 1024);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_ss(tmem_base + s_col(w), qd + 2 * k, kd + 2 * k, idesc_s, k != 0);
+            umma_commit(&s_full[w]);
+          };
+          {
+            const uint32_t s0 = kvit % ST, ph0 = (kvit / ST) & 1;
+            mbar_wait(&k_full[s0], ph0);
+            tcgen05_fence_after();
+            for (int w = 0; w < nw; ++w) issue_s(w, s0);
+            umma_commit(&k_empty[s0]);
+          }
+          for (int j = 0; j < a.n_kv; ++j, ++kvit) {
+            const uint32_t sj = kvit % ST, phj = (kvit / ST) & 1;
+            if (j + 1 < a.n_kv) {
+              const uint32_t sn = (kvit + 1) % ST, phn = ((kvit + 1) / ST) & 1;
+              mbar_wait(&k_full[sn], phn);
+              tcgen05_fence_after();
+              for (int w = 0; w < nw; ++w) issue_s(w, sn);
+              umma_commit(&k_empty[sn]);
+            }
+            mbar_wait(&v_full[sj], phj);
+            tcgen05_fence_after();
+            for (int w = 0; w < nw; ++w) {
+              uint32_t& pvs = w == 0 ? pvs0 : pvs1;
+              mbar_wait(&p_full[w], pvs & 1);
+              ++pvs;
+              if (j == 0) mbar_wait(&o_free[w], ((w == 0 ? items0 : items1) & 1) ^ 1);  // previous item's O_w read out
+              tcgen05_fence_after();
+              const uint32_t vbase = smem_u32(sV + sj * ATT_TILE);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {  // 16 kv rows (2048 B of the V tile) per step; P: 8 TMEM columns per step
+                const uint64_t vd = umma_desc_sw128(vbase + k * 2048, 1024, 1024);
+                umma_ts(tmem_base + o_col(w), tmem_base + p_col(w) + k * 8, vd, idesc_pv, (j | k) != 0);
+              }
+              umma_commit(&pv_done[w]);
+            }
+            umma_commit(&v_empty[sj]);
+          }
+          umma_commit(&q_empty[qb]);
+          ++items0;
+          if (nw == 2) ++items1;
+        }
+      }
+      __syncwarp();
+    }
+  } else {
+    // ---------------------------------------------------------------- softmax / correction / epilogue
+    setmaxnreg_inc<104>();
+    const int grp = (warp - 4) >> 2;
+    const int qt = grp >> 1;                     // query tile of this warpgroup
+    const int hf = grp & 1;                      // key half [64 hf, 64 hf + 64) of every score tile
+    const int row = (warp & 3) * 32 + (threadIdx.x & 31);
+    const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t s_addr = tmem_base + s_col(qt) + 64u * hf + lane_base;
+    const uint32_t o_addr = tmem_base + o_col(qt) + 32u * hf + lane_base;  // this thread rescales / reads 32 of the 64 O columns
+    const uint32_t p_addr = tmem_base + p_col(qt) + 32u * hf + lane_base;
+    const uint32_t stg = smem_u32(sO + qt * ATT_TILE);
+    const bool leader = hf == 0 && row == 0;
+    const bool ragged = (a.Lkv & 127) != 0;
+    const float2 scale2 = make_float2(a.scale_log2, a.scale_log2);
+    float* my_max = xmax + (qt * 4 + hf) * 128 + row;          // + parity * 256
+    const float* peer_max = xmax + (qt * 4 + (hf ^ 1)) * 128 + row;
+    uint32_t scount = 0, pvbase = 0;  // s_full[qt] phases consumed / pv_done[qt] phases of finished items
+
+    for (int item = blockIdx.x; item < a.total_items; item += gridDim.x) {
+      const int per_head = a.batch * a.n_qpairs;
+      const int h = item / per_head, rem = item % per_head;
+      const int b = rem / a.n_qpairs, q0 = (rem % a.n_qpairs) * 256;
+      if (qt == 1 && q0 + 128 >= a.Lq) continue;
+
+      float m = -INFINITY, l = 0.f;
+      for (int j = 0; j < a.n_kv; ++j, ++scount) {
+        mbar_wait(&s_full[qt], scount & 1);
+        tcgen05_fence_after();
+        uint32_t pk[32];
+        bool pv_waited = false;
+        if constexpr (BOUNDED) {
+          // two 32-column chunks, one after the other: at most 32 scores + 16 packed probabilities are live
+          float2 sum2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            uint32_t v[32];
+            tmem_ld_x32(s_addr + 32 * i, v);
+            tmem_wait_ld();
+            if (i == 1) {
+              tcgen05_fence_before();
+              mbar_arrive(&s_free[qt]);  // the MMA warp may overwrite S_qt once both halves have arrived
+            }
+            if (ragged && j == a.n_kv - 1) {
+              const int valid = a.Lkv - j * 128 - hf * 64 - i * 32;
+#pragma unroll
+              for (int c = 0; c < 32; ++c)
+                if (c >= valid) v[c] = 0xc2f00000u;  // -120: P = 2^-120, >= 2^40 below any real term (logit bound <= 80)
+            }
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              const float2 xs = make_float2(__uint_as_float(v[c]), __uint_as_float(v[c + 1]));
+              float2 p;
+              if (c >= 32 - NPOLY) {
+                p = exp2_poly2_bounded(xs);
+              } else {
+                p.x = ex2_approx(xs.x);
+                p.y = ex2_approx(xs.y);
+              }
+              sum2[(c >> 1) & 1] = fadd2(sum2[(c >> 1) & 1], p);
+              pk[i * 16 + (c >> 1)] = pack_bf16(p.x, p.y);
+            }
+          }
+          l += (sum2[0].x + sum2[0].y) + (sum2[1].x + sum2[1].y);
+        } else {
+          uint32_t v[2][32];
+          tmem_ld_x32(s_addr, v[0]);
+          tmem_ld_x32(s_addr + 32, v[1]);
+          tmem_wait_ld();
+          tcgen05_fence_before();
+          mbar_arrive(&s_free[qt]);  // the MMA warp may overwrite S_qt once both halves have arrived
+          if (ragged && j == a.n_kv - 1) {
+            const int valid = a.Lkv - j * 128 - hf * 64;
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+              for (int c = 0; c < 32; ++c)
+                if (i * 32 + c >= valid) v[i][c] = 0xff800000u;  // -inf
+          }
+          float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+          for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(v[i][c]));
+          const float mt = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+          my_max[(j & 1) * 256] = mt;
+          named_bar_sync(1 + qt, 256);
+          const float m_new = fmaxf(fmaxf(mt, peer_max[(j & 1) * 256]), m);
+          if (j == 0) {
+            m = m_new;
+          } else {
+            const bool need = (m_new - m) * a.scale_log2 > 8.0f;
+            if (__any_sync(0xffffffffu, need)) {
+              // O correction: wait for PV(j-1), then scale this thread's 32 columns of O and its partial l
+              mbar_wait(&pv_done[qt], (pvbase + j - 1) & 1);
+              pv_waited = true;
+              tcgen05_fence_after();
+              const float alpha = need ? ex2_approx((m - m_new) * a.scale_log2) : 1.0f;
+              if (need) m = m_new;
+              l *= alpha;
+              uint32_t o[32];
+              tmem_ld_x32(o_addr, o);
+              tmem_wait_ld();
+#pragma unroll
+              for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+              tmem_st_x32(o_addr, o);
+              tmem_wait_st();
+            }
+          }
+          const float ms = m * a.scale_log2;
+          const float2 nms2 = make_float2(-ms, -ms);
+          float2 sum2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              const float2 xs = ffma2(make_float2(__uint_as_float(v[i][c]), __uint_as_float(v[i][c + 1])), scale2, nms2);
+              float2 p;
+              if (c >= 32 - NPOLY) {
+                p = exp2_poly2(xs);
+              } else {
+                p.x = ex2_approx(xs.x);
+                p.y = ex2_approx(xs.y);
+              }
+              sum2[(c >> 1) & 1] = fadd2(sum2[(c >> 1) & 1], p);
+              pk[i * 16 + (c >> 1)] = pack_bf16(p.x, p.y);
+            }
+          }
+          l += (sum2[0].x + sum2[0].y) + (sum2[1].x + sum2[1].y);
+        }
+        if (j > 0 && !pv_waited) {  // P_qt is still being read by PV(j-1) until this completes (normally long done)
+          mbar_wait(&pv_done[qt], (pvbase + j - 1) & 1);
+          tcgen05_fence_after();
+        }
+        tmem_st_x32(p_addr, pk);
+        tmem_wait_st();
+        tcgen05_fence_before();
+        mbar_arrive(&p_full[qt]);
+      }
+      // ---- epilogue: merge the partial row sums, O / l -> bf16 -> swizzled staging tile -> TMA store
+      pvbase += a.n_kv;
+      mbar_wait(&pv_done[qt], (pvbase - 1) & 1);
+      tcgen05_fence_after();
+      uint32_t o[32];
+      tmem_ld_x32(o_addr, o);
+      tmem_wait_ld();
+      tcgen05_fence_before();
+      mbar_arrive(&o_free[qt]);  // the next item's first PV may overwrite O_qt
+      xsum[(qt * 2 + hf) * 128 + row] = l;
+      if (leader) tma_store_wait_read<0>();  // the previous store has drained the staging tile
+      named_bar_sync(1 + qt, 256);
+      const float inv = 1.0f / (l + xsum[(qt * 2 + (hf ^ 1)) * 128 + row]);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t pk4[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          pk4[i] = pack_bf16(__uint_as_float(o[8 * c + 2 * i]) * inv, __uint_as_float(o[8 * c + 2 * i + 1]) * inv);
+        st_shared_v4(stg + sw128_offset(row, 4 * hf + c), pk4[0], pk4[1], pk4[2], pk4[3]);
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1 + qt, 256);
+      if (leader) {
+        tma_store_3d(&tmO, sO + qt * ATT_TILE, h * 64, q0 + qt * 128, b);
+        tma_store_commit();
+      }
+    }
+    if (leader) tma_store_wait<0>();
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host
+template <int NPOLY, bool BOUNDED>
+static wm_status launch_split(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
+                              const CUtensorMap& to, const AttnArgs& a) {
+  static bool cfg = false;
+  if (!cfg) {
+    WM_CUDA(cudaFuncSetAttribute(attn_split_kernel<NPOLY, BOUNDED>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATS_SMEM));
+    cfg = true;
+  }
+  attn_split_kernel<NPOLY, BOUNDED><<<grid, ATS_THREADS, ATS_SMEM, st>>>(tq, tk, tv, to, a);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// variants 4..7 of flash_attention(): running-max softmax, polynomial share 0, 8, 10, 12 of every 32 exponentials;
+// variants 8..12: bounded-logit mode (q pre-scaled, |logit| bounded), polynomial share 0, 8, 12, 14, 16.
+wm_status flash_attention_split(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk,
+                                const CUtensorMap& tv, const CUtensorMap& to, const AttnArgs& a, int variant) {
+  switch (variant) {
+    case 4: return launch_split<0, false>(st, grid, tq, tk, tv, to, a);
+    case 5: return launch_split<8, false>(st, grid, tq, tk, tv, to, a);
+    case 6: return launch_split<10, false>(st, grid, tq, tk, tv, to, a);
+    case 7: return launch_split<12, false>(st, grid, tq, tk, tv, to, a);
+    case 8: return launch_split<0, true>(st, grid, tq, tk, tv, to, a);
+    case 9: return launch_split<8, true>(st, grid, tq, tk, tv, to, a);
+    case 10: return launch_split<12, true>(st, grid, tq, tk, tv, to, a);
+    case 11: return launch_split<14, true>(st, grid, tq, tk, tv, to, a);
+    case 12: return launch_split<16, true>(st, grid, tq, tk, tv, to, a);
+    default: return fail(WM_ERR_INVALID, "flash_attention: unknown split variant %d", variant);
+  }
+}
+
+}  // namespace wm

@@ -76,6 +76,8 @@ struct DevTensor {
 struct BlockW {
   const float *n1w, *n1b, *n2w, *n2b, *qkv_b, *qn_w, *qn_b, *kn_w, *kn_b, *proj_b, *ls1, *ls2, *fc1_b, *fc2_b;
   const __nv_bfloat16 *qkv_w, *proj_w, *fc1_w, *fc2_w;
+  // upper bound of |q . k| * scale * log2(e) implied by the QK-LayerNorm weights (0: no bound, DINOv2 blocks)
+  float logit_bound = 0.f;
 };
 
 typedef struct ncclComm* nccl_comm_t;
@@ -125,6 +127,8 @@ struct wm_handle {
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_ev[WM_PROF_CLASSES];
   size_t prof_used[WM_PROF_CLASSES] = {0};
   long long launches = 0;
+  // tuning knobs (wm_set_int): attention kernel variants and the bounded-logit switch
+  int attn_general_variant = 4, attn_bounded_variant = 9, attn_allow_bounded = 1;
 };
 
 namespace wm {
@@ -211,6 +215,8 @@ struct BlockShape {
   bool global;
 };
 
+constexpr float kMaxLogitBound = 80.0f;  // 2^80 * 2^19 keys stays far inside fp32; masked keys use 2^-120
+
 struct ProfScope {
   wm_handle* h;
   cudaStream_t st;
@@ -243,9 +249,13 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
                            float* x, float* out2, int out2_col, bool gather) {
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n1w, w.n1b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
   __nv_bfloat16* kv_local = ws.kv + (size_t)s.kv_row0 * 2 * kEmbed;
+  // QK-LayerNorm bounds the logits (|q . k| <= |q| |k|, both norms fixed by the norm weights): when the bound is
+  // small the softmax needs no running maximum, so q is pre-multiplied by scale * log2(e) and P = 2^(q . k).
+  const bool bounded = h->attn_allow_bounded && w.logit_bound > 0.f && w.logit_bound <= kMaxLogitBound;
+  const float q_scale = bounded ? 0.125f * 1.4426950408889634f : 1.0f;
   WM_OP(WM_PROF_QKV, gemm_qkv(st, ws.ln, kEmbed, w.qkv_w, w.qkv_b, w.qn_w, w.qn_b, w.kn_w, w.kn_b, 1e-5f,
                               s.rope ? h->rope_cos : nullptr, s.rope ? h->rope_sin : nullptr, s.tokens_per_view,
-                              s.patch_start, s.grid_w, s.T, ws.q, kv_local));
+                              s.patch_start, s.grid_w, q_scale, s.T, ws.q, kv_local));
   if (gather) {
     ProfScope _ps(h, st, WM_PROF_ALLGATHER);
     const size_t bytes = (size_t)s.T * 2 * kEmbed * 2;
@@ -255,7 +265,7 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
   const __nv_bfloat16* kbase = gather ? ws.kv : kv_local;
   WM_OP(s.global ? WM_PROF_ATTN_GLOBAL : WM_PROF_ATTN_LOCAL,
         flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
-                        0.125f, -1, 0, 0));
+                        0.125f, bounded ? h->attn_bounded_variant : h->attn_general_variant, 0, 0));
   WM_OP(WM_PROF_PROJ, gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x,
                                        kEmbed));
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
@@ -483,6 +493,20 @@ static wm_status resolve_block(wm_handle* h, const std::string& pre, bool qk_nor
   NEEDF(ls2, "ls2.gamma", C);
 #undef NEEDF
 #undef NEEDB
+  b->logit_bound = 0.f;
+  if (qk_norm) {
+    // LayerNorm output z has |z|_2 <= 8 (64 unit-variance entries), so |z * w + b|_2 <= 8 max|w| + |b|_2; RoPE is a
+    // rotation.  1.02 covers the bf16 rounding of q and k.
+    float hw[4][kHeadDim];
+    const float* src[4] = {b->qn_w, b->qn_b, b->kn_w, b->kn_b};
+    for (int i = 0; i < 4; ++i) WM_CUDA(cudaMemcpy(hw[i], src[i], sizeof(hw[i]), cudaMemcpyDeviceToHost));
+    auto norm_bound = [&](const float* w, const float* bias) {
+      float mw = 0.f, nb = 0.f;
+      for (int i = 0; i < kHeadDim; ++i) mw = fmaxf(mw, fabsf(w[i])), nb += bias[i] * bias[i];
+      return 8.0f * mw + sqrtf(nb);
+    };
+    b->logit_bound = 1.02f * norm_bound(hw[0], hw[1]) * norm_bound(hw[2], hw[3]) * 0.125f * 1.4426950408889634f;
+  }
   return WM_OK;
 }
 
@@ -654,9 +678,33 @@ wm_status wm_gemm_bias_act(wm_stream stream, const void* A, int lda, const void*
 
 wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const float* bias, const float* qn_w,
                       const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
-                      const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q, void* kv) {
+                      const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M, void* q,
+                      void* kv) {
   return gemm_qkv(static_cast<cudaStream_t>(stream), A, kEmbed, W, bias, qn_w, qn_b, kn_w, kn_b, qk_eps, rope_cos,
-                  rope_sin, tokens_per_view, patch_start, grid_w, M, q, kv);
+                  rope_sin, tokens_per_view, patch_start, grid_w, q_scale, M, q, kv);
+}
+
+wm_status wm_set_int(wm_handle* h, const char* name, int value) {
+  WM_CHECK(h && name, "wm_set_int: null argument");
+  const std::string n(name);
+  if (n == "attn_general_variant") {
+    WM_CHECK(value >= 0 && value <= 7, "attn_general_variant must be in [0,7]");
+    h->attn_general_variant = value;
+  } else if (n == "attn_bounded_variant") {
+    WM_CHECK(value >= 8 && value <= 12, "attn_bounded_variant must be in [8,12]");
+    h->attn_bounded_variant = value;
+  } else if (n == "attn_allow_bounded") {
+    h->attn_allow_bounded = value != 0;
+  } else {
+    return fail(WM_ERR_INVALID, "wm_set_int: unknown option %s", name);
+  }
+  return WM_OK;
+}
+
+float wm_logit_bound(const wm_handle* h, int kind, int layer) {
+  if (!h || !h->finalized || layer < 0) return -1.f;
+  const std::vector<BlockW>& v = kind == 0 ? h->dino : kind == 1 ? h->frame : h->global;
+  return layer < (int)v.size() ? v[layer].logit_bound : -1.f;
 }
 
 wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,

@@ -38,6 +38,7 @@ struct GemmArgs {
   const float *rope_cos, *rope_sin;        // [max_pos + 1][16], or null (DINOv2: no RoPE)
   int tokens_per_view, patch_start, grid_w;
   float qk_eps;
+  float q_scale;  // q is multiplied by this after norm + rope (softmax scale * log2 e folded in for bounded-logit attention)
   // EPI_RESID
   const float* gamma;  // null: out = acc + b (plain store); else out += gamma * (acc + b) (TMA reduce-add)
   // EPI_TABLE
@@ -264,6 +265,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               if (g.qn_w != nullptr)
                 head_layernorm(x, which == 0 ? g.qn_w : g.kn_w, which == 0 ? g.qn_b : g.kn_b, g.qk_eps);
               if (g.rope_cos != nullptr) head_rope(x, g.rope_cos, g.rope_sin, py, px);
+              if (which == 0 && g.q_scale != 1.0f) {
+#pragma unroll
+                for (int i = 0; i < 64; ++i) x[i] *= g.q_scale;
+              }
             }
           }
           if (et == 0) tma_store_wait_read<0>();  // the team's previous store has drained the staging tile
@@ -398,8 +403,8 @@ wm_status gemm_bias_act(cudaStream_t st, const void* A, int lda, const void* W, 
 
 wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const float* bias, const float* qn_w,
                    const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
-                   const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q_out,
-                   void* kv_out) {
+                   const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M,
+                   void* q_out, void* kv_out) {
   const int N = 3 * kEmbed, K = kEmbed;
   WM_TRY(check_common(A, W, M, N, K, lda, K));
   WM_CHECK(q_out && kv_out && bias, "gemm_qkv: null output or bias");
@@ -414,7 +419,7 @@ wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const
   WM_TRY(tmap_2d(&tkv, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, kv_out, M, 2 * kEmbed, 2 * kEmbed, 64, 128));
   GemmArgs g{};
   g.M = M, g.N = N, g.K = K, g.bias = bias;
-  g.qn_w = qn_w, g.qn_b = qn_b, g.kn_w = kn_w, g.kn_b = kn_b, g.qk_eps = qk_eps;
+  g.qn_w = qn_w, g.qn_b = qn_b, g.kn_w = kn_w, g.kn_b = kn_b, g.qk_eps = qk_eps, g.q_scale = q_scale;
   g.rope_cos = rope_cos, g.rope_sin = rope_sin;
   g.tokens_per_view = tokens_per_view > 0 ? tokens_per_view : 1, g.patch_start = patch_start,
   g.grid_w = grid_w > 0 ? grid_w : 1;

@@ -8,8 +8,8 @@ wm_status gemm_bias_act(cudaStream_t st, const void* A, int lda, const void* W, 
                         int N, int K, void* out, int ldo, int gelu);
 wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const float* bias, const float* qn_w,
                    const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
-                   const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q_out,
-                   void* kv_out);
+                   const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M,
+                   void* q_out, void* kv_out);
 wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias,
                            const float* gamma, int M, int N, int K, float* x, int ldx);
 wm_status copy_cols(cudaStream_t st, const float* x, long long rows, float* out, int ld_out, int col0);

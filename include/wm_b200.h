@@ -105,6 +105,12 @@ wm_status wm_profile_read(wm_handle* h, int cls, float* total_ms, int* count);
 /* Kernel (and collective) launches issued by forwards since the last wm_profile() call. */
 long long wm_launch_count(const wm_handle* h);
 
+/* Tuning knobs: "attn_general_variant" (0-7), "attn_bounded_variant" (8-12), "attn_allow_bounded" (0/1). */
+wm_status wm_set_int(wm_handle* h, const char* name, int value);
+/* Bound of |q . k| * scale * log2(e) implied by the QK-LayerNorm weights of block `layer` of kind 0 = DINOv2 (always 0),
+ * 1 = frame, 2 = global; the forward uses the bounded-logit attention when 0 < bound <= 80.  -1: invalid argument. */
+float wm_logit_bound(const wm_handle* h, int kind, int layer);
+
 /* ---- sequence parallelism: K|V all-gather of the global blocks through NCCL --------- */
 /* `nccl_lib` = path of libnccl.so.2 (the one torch loaded).  unique_id: 128 bytes. */
 wm_status wm_nccl_unique_id(const char* nccl_lib, void* unique_id_128);
@@ -121,10 +127,12 @@ wm_status wm_gemm_bias_act(wm_stream stream, const void* A, int lda, const void*
 /* Attention.qkv + q_norm/k_norm + rope (attention.py:50-56): A [M,1024] bf16, W [3072,1024] bf16 ->
  * q [M,1024] bf16, kv [M,2048] bf16 (k | v).  Norm / rope pointers may be NULL (DINOv2 blocks).
  * rope_cos/sin: [max_pos+1,16] fp32 from wm_rope_tables.  Token t sits at position
- * (0,0) if t % tokens_per_view < patch_start else (1 + i / grid_w, 1 + i % grid_w), i = t % tokens_per_view - patch_start. */
+ * (0,0) if t % tokens_per_view < patch_start else (1 + i / grid_w, 1 + i % grid_w), i = t % tokens_per_view - patch_start.
+ * q_scale multiplies q after norm and rope (1.0: none; scale * log2(e) for the bounded-logit attention variants). */
 wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const float* bias, const float* qn_w,
                       const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
-                      const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, int M, void* q, void* kv);
+                      const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M, void* q,
+                      void* kv);
 /* Linear + LayerScale + residual (block.py:91-92): x [M,N] fp32 += gamma * (A W^T + bias), the addition done by a
  * TMA reduce-add (each element is added exactly once: deterministic); gamma NULL: x = A W^T + bias. */
 wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
@@ -135,7 +143,10 @@ wm_status wm_copy_cols(wm_stream stream, const float* x, long long rows, float* 
 wm_status wm_gemm_table(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* table,
                         int period, int M, int N, int K, float* out, int ldo);
 /* F.scaled_dot_product_attention (attention.py:59), no mask: q [batch*Lq, ldq], k,v [batch*Lkv, ldkv],
- * o [batch*Lq, ldo] bf16, head h in columns [64h, 64h+64).  variant 0: P through TMEM, 1: P through shared memory. */
+ * o [batch*Lq, ldo] bf16, head h in columns [64h, 64h+64).  variant: -1 default; 0-3 one thread per query row
+ * (attn.cu) with 0/8/12/16 of every 32 exponentials on the FMA pipe; 4-7 two threads per query row (attn_split.cu)
+ * with 0/8/10/12; 8-12 bounded-logit mode of attn_split.cu (0/8/12/14/16): q must already be multiplied by
+ * scale * log2(e) (wm_gemm_qkv q_scale), |q . k| <= 80, `scale` is ignored and P = 2^(q . k) without a running max. */
 wm_status wm_flash_attn(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
                         int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant);
 /* As wm_flash_attn with explicit V-descriptor strides (test hook). */

@@ -38,6 +38,22 @@ if [ "$what" = correct ] || [ "$what" = all ]; then
     run attn 1 700 2900 3 8 $var 0 0 23
   done
 fi
+if [ "$what" = attn ]; then
+  for var in ${VARIANTS:-4 7 8 9 10 11 12}; do
+    run attn 2 331 331 2 1 $var 0 0 5
+    run attn 1 128 128 1 1 $var 0 0 1
+    run attn 1 1376 1376 16 1 $var 0 0 97
+    run attn 3 1376 1376 4 6 $var 0 0 61
+    run attn 1 512 11008 2 1 $var 0 0 31
+    run attn 1 700 2900 3 8 $var 0 0 23
+    run attn 1 200 70 1 1 $var 0 0 3
+  done
+  for var in ${VARIANTS:-4 7 8 9 10 11 12} 2; do
+    run bench_attn 8 1376 1376 16 $var
+    run bench_attn 1 11008 11008 16 $var
+    run bench_attn 1 22016 44032 16 $var
+  done
+fi
 if [ "$what" = bench ] || [ "$what" = all ]; then
   run bench_ln 11008
   run bench_gemm 0 11008 1024 1024

@@ -268,7 +268,7 @@ static int case_gemm_qkv(int M, int with_norm, int with_rope, int row_step) {
   uint16_t* dq = dev_alloc<uint16_t>((size_t)M * 1024);
   uint16_t* dkv = dev_alloc<uint16_t>((size_t)M * 2048);
   WM(wm_gemm_qkv(0, da, dw, db, with_norm ? dqw : nullptr, with_norm ? dqb : nullptr, with_norm ? dkw : nullptr,
-                 with_norm ? dkb : nullptr, 1e-5f, with_rope ? dcs : nullptr, with_rope ? dsn : nullptr, P, ps, gw, M, dq, dkv));
+                 with_norm ? dkb : nullptr, 1e-5f, with_rope ? dcs : nullptr, with_rope ? dsn : nullptr, P, ps, gw, 1.0f, M, dq, dkv));
   CK(cudaDeviceSynchronize());
   auto q = host(dq, (size_t)M * 1024);
   auto kv = host(dkv, (size_t)M * 2048);
@@ -320,7 +320,9 @@ static int case_attn(int batch, int Lq, int Lkv, int heads, float qscale, int va
                      int row_step) {
   const int ldq = heads * 64, ldkv = heads * 128;
   BF Q, KV;
-  Q.fill((size_t)batch * Lq * ldq, qscale);
+  // variants >= 8 (bounded-logit mode): q arrives pre-multiplied by scale * log2(e) and P = 2^(q . k)
+  const bool bounded = variant >= 8;
+  Q.fill((size_t)batch * Lq * ldq, bounded ? qscale * 0.125f * 1.4426950408889634f : qscale);
   KV.fill((size_t)batch * Lkv * ldkv, 1.0f);
   uint16_t *dq = dev(Q.h), *dkv = dev(KV.h);
   uint16_t* dout = dev_alloc<uint16_t>((size_t)batch * Lq * ldq);
@@ -338,7 +340,7 @@ static int case_attn(int batch, int Lq, int Lkv, int heads, float qscale, int va
           const float* kr = &KV.f[((size_t)b * Lkv + j) * ldkv + h * 64];
           double acc = 0;
           for (int d = 0; d < 64; ++d) acc += (double)qr[d] * kr[d];
-          s[j] = acc * 0.125;
+          s[j] = bounded ? acc * 0.6931471805599453 : acc * 0.125;
           if (s[j] > mx) mx = s[j];
         }
         double l = 0, o[64] = {0};
@@ -382,7 +384,7 @@ static void gemm_run(void* p) {
   if (c->kind == 0) WM(wm_gemm_bias_act(0, c->a, c->K, c->w, c->K, c->bias, c->M, c->N, c->K, c->out, c->N, 0));
   if (c->kind == 1) WM(wm_gemm_bias_act(0, c->a, c->K, c->w, c->K, c->bias, c->M, c->N, c->K, c->out, c->N, 1));
   if (c->kind == 2)
-    WM(wm_gemm_qkv(0, c->a, c->w, c->bias, c->qw, c->qw, c->qw, c->qw, 1e-5f, c->cs, c->cs, 1376, 7, 37, c->M, c->q, c->kv));
+    WM(wm_gemm_qkv(0, c->a, c->w, c->bias, c->qw, c->qw, c->qw, c->qw, 1e-5f, c->cs, c->cs, 1376, 7, 37, 1.0f, c->M, c->q, c->kv));
   if (c->kind == 3) WM(wm_gemm_ls_residual(0, c->a, c->K, c->w, c->K, c->bias, c->gamma, c->M, c->N, c->K, c->x, c->N));
 }
 static int bench_gemm(int kind, int M, int N, int K) {

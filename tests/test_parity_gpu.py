@@ -226,7 +226,7 @@ def test_micro_ops_match_oracle():
     q = torch.empty(T, 1024, dtype=torch.bfloat16, device="cuda")
     kv = torch.empty(T, 2048, dtype=torch.bfloat16, device="cuda")
     capi.check(lib.wm_gemm_qkv(st, ln.data_ptr(), wq.data_ptr(), bq.data_ptr(), nw[0].data_ptr(), nw[1].data_ptr(),
-                               nw[2].data_ptr(), nw[3].data_ptr(), 1e-5, cs.data_ptr(), sn.data_ptr(), P, 7, gw, T,
+                               nw[2].data_ptr(), nw[3].data_ptr(), 1e-5, cs.data_ptr(), sn.data_ptr(), P, 7, gw, 1.0, T,
                                q.data_ptr(), kv.data_ptr()))
     lnf = ln.float().cpu().reshape(n, P, 1024)
     qkv = lnf @ sd[pre + "attn.qkv.weight"].to(torch.bfloat16).float().t() + sd[pre + "attn.qkv.bias"]
@@ -244,6 +244,18 @@ def test_micro_ops_match_oracle():
     heads = lambda t: t.float().cpu().reshape(n, P, 16, 64).permute(0, 2, 1, 3)  # noqa: E731
     ref_o = O.sdpa(heads(q), heads(kv[:, :1024]), heads(kv[:, 1024:])).permute(0, 2, 1, 3).reshape(T, 1024)
     assert (o.float().cpu() - ref_o).abs().max().item() <= 0.02
+    # every kernel variant agrees with the oracle; 8-12 (bounded-logit mode) take q pre-multiplied by scale * log2(e)
+    qs = torch.empty_like(q)
+    capi.check(lib.wm_gemm_qkv(st, ln.data_ptr(), wq.data_ptr(), bq.data_ptr(), nw[0].data_ptr(), nw[1].data_ptr(),
+                               nw[2].data_ptr(), nw[3].data_ptr(), 1e-5, cs.data_ptr(), sn.data_ptr(), P, 7, gw,
+                               0.125 * 1.4426950408889634, T, qs.data_ptr(), kv.data_ptr()))
+    assert (qs.float().cpu() - to_rows(rq) * (0.125 * 1.4426950408889634)).abs().max().item() <= 0.01
+    for variant in range(1, 13):
+        ov = torch.zeros_like(o)
+        qq = qs if variant >= 8 else q
+        capi.check(lib.wm_flash_attn(st, qq.data_ptr(), 1024, kv.data_ptr(), kv.data_ptr() + 2048, 2048, ov.data_ptr(),
+                                     1024, n, P, P, 16, 0.125, variant))
+        assert (ov.float().cpu() - ref_o).abs().max().item() <= 0.02, f"variant {variant}"
     # proj + LayerScale + residual
     wp, bp, gm = bf(sd[pre + "attn.proj.weight"]), dev(sd[pre + "attn.proj.bias"]), dev(sd[pre + "ls1.gamma"])
     x2 = xd.clone()
@@ -253,6 +265,32 @@ def test_micro_ops_match_oracle():
         o.float().cpu() @ sd[pre + "attn.proj.weight"].to(torch.bfloat16).float().t() + sd[pre + "attn.proj.bias"])
     torch.cuda.synchronize()
     assert (x2.cpu() - ref_x).abs().max().item() <= 1e-4
+
+
+def test_logit_bound_and_bounded_switch(model_full, state_dict_full):
+    """QK-LayerNorm bounds the logits: the library reports the bound per block, uses the bounded-logit attention
+    when it is small, and both paths give the same outputs (the softmax shift is exact)."""
+    lib, h = capi.lib(), model_full._handle
+    assert lib.wm_logit_bound(h, 0, 0) == 0.0  # DINOv2 blocks have no QK-norm
+    for kind in (1, 2):
+        b = lib.wm_logit_bound(h, kind, 0)
+        nq, nk = (8.0 * model_sd_max(state_dict_full, f"{'frame' if kind == 1 else 'global'}_blocks.0.attn.{k}_norm")
+                  for k in "qk")
+        assert 0 < b <= 80 and abs(b - 1.02 * nq * nk * 0.125 * 1.4426950408889634) <= 1e-3 * b
+    imgs = W.synthetic_images(2, 70, 98, seed=5).cuda()
+    a, _ = model_full(imgs)
+    capi.check(lib.wm_set_int(h, b"attn_allow_bounded", 0))
+    try:
+        b2, _ = model_full(imgs)
+    finally:
+        capi.check(lib.wm_set_int(h, b"attn_allow_bounded", 1))
+    for x, y in zip(a, b2):
+        assert rel_fro(x.cpu().numpy(), y.cpu().numpy()) <= 3e-3
+
+
+def model_sd_max(sd, prefix):
+    w, b = sd[prefix + ".weight"], sd[prefix + ".bias"]
+    return (w.abs().max() + b.norm() / 8.0).item()
 
 
 def test_error_behaviour(model_full):
