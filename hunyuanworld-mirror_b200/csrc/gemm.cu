@@ -9,12 +9,17 @@
 //              gamma null: x = acc + b   (attn.proj / Mlp.fc2 + LayerScale + residual: block.py:91-92)
 //   EPI_TABLE  out fp32 = acc + table[row % period][col]            DINOv2 patch embed + pos_embed / cls / reg
 //
-// One CTA per SM, 384 threads: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
+// CTA pairs (clusters of 2, tcgen05 cta_group::2): a pair computes a 256 x 256 tile, CTA r owning rows
+// [128 r, 128 r + 128) of A and of the accumulator and rows [128 r, 128 r + 128) of the 256-row W tile.  One
+// M = 256 MMA issued by the leader CTA reads both halves, so every SM streams 32 KB instead of 48 KB per k-block
+// through its shared memory: the single-CTA 128 x 256 version measured 70-73 % tensor-pipe utilisation on every
+// shape, the ratio of the 128 B/clk shared-memory port to its 192 B/clk of TMA writes + MMA operand reads.
+// Per CTA, 384 threads: warp 0 = TMA producer, warp 1 = MMA issuer (leader CTA only, one elected lane),
 // warp 2 = TMEM allocator, warps 4-11 = epilogue in two teams of four warps (team t owns accumulator columns
 // [128 t, 128 t + 128); thread == accumulator row; TMEM lane quarter = warp % 4).
-// Tile 128 x 256 x 64, 4-stage smem ring (SWIZZLE_128B, K-major for both operands), two 256-column TMEM
-// accumulators so the epilogue of tile i overlaps the main loop of tile i+1.  Outputs leave through one
-// swizzled staging tile per team and TMA stores / reduce-adds (row clipping for the M tail comes for free).
+// 5-stage smem ring (SWIZZLE_128B, K-major for both operands), two 256-column TMEM accumulators so the epilogue
+// of tile i overlaps the main loop of tile i+1.  Outputs leave through one swizzled staging tile per team and
+// TMA stores / reduce-adds (row clipping for the M tail comes for free).
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -22,9 +27,9 @@ namespace wm {
 
 enum : int { EPI_BIAS = 0, EPI_GELU = 1, EPI_QKV = 2, EPI_RESID = 3, EPI_TABLE = 4 };
 
-constexpr int BM = 128, BN = 256, BK = 64, STAGES = 4;
+constexpr int BM = 128, BN = 256, BK = 64, STAGES = 5;  // BM: rows per CTA (the pair tile has 2 BM)
 constexpr int A_BYTES = BM * BK * 2;        // 16 KB
-constexpr int B_BYTES = BN * BK * 2;        // 32 KB
+constexpr int B_BYTES = (BN / 2) * BK * 2;  // 16 KB: this CTA's half of the W tile
 constexpr int STG_BYTES = 128 * 128;        // 128 rows x 128 B, one per epilogue team
 constexpr int GEMM_THREADS = 384;           // 4 control warps + 2 epilogue teams of 4 warps
 constexpr int GEMM_SMEM = STAGES * (A_BYTES + B_BYTES) + 2 * STG_BYTES + 256 + 1024;
@@ -119,7 +124,7 @@ __device__ __forceinline__ void head_rope(float (&x)[64], const float* __restric
 }
 
 template <int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC0, const __grid_constant__ CUtensorMap tmC1, const GemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
@@ -134,7 +139,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5;
-  const int total_tiles = g.num_m_tiles * g.num_n_tiles;
+  const int total_tiles = g.num_m_tiles * g.num_n_tiles;  // pair tiles (256 x 256)
+  const uint32_t rank = cluster_ctarank();
+  const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
 
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmA);
@@ -144,21 +151,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < STAGES; ++i) {
-      mbar_init(&full[i], 1);
-      mbar_init(&empty[i], 1);
+      mbar_init(&full[i], 2);   // leader only: one arrive per producer of the pair + 64 KB of TMA bytes
+      mbar_init(&empty[i], 1);  // per CTA: the leader's MMA commit is multicast to both
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 256);
+      mbar_init(&tfull[i], 1);     // per CTA: multicast commit of the tile's last MMA
+      mbar_init(&tempty[i], 512);  // leader only: the epilogue threads of both CTAs
     }
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_ptr, 512);
-    tmem_relinquish();
+    tmem_alloc_pair(tmem_ptr, 512);
+    tmem_relinquish_pair();
   }
   tcgen05_fence_before();
   __syncthreads();
+  cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them remotely
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
@@ -166,25 +174,29 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m0 = (tile / g.num_n_tiles) * BM;
-        const int n0 = (tile % g.num_n_tiles) * BN;
+      for (int tile = pair_id; tile < total_tiles; tile += num_pairs) {
+        const int m0 = (tile / g.num_n_tiles) * (2 * BM) + rank * BM;
+        const int n0 = (tile % g.num_n_tiles) * BN + rank * (BN / 2);
         for (int kb = 0; kb < g.num_k_blocks; ++kb, ++it) {
           const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
           mbar_wait(&empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full[s], A_BYTES + B_BYTES);
-          tma_load_2d(sA + s * A_BYTES, &tmA, &full[s], kb * BK, m0, kEvictNormal);
-          tma_load_2d(sB + s * B_BYTES, &tmB, &full[s], kb * BK, n0, kEvictLast);
+          const uint32_t lead_full = mapa_shared(smem_u32(&full[s]), 0);
+          if (rank == 0)
+            mbar_arrive_expect_tx(&full[s], 2 * (A_BYTES + B_BYTES));
+          else
+            mbar_arrive_cluster(lead_full);
+          tma_load_2d_pair(sA + s * A_BYTES, &tmA, lead_full, kb * BK, m0, kEvictNormal);
+          tma_load_2d_pair(sB + s * B_BYTES, &tmB, lead_full, kb * BK, n0, kEvictLast);
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer
-    if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, false, false);
+    // ------------------------------------------------------------ MMA issuer (leader CTA of the pair)
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(2 * BM, BN, false, false);
       uint32_t it = 0, tcount = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      for (int tile = pair_id; tile < total_tiles; tile += num_pairs, ++tcount) {
         const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
         mbar_wait(&tempty[acc], aph ^ 1);
         tcgen05_fence_after();
@@ -197,10 +209,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + s * B_BYTES), 16, 1024);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)  // +32 bytes (>>4 = 2) per 16-element K step inside the 128B swizzle row
-            umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-          umma_commit(&empty[s]);
+            umma_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          umma_commit_pair(&empty[s], 3);
         }
-        umma_commit(&tfull[acc]);
+        umma_commit_pair(&tfull[acc], 3);
       }
     }
     __syncwarp();
@@ -214,9 +226,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t stg = smem_u32(stg_ptr);
     const uint32_t bar_id = 1 + team;
     uint32_t tcount = 0;
+    const uint32_t lead_tempty[2] = {mapa_shared(smem_u32(&tempty[0]), 0), mapa_shared(smem_u32(&tempty[1]), 0)};
 
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-      const int m0 = (tile / g.num_n_tiles) * BM;
+    for (int tile = pair_id; tile < total_tiles; tile += num_pairs, ++tcount) {
+      const int m0 = (tile / g.num_n_tiles) * (2 * BM) + rank * BM;
       const int n0 = (tile % g.num_n_tiles) * BN + team * 128;
       const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
       mbar_wait(&tfull[acc], aph);
@@ -251,7 +264,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           if (grp == 1) {  // this thread's share of the accumulator is in registers: hand TMEM back to the MMA warp
             tcgen05_fence_before();
-            mbar_arrive(&tempty[acc]);
+            mbar_arrive_cluster(lead_tempty[acc]);
           }
           const int col0 = n0 + grp * 64;
           add_vec64(x, g.bias + col0);
@@ -298,7 +311,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tmem_wait_ld();
           if (ch == 3) {
             tcgen05_fence_before();
-            mbar_arrive(&tempty[acc]);
+            mbar_arrive_cluster(lead_tempty[acc]);
           }
           float o[32];
           if (EPI == EPI_TABLE) {
@@ -344,9 +357,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   tcgen05_fence_before();
   __syncthreads();
+  cluster_sync_all();  // no CTA leaves (or frees TMEM) while its peer may still signal or write into it
   if (warp == 2) {
     tcgen05_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    tmem_dealloc_pair(tmem_base, 512);
   }
 }
 
@@ -362,11 +376,12 @@ static wm_status launch(cudaStream_t st, const CUtensorMap& a, const CUtensorMap
     WM_CUDA(cudaFuncSetAttribute(gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
     configured = true;
   }
-  g.num_m_tiles = (g.M + BM - 1) / BM;
+  g.num_m_tiles = (g.M + 2 * BM - 1) / (2 * BM);  // pair tiles: 256 rows
   g.num_n_tiles = g.N / BN;
   g.num_k_blocks = (g.K + BK - 1) / BK;
   const int tiles = g.num_m_tiles * g.num_n_tiles;
-  const int grid = tiles < g_sm_count ? tiles : g_sm_count;
+  const int pairs = g_sm_count / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
   gemm_kernel<EPI><<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(a, b, c0, c1, g);
   WM_LAUNCH_CHECK();
   return WM_OK;
@@ -385,7 +400,7 @@ static wm_status check_common(const void* A, const void* W, int M, int N, int K,
 static wm_status operand_maps(CUtensorMap* ta, CUtensorMap* tb, const void* A, int lda, const void* W, int ldw, int M,
                               int N, int K) {
   WM_TRY(tmap_2d(ta, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, M, K, lda, BK, BM));
-  WM_TRY(tmap_2d(tb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, N, K, ldw, BK, BN));
+  WM_TRY(tmap_2d(tb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, N, K, ldw, BK, BN / 2));
   return WM_OK;
 }
 
