@@ -50,6 +50,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   uint64_t* o_free = pv_done + 2;      // 2  epilogue -> MMA: O_w has been read out
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 2);
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
 
   if (warp == 0 && elect_one()) {
@@ -84,6 +85,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
 
   if (warp < 4) {
     setmaxnreg_dec<56>();
@@ -417,9 +419,7 @@ static wm_status launch_attn(cudaStream_t st, int grid, const CUtensorMap& tq, c
     WM_CUDA(cudaFuncSetAttribute(attn_kernel<NPOLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
     cfg = true;
   }
-  attn_kernel<NPOLY><<<grid, ATT_THREADS, ATT_SMEM, st>>>(tq, tk, tv, to, a);
-  WM_LAUNCH_CHECK();
-  return WM_OK;
+  return launch_pdl(attn_kernel<NPOLY>, dim3(grid), dim3(ATT_THREADS), ATT_SMEM, st, tq, tk, tv, to, a);
 }
 
 // variant: how many of every 32 exponentials run as a polynomial on the FMA pipe (0 -> 0, 1 -> 8, 2 -> 12, 3 -> 16);

@@ -50,6 +50,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
   float* xmax = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);  // [qt][parity][half][128]
   float* xsum = xmax + 2 * 2 * 2 * 128;                                            // [qt][half][128]
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
 
   if (warp == 0 && elect_one()) {
@@ -84,6 +85,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();  // q, k, v of the preceding GEMM (or all-gather) are complete and visible from here on
 
   if (warp < 4) {
     setmaxnreg_dec<56>();
@@ -366,9 +368,7 @@ static wm_status launch_split(cudaStream_t st, int grid, const CUtensorMap& tq, 
     WM_CUDA(cudaFuncSetAttribute(attn_split_kernel<NPOLY, BOUNDED>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATS_SMEM));
     cfg = true;
   }
-  attn_split_kernel<NPOLY, BOUNDED><<<grid, ATS_THREADS, ATS_SMEM, st>>>(tq, tk, tv, to, a);
-  WM_LAUNCH_CHECK();
-  return WM_OK;
+  return launch_pdl(attn_split_kernel<NPOLY, BOUNDED>, dim3(grid), dim3(ATS_THREADS), ATS_SMEM, st, tq, tk, tv, to, a);
 }
 
 // variants 4..7 of flash_attention(): running-max softmax, polynomial share 0, 8, 10, 12 of every 32 exponentials;

@@ -79,4 +79,17 @@ inline wm_status tmap_3d(CUtensorMap* out, CUtensorMapDataType dtype, int elem_b
 
 wm_status require_sm100(int* sm_count);
 
+// Launch with programmatic stream serialization (the kernel must call pdl_wait() before touching global data).
+template <typename... KArgs, typename... Args>
+inline wm_status launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr, cfg.numAttrs = 1;
+  WM_CUDA(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
+  return WM_OK;
+}
+
 }  // namespace wm

@@ -138,6 +138,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   const int total_tiles = g.num_m_tiles * g.num_n_tiles;  // pair tiles (256 x 256)
   const uint32_t rank = cluster_ctarank();
@@ -169,6 +170,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them remotely
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();  // the predecessor's outputs (A, the residual stream) are complete and visible from here on
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
@@ -382,9 +384,7 @@ static wm_status launch(cudaStream_t st, const CUtensorMap& a, const CUtensorMap
   const int tiles = g.num_m_tiles * g.num_n_tiles;
   const int pairs = g_sm_count / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
-  gemm_kernel<EPI><<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(a, b, c0, c1, g);
-  WM_LAUNCH_CHECK();
-  return WM_OK;
+  return launch_pdl(gemm_kernel<EPI>, dim3(grid), dim3(GEMM_THREADS), GEMM_SMEM, st, a, b, c0, c1, g);
 }
 
 static wm_status check_common(const void* A, const void* W, int M, int N, int K, int lda, int ldw) {

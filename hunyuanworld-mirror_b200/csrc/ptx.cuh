@@ -313,6 +313,14 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar, uint16_t cta_mas
                : "memory");
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Kernels launched with launch_pdl() (common.cuh) may start while their predecessor in the stream is still running:
+// pdl_launch_dependents() lets the successor's CTAs be placed on SMs as they free up, pdl_wait() blocks until the
+// predecessor grid has completed and its memory is visible.  Everything before pdl_wait() (barrier init, TMEM
+// allocation, descriptor prefetch) overlaps the predecessor's tail; nothing before it may touch global data.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---------------------------------------------------------------- register budget (whole warpgroup, .sync.aligned)
 template <int N>
 __device__ __forceinline__ void setmaxnreg_inc() {

@@ -17,6 +17,8 @@ __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b, float eps,
                  int rows, int rows_per_group, int in_group_rows, int in_offset, int out_group_rows, int out_offset,
                  OutT* __restrict__ y) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (r >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -73,18 +75,14 @@ wm_status layernorm(cudaStream_t st, const float* x, const float* w, const float
   const int grid = (rows + 7) / 8;
   if (!out_f32) {
     WM_CHECK(!accumulate, "layernorm: accumulate needs an fp32 output");
-    layernorm_kernel<__nv_bfloat16, false><<<grid, 256, 0, st>>>(x, w, b, eps, rows, rows_per_group, in_group_rows,
-                                                                  in_offset, out_group_rows, out_offset,
-                                                                  static_cast<__nv_bfloat16*>(y));
-  } else if (accumulate) {
-    layernorm_kernel<float, true><<<grid, 256, 0, st>>>(x, w, b, eps, rows, rows_per_group, in_group_rows, in_offset,
-                                                         out_group_rows, out_offset, static_cast<float*>(y));
-  } else {
-    layernorm_kernel<float, false><<<grid, 256, 0, st>>>(x, w, b, eps, rows, rows_per_group, in_group_rows, in_offset,
-                                                          out_group_rows, out_offset, static_cast<float*>(y));
+    return launch_pdl(layernorm_kernel<__nv_bfloat16, false>, dim3(grid), dim3(256), 0, st, x, w, b, eps, rows, rows_per_group,
+                      in_group_rows, in_offset, out_group_rows, out_offset, static_cast<__nv_bfloat16*>(y));
   }
-  WM_LAUNCH_CHECK();
-  return WM_OK;
+  if (accumulate)
+    return launch_pdl(layernorm_kernel<float, true>, dim3(grid), dim3(256), 0, st, x, w, b, eps, rows, rows_per_group,
+                      in_group_rows, in_offset, out_group_rows, out_offset, static_cast<float*>(y));
+  return launch_pdl(layernorm_kernel<float, false>, dim3(grid), dim3(256), 0, st, x, w, b, eps, rows, rows_per_group,
+                    in_group_rows, in_offset, out_group_rows, out_offset, static_cast<float*>(y));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -211,6 +209,8 @@ wm_status special_tokens(cudaStream_t st, const float* cam, const float* reg, in
 // reference's `cat([frame, global], -1)` written in place, one float4 per thread.
 __global__ void __launch_bounds__(256)
 copy_cols_kernel(const float4* __restrict__ x, long long rows, int ld_out4, int col4, float4* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= rows * (kEmbed / 4)) return;
   const long long r = t / (kEmbed / 4);
@@ -221,10 +221,8 @@ copy_cols_kernel(const float4* __restrict__ x, long long rows, int ld_out4, int 
 wm_status copy_cols(cudaStream_t st, const float* x, long long rows, float* out, int ld_out, int col0) {
   WM_CHECK(x && out && rows > 0 && ld_out % 4 == 0 && col0 % 4 == 0 && col0 + kEmbed <= ld_out, "copy_cols: bad arguments");
   const long long total = rows * (kEmbed / 4);
-  copy_cols_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(x), rows, ld_out / 4,
-                                                                    col0 / 4, reinterpret_cast<float4*>(out));
-  WM_LAUNCH_CHECK();
-  return WM_OK;
+  return launch_pdl(copy_cols_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st,
+                    reinterpret_cast<const float4*>(x), rows, ld_out / 4, col0 / 4, reinterpret_cast<float4*>(out));
 }
 
 // ------------------------------------------------------------------------------------------------
