@@ -156,6 +156,9 @@ def run_b200(args):
     model.load_state_dict(W.synthetic_state_dict(seed=0))
     if world > 1:
         model.init_sequence_parallel()
+    for kv in args.set:  # library tuning knobs (wm_set_int), e.g. --set attn_bounded_variant=10
+        k, v = kv.split("=")
+        capi.check(capi.lib().wm_set_int(model._handle, k.encode(), int(v)))
     n_local, n_total = args.views, args.views * world
     imgs_host = W.synthetic_images(n_total, SIZE, SIZE, seed=1)[:, rank * n_local:(rank + 1) * n_local].contiguous().pin_memory()
     imgs_dev = imgs_host.to(dev)
@@ -267,6 +270,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--views", type=int, default=VIEWS_PER_RANK, help="views per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--set", action="append", default=[], metavar="KNOB=INT", help="wm_set_int tuning knob (repeatable)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

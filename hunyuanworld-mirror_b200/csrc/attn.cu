@@ -456,7 +456,7 @@ wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k
     case 1: return launch_attn<8>(st, grid, tq, tk, tv, to, a);
     case 2: return launch_attn<12>(st, grid, tq, tk, tv, to, a);
     case 3: return launch_attn<16>(st, grid, tq, tk, tv, to, a);
-    default: return fail(WM_ERR_INVALID, "flash_attention: variant must be -1 (default) or 0..7");
+    default: return fail(WM_ERR_INVALID, "flash_attention: variant must be -1 (default) or 0..12");
   }
 }
 

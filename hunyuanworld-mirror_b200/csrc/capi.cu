@@ -128,7 +128,7 @@ struct wm_handle {
   size_t prof_used[WM_PROF_CLASSES] = {0};
   long long launches = 0;
   // tuning knobs (wm_set_int): attention kernel variants and the bounded-logit switch
-  int attn_general_variant = 4, attn_bounded_variant = 9, attn_allow_bounded = 1;
+  int attn_general_variant = 4, attn_bounded_variant = 10, attn_allow_bounded = 1;
 };
 
 namespace wm {
@@ -691,7 +691,7 @@ wm_status wm_set_int(wm_handle* h, const char* name, int value) {
     WM_CHECK(value >= 0 && value <= 7, "attn_general_variant must be in [0,7]");
     h->attn_general_variant = value;
   } else if (n == "attn_bounded_variant") {
-    WM_CHECK(value >= 8 && value <= 12, "attn_bounded_variant must be in [8,12]");
+    WM_CHECK(value >= 8 && value <= 14, "attn_bounded_variant must be in [8,14]");
     h->attn_bounded_variant = value;
   } else if (n == "attn_allow_bounded") {
     h->attn_allow_bounded = value != 0;

@@ -157,7 +157,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);     // per CTA: multicast commit of the tile's last MMA
-      mbar_init(&tempty[i], 512);  // leader only: the epilogue threads of both CTAs
+      mbar_init(&tempty[i], 16);   // leader only: one arrival per epilogue warp of both CTAs
     }
     fence_barrier_init();
   }
@@ -266,7 +266,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           if (grp == 1) {  // this thread's share of the accumulator is in registers: hand TMEM back to the MMA warp
             tcgen05_fence_before();
-            mbar_arrive_cluster(lead_tempty[acc]);
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(lead_tempty[acc]);
           }
           const int col0 = n0 + grp * 64;
           add_vec64(x, g.bias + col0);
@@ -313,7 +314,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tmem_wait_ld();
           if (ch == 3) {
             tcgen05_fence_before();
-            mbar_arrive_cluster(lead_tempty[acc]);
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(lead_tempty[acc]);
           }
           float o[32];
           if (EPI == EPI_TABLE) {
