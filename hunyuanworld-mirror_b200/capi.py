@@ -55,7 +55,8 @@ SIGNATURES = {
     "wm_copy_cols": (C.c_int, [_vp, _fp, C.c_longlong, _fp, _i, _i]),
     "wm_gemm_table": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _i, _i, _i, _i, _fp, _i]),
     "wm_flash_attn": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _i]),
-    "wm_flash_attn_dbg": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _i, _u, _u]),
+    "wm_flash_attn_ws": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _i, _vp, C.c_size_t]),
+    "wm_attn_workspace_bytes": (C.c_size_t, []),
     "wm_umma_probe": (C.c_int, [_vp, _vp, _vp, _fp, _i, _u, _u]),
     "wm_patch_gather": (C.c_int, [_vp, _fp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "wm_rope_tables": (None, [_i, C.POINTER(C.c_float), C.POINTER(C.c_float)]),

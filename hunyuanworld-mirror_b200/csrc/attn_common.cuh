@@ -16,7 +16,40 @@ struct AttnArgs {
   int Lq, Lkv, batch;
   int n_qpairs, n_kv, total_items;
   float scale_log2;
+  // attn_split.cu only.  Work items are dealt out in `full_waves` strided waves (item = wave * grid + cta: CTAs that
+  // run at the same time share a head's K|V in L2), then the remaining items' (item, kv tile) steps are split into
+  // equal contiguous runs of `per_cta` steps, so a tail item may be shared by several CTAs; a CTA's share of a split
+  // item leaves as an unnormalised fp32 partial (O [256][64], row sum l [256], reference max m [256]) in slot
+  // 2 * cta + {0: first, 1: last tail segment of the CTA} and attn_merge_kernel adds the partials up in CTA order.
+  int full_waves, per_cta, tail_steps, merge_grid;
+  float *part_o, *part_l, *part_m;
 };
+
+// The segment sequence of one CTA; producer, MMA issuer and softmax warps walk it in lockstep.
+struct AttnSched {
+  int w, tstep, tbegin, tend;
+  __device__ explicit AttnSched(const AttnArgs& a) : w(0) {
+    tbegin = tstep = blockIdx.x * a.per_cta;
+    tend = min(tbegin + a.per_cta, a.tail_steps);
+  }
+  __device__ bool next(const AttnArgs& a, int& item, int& kv0, int& kv1, int& slot) {
+    if (w < a.full_waves) {
+      item = w * gridDim.x + blockIdx.x;
+      ++w;
+      kv0 = 0, kv1 = a.n_kv, slot = -1;
+      return true;
+    }
+    if (tstep >= tend) return false;
+    const int ti = tstep / a.n_kv;
+    kv0 = tstep - ti * a.n_kv;
+    kv1 = min(a.n_kv, kv0 + (tend - tstep));
+    item = a.full_waves * gridDim.x + ti;
+    slot = (kv0 == 0 && kv1 == a.n_kv) ? -1 : 2 * blockIdx.x + (tstep == tbegin ? 0 : 1);
+    tstep += kv1 - kv0;
+    return true;
+  }
+};
+constexpr size_t kAttnSlotFloats = 256 * 64 + 256 + 256;  // floats per partial slot (O, l, m)
 
 __host__ __device__ constexpr uint32_t s_col(int w) { return 128u * w; }         // S0 / S1
 __host__ __device__ constexpr uint32_t o_col(int w) { return 256u + 64u * w; }   // O0 / O1

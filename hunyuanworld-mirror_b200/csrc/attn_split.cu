@@ -93,7 +93,8 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
       // -------------------------------------------------------------- TMA producer
       if (elect_one()) {
         uint32_t kvit = 0, icount = 0;
-        for (int item = blockIdx.x; item < a.total_items; item += gridDim.x, ++icount) {
+        AttnSched sched(a);
+        for (int item, kv0, kv1, slot; sched.next(a, item, kv0, kv1, slot); ++icount) {
           const int per_head = a.batch * a.n_qpairs;
           const int h = item / per_head, rem = item % per_head;
           const int b = rem / a.n_qpairs, q0 = (rem % a.n_qpairs) * 256;
@@ -102,7 +103,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           mbar_arrive_expect_tx(&q_full[qb], 2 * ATT_TILE);
           tma_load_3d(sQ + (2 * qb) * ATT_TILE, &tmQ, &q_full[qb], h * 64, q0, b, kEvictFirst);
           tma_load_3d(sQ + (2 * qb + 1) * ATT_TILE, &tmQ, &q_full[qb], h * 64, q0 + 128, b, kEvictFirst);
-          for (int j = 0; j < a.n_kv; ++j, ++kvit) {
+          for (int j = kv0; j < kv1; ++j, ++kvit) {
             const uint32_t s = kvit % ST, ph = (kvit / ST) & 1;
             mbar_wait(&k_empty[s], ph ^ 1);
             mbar_arrive_expect_tx(&k_full[s], ATT_TILE);
@@ -123,7 +124,8 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         uint32_t tiles0 = 0, tiles1 = 0;  // S tiles issued per query tile (s_free phase bookkeeping)
         uint32_t pvs0 = 0, pvs1 = 0;      // PVs issued per query tile (p_full phases consumed)
         uint32_t items0 = 0, items1 = 0;  // work items started per query tile (o_free phases)
-        for (int item = blockIdx.x; item < a.total_items; item += gridDim.x, ++icount) {
+        AttnSched sched(a);
+        for (int item, kv0, kv1, slot; sched.next(a, item, kv0, kv1, slot); ++icount) {
           const int q0 = (item % a.n_qpairs) * 256;
           const int nw = (q0 + 128 < a.Lq) ? 2 : 1;  // second query tile entirely out of range: skip it
           const uint32_t qb = icount & 1, qph = (icount >> 1) & 1;
@@ -147,9 +149,9 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             for (int w = 0; w < nw; ++w) issue_s(w, s0);
             umma_commit(&k_empty[s0]);
           }
-          for (int j = 0; j < a.n_kv; ++j, ++kvit) {
+          for (int j = kv0; j < kv1; ++j, ++kvit) {
             const uint32_t sj = kvit % ST, phj = (kvit / ST) & 1;
-            if (j + 1 < a.n_kv) {
+            if (j + 1 < kv1) {
               const uint32_t sn = (kvit + 1) % ST, phn = ((kvit + 1) / ST) & 1;
               mbar_wait(&k_full[sn], phn);
               tcgen05_fence_after();
@@ -162,13 +164,13 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
               uint32_t& pvs = w == 0 ? pvs0 : pvs1;
               mbar_wait(&p_full[w], pvs & 1);
               ++pvs;
-              if (j == 0) mbar_wait(&o_free[w], ((w == 0 ? items0 : items1) & 1) ^ 1);  // previous item's O_w read out
+              if (j == kv0) mbar_wait(&o_free[w], ((w == 0 ? items0 : items1) & 1) ^ 1);  // previous segment's O_w read out
               tcgen05_fence_after();
               const uint32_t vbase = smem_u32(sV + sj * ATT_TILE);
 #pragma unroll
               for (int k = 0; k < 8; ++k) {  // 16 kv rows (2048 B of the V tile) per step; P: 8 TMEM columns per step
                 const uint64_t vd = umma_desc_sw128(vbase + k * 2048, 1024, 1024);
-                umma_ts(tmem_base + o_col(w), tmem_base + p_col(w) + k * 8, vd, idesc_pv, (j | k) != 0);
+                umma_ts(tmem_base + o_col(w), tmem_base + p_col(w) + k * 8, vd, idesc_pv, ((j - kv0) | k) != 0);
               }
               umma_commit(&pv_done[w]);
             }
@@ -201,14 +203,15 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     const float* peer_max = xmax + (qt * 4 + (hf ^ 1)) * 128 + row;
     uint32_t scount = 0, pvbase = 0;  // s_full[qt] phases consumed / pv_done[qt] phases of finished items
 
-    for (int item = blockIdx.x; item < a.total_items; item += gridDim.x) {
+    AttnSched sched(a);
+    for (int item, kv0, kv1, slot; sched.next(a, item, kv0, kv1, slot);) {
       const int per_head = a.batch * a.n_qpairs;
       const int h = item / per_head, rem = item % per_head;
       const int b = rem / a.n_qpairs, q0 = (rem % a.n_qpairs) * 256;
       if (qt == 1 && q0 + 128 >= a.Lq) continue;
 
-      float m = -INFINITY, l = 0.f;
-      for (int j = 0; j < a.n_kv; ++j, ++scount) {
+      float m = BOUNDED ? 0.f : -INFINITY, l = 0.f;
+      for (int j = kv0; j < kv1; ++j, ++scount) {
         mbar_wait(&s_full[qt], scount & 1);
         tcgen05_fence_after();
         uint32_t pk[32];
@@ -273,13 +276,13 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           my_max[(j & 1) * 256] = mt;
           named_bar_sync(1 + qt, 256);
           const float m_new = fmaxf(fmaxf(mt, peer_max[(j & 1) * 256]), m);
-          if (j == 0) {
+          if (j == kv0) {
             m = m_new;
           } else {
             const bool need = (m_new - m) * a.scale_log2 > 8.0f;
             if (__any_sync(0xffffffffu, need)) {
               // O correction: wait for PV(j-1), then scale this thread's 32 columns of O and its partial l
-              mbar_wait(&pv_done[qt], (pvbase + j - 1) & 1);
+              mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
               pv_waited = true;
               tcgen05_fence_after();
               const float alpha = need ? ex2_approx((m - m_new) * a.scale_log2) : 1.0f;
@@ -315,8 +318,8 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           }
           l += (sum2[0].x + sum2[0].y) + (sum2[1].x + sum2[1].y);
         }
-        if (j > 0 && !pv_waited) {  // P_qt is still being read by PV(j-1) until this completes (normally long done)
-          mbar_wait(&pv_done[qt], (pvbase + j - 1) & 1);
+        if (j > kv0 && !pv_waited) {  // P_qt is still being read by PV(j-1) until this completes (normally long done)
+          mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
           tcgen05_fence_after();
         }
         tmem_st_x32(p_addr, pk);
@@ -326,7 +329,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         if (lane == 0) mbar_arrive(&p_full[qt]);
       }
       // ---- epilogue: merge the partial row sums, O / l -> bf16 -> swizzled staging tile -> TMA store
-      pvbase += a.n_kv;
+      pvbase += kv1 - kv0;
       mbar_wait(&pv_done[qt], (pvbase - 1) & 1);
       tcgen05_fence_after();
       uint32_t o[32];
@@ -338,7 +341,22 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
       xsum[(qt * 2 + hf) * 128 + row] = l;
       if (leader) tma_store_wait_read<0>();  // the previous store has drained the staging tile
       named_bar_sync(1 + qt, 256);
-      const float inv = 1.0f / (l + xsum[(qt * 2 + (hf ^ 1)) * 128 + row]);
+      const float l_row = l + xsum[(qt * 2 + (hf ^ 1)) * 128 + row];
+      if (slot >= 0) {
+        // this CTA holds only part of the item's keys: leave the unnormalised share for attn_merge_kernel
+        float4* po = reinterpret_cast<float4*>(a.part_o + ((size_t)slot * 256 + qt * 128 + row) * 64 + 32 * hf);
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          po[c] = make_float4(__uint_as_float(o[4 * c]), __uint_as_float(o[4 * c + 1]), __uint_as_float(o[4 * c + 2]),
+                              __uint_as_float(o[4 * c + 3]));
+        if (hf == 0) {
+          a.part_l[(size_t)slot * 256 + qt * 128 + row] = l_row;
+          a.part_m[(size_t)slot * 256 + qt * 128 + row] = m;
+        }
+        named_bar_sync(1 + qt, 256);  // xsum is rewritten by the next segment
+        continue;
+      }
+      const float inv = 1.0f / l_row;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         uint32_t pk4[4];
@@ -365,6 +383,44 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
   }
 }
 
+// ------------------------------------------------------------------------------------------------ merge
+// Adds up the partials of every work item whose keys were split between CTAs (at most a handful per launch) and
+// writes the normalised bf16 rows.  One block per tail item; items that were computed whole return at once.
+// Partials are visited in CTA order, so the result does not depend on timing.
+__global__ void __launch_bounds__(256)
+attn_merge_kernel(const AttnArgs a, __nv_bfloat16* __restrict__ out, int ldo) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int ti = blockIdx.x >> 4;                         // tail item; 16 blocks of 16 rows each
+  const int item = a.full_waves * a.merge_grid + ti;
+  const int s0 = ti * a.n_kv, s1 = s0 + a.n_kv;           // its steps inside the tail
+  const int c0 = s0 / a.per_cta, c1 = (s1 - 1) / a.per_cta;
+  if (c0 == c1) return;
+  const int per_head = a.batch * a.n_qpairs;
+  const int h = item / per_head, rem = item % per_head;
+  const int b = rem / a.n_qpairs, q0 = (rem % a.n_qpairs) * 256;
+  const int c4 = threadIdx.x & 15;
+  const int r = (blockIdx.x & 15) * 16 + (threadIdx.x >> 4);
+  if (q0 + r >= a.Lq) return;
+  const int first_slot = 2 * c0 + (s0 != c0 * a.per_cta ? 1 : 0);  // later CTAs hold the item in their first segment
+  float M = a.part_m[(size_t)first_slot * 256 + r];
+#pragma unroll 4
+  for (int c = c0 + 1; c <= c1; ++c) M = fmaxf(M, a.part_m[(size_t)(2 * c) * 256 + r]);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float L = 0.f;
+#pragma unroll 4
+  for (int c = c0; c <= c1; ++c) {
+    const int slot = c == c0 ? first_slot : 2 * c;
+    const float w = ex2_approx((a.part_m[(size_t)slot * 256 + r] - M) * a.scale_log2);
+    const float4 o = reinterpret_cast<const float4*>(a.part_o + ((size_t)slot * 256 + r) * 64)[c4];
+    acc.x = fmaf(w, o.x, acc.x), acc.y = fmaf(w, o.y, acc.y), acc.z = fmaf(w, o.z, acc.z), acc.w = fmaf(w, o.w, acc.w);
+    L = fmaf(w, a.part_l[(size_t)slot * 256 + r], L);
+  }
+  const float inv = 1.0f / L;
+  uint2 pk = make_uint2(pack_bf16(acc.x * inv, acc.y * inv), pack_bf16(acc.z * inv, acc.w * inv));
+  *reinterpret_cast<uint2*>(out + ((size_t)b * a.Lq + q0 + r) * ldo + h * 64 + c4 * 4) = pk;
+}
+
 // ------------------------------------------------------------------------------------------------ host
 template <int NPOLY, bool BOUNDED>
 static wm_status launch_split(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
@@ -377,22 +433,50 @@ static wm_status launch_split(cudaStream_t st, int grid, const CUtensorMap& tq, 
   return launch_pdl(attn_split_kernel<NPOLY, BOUNDED>, dim3(grid), dim3(ATS_THREADS), ATS_SMEM, st, tq, tk, tv, to, a);
 }
 
+size_t attn_partial_bytes(int sm_count) { return (size_t)2 * sm_count * kAttnSlotFloats * sizeof(float); }
+
 // variants 4..7 of flash_attention(): running-max softmax, polynomial share 0, 8, 10, 12 of every 32 exponentials;
 // variants 8..12: bounded-logit mode (q pre-scaled, |logit| bounded), polynomial share 0, 8, 12, 14, 16.
-wm_status flash_attention_split(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk,
-                                const CUtensorMap& tv, const CUtensorMap& to, const AttnArgs& a, int variant) {
+// With a partial workspace (attn_partial_bytes) the (item, kv tile) steps are dealt out evenly and split items are
+// merged by attn_merge_kernel; without one every CTA gets whole items.
+wm_status flash_attention_split(cudaStream_t st, int sm_count, const CUtensorMap& tq, const CUtensorMap& tk,
+                                const CUtensorMap& tv, const CUtensorMap& to, AttnArgs a, int variant, void* out, int ldo,
+                                float* partial_ws, size_t partial_ws_bytes) {
+  const bool balance = partial_ws != nullptr && partial_ws_bytes >= attn_partial_bytes(sm_count) && a.total_items > 0;
+  const int grid = a.total_items < sm_count ? a.total_items : sm_count;
+  a.full_waves = a.total_items / grid;
+  const int tail_items = a.total_items - a.full_waves * grid;
+  a.tail_steps = tail_items * a.n_kv;
+  a.merge_grid = grid;
+  // splitting the tail pays a partial store, a merge launch and a pipeline refill: about ten tile times (measured
+  // at 1376 keys, where whole items are faster); take it only when more than that is saved
+  const int even_share = (a.tail_steps + grid - 1) / grid;
+  if (balance && tail_items > 0 && even_share + 10 <= a.n_kv) {
+    a.per_cta = even_share;
+    a.part_o = partial_ws;
+    a.part_l = partial_ws + (size_t)2 * sm_count * 256 * 64;
+    a.part_m = a.part_l + (size_t)2 * sm_count * 256;
+  } else {
+    a.per_cta = a.n_kv;  // whole items only: CTA c takes tail item c, no partials
+    a.part_o = a.part_l = a.part_m = nullptr;
+  }
+  wm_status r;
   switch (variant) {
-    case 4: return launch_split<0, false>(st, grid, tq, tk, tv, to, a);
-    case 5: return launch_split<8, false>(st, grid, tq, tk, tv, to, a);
-    case 6: return launch_split<10, false>(st, grid, tq, tk, tv, to, a);
-    case 7: return launch_split<12, false>(st, grid, tq, tk, tv, to, a);
-    case 8: return launch_split<0, true>(st, grid, tq, tk, tv, to, a);
-    case 9: return launch_split<8, true>(st, grid, tq, tk, tv, to, a);
-    case 10: return launch_split<12, true>(st, grid, tq, tk, tv, to, a);
-    case 11: return launch_split<14, true>(st, grid, tq, tk, tv, to, a);
-    case 12: return launch_split<16, true>(st, grid, tq, tk, tv, to, a);
+    case 4: r = launch_split<0, false>(st, grid, tq, tk, tv, to, a); break;
+    case 5: r = launch_split<8, false>(st, grid, tq, tk, tv, to, a); break;
+    case 6: r = launch_split<10, false>(st, grid, tq, tk, tv, to, a); break;
+    case 7: r = launch_split<12, false>(st, grid, tq, tk, tv, to, a); break;
+    case 8: r = launch_split<0, true>(st, grid, tq, tk, tv, to, a); break;
+    case 9: r = launch_split<8, true>(st, grid, tq, tk, tv, to, a); break;
+    case 10: r = launch_split<12, true>(st, grid, tq, tk, tv, to, a); break;
+    case 11: r = launch_split<14, true>(st, grid, tq, tk, tv, to, a); break;
+    case 12: r = launch_split<16, true>(st, grid, tq, tk, tv, to, a); break;
     default: return fail(WM_ERR_INVALID, "flash_attention: unknown split variant %d", variant);
   }
+  WM_TRY(r);
+  if (a.part_o != nullptr && a.per_cta % a.n_kv != 0)
+    return launch_pdl(attn_merge_kernel, dim3(16 * tail_items), dim3(256), 0, st, a, static_cast<__nv_bfloat16*>(out), ldo);
+  return WM_OK;
 }
 
 }  // namespace wm

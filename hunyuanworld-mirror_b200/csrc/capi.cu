@@ -128,7 +128,7 @@ struct wm_handle {
   size_t prof_used[WM_PROF_CLASSES] = {0};
   long long launches = 0;
   // tuning knobs (wm_set_int): attention kernel variants and the bounded-logit switch
-  int attn_general_variant = 4, attn_bounded_variant = 10, attn_allow_bounded = 1;
+  int attn_general_variant = 4, attn_bounded_variant = 10, attn_allow_bounded = 1, attn_balance = 1;
 };
 
 namespace wm {
@@ -175,6 +175,7 @@ static wm_status build_dino_table(wm_handle* h, int gh, int gw, const float* pos
 struct Workspace {
   float *xd, *x;
   __nv_bfloat16 *ln, *q, *kv, *att, *hid;
+  float* attn_part;  // partials of attention work items split between CTAs (attn_split.cu)
   size_t bytes;
 };
 
@@ -197,6 +198,7 @@ static Workspace carve(void* base, int n, int gh, int gw, int world) {
   ws.kv = reinterpret_cast<__nv_bfloat16*>(take(T * (size_t)world * 2 * kEmbed * 2));
   ws.att = reinterpret_cast<__nv_bfloat16*>(take(T * kEmbed * 2));
   ws.hid = reinterpret_cast<__nv_bfloat16*>(take(T * kMlp * 2));
+  ws.attn_part = reinterpret_cast<float*>(take(attn_partial_bytes(kNumSms)));
   ws.bytes = off + 1024;  // slack so the caller's base may be aligned up to 1024
   return ws;
 }
@@ -265,7 +267,8 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
   const __nv_bfloat16* kbase = gather ? ws.kv : kv_local;
   WM_OP(s.global ? WM_PROF_ATTN_GLOBAL : WM_PROF_ATTN_LOCAL,
         flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
-                        0.125f, bounded ? h->attn_bounded_variant : h->attn_general_variant, 0, 0));
+                        0.125f, bounded ? h->attn_bounded_variant : h->attn_general_variant,
+                        h->attn_balance ? ws.attn_part : nullptr, attn_partial_bytes(kNumSms)));
   WM_OP(WM_PROF_PROJ, gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x,
                                        kEmbed));
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
@@ -695,6 +698,8 @@ wm_status wm_set_int(wm_handle* h, const char* name, int value) {
     h->attn_bounded_variant = value;
   } else if (n == "attn_allow_bounded") {
     h->attn_allow_bounded = value != 0;
+  } else if (n == "attn_balance") {
+    h->attn_balance = value != 0;
   } else {
     return fail(WM_ERR_INVALID, "wm_set_int: unknown option %s", name);
   }
@@ -726,15 +731,17 @@ wm_status wm_gemm_table(wm_stream stream, const void* A, int lda, const void* W,
 wm_status wm_flash_attn(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
                         int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant) {
   return flash_attention(static_cast<cudaStream_t>(stream), q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, heads, scale,
-                         variant, 0, 0);
+                         variant, nullptr, 0);
 }
 
-wm_status wm_flash_attn_dbg(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
-                            int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, unsigned v_lbo,
-                            unsigned v_sbo) {
+wm_status wm_flash_attn_ws(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                           int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, void* workspace,
+                           size_t workspace_bytes) {
   return flash_attention(static_cast<cudaStream_t>(stream), q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, heads, scale,
-                         variant, v_lbo, v_sbo);
+                         variant, static_cast<float*>(workspace), workspace_bytes);
 }
+
+size_t wm_attn_workspace_bytes(void) { return attn_partial_bytes(kNumSms); }
 
 wm_status wm_umma_probe(wm_stream stream, const void* p, const void* v, float* d, int mode, unsigned v_lbo,
                         unsigned v_sbo) {

@@ -105,7 +105,8 @@ wm_status wm_profile_read(wm_handle* h, int cls, float* total_ms, int* count);
 /* Kernel (and collective) launches issued by forwards since the last wm_profile() call. */
 long long wm_launch_count(const wm_handle* h);
 
-/* Tuning knobs: "attn_general_variant" (0-7), "attn_bounded_variant" (8-12), "attn_allow_bounded" (0/1). */
+/* Tuning knobs: "attn_general_variant" (0-7), "attn_bounded_variant" (8-12), "attn_allow_bounded" (0/1),
+ * "attn_balance" (0/1: even split of attention work with partial merge). */
 wm_status wm_set_int(wm_handle* h, const char* name, int value);
 /* Bound of |q . k| * scale * log2(e) implied by the QK-LayerNorm weights of block `layer` of kind 0 = DINOv2 (always 0),
  * 1 = frame, 2 = global; the forward uses the bounded-logit attention when 0 < bound <= 80.  -1: invalid argument. */
@@ -149,10 +150,13 @@ wm_status wm_gemm_table(wm_stream stream, const void* A, int lda, const void* W,
  * scale * log2(e) (wm_gemm_qkv q_scale), |q . k| <= 80, `scale` is ignored and P = 2^(q . k) without a running max. */
 wm_status wm_flash_attn(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
                         int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant);
-/* As wm_flash_attn with explicit V-descriptor strides (test hook). */
-wm_status wm_flash_attn_dbg(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
-                            int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, unsigned v_lbo,
-                            unsigned v_sbo);
+/* As wm_flash_attn with a scratch buffer of wm_attn_workspace_bytes() (device memory, 16-byte aligned): variants 4-12
+ * then deal the (work item, key tile) steps out evenly over the SMs, split items leave fp32 partials in the
+ * workspace and a merge kernel adds them in a fixed order (deterministic).  This is what the forward pass uses. */
+wm_status wm_flash_attn_ws(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                           int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, void* workspace,
+                           size_t workspace_bytes);
+size_t wm_attn_workspace_bytes(void);
 /* Single-tile probe: d [128,64] fp32 = p [128,128] bf16 x v [128,64] bf16; mode 0 = P in smem, 1 = P in TMEM. */
 wm_status wm_umma_probe(wm_stream stream, const void* p, const void* v, float* d, int mode, unsigned v_lbo,
                         unsigned v_sbo);

@@ -47,11 +47,16 @@ if [ "$what" = attn ]; then
     run attn 1 512 11008 2 1 $var 0 0 31
     run attn 1 700 2900 3 8 $var 0 0 23
     run attn 1 200 70 1 1 $var 0 0 3
+    run attn 1 1376 1376 16 1 $var 1 0 97
+    run attn 1 3000 5000 16 2 $var 0 0 211
+    run attn 2 640 9000 3 2 $var 0 0 37
   done
   for var in ${VARIANTS:-4 7 8 9 10 11 12} 2; do
     run bench_attn 8 1376 1376 16 $var
     run bench_attn 1 11008 11008 16 $var
     run bench_attn 1 22016 44032 16 $var
+    run bench_attn 8 1376 1376 16 $var 1
+    run bench_attn 1 11008 11008 16 $var 1
   done
 fi
 if [ "$what" = bench ] || [ "$what" = all ]; then

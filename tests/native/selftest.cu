@@ -326,7 +326,11 @@ static int case_attn(int batch, int Lq, int Lkv, int heads, float qscale, int va
   KV.fill((size_t)batch * Lkv * ldkv, 1.0f);
   uint16_t *dq = dev(Q.h), *dkv = dev(KV.h);
   uint16_t* dout = dev_alloc<uint16_t>((size_t)batch * Lq * ldq);
-  WM(wm_flash_attn_dbg(0, dq, ldq, dkv, dkv + heads * 64, ldkv, dout, ldq, batch, Lq, Lkv, heads, 0.125f, variant, lbo, sbo));
+  // lbo != 0: no workspace (whole items per CTA); default: balanced steps + partial merge
+  void* ws = lbo ? nullptr : (void*)dev_alloc<uint8_t>(wm_attn_workspace_bytes());
+  (void)sbo;
+  WM(wm_flash_attn_ws(0, dq, ldq, dkv, dkv + heads * 64, ldkv, dout, ldq, batch, Lq, Lkv, heads, 0.125f, variant, ws,
+                      ws ? wm_attn_workspace_bytes() : 0));
   CK(cudaDeviceSynchronize());
   auto out = host(dout, (size_t)batch * Lq * ldq);
   Err e;
@@ -410,21 +414,23 @@ static int bench_gemm(int kind, int M, int N, int K) {
 struct AttnCtx {
   uint16_t *q, *kv, *o;
   int batch, Lq, Lkv, heads, variant;
+  void* ws;
 };
 static void attn_run(void* p) {
   AttnCtx* c = (AttnCtx*)p;
-  WM(wm_flash_attn(0, c->q, c->heads * 64, c->kv, c->kv + c->heads * 64, c->heads * 128, c->o, c->heads * 64, c->batch, c->Lq,
-                   c->Lkv, c->heads, 0.125f, c->variant));
+  WM(wm_flash_attn_ws(0, c->q, c->heads * 64, c->kv, c->kv + c->heads * 64, c->heads * 128, c->o, c->heads * 64, c->batch,
+                      c->Lq, c->Lkv, c->heads, 0.125f, c->variant, c->ws, c->ws ? wm_attn_workspace_bytes() : 0));
 }
-static int bench_attn(int batch, int Lq, int Lkv, int heads, int variant) {
+static int bench_attn(int batch, int Lq, int Lkv, int heads, int variant, int no_ws) {
   AttnCtx c{};
   c.batch = batch, c.Lq = Lq, c.Lkv = Lkv, c.heads = heads, c.variant = variant;
+  c.ws = no_ws ? nullptr : (void*)dev_alloc<uint8_t>(wm_attn_workspace_bytes());
   BF Q, KV;
   Q.fill((size_t)batch * Lq * heads * 64, 1.0f);
   KV.fill((size_t)batch * Lkv * heads * 128, 1.0f);
   c.q = dev(Q.h), c.kv = dev(KV.h), c.o = dev_alloc<uint16_t>((size_t)batch * Lq * heads * 64);
   const float ms = time_ms(Lkv > 50000 ? 3 : 10, attn_run, &c);
-  printf("BENCH attn batch=%d Lq=%d Lkv=%d heads=%d variant=%d  %.3f ms  %.1f TFLOP/s\n", batch, Lq, Lkv, heads, variant, ms,
+  printf("BENCH attn batch=%d Lq=%d Lkv=%d heads=%d variant=%d balanced=%d  %.3f ms  %.1f TFLOP/s\n", batch, Lq, Lkv, heads, variant, !no_ws, ms,
          4.0 * batch * (double)Lq * Lkv * heads * 64 / ms * 1e-9);
   return 0;
 }
@@ -458,7 +464,7 @@ int main(int argc, char** argv) {
   if (c == "gemm_qkv") return case_gemm_qkv(I(2, 300), I(3, 1), I(4, 1), I(5, 3));
   if (c == "attn") return case_attn(I(2, 2), I(3, 331), I(4, 331), I(5, 2), (float)I(6, 1), I(7, 0), I(8, 0), I(9, 0), I(10, 5));
   if (c == "bench_gemm") return bench_gemm(I(2, 0), I(3, 11008), I(4, 1024), I(5, 1024));
-  if (c == "bench_attn") return bench_attn(I(2, 1), I(3, 11008), I(4, 11008), I(5, 16), I(6, 0));
+  if (c == "bench_attn") return bench_attn(I(2, 1), I(3, 11008), I(4, 11008), I(5, 16), I(6, 0), I(7, 0));
   if (c == "bench_ln") return bench_ln(I(2, 11008));
   printf("unknown case %s\n", c.c_str());
   return 64;
