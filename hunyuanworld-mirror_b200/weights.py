@@ -84,9 +84,102 @@ def state_dict_schema(depth: int = 24, dino_depth: int = 24) -> "OrderedDict[str
     return s
 
 
+def _dpt_shapes(prefix: str, out_dim: int, dim_in: int = 2 * EMBED, features: int = 256) -> "OrderedDict[str, Tuple[int, ...]]":
+    """DPTHead(dim_in=2048, output_dim=out_dim) state_dict (dense_head.py:36-106), registration order."""
+    oc = (256, 512, 1024, 1024)
+    s: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    s[prefix + "norm.weight"] = (dim_in,)
+    s[prefix + "norm.bias"] = (dim_in,)
+    for i, c in enumerate(oc):
+        s[prefix + f"projects.{i}.weight"] = (c, dim_in, 1, 1)
+        s[prefix + f"projects.{i}.bias"] = (c,)
+    s[prefix + "resize_layers.0.weight"] = (oc[0], oc[0], 4, 4)  # ConvTranspose2d: [in, out, k, k]
+    s[prefix + "resize_layers.0.bias"] = (oc[0],)
+    s[prefix + "resize_layers.1.weight"] = (oc[1], oc[1], 2, 2)
+    s[prefix + "resize_layers.1.bias"] = (oc[1],)
+    s[prefix + "resize_layers.3.weight"] = (oc[3], oc[3], 3, 3)
+    s[prefix + "resize_layers.3.bias"] = (oc[3],)
+    for i, c in enumerate(oc):
+        s[prefix + f"scratch.layer{i + 1}_rn.weight"] = (features, c, 3, 3)
+    for r in (1, 2, 3, 4):
+        p = prefix + f"scratch.refinenet{r}."
+        s[p + "out_conv.weight"] = (features, features, 1, 1)
+        s[p + "out_conv.bias"] = (features,)
+        for u in ((1, 2) if r != 4 else (2,)):
+            for c in (1, 2):
+                s[p + f"resConfUnit{u}.conv{c}.weight"] = (features, features, 3, 3)
+                s[p + f"resConfUnit{u}.conv{c}.bias"] = (features,)
+    s[prefix + "scratch.output_conv1.weight"] = (features // 2, features, 3, 3)
+    s[prefix + "scratch.output_conv1.bias"] = (features // 2,)
+    s[prefix + "scratch.output_conv2.0.weight"] = (32, features // 2, 3, 3)
+    s[prefix + "scratch.output_conv2.0.bias"] = (32,)
+    s[prefix + "scratch.output_conv2.2.weight"] = (out_dim, 32, 1, 1)
+    s[prefix + "scratch.output_conv2.2.bias"] = (out_dim,)
+    return s
+
+
+def _camera_shapes(prefix: str, dim: int = 2 * EMBED, trunk_depth: int = 4) -> "OrderedDict[str, Tuple[int, ...]]":
+    """CameraHead(dim_in=2048) state_dict (camera_head.py:16-56), registration order."""
+    s: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    s[prefix + "init_token"] = (1, 1, 9)
+    for i in range(trunk_depth):
+        p = prefix + f"refine_net.{i}."
+        s[p + "norm1.weight"] = (dim,)
+        s[p + "norm1.bias"] = (dim,)
+        s[p + "attn.qkv.weight"] = (3 * dim, dim)
+        s[p + "attn.qkv.bias"] = (3 * dim,)
+        s[p + "attn.proj.weight"] = (dim, dim)
+        s[p + "attn.proj.bias"] = (dim,)
+        s[p + "ls1.gamma"] = (dim,)
+        s[p + "norm2.weight"] = (dim,)
+        s[p + "norm2.bias"] = (dim,)
+        s[p + "mlp.fc1.weight"] = (4 * dim, dim)
+        s[p + "mlp.fc1.bias"] = (4 * dim,)
+        s[p + "mlp.fc2.weight"] = (dim, 4 * dim)
+        s[p + "mlp.fc2.bias"] = (dim,)
+        s[p + "ls2.gamma"] = (dim,)
+    s[prefix + "token_norm.weight"] = (dim,)
+    s[prefix + "token_norm.bias"] = (dim,)
+    s[prefix + "out_norm.weight"] = (dim,)
+    s[prefix + "out_norm.bias"] = (dim,)
+    s[prefix + "param_embed.weight"] = (dim, 9)
+    s[prefix + "param_embed.bias"] = (dim,)
+    s[prefix + "adapt_norm_gen.1.weight"] = (3 * dim, dim)
+    s[prefix + "adapt_norm_gen.1.bias"] = (3 * dim,)
+    s[prefix + "param_predictor.fc1.weight"] = (dim // 2, dim)
+    s[prefix + "param_predictor.fc1.bias"] = (dim // 2,)
+    s[prefix + "param_predictor.fc2.weight"] = (9, dim // 2)
+    s[prefix + "param_predictor.fc2.bias"] = (9,)
+    return s
+
+
+def heads_schema() -> "OrderedDict[str, Tuple[int, ...]]":
+    """Key -> shape of WorldMirror's prediction heads under their attribute names (worldmirror.py:66-98):
+    cam_head (CameraHead), pts_head / depth_head / norm_head (DPTHead with output_dim 4 / 2 / 4)."""
+    s: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    s.update(_camera_shapes("cam_head."))
+    s.update(_dpt_shapes("pts_head.", 4))
+    s.update(_dpt_shapes("depth_head.", 2))
+    s.update(_dpt_shapes("norm_head.", 4))
+    return s
+
+
+def synthetic_heads_state_dict(seed: int = 0) -> Dict[str, torch.Tensor]:
+    """Deterministic head weights under the reference keys (same recipe as `synthetic_state_dict`)."""
+    return OrderedDict((k, synthetic_tensor(k, shp, seed)) for k, shp in heads_schema().items())
+
+
 def _role(key: str, shape: Tuple[int, ...]) -> Tuple[float, float]:
     """(mean, std) per tensor role."""
     leaf = key.rsplit(".", 1)[-1]
+    if key.endswith("init_token"):
+        return 0.0, 0.1
+    if "resize_layers.0." in key or "resize_layers.1." in key:
+        # ConvTranspose2d with kernel == stride: every output pixel sees one tap, fan-in = in_channels (dim 0)
+        return (0.0, 0.02) if leaf == "bias" else (0.0, 1.0 / float(shape[0]) ** 0.5)
+    if "_head." in key and not key.startswith("cam_head.") and leaf == "weight" and len(shape) == 4:
+        fan_in = shape[1] * shape[2] * shape[3]
+        return 0.0, 1.0 / float(fan_in) ** 0.5
     if key.endswith("mask_token"):
         return 0.0, 0.0
     if key in ("cam_token", "reg_token"):
