@@ -235,9 +235,17 @@ def run_b200(args):
         attn_flops_per_launch = fl["global_attention"] / 24
         attn_avg_ms = attn_ms.value / max(attn_n.value, 1)
         achieved = attn_flops_per_launch / (attn_avg_ms * 1e-3) / 1e12
-        roofline = {"kernel": "attn_kernel<true> (global attention, Lq=%d Lkv=%d, 16 heads)" % (n_local * 1376, n_total * 1376),
+        # DRAM bytes of that kernel per launch from the committed ncu --set full capture (same shape only)
+        traffic = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "attn_global_traffic.json")))
+            if tr["Lq"] == n_local * 1376 and tr["Lkv"] == n_total * 1376:
+                traffic = tr["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        roofline = {"kernel": "attn_split_kernel (global attention, Lq=%d Lkv=%d, 16 heads)" % (n_local * 1376, n_total * 1376),
                     "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
-                    "traffic": None, "peak_source": peak_src, "avg_launch_ms": attn_avg_ms, "launches_timed": attn_n.value,
+                    "traffic": traffic, "peak_source": peak_src, "avg_launch_ms": attn_avg_ms, "launches_timed": attn_n.value,
                     "share_of_step": attn_ms.value / total_ms,
                     "whole_step_tflops": fl["total"] / (ms_per_step * 1e-3) / 1e12}
         cpu = None

@@ -81,10 +81,14 @@ def camera_head(cam_tokens: Tensor, sd: Dict[str, Tensor], pre: str = "cam_head.
 
 
 def quat_angle(qa: Tensor, qb: Tensor) -> Tensor:
-    """Rotation angle (rad) between unit-normalised quaternions qa, qb [..., 4] (sign-invariant)."""
+    """Rotation angle (rad) between the rotations of quaternions qa, qb [..., 4] (normalised here, sign-invariant).
+    2 acos|<qa,qb>| loses everything below 1e-3 rad in fp32 (acos near 1), so the chord form
+    4 asin(|qa - s qb| / 2), s = sign<qa,qb>, is evaluated in float64."""
+    qa, qb = qa.double(), qb.double()
     qa = qa / qa.norm(dim=-1, keepdim=True)
     qb = qb / qb.norm(dim=-1, keepdim=True)
-    return 2.0 * torch.acos((qa * qb).sum(-1).abs().clamp(max=1.0))
+    s = torch.where((qa * qb).sum(-1, keepdim=True) < 0, -1.0, 1.0)
+    return 4.0 * torch.asin(((qa - s * qb).norm(dim=-1) / 2.0).clamp(max=1.0))
 
 
 # --------------------------------------------------------------------------------------
