@@ -223,6 +223,13 @@ def run_b200(args):
     e2e = {"value": n_total / (e2e_ms * 1e-3), "unit": "views/s", "h2d_bytes_per_step": imgs_host.numel() * 4,
            "d2h_bytes_per_step": cam_host.numel() * 4, "ms_per_step": e2e_ms}
 
+    sp_exchange = None
+    if world > 1:
+        enabled, timed_out = model.peer_gather_status()
+        if timed_out:
+            raise SystemExit("peer-memory K|V exchange timed out during the run: the numbers are invalid")
+        sp_exchange = ("K|V shards pushed into peer memory over NVLink by the copy engines, overlapped with attention "
+                       "(arrival words per shard)") if enabled else "ncclAllGather of K|V, then attention"
     if rank == 0:
         peaks = {}
         try:
@@ -259,7 +266,7 @@ def run_b200(args):
                 "config": {"workload": f"aggregator fwd (DINOv2 ViT-L/14 + 24x(frame,global) blocks), {n_local} views/GPU x {world} GPU = "
                                        f"{n_total} views {SIZE}x{SIZE}, no priors (BASELINE configs[1] at N=1; heads out of scope, SURVEY 8f)",
                            "views_per_gpu": n_local, "views_total": n_total, "size": SIZE, "tokens_per_view": 1376,
-                           "parallelism": "views sharded; global-attention K|V all-gather (NCCL)" if world > 1 else "single GPU",
+                           "parallelism": f"views sharded; global attention: {sp_exchange}" if world > 1 else "single GPU",
                            "l2": "per-step working set (1.8 GB bf16 weights + activations) exceeds the 126 MB L2; no flush needed"},
                 "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
                 "breakdown_ms": breakdown}

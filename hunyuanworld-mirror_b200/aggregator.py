@@ -66,6 +66,7 @@ class B200VisualGeometryTransformer(torch.nn.Module):
         self._pos_grid = (DINO_GRID, DINO_GRID)
         self._workspace: Dict[Tuple[int, int, int], torch.Tensor] = {}
         self.rank, self.world = 0, 1
+        self._sp_group, self._p2p_rows = None, 0
 
     # ------------------------------------------------------------------ library handle
     def _ensure_handle(self):
@@ -151,6 +152,40 @@ class B200VisualGeometryTransformer(torch.nn.Module):
         raw = (C.c_uint8 * 128)(*broadcast_unique_id(uid, group, dev))
         capi.check(capi.lib().wm_nccl_init(self._ensure_handle(), path.encode(), raw, rank, world))
         self.rank, self.world = rank, world
+        self._sp_group = group
+        self._p2p_rows = 0
+
+    def _ensure_peer_gather(self, rows_per_rank: int, device):
+        """Peer-memory K|V exchange (include/wm_b200.h, wm_p2p_*): every rank allocates its gather block, the
+        cudaIpcMemHandle_t's travel over the torch.distributed group, every rank maps its peers' blocks.  Collective:
+        all ranks reach this with the same `rows_per_rank` (they run the same forwards).  WM_SP_MODE=nccl keeps
+        the plain ncclAllGather path."""
+        import os
+
+        import torch.distributed as dist
+
+        if os.environ.get("WM_SP_MODE", "p2p") == "nccl" or rows_per_rank <= self._p2p_rows:
+            return
+        group = self._sp_group
+        torch.cuda.synchronize(device)
+        dist.barrier(group)  # nobody is still pushing into a block that is about to be freed
+        mine = (C.c_uint8 * 64)()
+        capi.check(capi.lib().wm_p2p_alloc(self._handle, self.rank, self.world, rows_per_rank, mine))
+        t = torch.tensor(list(bytes(mine)), dtype=torch.uint8)
+        if dist.get_backend(group) == "nccl":
+            t = t.to(device)
+        parts = [torch.empty_like(t) for _ in range(self.world)]
+        dist.all_gather(parts, t, group=group)
+        raw = b"".join(bytes(x.cpu().tolist()) for x in parts)
+        capi.check(capi.lib().wm_p2p_attach(self._handle, (C.c_uint8 * len(raw)).from_buffer_copy(raw)))
+        dist.barrier(group)
+        self._p2p_rows = rows_per_rank
+
+    def peer_gather_status(self):
+        """(enabled, timed_out) of the peer-memory exchange; timed_out means a forward ran on stale keys."""
+        en, to = C.c_int(), C.c_int()
+        capi.check(capi.lib().wm_p2p_status(self._handle, C.byref(en), C.byref(to)))
+        return bool(en.value), bool(to.value)
 
     # ------------------------------------------------------------------ forward
     def _workspace_for(self, n: int, H: int, W: int, device) -> torch.Tensor:
@@ -191,6 +226,8 @@ class B200VisualGeometryTransformer(torch.nn.Module):
         with torch.cuda.device(device):
             self._ensure_pos_table(gh, gw)
             ws = self._workspace_for(s, H, W, device)
+            if self.world > 1:
+                self._ensure_peer_gather(s * P, device)
             stream = torch.cuda.current_stream(device).cuda_stream
             cflags = (C.c_int * 3)(*flags)
             for bi in range(b):
@@ -217,6 +254,8 @@ class B200VisualGeometryTransformer(torch.nn.Module):
         outs = [torch.empty(1, s, P, 2 * EMBED, dtype=torch.float32, device=device) for _ in self.intermediate_idxs]
         with torch.cuda.device(device):
             ws = self._workspace_for(s, gh * PATCH, gw * PATCH, device)
+            if self.world > 1:
+                self._ensure_peer_gather(s * P, device)
             optrs = (C.c_void_p * 4)(*[o.data_ptr() for o in outs] + [None] * (4 - len(outs)))
             capi.check(capi.lib().wm_forward_tokens(self._handle, torch.cuda.current_stream(device).cuda_stream,
                                                     x.data_ptr(), s, gh, gw, optrs, ws.data_ptr(), ws.numel()))

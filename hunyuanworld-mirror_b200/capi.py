@@ -46,6 +46,12 @@ SIGNATURES = {
     "wm_nccl_unique_id": (C.c_int, [C.c_char_p, _vp]),
     "wm_nccl_init": (C.c_int, [_vp, C.c_char_p, _vp, _i, _i]),
     "wm_nccl_allgather": (C.c_int, [_vp, _vp, _vp, C.c_size_t]),
+    "wm_p2p_alloc": (C.c_int, [_vp, _i, _i, _i, _vp]),
+    "wm_p2p_attach": (C.c_int, [_vp, _vp]),
+    "wm_p2p_status": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "wm_flash_attn_gathered": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _f, _i, _vp, C.c_size_t, _i, _i,
+                                         _vp, _u, _vp]),
+    "wm_p2p_raise_flag": (C.c_int, [_vp, _vp, _u]),
     "wm_layernorm": (C.c_int, [_vp, _fp, _fp, _fp, _f, _i, _vp, _i]),
     "wm_gemm_bias_act": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _i, _i, _i, _vp, _i, _i]),
     "wm_gemm_qkv": (C.c_int, [_vp, _vp, _vp, _fp, _fp, _fp, _fp, _fp, _f, _fp, _fp, _i, _i, _i, _f, _i, _vp, _vp]),

@@ -23,7 +23,45 @@ struct AttnArgs {
   // 2 * cta + {0: first, 1: last tail segment of the CTA} and attn_merge_kernel adds the partials up in CTA order.
   int full_waves, per_cta, tail_steps, merge_grid;
   float *part_o, *part_l, *part_m;
+  // attn_split.cu only: sequence-parallel global attention over a K|V buffer that peer GPUs are still filling
+  // (capi.cu, wm_p2p_*).  Logical key tile j reads physical tile (j + kv_rot) % n_kv, so every rank starts with the
+  // keys it produced itself; shard r (rows [r * shard_rows, (r+1) * shard_rows)) may be read once
+  // (int)(flags[r] - epoch) >= 0.  shard_rows == 0: every key is present at launch (flags unused).
+  int kv_rot, shard_rows, self_rank;
+  unsigned epoch;
+  const unsigned* flags;
+  unsigned* err;  // set to 1 when a shard did not arrive within kGatherTimeoutNs (the launch then finishes on stale keys)
 };
+constexpr unsigned long long kGatherTimeoutNs = 4000000000ull;
+
+__device__ __forceinline__ int attn_phys_tile(const AttnArgs& a, int j) {
+  const int jp = j + a.kv_rot;
+  return jp >= a.n_kv ? jp - a.n_kv : jp;
+}
+
+// Producer side: block until every shard that key tile `jp` touches has arrived.  `have` caches the answer per shard.
+__device__ __forceinline__ void attn_wait_shards(const AttnArgs& a, int jp, unsigned& have) {
+  const int row0 = jp * 128, row1 = min(row0 + 127, a.Lkv - 1);
+  for (int r = row0 / a.shard_rows; r <= row1 / a.shard_rows; ++r) {
+    if ((have >> r) & 1u) continue;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+      unsigned v;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flags + r) : "memory");
+      if (static_cast<int>(v - a.epoch) >= 0) break;
+      __nanosleep(256);
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > kGatherTimeoutNs) {
+        atomicExch(a.err, 1u);
+        break;
+      }
+    }
+    asm volatile("fence.proxy.async;" ::: "memory");  // the keys were written by a peer's copy engine; TMA reads them next
+    have |= 1u << r;
+  }
+}
 
 // The segment sequence of one CTA; producer, MMA issuer and softmax warps walk it in lockstep.
 struct AttnSched {

@@ -93,6 +93,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
       // -------------------------------------------------------------- TMA producer
       if (elect_one()) {
         uint32_t kvit = 0, icount = 0;
+        unsigned have = a.shard_rows > 0 ? (1u << a.self_rank) : 0xffffffffu;  // shards known to be present
         AttnSched sched(a);
         for (int item, kv0, kv1, slot; sched.next(a, item, kv0, kv1, slot); ++icount) {
           const int per_head = a.batch * a.n_qpairs;
@@ -105,12 +106,14 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           tma_load_3d(sQ + (2 * qb + 1) * ATT_TILE, &tmQ, &q_full[qb], h * 64, q0 + 128, b, kEvictFirst);
           for (int j = kv0; j < kv1; ++j, ++kvit) {
             const uint32_t s = kvit % ST, ph = (kvit / ST) & 1;
+            const int jp = attn_phys_tile(a, j);
+            if (have != 0xffffffffu) attn_wait_shards(a, jp, have);
             mbar_wait(&k_empty[s], ph ^ 1);
             mbar_arrive_expect_tx(&k_full[s], ATT_TILE);
-            tma_load_3d(sK + s * ATT_TILE, &tmK, &k_full[s], h * 64, j * 128, b, kEvictLast);
+            tma_load_3d(sK + s * ATT_TILE, &tmK, &k_full[s], h * 64, jp * 128, b, kEvictLast);
             mbar_wait(&v_empty[s], ph ^ 1);
             mbar_arrive_expect_tx(&v_full[s], ATT_TILE);
-            tma_load_3d(sV + s * ATT_TILE, &tmV, &v_full[s], h * 64, j * 128, b, kEvictLast);
+            tma_load_3d(sV + s * ATT_TILE, &tmV, &v_full[s], h * 64, jp * 128, b, kEvictLast);
           }
         }
       }
@@ -230,8 +233,8 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
               __syncwarp();
               if (lane == 0) mbar_arrive(&s_free[qt]);  // the MMA warp may overwrite S_qt once both halves have arrived
             }
-            if (ragged && j == a.n_kv - 1) {
-              const int valid = a.Lkv - j * 128 - hf * 64 - i * 32;
+            if (ragged && attn_phys_tile(a, j) == a.n_kv - 1) {
+              const int valid = a.Lkv - (a.n_kv - 1) * 128 - hf * 64 - i * 32;
 #pragma unroll
               for (int c = 0; c < 32; ++c)
                 if (c >= valid) v[c] = 0xc2f00000u;  // -120: P = 2^-120, >= 2^40 below any real term (logit bound <= 80)
@@ -259,8 +262,8 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           tcgen05_fence_before();
           __syncwarp();
               if (lane == 0) mbar_arrive(&s_free[qt]);  // the MMA warp may overwrite S_qt once both halves have arrived
-          if (ragged && j == a.n_kv - 1) {
-            const int valid = a.Lkv - j * 128 - hf * 64;
+          if (ragged && attn_phys_tile(a, j) == a.n_kv - 1) {
+            const int valid = a.Lkv - (a.n_kv - 1) * 128 - hf * 64;
 #pragma unroll
             for (int i = 0; i < 2; ++i)
 #pragma unroll
@@ -441,7 +444,16 @@ size_t attn_partial_bytes(int sm_count) { return (size_t)2 * sm_count * kAttnSlo
 // merged by attn_merge_kernel; without one every CTA gets whole items.
 wm_status flash_attention_split(cudaStream_t st, int sm_count, const CUtensorMap& tq, const CUtensorMap& tk,
                                 const CUtensorMap& tv, const CUtensorMap& to, AttnArgs a, int variant, void* out, int ldo,
-                                float* partial_ws, size_t partial_ws_bytes) {
+                                float* partial_ws, size_t partial_ws_bytes, const AttnGather* gather) {
+  a.kv_rot = 0, a.shard_rows = 0, a.self_rank = 0, a.epoch = 0, a.flags = nullptr, a.err = nullptr;
+  if (gather) {
+    WM_CHECK(gather->shard_rows > 0 && gather->flags && gather->err && gather->self_rank >= 0 && gather->self_rank < 32 &&
+                 (long long)gather->shard_rows * (gather->self_rank + 1) <= a.Lkv && a.batch == 1,
+             "flash_attention: bad gather description");
+    a.shard_rows = gather->shard_rows, a.self_rank = gather->self_rank, a.epoch = gather->epoch;
+    a.flags = gather->flags, a.err = gather->err;
+    a.kv_rot = (int)(((long long)gather->self_rank * gather->shard_rows) / 128);  // own shard first (floor: a tile that
+  }                                                                               // straddles two shards waits for both)
   const bool balance = partial_ws != nullptr && partial_ws_bytes >= attn_partial_bytes(sm_count) && a.total_items > 0;
   const int grid = a.total_items < sm_count ? a.total_items : sm_count;
   a.full_waves = a.total_items / grid;

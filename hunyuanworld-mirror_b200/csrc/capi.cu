@@ -108,6 +108,35 @@ static wm_status nccl_open(const char* path, NcclApi* api) {
   return WM_OK;
 }
 
+// Sequence-parallel K|V exchange over peer memory (NVLink), overlapped with the attention that consumes it.
+// Every rank owns one cudaMalloc'ed block [4096 B header | buffer 0 | buffer 1]; header = arrival words flags[r]
+// (one per source rank) and an error word at [64].  Buffer b holds the gathered K|V rows of the global block whose
+// sequence number (epoch) has parity b: rank r's rows at r * T.  After its QKV GEMM a rank pushes its shard into every
+// peer's buffer with the copy engines and then raises flags[self] = epoch there; the attention kernel scans its own
+// shard first and waits per shard (attn_common.cuh).  Two buffers make acknowledgements unnecessary: a rank can only
+// push epoch e after it attended epoch e-1, which needed every peer's e-1 shard, which each peer sent after it had
+// finished attending e-2 -- the last reader of buffer e & 1.
+constexpr int kP2pHeader = 4096;
+constexpr int kP2pMaxWorld = 32;
+struct PeerGather {
+  bool on = false;
+  int max_rows = 0;
+  uint8_t* base = nullptr;
+  size_t buf_bytes = 0;
+  uint8_t* peer[kP2pMaxWorld] = {};
+  cudaStream_t comm = nullptr;
+  cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
+  unsigned epoch = 0;
+  bool used = false;  // pushes were enqueued since the last join with the forward's stream
+};
+
+__global__ void p2p_flag_kernel(unsigned* flag, unsigned epoch) {
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(epoch) : "memory");
+  }
+}
+
 }  // namespace wm
 
 struct wm_handle {
@@ -122,6 +151,8 @@ struct wm_handle {
   wm::NcclApi nccl;
   wm::nccl_comm_t comm = nullptr;
   int rank = 0, world = 1;
+  wm::PeerGather p2p;
+  int sp_mode = 1;  // 1: peer-memory push overlapped with attention when wm_p2p_attach succeeded; 0: ncclAllGather
   // opt-in per-kernel-class timing (CUDA events on the forward's stream) and a launch counter
   unsigned prof_mask = 0;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_ev[WM_PROF_CLASSES];
@@ -250,7 +281,14 @@ struct ProfScope {
 static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const BlockShape& s, const Workspace& ws,
                            float* x, float* out2, int out2_col, bool gather) {
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n1w, w.n1b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
-  __nv_bfloat16* kv_local = ws.kv + (size_t)s.kv_row0 * 2 * kEmbed;
+  const bool p2p = gather && h->p2p.on && h->sp_mode == 1 && s.T <= h->p2p.max_rows;
+  __nv_bfloat16* kv_all = ws.kv;
+  unsigned epoch = 0;
+  if (p2p) {
+    epoch = ++h->p2p.epoch;
+    kv_all = reinterpret_cast<__nv_bfloat16*>(h->p2p.base + kP2pHeader + (size_t)(epoch & 1u) * h->p2p.buf_bytes);
+  }
+  __nv_bfloat16* kv_local = kv_all + (size_t)s.kv_row0 * 2 * kEmbed;
   // QK-LayerNorm bounds the logits (|q . k| <= |q| |k|, both norms fixed by the norm weights): when the bound is
   // small the softmax needs no running maximum, so q is pre-multiplied by scale * log2(e) and P = 2^(q . k).
   const bool bounded = h->attn_allow_bounded && w.logit_bound > 0.f && w.logit_bound <= kMaxLogitBound;
@@ -258,17 +296,38 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
   WM_OP(WM_PROF_QKV, gemm_qkv(st, ws.ln, kEmbed, w.qkv_w, w.qkv_b, w.qn_w, w.qn_b, w.kn_w, w.kn_b, 1e-5f,
                               s.rope ? h->rope_cos : nullptr, s.rope ? h->rope_sin : nullptr, s.tokens_per_view,
                               s.patch_start, s.grid_w, q_scale, s.T, ws.q, kv_local));
-  if (gather) {
+  AttnGather ag{};
+  if (p2p) {
+    // push this rank's K|V rows into every peer's buffer (copy engines, side stream) while attention starts on them
+    PeerGather& g = h->p2p;
+    const size_t bytes = (size_t)s.T * 2 * kEmbed * 2;
+    const size_t off = kP2pHeader + (size_t)(epoch & 1u) * g.buf_bytes + (size_t)h->rank * bytes;
+    WM_CUDA(cudaEventRecord(g.ev_ready, st));
+    WM_CUDA(cudaStreamWaitEvent(g.comm, g.ev_ready, 0));
+    {
+      ProfScope _ps(h, g.comm, WM_PROF_ALLGATHER);
+      for (int k = 1; k < h->world; ++k) {
+        const int peer = (h->rank - k + h->world) % h->world;  // the peer that reaches this shard first goes first
+        WM_CUDA(cudaMemcpyAsync(g.peer[peer] + off, kv_local, bytes, cudaMemcpyDefault, g.comm));
+        p2p_flag_kernel<<<1, 32, 0, g.comm>>>(reinterpret_cast<unsigned*>(g.peer[peer]) + h->rank, epoch);
+        WM_LAUNCH_CHECK();
+      }
+    }
+    g.used = true;
+    ag.shard_rows = s.T, ag.self_rank = h->rank, ag.epoch = epoch;
+    ag.flags = reinterpret_cast<const unsigned*>(g.base);
+    ag.err = reinterpret_cast<unsigned*>(g.base) + 64;
+  } else if (gather) {
     ProfScope _ps(h, st, WM_PROF_ALLGATHER);
     const size_t bytes = (size_t)s.T * 2 * kEmbed * 2;
     const int r = h->nccl.AllGather(kv_local, ws.kv, bytes, /*ncclChar*/ 0, h->comm, st);
     if (r != 0) return fail(WM_ERR_NCCL, "ncclAllGather: %s", h->nccl.GetErrorString(r));
   }
-  const __nv_bfloat16* kbase = gather ? ws.kv : kv_local;
+  const __nv_bfloat16* kbase = gather ? kv_all : kv_local;
   WM_OP(s.global ? WM_PROF_ATTN_GLOBAL : WM_PROF_ATTN_LOCAL,
         flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
                         0.125f, bounded ? h->attn_bounded_variant : h->attn_general_variant,
-                        h->attn_balance ? ws.attn_part : nullptr, attn_partial_bytes(kNumSms)));
+                        h->attn_balance ? ws.attn_part : nullptr, attn_partial_bytes(kNumSms), p2p ? &ag : nullptr));
   WM_OP(WM_PROF_PROJ, gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x,
                                        kEmbed));
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
@@ -300,6 +359,11 @@ static wm_status run_stack(wm_handle* h, cudaStream_t st, const Workspace& ws, i
     if (next_out < h->cfg.n_intermediate && h->cfg.intermediate[next_out] == i) o = out[next_out++];
     WM_TRY(run_block(h, st, h->frame[i], fs, ws, ws.x, o, 0, false));
     WM_TRY(run_block(h, st, h->global[i], gs, ws, ws.x, o, kEmbed, h->world > 1));
+  }
+  if (h->p2p.used) {  // the caller's stream must also cover the pushes this rank still has in flight
+    WM_CUDA(cudaEventRecord(h->p2p.ev_done, h->p2p.comm));
+    WM_CUDA(cudaStreamWaitEvent(st, h->p2p.ev_done, 0));
+    h->p2p.used = false;
   }
   return WM_OK;
 }
@@ -352,6 +416,18 @@ static wm_status run_embed(wm_handle* h, cudaStream_t st, const Workspace& ws, c
   return WM_OK;
 }
 
+static void p2p_release(wm_handle* h) {
+  PeerGather& g = h->p2p;
+  if (g.comm) cudaStreamSynchronize(g.comm);
+  for (int r = 0; r < kP2pMaxWorld; ++r)
+    if (g.peer[r] && g.peer[r] != g.base) cudaIpcCloseMemHandle(g.peer[r]);
+  if (g.base) cudaFree(g.base);
+  if (g.ev_ready) cudaEventDestroy(g.ev_ready);
+  if (g.ev_done) cudaEventDestroy(g.ev_done);
+  if (g.comm) cudaStreamDestroy(g.comm);
+  g = PeerGather{};
+}
+
 }  // namespace wm
 
 using namespace wm;
@@ -400,6 +476,7 @@ void wm_destroy(wm_handle* h) {
   if (h->rope_sin) cudaFree(h->rope_sin);
   if (h->dino_table) cudaFree(h->dino_table);
   if (h->comm && h->nccl.CommDestroy) h->nccl.CommDestroy(h->comm);
+  p2p_release(h);
   for (auto& v : h->prof_ev)
     for (auto& e : v) {
       cudaEventDestroy(e.first);
@@ -666,6 +743,84 @@ wm_status wm_nccl_allgather(wm_handle* h, wm_stream stream, void* buf, size_t by
   return WM_OK;
 }
 
+// ---------------------------------------------------------------------------------------------- peer-memory gather
+wm_status wm_p2p_alloc(wm_handle* h, int rank, int world, int max_rows_per_rank, void* ipc_handle_64) {
+  WM_CHECK(h && ipc_handle_64 && world >= 2 && world <= kP2pMaxWorld && rank >= 0 && rank < world && max_rows_per_rank > 0,
+           "wm_p2p_alloc: bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  int sms = 0;
+  WM_TRY(require_sm100(&sms));
+  WM_CUDA(cudaDeviceSynchronize());
+  p2p_release(h);
+  PeerGather& g = h->p2p;
+  g.max_rows = max_rows_per_rank;
+  g.buf_bytes = (size_t)world * max_rows_per_rank * 2 * kEmbed * 2;
+  WM_CUDA(cudaMalloc(&g.base, kP2pHeader + 2 * g.buf_bytes));
+  WM_CUDA(cudaMemset(g.base, 0, kP2pHeader));
+  cudaIpcMemHandle_t mh;
+  WM_CUDA(cudaIpcGetMemHandle(&mh, g.base));
+  memcpy(ipc_handle_64, &mh, 64);
+  h->rank = rank, h->world = world;
+  return WM_OK;
+}
+
+wm_status wm_p2p_attach(wm_handle* h, const void* ipc_handles_all) {
+  WM_CHECK(h && ipc_handles_all, "wm_p2p_attach: null argument");
+  PeerGather& g = h->p2p;
+  if (!g.base) return fail(WM_ERR_STATE, "wm_p2p_attach: call wm_p2p_alloc first");
+  for (int r = 0; r < h->world; ++r) {
+    if (r == h->rank) {
+      g.peer[r] = g.base;
+      continue;
+    }
+    cudaIpcMemHandle_t mh;
+    memcpy(&mh, static_cast<const uint8_t*>(ipc_handles_all) + 64 * r, 64);
+    void* ptr = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&ptr, mh, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(WM_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d): %s (peers must sit on one NVLink domain)", r, cudaGetErrorString(e));
+    }
+    g.peer[r] = static_cast<uint8_t*>(ptr);
+  }
+  int lo = 0, hi = 0;
+  WM_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  WM_CUDA(cudaStreamCreateWithPriority(&g.comm, cudaStreamNonBlocking, hi));
+  WM_CUDA(cudaEventCreateWithFlags(&g.ev_ready, cudaEventDisableTiming));
+  WM_CUDA(cudaEventCreateWithFlags(&g.ev_done, cudaEventDisableTiming));
+  g.epoch = 0;
+  g.on = true;
+  return WM_OK;
+}
+
+wm_status wm_p2p_status(wm_handle* h, int* enabled, int* timed_out) {
+  WM_CHECK(h && enabled && timed_out, "wm_p2p_status: null argument");
+  *enabled = h->p2p.on && h->sp_mode == 1;
+  *timed_out = 0;
+  if (h->p2p.base) {
+    unsigned e = 0;
+    WM_CUDA(cudaMemcpy(&e, h->p2p.base + 64 * sizeof(unsigned), sizeof(e), cudaMemcpyDeviceToHost));
+    *timed_out = (int)e;
+  }
+  return WM_OK;
+}
+
+wm_status wm_flash_attn_gathered(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                                 int ldo, int Lq, int Lkv, int heads, float scale, int variant, void* workspace,
+                                 size_t workspace_bytes, int shard_rows, int self_rank, const unsigned* flags,
+                                 unsigned epoch, unsigned* err) {
+  AttnGather ag{shard_rows, self_rank, epoch, flags, err};
+  return flash_attention(static_cast<cudaStream_t>(stream), q, ldq, k, v, ldkv, o, ldo, 1, Lq, Lkv, heads, scale, variant,
+                         static_cast<float*>(workspace), workspace_bytes, &ag);
+}
+
+wm_status wm_p2p_raise_flag(wm_stream stream, unsigned* flag, unsigned epoch) {
+  WM_CHECK(flag, "wm_p2p_raise_flag: null flag");
+  p2p_flag_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(flag, epoch);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
 // ---------------------------------------------------------------------------------------------- micro-ops
 wm_status wm_layernorm(wm_stream stream, const float* x, const float* w, const float* b, float eps, int rows, void* y,
                        int out_f32) {
@@ -700,6 +855,9 @@ wm_status wm_set_int(wm_handle* h, const char* name, int value) {
     h->attn_allow_bounded = value != 0;
   } else if (n == "attn_balance") {
     h->attn_balance = value != 0;
+  } else if (n == "sp_mode") {
+    WM_CHECK(value == 0 || value == 1, "sp_mode must be 0 (ncclAllGather) or 1 (peer-memory push)");
+    h->sp_mode = value;
   } else {
     return fail(WM_ERR_INVALID, "wm_set_int: unknown option %s", name);
   }

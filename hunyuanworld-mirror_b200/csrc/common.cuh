@@ -25,6 +25,15 @@ constexpr int kNumSms = 148;
 
 char* error_buffer();  // thread-local, 512 bytes (capi.cu)
 
+// What flash_attention() needs to know about a K|V gather that is still in flight when it launches (nullptr: none):
+// shard r of the key buffer may be read once (int)(flags[r] - epoch) >= 0 (attn_common.cuh, capi.cu wm_p2p_*).
+struct AttnGather {
+  int shard_rows, self_rank;
+  unsigned epoch;
+  const unsigned* flags;
+  unsigned* err;
+};
+
 inline wm_status fail(wm_status code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);

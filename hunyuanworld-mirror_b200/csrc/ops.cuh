@@ -17,7 +17,7 @@ wm_status gemm_table(cudaStream_t st, const void* A, int lda, const void* W, int
                      int table_period, int M, int N, int K, float* out, int ldo);
 wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
                           int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, float* partial_ws,
-                          size_t partial_ws_bytes);
+                          size_t partial_ws_bytes, const AttnGather* gather = nullptr);
 size_t attn_partial_bytes(int sm_count);  // workspace that lets the split-row kernel balance (item, kv tile) steps
 wm_status umma_probe(cudaStream_t st, const void* p, const void* v, float* d, int mode, uint32_t v_lbo, uint32_t v_sbo);
 wm_status layernorm(cudaStream_t st, const float* x, const float* w, const float* b, float eps, int rows,

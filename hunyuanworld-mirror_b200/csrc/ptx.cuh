@@ -14,10 +14,10 @@
 
 namespace wm {
 
-// Bounded spin: a lost arrive must never hang the GPU box (a hang is a strike).  ~2^28 polls of
-// a try_wait that itself sleeps up to the HW time limit is seconds; then we trap.
-#ifndef WM_MBAR_SPIN_LIMIT
-#define WM_MBAR_SPIN_LIMIT (1u << 18)
+// Bounded wait: a lost arrive must never hang the GPU box (a hang is a strike).  After 3 ticks of the upper
+// %globaltimer word (8.6 - 12.9 s) mbar_wait traps.
+#ifndef WM_MBAR_TIMEOUT_TICKS
+#define WM_MBAR_TIMEOUT_TICKS 3u
 #endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -66,14 +66,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t spins = 0;
+  uint32_t spins = 0, t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > WM_MBAR_SPIN_LIMIT) {
+    if ((++spins & 0xfffu) == 0) {
+      // time-based bound (seconds, not polls): a rank of a sequence-parallel job may legitimately wait for a slow
+      // peer's keys (attn_common.cuh gives up after 4 s), a lost arrive must still not hang the box
+      uint32_t t;
+      asm volatile("mov.u32 %0, %%globaltimer_hi;" : "=r"(t));  // units of 2^32 ns = 4.29 s
+      if (t0 == 0) {
+        t0 = t | 0x80000000u;
+      } else if (((t | 0x80000000u) - t0) >= WM_MBAR_TIMEOUT_TICKS) {
 #ifdef WM_MBAR_DEBUG  // a printf call site costs the hot loops registers (caller-saved state around the call)
-      printf("wm_b200: mbarrier timeout block=(%d,%d,%d) thread=%d bar=%u parity=%u\n", blockIdx.x, blockIdx.y,
-             blockIdx.z, threadIdx.x, smem_u32(bar), parity);
+        printf("wm_b200: mbarrier timeout block=(%d,%d,%d) thread=%d bar=%u parity=%u\n", blockIdx.x, blockIdx.y,
+               blockIdx.z, threadIdx.x, smem_u32(bar), parity);
 #endif
-      __trap();  // surfaces as a launch failure on the host instead of a hung GPU
+        __trap();  // surfaces as a launch failure on the host instead of a hung GPU
+      }
     }
   }
 }

@@ -118,6 +118,18 @@ wm_status wm_nccl_unique_id(const char* nccl_lib, void* unique_id_128);
 wm_status wm_nccl_init(wm_handle* h, const char* nccl_lib, const void* unique_id_128, int rank, int world);
 wm_status wm_nccl_allgather(wm_handle* h, wm_stream stream, void* buf, size_t bytes_per_rank); /* in place, test hook */
 
+/* Peer-memory variant of the same exchange (default once attached; wm_set_int "sp_mode" 0 selects ncclAllGather):
+ * after its QKV GEMM every rank pushes its K|V rows into each peer's gather buffer with the copy engines on a side
+ * stream and raises an arrival word there; the attention kernel starts on the rank's own keys and waits per shard,
+ * so the transfer overlaps the math.  Two buffers alternate per global block (no acknowledgement round trip).
+ * wm_p2p_alloc: allocate this rank's block for up to max_rows_per_rank tokens per rank and return its
+ * cudaIpcMemHandle_t (64 bytes); exchange the handles (rank order) and hand all of them to wm_p2p_attach.
+ * Every rank must run the same sequence of forwards.  wm_p2p_status: *timed_out != 0 if a shard ever failed to
+ * arrive within 4 s (the forward then finished on stale keys; treat as an error). */
+wm_status wm_p2p_alloc(wm_handle* h, int rank, int world, int max_rows_per_rank, void* ipc_handle_64);
+wm_status wm_p2p_attach(wm_handle* h, const void* ipc_handles_all /* world x 64 bytes */);
+wm_status wm_p2p_status(wm_handle* h, int* enabled, int* timed_out);
+
 /* ---- micro-ops (unit parity + microbenchmarks); C = 1024, head_dim = 64 ----------------------------------- */
 /* nn.LayerNorm(1024) (block.py:44,61): x [rows,1024] fp32 -> y [rows,1024] bf16 (or fp32 when out_f32). */
 wm_status wm_layernorm(wm_stream stream, const float* x, const float* w, const float* b, float eps, int rows, void* y,
@@ -157,6 +169,14 @@ wm_status wm_flash_attn_ws(wm_stream stream, const void* q, int ldq, const void*
                            int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, void* workspace,
                            size_t workspace_bytes);
 size_t wm_attn_workspace_bytes(void);
+/* wm_flash_attn_ws (batch 1, variants 4-12) over a key buffer of Lkv / shard_rows shards that may still be filling:
+ * keys are scanned starting with shard `self_rank`; shard r is read only once (int)(flags[r] - epoch) >= 0
+ * (flags: device words written by wm_p2p_raise_flag or a peer's push; *err is set to 1 on a 4 s time-out). */
+wm_status wm_flash_attn_gathered(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                                 int ldo, int Lq, int Lkv, int heads, float scale, int variant, void* workspace,
+                                 size_t workspace_bytes, int shard_rows, int self_rank, const unsigned* flags,
+                                 unsigned epoch, unsigned* err);
+wm_status wm_p2p_raise_flag(wm_stream stream, unsigned* flag, unsigned epoch);
 /* Single-tile probe: d [128,64] fp32 = p [128,128] bf16 x v [128,64] bf16; mode 0 = P in smem, 1 = P in TMEM. */
 wm_status wm_umma_probe(wm_stream stream, const void* p, const void* v, float* d, int mode, unsigned v_lbo,
                         unsigned v_sbo);

@@ -1,0 +1,64 @@
+"""Run under torchrun on >= 2 B200s (tests/test_sp_gpu.py launches it): sequence-parallel forward with the
+peer-memory K|V exchange against (a) the ncclAllGather path and (b) a single-GPU forward of all views."""
+import importlib
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    pkg = importlib.import_module("hunyuanworld-mirror_b200")
+    W, capi = pkg.weights, pkg.capi
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    depth, dino_depth, per, H, Wd = 3, 1, 2, 126, 154  # P = 7 + 9*11 = 106 rows/view: shards of 212 rows, not tile-aligned
+    sd = W.synthetic_state_dict(seed=0, depth=depth, dino_depth=dino_depth)
+    m = pkg.B200VisualGeometryTransformer(depth=depth, dino_depth=dino_depth, intermediate_idxs=(0, 2))
+    m.load_state_dict(sd)
+    m.init_sequence_parallel()
+    imgs = W.synthetic_images(per * world, H, Wd, seed=1)
+    pri = W.synthetic_priors(per * world, H, Wd, seed=2)
+    sl = slice(rank * per, (rank + 1) * per)
+    mine = imgs[:, sl].to(dev)
+    pmine = tuple(p[:, sl].to(dev) for p in pri)
+    res = {}
+    for mode in (1, 0, 1):
+        capi.check(capi.lib().wm_set_int(m._handle, b"sp_mode", mode))
+        for _ in range(2):  # twice: epochs and buffer parity continue across forwards
+            outs, _ = m(mine, pmine, cond_flags=[1, 1, 1])
+        torch.cuda.synchronize()
+        res[mode] = [o.clone() for o in outs]
+    enabled, timed_out = m.peer_gather_status()
+    assert enabled and not timed_out, (enabled, timed_out)
+    ok = True
+    for a, b in zip(res[1], res[0]):
+        e = ((a - b).norm() / b.norm()).item()
+        ok &= e < 2e-3
+        print(f"rank {rank}: p2p vs nccl rel fro {e:.3e}", flush=True)
+    # single-GPU forward of all views on this rank's GPU
+    ref = pkg.B200VisualGeometryTransformer(depth=depth, dino_depth=dino_depth, intermediate_idxs=(0, 2))
+    ref.load_state_dict(sd)
+    full, _ = ref(imgs.to(dev), tuple(p.to(dev) for p in pri), cond_flags=[1, 1, 1])
+    torch.cuda.synchronize()
+    for a, f in zip(res[1], full):
+        e = ((a - f[:, sl]).norm() / f[:, sl].norm()).item()
+        ok &= e < 2e-3
+        print(f"rank {rank}: p2p (world {world}) vs single GPU rel fro {e:.3e}", flush=True)
+    t = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    if t.item() != 1:
+        raise SystemExit(1)
+    if rank == 0:
+        print("SP_CHECK_OK", flush=True)
+
+
+if __name__ == "__main__":
+    main()

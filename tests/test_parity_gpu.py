@@ -354,3 +354,55 @@ def test_north_star_tolerances_end_to_end(model_full):
     assert report["depth"][0] <= min(2e-2, 1.25 * 1.33e-2), report
     assert ang <= 1e-3, ang
     assert trel <= 1e-2, trel
+
+
+def _bf16_rand(shape, seed, scale=1.0):
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(torch.bfloat16).cuda()
+
+
+@pytest.mark.parametrize("variant,self_rank,late", [(4, 2, False), (10, 0, False), (10, 3, True), (4, 1, True)])
+def test_gathered_attention_scan_order_and_flags(variant, self_rank, late):
+    """Sequence-parallel global attention reads a key buffer that peers are still filling: keys are scanned from the
+    rank's own shard on (rotation), each other shard only after its arrival word reached the epoch.  Shards of 900
+    rows do not align with the 128-row key tiles, Lkv = 3600 leaves a ragged last tile.  `late`: the words are raised
+    from a second stream while the kernel is already waiting.  Reference: the same kernel on complete keys."""
+    lib = capi.lib()
+    heads, Lq, shard, world = 4, 700, 900, 4
+    Lkv = shard * world
+    scale = 0.125 * (1.4426950408889634 if variant >= 8 else 1.0)
+    q = _bf16_rand((Lq, heads * 64), 1, 0.25 if variant >= 8 else 1.0)
+    kv = _bf16_rand((Lkv, 2 * heads * 64), 2)
+    o_ref = torch.empty(Lq, heads * 64, dtype=torch.bfloat16, device="cuda")
+    o = torch.zeros_like(o_ref)
+    ws = torch.empty(lib.wm_attn_workspace_bytes(), dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    k_ptr, v_ptr = kv.data_ptr(), kv.data_ptr() + heads * 64 * 2
+    capi.check(lib.wm_flash_attn_ws(st, q.data_ptr(), heads * 64, k_ptr, v_ptr, 2 * heads * 64, o_ref.data_ptr(), heads * 64,
+                                    1, Lq, Lkv, heads, scale, variant, ws.data_ptr(), ws.numel()))
+    words = torch.zeros(128, dtype=torch.int32, device="cuda")  # flags[0..63], err at [64]
+    epoch = 7
+    # two non-default streams, created before the launch: the legacy default stream would serialise the side stream
+    # behind the waiting kernel, and stream creation may synchronise with running kernels
+    main, side = torch.cuda.Stream(), torch.cuda.Stream()
+    if not late:
+        words[:world] = epoch
+    torch.cuda.synchronize()
+    capi.check(lib.wm_flash_attn_gathered(main.cuda_stream, q.data_ptr(), heads * 64, k_ptr, v_ptr, 2 * heads * 64, o.data_ptr(),
+                                          heads * 64, Lq, Lkv, heads, scale, variant, ws.data_ptr(), ws.numel(), shard,
+                                          self_rank, words.data_ptr(), epoch, words.data_ptr() + 64 * 4))
+    if late:
+        with torch.cuda.stream(side):
+            for r in range(world):
+                torch.cuda._sleep(2_000_000)  # ~1 ms apart
+                if r != self_rank:
+                    capi.check(lib.wm_p2p_raise_flag(side.cuda_stream, words.data_ptr() + 4 * r, epoch))
+        side.synchronize()
+    torch.cuda.synchronize()
+    assert int(words[64].item()) == 0, "a shard timed out"
+    a, b = o.float().cpu(), o_ref.float().cpu()
+    assert torch.isfinite(a).all()
+    err = (a - b).abs().max().item()
+    print(f"gathered attention variant {variant} self {self_rank} late {late}: max abs diff {err:.3e}")
+    assert err <= 2e-2 * b.abs().max().item() + 1e-3  # same math, different summation order (bf16 output)
