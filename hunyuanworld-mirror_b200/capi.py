@@ -66,6 +66,12 @@ SIGNATURES = {
     "wm_umma_probe": (C.c_int, [_vp, _vp, _vp, _fp, _i, _u, _u]),
     "wm_patch_gather": (C.c_int, [_vp, _fp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "wm_rope_tables": (None, [_i, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "wm_conv2d_nhwc": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _vp, _i, _i, _fp, _vp, _i, _vp, _i, _vp]),
+    "wm_conv2d_final": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _vp, _fp, _fp, _fp, _i, _i, _fp, _fp]),
+    "wm_layernorm_rows": (C.c_int, [_vp, _fp, _fp, _fp, _f, C.c_longlong, _i, _i, _i, _i, _vp]),
+    "wm_bilinear_nhwc": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _i, _fp, _fp, _vp]),
+    "wm_pixel_shuffle": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "wm_im2col_s2": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "wm_pack_bf16": (C.c_int, [_vp, _fp, C.c_longlong, _i, _i, _vp]),
 }
 

@@ -927,6 +927,44 @@ void wm_rope_tables(int max_pos, float* cos_host, float* sin_host) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------- prediction heads
+wm_status wm_conv2d_nhwc(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* weight, int taps, int Cout,
+                         const float* bias, const void* res1, int res1_bcast, const void* res2, int relu, void* out) {
+  return conv2d_nhwc(static_cast<cudaStream_t>(stream), in, n, H, W, Cin, weight, taps, Cout, bias, res1, res1_bcast, res2, relu,
+                     out);
+}
+
+wm_status wm_conv2d_final(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
+                          const float* w2, const float* b2, int od, int act, float* pred, float* conf) {
+  return conv2d_final(static_cast<cudaStream_t>(stream), in, n, H, W, Cin, w1, b1, w2, b2, od, act, pred, conf);
+}
+
+wm_status wm_layernorm_rows(wm_stream stream, const float* x, const float* w, const float* b, float eps, long long rows,
+                            int rows_per_group, int in_group_rows, int in_offset, int C, void* y) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return ln_rows(static_cast<cudaStream_t>(stream), x, w, b, eps, rows, rows_per_group, in_group_rows, in_offset, C, y);
+}
+
+wm_status wm_bilinear_nhwc(wm_stream stream, const void* in, int n, int Hi, int Wi, int C, int Ho, int Wo, const float* pos_u,
+                           const float* pos_v, void* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return bilinear_nhwc(static_cast<cudaStream_t>(stream), in, n, Hi, Wi, C, Ho, Wo, pos_u, pos_v, out);
+}
+
+wm_status wm_pixel_shuffle(wm_stream stream, const void* in, int n, int Hi, int Wi, int C, int k, void* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return pixel_shuffle(static_cast<cudaStream_t>(stream), in, n, Hi, Wi, C, k, out);
+}
+
+wm_status wm_im2col_s2(wm_stream stream, const void* in, int n, int Hi, int Wi, int C, void* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return im2col_s2(static_cast<cudaStream_t>(stream), in, n, Hi, Wi, C, out);
+}
+
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
   int sms;
   WM_TRY(require_sm100(&sms));

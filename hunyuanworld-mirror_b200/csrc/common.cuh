@@ -86,6 +86,15 @@ inline wm_status tmap_3d(CUtensorMap* out, CUtensorMapDataType dtype, int elem_b
   return tmap_encode(out, dtype, 3, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
+// 4D NHWC activations [n, H, W, C] (C contiguous); box = [box_c, box_w, box_h, 1]; SWIZZLE_128B (box_c * elem = 128 B)
+inline wm_status tmap_nhwc(CUtensorMap* out, CUtensorMapDataType dtype, int elem_bytes, const void* base, uint64_t n,
+                           uint64_t H, uint64_t W, uint64_t C, uint32_t box_c, uint32_t box_w, uint32_t box_h) {
+  uint64_t dims[4] = {C, W, H, n};
+  uint64_t strides[3] = {C * elem_bytes, W * C * elem_bytes, H * W * C * elem_bytes};
+  uint32_t box[4] = {box_c, box_w, box_h, 1};
+  return tmap_encode(out, dtype, 4, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
 wm_status require_sm100(int* sm_count);
 
 // Launch with programmatic stream serialization (the kernel must call pdl_wait() before touching global data).

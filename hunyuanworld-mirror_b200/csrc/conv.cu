@@ -1,0 +1,344 @@
+// Implicit-GEMM convolution on tcgen05 for the DPT prediction heads (SURVEY.md section 8f row 1;
+// reference: src/models/heads/dense_head.py:164-344).  The reference runs its heads with autocast disabled
+// (worldmirror.py:146), i.e. in fp32; bf16 activations measured 1.5e-2 relative error on pts3d (the inv_log output
+// amplifies), above the stated 1e-2, so activations and weights stay fp32 in memory and the tensor cores run
+// kind::tf32 (10-bit mantissa operands, fp32 accumulation).  Every producer rounds what it stores to TF32 (nearest),
+// weights are rounded at load time: the MMA's own operand truncation is then exact and no bias accumulates.  Activations are NHWC, so a 3x3 convolution is a GEMM
+//     acc[pixel, co] (fp32, TMEM) = sum over (tap, ci) of  in[pixel + tap offset, ci] * w[co, tap, ci]
+// whose A operand needs no im2col buffer: the producer issues one 4D TMA tile load per (tap, 32-channel block) with
+// the tile origin shifted by the tap offset, and TMA's out-of-bounds zero fill IS the convolution's zero padding.
+// A tile = 8 x 16 pixels x 32 channels (fp32) = 128 rows of 128 B in the SWIZZLE_128B layout the UMMA descriptors expect.
+//
+// One CTA per SM, persistent over (image, tile row, tile column, Cout tile), 256 threads:
+//   warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (one elected lane), warp 2 = TMEM allocator, warp 3 idle,
+//   warps 4-7 = epilogue (thread == pixel == accumulator row == TMEM lane).
+// 4-stage smem ring; two TMEM accumulators of NT columns so the epilogue of tile i overlaps the main loop of i+1.
+//
+// Epilogues (the reference's module boundaries they fuse are cited at the launchers):
+//   NT = 128 / 256:  out fp32 = [relu]( acc + bias + res1 + res2 ), written as NHWC through a 4D TMA store (pixels of a
+//                    border tile that fall outside the image are clipped by the store);
+//   NT = 32 (final): relu(acc + bias) -> 1x1 conv (32 -> od) -> activate_head -> fp32 prediction + confidence.
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace wm {
+
+constexpr int CV_TW = 16, CV_TH = 8;   // tile = 8 rows x 16 columns of pixels
+constexpr int CV_STAGES = 4;
+constexpr int CV_KE = 32;              // fp32 elements per k-block (one 128-byte swizzle row)
+constexpr int CV_A_BYTES = 128 * CV_KE * 4;
+constexpr int CV_THREADS = 256;
+constexpr int CV_STG_BYTES = 128 * 128;
+template <int NT>
+constexpr int cv_smem() {
+  return CV_STAGES * (CV_A_BYTES + NT * 128) + CV_STG_BYTES + 256 + 1024;
+}
+
+enum : int { ACT_EXP = 0, ACT_INV_LOG = 1, ACT_NORM = 2 };
+
+struct ConvArgs {
+  int n, H, W, Cin, Cout, taps;  // taps: 1 (1x1) or 9 (3x3, stride 1, pad 1)
+  int tiles_x, tiles_y, n_tiles, total_tiles, kblocks;  // kblocks = taps * Cin / 32
+  const float* bias;            // [Cout] or null
+  const float* res1;            // [n or 1, H, W, Cout] or null
+  const float* res2;            // [n, H, W, Cout] or null
+  int res1_bcast;               // res1 has no image axis (positional table)
+  int relu;
+  // final epilogue
+  const float *w2, *b2;         // [od, 32], [od]
+  int od, act;
+  float *pred, *conf;           // [n, H, W, od - 1], [n, H, W]
+};
+
+template <int NT>
+__global__ void __launch_bounds__(CV_THREADS, 1)
+conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const ConvArgs g) {
+  constexpr int B_BYTES = NT * 128;
+  constexpr bool FINAL = NT == 32;
+  constexpr uint32_t TMEM_COLS = 2 * NT < 32 ? 32 : 2 * NT;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + CV_STAGES * CV_A_BYTES;
+  uint8_t* sC = sB + CV_STAGES * B_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sC + CV_STG_BYTES);
+  uint64_t* empty = full + CV_STAGES;
+  uint64_t* tfull = empty + CV_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  pdl_launch_dependents();
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    if (!FINAL) tma_prefetch_desc(&tmC);
+  }
+  if (warp == 1 && elect_one()) {
+    for (int i = 0; i < CV_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 4);  // one arrival per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+
+  // tile -> (Cout tile, tile column, tile row, image); the Cout tile varies fastest so CTAs that run together share A
+  auto decode = [&](int tile, int& n0, int& x0, int& y0, int& img) {
+    n0 = (tile % g.n_tiles) * NT;
+    int r = tile / g.n_tiles;
+    x0 = (r % g.tiles_x) * CV_TW;
+    r /= g.tiles_x;
+    y0 = (r % g.tiles_y) * CV_TH;
+    img = r / g.tiles_y;
+  };
+  const int cblocks = g.Cin / CV_KE;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x) {
+        int n0, x0, y0, img;
+        decode(tile, n0, x0, y0, img);
+        for (int kb = 0; kb < g.kblocks; ++kb, ++it) {
+          const uint32_t s = it % CV_STAGES, ph = (it / CV_STAGES) & 1;
+          const int tap = kb / cblocks, cb = kb - tap * cblocks;
+          const int dy = g.taps == 9 ? tap / 3 - 1 : 0, dx = g.taps == 9 ? tap % 3 - 1 : 0;
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&full[s], CV_A_BYTES + B_BYTES);
+          tma_load_4d(sA + s * CV_A_BYTES, &tmA, &full[s], cb * CV_KE, x0 + dx, y0 + dy, img, kEvictNormal);
+          tma_load_2d(sB + s * B_BYTES, &tmB, &full[s], kb * CV_KE, n0, kEvictLast);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_tf32(128, NT);
+      uint32_t it = 0, tcount = 0;
+      for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++tcount) {
+        const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
+        mbar_wait(&tempty[acc], aph ^ 1);
+        tcgen05_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * NT;
+        for (int kb = 0; kb < g.kblocks; ++kb, ++it) {
+          const uint32_t s = it % CV_STAGES, ph = (it / CV_STAGES) & 1;
+          mbar_wait(&full[s], ph);
+          tcgen05_fence_after();
+          const uint64_t adesc = umma_desc_sw128(smem_u32(sA + s * CV_A_BYTES), 16, 1024);
+          const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + s * B_BYTES), 16, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)  // K = 8 fp32 = 32 bytes (>> 4 = 2) per instruction inside the swizzle row
+            umma_ss_tf32(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&tfull[acc]);
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    const int et = threadIdx.x - 128;  // accumulator row == pixel of the tile
+    const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t stg = smem_u32(sC);
+    uint32_t tcount = 0;
+    for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++tcount) {
+      int n0, x0, y0, img;
+      decode(tile, n0, x0, y0, img);
+      const int y = y0 + et / CV_TW, x = x0 + et % CV_TW;
+      const bool valid = y < g.H && x < g.W;
+      const size_t pix = ((size_t)img * g.H + y) * g.W + x;
+      const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
+      mbar_wait(&tfull[acc], aph);
+      tcgen05_fence_after();
+      const uint32_t taddr = tmem_base + acc * NT + lane_base;
+      if constexpr (FINAL) {
+        // output_conv2 (dense_head.py:85-89): relu(conv3x3 + b) -> conv1x1(32 -> od) -> activate_head (:297-344)
+        uint32_t v[32];
+        tmem_ld_x32(taddr, v);
+        tmem_wait_ld();
+        tcgen05_fence_before();
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(&tempty[acc]);
+        float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (j < g.od) o[j] = __ldg(g.b2 + j);
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          const float h = fmaxf(__uint_as_float(v[c]) + __ldg(g.bias + c), 0.f);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (j < g.od) o[j] = fmaf(__ldg(g.w2 + j * 32 + c), h, o[j]);
+        }
+        if (valid) {
+          const int na = g.od - 1;  // 1 (depth) or 3 (points, normals); the last channel is the confidence logit
+          const float cl = na == 1 ? o[1] : o[3];
+          g.conf[pix] = 1.0f + expf(cl);
+          float* pr = g.pred + pix * na;
+          float nn = 0.f;
+#pragma unroll
+          for (int j = 0; j < 3; ++j)
+            if (j < na) nn = fmaf(o[j], o[j], nn);
+          const float inv = 1.0f / sqrtf(nn);
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            if (j < na) {
+              float r;
+              if (g.act == ACT_EXP)
+                r = expf(o[j]);
+              else if (g.act == ACT_INV_LOG)
+                r = copysignf(expm1f(fabsf(o[j])), o[j]);
+              else
+                r = o[j] * inv;
+              pr[j] = r;
+            }
+          }
+        }
+      } else {
+#pragma unroll 1
+        for (int grp = 0; grp < NT / 32; ++grp) {
+          float xv[32];
+          {
+            uint32_t v0[32];
+            tmem_ld_x32(taddr + grp * 32, v0);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) xv[i] = __uint_as_float(v0[i]);
+          }
+          if (grp == NT / 32 - 1) {
+            tcgen05_fence_before();
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive(&tempty[acc]);
+          }
+          const int col0 = n0 + grp * 32;
+          if (g.bias != nullptr) {
+            const float4* b4 = reinterpret_cast<const float4*>(g.bias + col0);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 b = __ldg(b4 + i);
+              xv[4 * i] += b.x, xv[4 * i + 1] += b.y, xv[4 * i + 2] += b.z, xv[4 * i + 3] += b.w;
+            }
+          }
+          if (valid) {
+#pragma unroll
+            for (int rsel = 0; rsel < 2; ++rsel) {
+              const float* rp = rsel == 0 ? g.res1 : g.res2;
+              if (rp == nullptr) continue;
+              const size_t rpix = (rsel == 0 && g.res1_bcast) ? (size_t)y * g.W + x : pix;
+              const float4* r4 = reinterpret_cast<const float4*>(rp + rpix * g.Cout + col0);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float4 r = __ldg(r4 + i);
+                xv[4 * i] += r.x, xv[4 * i + 1] += r.y, xv[4 * i + 2] += r.z, xv[4 * i + 3] += r.w;
+              }
+            }
+          }
+          if (g.relu) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) xv[i] = fmaxf(xv[i], 0.f);
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) xv[i] = tf32_rn(xv[i]);  // the next convolution's operand: round once, here
+          if (et == 0) tma_store_wait_read<0>();  // the previous store has drained the staging tile
+          named_bar_sync(1, 128);
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            st_shared_v4(stg + sw128_offset(et, c), __float_as_uint(xv[4 * c]), __float_as_uint(xv[4 * c + 1]),
+                         __float_as_uint(xv[4 * c + 2]), __float_as_uint(xv[4 * c + 3]));
+          fence_proxy_async_smem();
+          named_bar_sync(1, 128);
+          if (et == 0) {
+            tma_store_4d(&tmC, sC, col0, x0, y0, img);
+            tma_store_commit();
+          }
+        }
+      }
+    }
+    if (!FINAL && et == 0) tma_store_wait<0>();
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host
+template <int NT>
+static wm_status launch_conv(cudaStream_t st, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, ConvArgs g) {
+  int sms = 0;
+  WM_TRY(require_sm100(&sms));
+  static bool configured = false;
+  if (!configured) {
+    WM_CUDA(cudaFuncSetAttribute(conv_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, cv_smem<NT>()));
+    configured = true;
+  }
+  g.tiles_x = (g.W + CV_TW - 1) / CV_TW;
+  g.tiles_y = (g.H + CV_TH - 1) / CV_TH;
+  g.n_tiles = g.Cout / NT;
+  g.total_tiles = g.n * g.tiles_x * g.tiles_y * g.n_tiles;
+  g.kblocks = g.taps * (g.Cin / CV_KE);
+  const int grid = g.total_tiles < sms ? g.total_tiles : sms;
+  return launch_pdl(conv_kernel<NT>, dim3(grid), dim3(CV_THREADS), cv_smem<NT>(), st, ta, tb, tc, g);
+}
+
+static wm_status conv_check(const void* in, const void* w, int n, int H, int W, int Cin, int Cout, int taps) {
+  WM_CHECK(in && w, "conv2d: null operand");
+  WM_CHECK(n > 0 && H > 0 && W > 0 && Cin > 0 && Cin % CV_KE == 0 && Cout > 0, "conv2d: bad geometry n=%d H=%d W=%d Cin=%d Cout=%d", n,
+           H, W, Cin, Cout);
+  WM_CHECK(taps == 1 || taps == 9, "conv2d: taps must be 1 (1x1) or 9 (3x3, stride 1, pad 1)");
+  WM_CHECK((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0, "conv2d: operands must be 16-byte aligned");
+  return WM_OK;
+}
+
+// nn.Conv2d(Cin, Cout, 1 | 3, stride 1, padding 0 | 1) on NHWC fp32 with the surrounding elementwise work fused:
+// out = [relu](conv(in) + bias + res1 + res2).  weight: fp32 [Cout, taps * Cin], tap-major (ky, kx, ci).
+wm_status conv2d_nhwc(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* weight, int taps, int Cout,
+                      const float* bias, const void* res1, int res1_bcast, const void* res2, int relu, void* out) {
+  WM_TRY(conv_check(in, weight, n, H, W, Cin, Cout, taps));
+  WM_CHECK(out && (Cout % 256 == 0 || Cout == 128), "conv2d: Cout must be 128 or a multiple of 256 (got %d)", Cout);
+  const CUtensorMapDataType f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  const int NT = Cout == 128 ? 128 : 256;
+  CUtensorMap ta, tb, tc;
+  WM_TRY(tmap_nhwc(&ta, f32, 4, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
+  WM_TRY(tmap_2d(&tb, f32, 4, weight, Cout, (uint64_t)taps * Cin, (uint64_t)taps * Cin, CV_KE, NT));
+  WM_TRY(tmap_nhwc(&tc, f32, 4, out, n, H, W, Cout, 32, CV_TW, CV_TH));
+  ConvArgs g{};
+  g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = Cout, g.taps = taps;
+  g.bias = bias, g.res1 = static_cast<const float*>(res1), g.res1_bcast = res1_bcast;
+  g.res2 = static_cast<const float*>(res2), g.relu = relu;
+  return NT == 128 ? launch_conv<128>(st, ta, tb, tc, g) : launch_conv<256>(st, ta, tb, tc, g);
+}
+
+// scratch.output_conv2 + activate_head (dense_head.py:85-89, 297-344): conv3x3(Cin -> 32) + ReLU + conv1x1(32 -> od)
+// + attribute / confidence activations, fp32 out.  w1: fp32 [32, 9 * Cin] tap-major; w2: fp32 [od, 32].
+wm_status conv2d_final(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
+                       const float* w2, const float* b2, int od, int act, float* pred, float* conf) {
+  WM_TRY(conv_check(in, w1, n, H, W, Cin, 32, 9));
+  WM_CHECK(b1 && w2 && b2 && pred && conf && (od == 2 || od == 4) && act >= ACT_EXP && act <= ACT_NORM, "conv2d_final: bad argument");
+  const CUtensorMapDataType f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  CUtensorMap ta, tb;
+  WM_TRY(tmap_nhwc(&ta, f32, 4, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
+  WM_TRY(tmap_2d(&tb, f32, 4, w1, 32, (uint64_t)9 * Cin, (uint64_t)9 * Cin, CV_KE, 32));
+  ConvArgs g{};
+  g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = 32, g.taps = 9;
+  g.bias = b1, g.w2 = w2, g.b2 = b2, g.od = od, g.act = act, g.pred = pred, g.conf = conf;
+  return launch_conv<32>(st, ta, tb, ta, g);
+}
+
+}  // namespace wm

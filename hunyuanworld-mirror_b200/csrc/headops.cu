@@ -1,0 +1,180 @@
+// HBM-bound kernels around the DPT heads' convolutions: LayerNorm of the 2048-wide
+// patch tokens, bilinear resampling (align_corners=True) of NHWC fp32 maps with the optional sinusoidal UV
+// positional embedding, the ConvTranspose2d(k == stride) scatter, and the im2col of the one stride-2 convolution.
+// Activations are fp32 (see conv.cu); every kernel moves 16 bytes per thread per access along the contiguous channel axis.
+#include <algorithm>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace wm {
+
+// nn.LayerNorm(C) over rows gathered from a strided token tensor: output row r = group g * rows_per_group + i reads
+// input row g * in_group_rows + in_offset + i (DPTHead: tokens[:, :, patch_start:], dense_head.py:203-211).
+// One warp per row, the row lives in registers (C <= 2048), two-pass variance, fp32 out rounded to TF32 (conv.cu).
+template <int C>
+__global__ void __launch_bounds__(256) ln_rows_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                      const float* __restrict__ b, float eps, long long rows,
+                                                      int rows_per_group, int in_group_rows, int in_offset,
+                                                      float* __restrict__ y) {
+  constexpr int V = C / 128;  // float4 per lane
+  pdl_launch_dependents();
+  pdl_wait();
+  const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const long long grp = r / rows_per_group, i = r - grp * rows_per_group;
+  const float4* xr = reinterpret_cast<const float4*>(x + (grp * in_group_rows + in_offset + i) * C);
+  float4 v[V];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    v[k] = __ldg(xr + k * 32 + lane);
+    s += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mu = s * (1.0f / C);
+  float q = 0.f;
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const float a = v[k].x - mu, bb = v[k].y - mu, c = v[k].z - mu, d = v[k].w - mu;
+    q += (a * a + bb * bb) + (c * c + d * d);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q * (1.0f / C) + eps);
+  float4* yr = reinterpret_cast<float4*>(y + r * C);
+  const float4* w4 = reinterpret_cast<const float4*>(w);
+  const float4* b4 = reinterpret_cast<const float4*>(b);
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const float4 ww = __ldg(w4 + k * 32 + lane), bb = __ldg(b4 + k * 32 + lane);
+    yr[k * 32 + lane] = make_float4(tf32_rn((v[k].x - mu) * rstd * ww.x + bb.x), tf32_rn((v[k].y - mu) * rstd * ww.y + bb.y),
+                                    tf32_rn((v[k].z - mu) * rstd * ww.z + bb.z), tf32_rn((v[k].w - mu) * rstd * ww.w + bb.w));
+  }
+}
+
+wm_status ln_rows(cudaStream_t st, const float* x, const float* w, const float* b, float eps, long long rows,
+                  int rows_per_group, int in_group_rows, int in_offset, int C, void* y) {
+  WM_CHECK(x && w && b && y && rows > 0 && rows_per_group > 0, "ln_rows: bad argument");
+  const unsigned grid = (unsigned)((rows + 7) / 8);
+  float* yo = static_cast<float*>(y);
+  if (C == 2048)
+    return launch_pdl(ln_rows_kernel<2048>, dim3(grid), dim3(256), 0, st, x, w, b, eps, rows, rows_per_group, in_group_rows, in_offset, yo);
+  if (C == 1024)
+    return launch_pdl(ln_rows_kernel<1024>, dim3(grid), dim3(256), 0, st, x, w, b, eps, rows, rows_per_group, in_group_rows, in_offset, yo);
+  return fail(WM_ERR_INVALID, "ln_rows: C must be 1024 or 2048 (got %d)", C);
+}
+
+// F.interpolate(mode="bilinear", align_corners=True) on NHWC fp32 (dense_head.py:216-226, 529 via custom_interpolate
+// :539-579): src = dst * (in - 1) / (out - 1).  Optional positional embedding added after resampling
+// (_apply_pos_embed, dense_head.py:262-271): channel c < C/2 takes pos_u[x][c], c >= C/2 takes pos_v[y][c - C/2]
+// (the UV embedding is separable: utils/grid.py:4-42).  One thread per 4 channels of one output pixel.
+__global__ void __launch_bounds__(256) bilinear_kernel(const float* __restrict__ in, int n, int Hi, int Wi, int C,
+                                                       int Ho, int Wo, float sy, float sx, const float* __restrict__ pos_u,
+                                                       const float* __restrict__ pos_v, float* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int c4 = C >> 2;
+  const long long total = (long long)n * Ho * Wo * c4;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(t % c4);
+    long long p = t / c4;
+    const int xo = (int)(p % Wo);
+    p /= Wo;
+    const int yo = (int)(p % Ho), img = (int)(p / Ho);
+    const float fy = yo * sy, fx = xo * sx;
+    const int y0 = min((int)fy, Hi - 1), x0 = min((int)fx, Wi - 1);
+    const int y1 = min(y0 + 1, Hi - 1), x1 = min(x0 + 1, Wi - 1);
+    const float ly = fy - y0, lx = fx - x0;
+    const float4* base = reinterpret_cast<const float4*>(in + (size_t)img * Hi * Wi * C) + c;
+    const float4 a = __ldg(base + ((size_t)y0 * Wi + x0) * c4), b = __ldg(base + ((size_t)y0 * Wi + x1) * c4);
+    const float4 d = __ldg(base + ((size_t)y1 * Wi + x0) * c4), e = __ldg(base + ((size_t)y1 * Wi + x1) * c4);
+    // the order PyTorch's upsample_bilinear2d kernel uses: h0 * (w0 * a + w1 * b) + h1 * (w0 * d + w1 * e)
+    const float hy0 = 1.f - ly, hx0 = 1.f - lx;
+    float4 r;
+    r.x = hy0 * (hx0 * a.x + lx * b.x) + ly * (hx0 * d.x + lx * e.x);
+    r.y = hy0 * (hx0 * a.y + lx * b.y) + ly * (hx0 * d.y + lx * e.y);
+    r.z = hy0 * (hx0 * a.z + lx * b.z) + ly * (hx0 * d.z + lx * e.z);
+    r.w = hy0 * (hx0 * a.w + lx * b.w) + ly * (hx0 * d.w + lx * e.w);
+    if (pos_u != nullptr) {
+      const int half = C >> 1, ch = c * 4;
+      const float* pp = ch < half ? pos_u + (size_t)xo * half + ch : pos_v + (size_t)yo * half + (ch - half);
+      const float4 p0 = __ldg(reinterpret_cast<const float4*>(pp));
+      r.x += p0.x, r.y += p0.y, r.z += p0.z, r.w += p0.w;
+    }
+    reinterpret_cast<float4*>(out)[t] = make_float4(tf32_rn(r.x), tf32_rn(r.y), tf32_rn(r.z), tf32_rn(r.w));
+  }
+}
+
+wm_status bilinear_nhwc(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, int Ho, int Wo, const float* pos_u,
+                        const float* pos_v, void* out) {
+  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && Ho > 0 && Wo > 0 && C > 0 && C % 8 == 0, "bilinear: bad geometry");
+  WM_CHECK((pos_u == nullptr) == (pos_v == nullptr), "bilinear: pos_u and pos_v go together");
+  const float sy = Ho > 1 ? (float)(Hi - 1) / (float)(Ho - 1) : 0.f, sx = Wo > 1 ? (float)(Wi - 1) / (float)(Wo - 1) : 0.f;
+  const long long total = (long long)n * Ho * Wo * (C / 4);
+  const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, 148LL * 32);
+  return launch_pdl(bilinear_kernel, dim3(grid), dim3(256), 0, st, static_cast<const float*>(in), n, Hi, Wi, C, Ho, Wo, sy, sx,
+                    pos_u, pos_v, static_cast<float*>(out));
+}
+
+// nn.ConvTranspose2d(C, C, k, stride=k) (dense_head.py:57-64) = GEMM [pixels, Cin] x [Cin, (ky, kx, co)] followed by
+// this scatter: in [n*Hi*Wi, k*k*C] -> out [n, Hi*k, Wi*k, C].
+__global__ void __launch_bounds__(256) pixel_shuffle_kernel(const uint4* __restrict__ in, int n, int Hi, int Wi, int C, int k,
+                                                            uint4* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int c8 = C >> 2;  // 16-byte chunks (4 fp32) per pixel
+  const long long total = (long long)n * Hi * k * Wi * k * c8;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(t % c8);
+    long long p = t / c8;
+    const int xo = (int)(p % (Wi * k));
+    p /= Wi * k;
+    const int yo = (int)(p % (Hi * k)), img = (int)(p / (Hi * k));
+    const int y = yo / k, ky = yo - y * k, x = xo / k, kx = xo - x * k;
+    out[t] = __ldg(in + (((size_t)img * Hi + y) * Wi + x) * (k * k * c8) + (size_t)(ky * k + kx) * c8 + c);
+  }
+}
+
+wm_status pixel_shuffle(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, int k, void* out) {
+  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && C > 0 && C % 4 == 0 && k > 0, "pixel_shuffle: bad geometry");
+  const long long total = (long long)n * Hi * k * Wi * k * (C / 4);
+  const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, 148LL * 32);
+  return launch_pdl(pixel_shuffle_kernel, dim3(grid), dim3(256), 0, st, static_cast<const uint4*>(in), n, Hi, Wi, C, k,
+                    static_cast<uint4*>(out));
+}
+
+// im2col of nn.Conv2d(C, C, 3, stride=2, padding=1) (dense_head.py:66-68): out [n*Ho*Wo, 9*C], tap-major.
+__global__ void __launch_bounds__(256) im2col_s2_kernel(const uint4* __restrict__ in, int n, int Hi, int Wi, int C, int Ho, int Wo,
+                                                        uint4* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int c8 = C >> 2;  // 16-byte chunks (4 fp32) per pixel
+  const long long total = (long long)n * Ho * Wo * 9 * c8;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(t % c8);
+    long long p = t / c8;
+    const int tap = (int)(p % 9);
+    p /= 9;
+    const int xo = (int)(p % Wo);
+    p /= Wo;
+    const int yo = (int)(p % Ho), img = (int)(p / Ho);
+    const int y = 2 * yo + tap / 3 - 1, x = 2 * xo + tap % 3 - 1;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (y >= 0 && y < Hi && x >= 0 && x < Wi) v = __ldg(in + (((size_t)img * Hi + y) * Wi + x) * c8 + c);
+    out[t] = v;
+  }
+}
+
+wm_status im2col_s2(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, void* out) {
+  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && C > 0 && C % 4 == 0, "im2col_s2: bad geometry");
+  const int Ho = (Hi - 1) / 2 + 1, Wo = (Wi - 1) / 2 + 1;
+  const long long total = (long long)n * Ho * Wo * 9 * (C / 4);
+  const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, 148LL * 32);
+  return launch_pdl(im2col_s2_kernel, dim3(grid), dim3(256), 0, st, static_cast<const uint4*>(in), n, Hi, Wi, C, Ho, Wo,
+                    static_cast<uint4*>(out));
+}
+
+}  // namespace wm

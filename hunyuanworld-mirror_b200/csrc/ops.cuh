@@ -29,6 +29,17 @@ wm_status prior_token(cudaStream_t st, const float* in, int n_views, int d_in, c
                       const float* w2, const float* b2, int rows_per_view, int row, float* x);
 wm_status special_tokens(cudaStream_t st, const float* cam, const float* reg, int n_views, int rows_per_view,
                          int first_view_global, int zero_pose, int zero_ray, float* x);
+// prediction heads (conv.cu, headops.cu)
+wm_status conv2d_nhwc(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* weight, int taps, int Cout,
+                      const float* bias, const void* res1, int res1_bcast, const void* res2, int relu, void* out);
+wm_status conv2d_final(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
+                       const float* w2, const float* b2, int od, int act, float* pred, float* conf);
+wm_status ln_rows(cudaStream_t st, const float* x, const float* w, const float* b, float eps, long long rows,
+                  int rows_per_group, int in_group_rows, int in_offset, int C, void* y);
+wm_status bilinear_nhwc(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, int Ho, int Wo, const float* pos_u,
+                        const float* pos_v, void* out);
+wm_status pixel_shuffle(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, int k, void* out);
+wm_status im2col_s2(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, void* out);
 wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);
 
 }  // namespace wm

@@ -1,0 +1,219 @@
+"""B200 prediction heads behind the reference's module interface.
+
+`B200DPTHead` mirrors `DPTHead` (src/models/heads/dense_head.py:11-260, is_gsdpt=False): same constructor keywords,
+same `state_dict` keys on the way in, same `forward(token_list, images, patch_start_idx, frames_chunk_size)` and the
+same return value `(pred [B,S,H,W,C-1], conf [B,S,H,W])` in fp32.  Every convolution runs as an implicit GEMM on
+tcgen05 (csrc/conv.cu) over NHWC fp32 activations at kind::tf32 with fp32 accumulation (the reference runs its heads
+in fp32, worldmirror.py:146; bf16 activations measured 1.5e-2 on pts3d); bias, ReLU, the residual adds of
+ResidualConvUnit / FeatureFusionBlock, the positional embedding and the output activations are fused into the
+epilogues; LayerNorm, bilinear resampling and the ConvTranspose scatter are bandwidth kernels (csrc/headops.cu).
+Two algebraic rewrites, both exact in real arithmetic:
+  * FeatureFusionBlock runs `out_conv` (1x1) BEFORE the bilinear upsample instead of after (dense_head.py:529-530):
+    both are linear and the interpolation weights sum to one, so they commute; 4x fewer FLOPs.
+  * nn.ReLU(inplace=True) inside ResidualConvUnit overwrites its input (dense_head.py:448), so the skip connection
+    adds relu(x); producers therefore store relu(x) only.
+PyTorch is used for device memory and for packing weights at load time.  There is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, List, Sequence, Tuple
+
+import torch
+
+from . import capi
+
+PATCH = 14
+_ACT = {"exp": 0, "inv_log": 1, "norm": 2}
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def round_tf32(t: torch.Tensor) -> torch.Tensor:
+    """Round fp32 to TF32 (10-bit mantissa), nearest with ties away from zero = PTX cvt.rna.tf32.f32.  The tensor
+    cores truncate fp32 operands; rounding once at load time makes that truncation exact (csrc/conv.cu)."""
+    i = t.contiguous().view(torch.int32)
+    return ((i + 0x1000) & ~0x1FFF).view(torch.float32)
+
+
+def uv_tables(w: int, h: int, channels: int, aspect: float, ratio: float = 0.1) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Separable form of `_apply_pos_embed` (dense_head.py:262-271; utils/grid.py:4-89): the embedding of pixel (x, y)
+    is [sin(u w_k), cos(u w_k), sin(v w_k), cos(v w_k)] * ratio with u = u(x), v = v(y), w_k = 100^(-k/(C/4)) in float64.
+    Returns (pos_u [w, C/2], pos_v [h, C/2]) fp32 on the CPU."""
+    diag = math.sqrt(aspect * aspect + 1.0)
+    sx, sy = aspect / diag, 1.0 / diag
+    u = torch.linspace(-sx * (w - 1) / w, sx * (w - 1) / w, w, dtype=torch.float32).double()
+    v = torch.linspace(-sy * (h - 1) / h, sy * (h - 1) / h, h, dtype=torch.float32).double()
+    omega = 1.0 / 100.0 ** (torch.arange(channels // 4, dtype=torch.float64) / (channels / 4.0))
+    au, av = u[:, None] * omega[None], v[:, None] * omega[None]
+    pu = torch.cat([au.sin(), au.cos()], dim=1).float() * ratio
+    pv = torch.cat([av.sin(), av.cos()], dim=1).float() * ratio
+    return pu.contiguous(), pv.contiguous()
+
+
+class B200DPTHead(torch.nn.Module):
+    def __init__(self, dim_in: int = 2048, patch_size: int = 14, output_dim: int = 4, activation: str = "inv_log+expp1",
+                 features: int = 256, out_channels: Sequence[int] = (256, 512, 1024, 1024), pos_embed: bool = True,
+                 down_ratio: int = 1, is_gsdpt: bool = False):
+        super().__init__()
+        if is_gsdpt or down_ratio != 1 or not pos_embed or patch_size != PATCH:
+            raise NotImplementedError("B200DPTHead covers the depth / points / normals configuration of WorldMirror")
+        if dim_in not in (1024, 2048) or features != 256 or tuple(out_channels) != (256, 512, 1024, 1024):
+            raise NotImplementedError("B200DPTHead is built for dim_in 2048, features 256, out_channels (256,512,1024,1024)")
+        act, conf = activation.split("+") if "+" in activation else (activation, "expp1")
+        if act not in _ACT or conf != "expp1" or output_dim not in (2, 4):
+            raise ValueError(f"Unknown attribute activation: {activation}")
+        self.dim_in, self.output_dim, self.activation, self.act = dim_in, output_dim, activation, _ACT[act]
+        self.oc = tuple(out_channels)
+        self.w: Dict[str, torch.Tensor] = {}
+        self._pos: Dict[tuple, tuple] = {}
+        self._loaded = False
+
+    # ------------------------------------------------------------------ weights
+    def load_state_dict(self, sd, strict: bool = True, device=None):
+        """Reference keys and shapes (DPTHead.state_dict()).  Convolution weights are repacked to fp32
+        [Cout, (ky, kx, ci)]; ConvTranspose2d weights [ci, co, ky, kx] to [(ky, kx, co), ci] with the bias tiled."""
+        capi.lib()  # raises if the CUDA library is missing: no fallback
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        w = {}
+
+        def conv(key):
+            t = sd[key].detach().to(dev, torch.float32)
+            co, ci, kh, kw = t.shape
+            return round_tf32(t.permute(0, 2, 3, 1).reshape(co, kh * kw * ci).contiguous())
+
+        def vec(key):
+            return sd[key].detach().to(dev, torch.float32).contiguous()
+
+        w["norm.w"], w["norm.b"] = vec("norm.weight"), vec("norm.bias")
+        for i in range(4):
+            w[f"proj{i}.w"], w[f"proj{i}.b"] = conv(f"projects.{i}.weight"), vec(f"projects.{i}.bias")
+            w[f"rn{i}.w"] = conv(f"scratch.layer{i + 1}_rn.weight")
+        for i, k in ((0, 4), (1, 2)):
+            t = sd[f"resize_layers.{i}.weight"].detach().to(dev, torch.float32)  # [ci, co, k, k]
+            ci, co = t.shape[0], t.shape[1]
+            w[f"up{i}.w"] = round_tf32(t.permute(2, 3, 1, 0).reshape(k * k * co, ci).contiguous())
+            w[f"up{i}.b"] = vec(f"resize_layers.{i}.bias").repeat(k * k).contiguous()
+        w["down3.w"], w["down3.b"] = conv("resize_layers.3.weight"), vec("resize_layers.3.bias")
+        for r in (1, 2, 3, 4):
+            p = f"scratch.refinenet{r}."
+            w[f"rf{r}.out.w"], w[f"rf{r}.out.b"] = conv(p + "out_conv.weight"), vec(p + "out_conv.bias")
+            for u in ((1, 2) if r != 4 else (2,)):
+                for c in (1, 2):
+                    w[f"rf{r}.u{u}.c{c}.w"] = conv(p + f"resConfUnit{u}.conv{c}.weight")
+                    w[f"rf{r}.u{u}.c{c}.b"] = vec(p + f"resConfUnit{u}.conv{c}.bias")
+        w["oc1.w"], w["oc1.b"] = conv("scratch.output_conv1.weight"), vec("scratch.output_conv1.bias")
+        w["oc2.w"], w["oc2.b"] = conv("scratch.output_conv2.0.weight"), vec("scratch.output_conv2.0.bias")
+        w["oc3.w"] = sd["scratch.output_conv2.2.weight"].detach().to(dev, torch.float32).reshape(self.output_dim, 32).contiguous()
+        w["oc3.b"] = vec("scratch.output_conv2.2.bias")
+        assert tuple(w["proj0.w"].shape) == (self.oc[0], self.dim_in)
+        self.w, self._loaded, self._dev = w, True, dev
+        return torch.nn.modules.module._IncompatibleKeys([], [])
+
+    def _pos_tables(self, gh, gw, H, W):
+        key = (gh, gw, H, W)
+        if key not in self._pos:
+            tabs = []
+            for c in self.oc:  # positional table of the projected features, fp32 [gh, gw, c]
+                pu, pv = uv_tables(gw, gh, c, W / H)
+                full = torch.cat([pu[None].expand(gh, -1, -1), pv[:, None].expand(-1, gw, -1)], dim=-1)
+                tabs.append(full.to(self._dev).contiguous())
+            pu, pv = uv_tables(W, H, 128, W / H)
+            self._pos = {key: (tabs, pu.to(self._dev), pv.to(self._dev))}  # one live geometry
+        return self._pos[key]
+
+    # ------------------------------------------------------------------ ops
+    def _conv(self, x, n, H, W, cin, wkey, taps, cout, bias=None, res1=None, bcast=0, res2=None, relu=0):
+        out = torch.empty(n, H, W, cout, dtype=torch.float32, device=x.device)
+        capi.check(capi.lib().wm_conv2d_nhwc(_st(), x.data_ptr(), n, H, W, cin, self.w[wkey].data_ptr(), taps, cout, _p(bias),
+                                             _p(res1), bcast, _p(res2), relu, out.data_ptr()))
+        return out
+
+    def _resize(self, x, n, Hi, Wi, c, Ho, Wo, pu=None, pv=None):
+        out = torch.empty(n, Ho, Wo, c, dtype=torch.float32, device=x.device)
+        capi.check(capi.lib().wm_bilinear_nhwc(_st(), x.data_ptr(), n, Hi, Wi, c, Ho, Wo, _p(pu), _p(pv), out.data_ptr()))
+        return out
+
+    def _rcu(self, r, unit, x, n, H, W, extra=None, relu_out=0):
+        """ResidualConvUnit on x = relu(input): conv2(relu(conv1(x))) + x [+ extra], optional ReLU on the sum."""
+        w = self.w
+        t = self._conv(x, n, H, W, 256, f"rf{r}.u{unit}.c1.w", 9, 256, w[f"rf{r}.u{unit}.c1.b"], relu=1)
+        return self._conv(t, n, H, W, 256, f"rf{r}.u{unit}.c2.w", 9, 256, w[f"rf{r}.u{unit}.c2.b"], res1=x, res2=extra, relu=relu_out)
+
+    # ------------------------------------------------------------------ forward
+    @torch.no_grad()
+    def forward(self, token_list: List[torch.Tensor], images: torch.Tensor, patch_start_idx: int, frames_chunk_size: int = 8):
+        if not self._loaded:
+            raise RuntimeError("B200DPTHead: load_state_dict() has not been called")
+        B, S, _, H, W = images.shape
+        if not token_list[0].is_cuda:
+            raise RuntimeError("B200DPTHead needs CUDA tensors (there is no CPU path)")
+        chunk = S if (frames_chunk_size is None or frames_chunk_size >= S) else frames_chunk_size
+        assert chunk > 0
+        dev = token_list[0].device
+        na = self.output_dim - 1
+        pred = torch.empty(B, S, H, W, na, dtype=torch.float32, device=dev)
+        conf = torch.empty(B, S, H, W, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            for b in range(B):
+                for f0 in range(0, S, chunk):
+                    f1 = min(f0 + chunk, S)
+                    self._forward_chunk([t[b, f0:f1] for t in token_list], H, W, patch_start_idx, pred[b, f0:f1], conf[b, f0:f1])
+        return pred, conf
+
+    def _forward_chunk(self, toks, H, W, psi, pred, conf):
+        lib, w = capi.lib(), self.w
+        n, P, Cd = toks[0].shape
+        gh, gw = H // PATCH, W // PATCH
+        g = gh * gw
+        assert P == psi + g and Cd == self.dim_in
+        tabs, pu, pv = self._pos_tables(gh, gw, H, W)
+        dev = toks[0].device
+        rn, sizes = [], []
+        for i, t in enumerate(toks):
+            t = t.to(torch.float32).contiguous()
+            ln = torch.empty(n, gh, gw, Cd, dtype=torch.float32, device=dev)
+            capi.check(lib.wm_layernorm_rows(_st(), t.data_ptr(), w["norm.w"].data_ptr(), w["norm.b"].data_ptr(), 1e-5, n * g, g, P,
+                                             psi, Cd, ln.data_ptr()))
+            c = self.oc[i]
+            f = self._conv(ln, n, gh, gw, Cd, f"proj{i}.w", 1, c, w[f"proj{i}.b"], res1=tabs[i], bcast=1)
+            h_, w_ = gh, gw
+            if i in (0, 1):  # ConvTranspose2d(c, c, k, stride k) = 1x1 convolution to k*k*c channels + scatter
+                k = 4 if i == 0 else 2
+                tmp = self._conv(f, n, gh, gw, c, f"up{i}.w", 1, k * k * c, w[f"up{i}.b"])
+                f = torch.empty(n, gh * k, gw * k, c, dtype=torch.float32, device=dev)
+                capi.check(lib.wm_pixel_shuffle(_st(), tmp.data_ptr(), n, gh, gw, c, k, f.data_ptr()))
+                h_, w_ = gh * k, gw * k
+            elif i == 3:  # Conv2d(c, c, 3, stride 2, padding 1) = im2col + 1x1 convolution over 9c channels
+                h_, w_ = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
+                col = torch.empty(n, h_, w_, 9 * c, dtype=torch.float32, device=dev)
+                capi.check(lib.wm_im2col_s2(_st(), f.data_ptr(), n, gh, gw, c, col.data_ptr()))
+                f = self._conv(col, n, h_, w_, 9 * c, "down3.w", 1, c, w["down3.b"])
+            # scratch.layer{i}_rn (no bias); only relu(rn) is ever read (in-place ReLU of the consuming RCU)
+            rn.append(self._conv(f, n, h_, w_, c, f"rn{i}.w", 9, 256, relu=1))
+            sizes.append((h_, w_))
+        # refinenet4 .. refinenet1 (dense_head.py:283-291)
+        path = None
+        for r in (4, 3, 2, 1):
+            h_, w_ = sizes[r - 1]
+            if r == 4:
+                x = rn[3]
+            else:  # x = relu(path + RCU1(skip))
+                x = self._rcu(r, 1, rn[r - 1], n, h_, w_, extra=path, relu_out=1)
+            u = self._rcu(r, 2, x, n, h_, w_)
+            v = self._conv(u, n, h_, w_, 256, f"rf{r}.out.w", 1, 256, w[f"rf{r}.out.b"])
+            ho, wo = sizes[r - 2] if r > 1 else (2 * h_, 2 * w_)
+            path = self._resize(v, n, h_, w_, 256, ho, wo)
+            hp, wp = ho, wo
+        o1 = self._conv(path, n, hp, wp, 256, "oc1.w", 9, 128, w["oc1.b"])
+        fused = self._resize(o1, n, hp, wp, 128, gh * PATCH, gw * PATCH, pu, pv)
+        capi.check(lib.wm_conv2d_final(_st(), fused.data_ptr(), n, H, W, 128, w["oc2.w"].data_ptr(), w["oc2.b"].data_ptr(),
+                                       w["oc3.w"].data_ptr(), w["oc3.b"].data_ptr(), self.output_dim, self.act, pred.data_ptr(),
+                                       conf.data_ptr()))

@@ -188,6 +188,37 @@ void wm_rope_tables(int max_pos, float* cos_host, float* sin_host);
 /* fp32 [rows, cols] -> bf16 [rows, ld] with zero tail columns. */
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst);
 
+/* ---- prediction heads: DPTHead (src/models/heads/dense_head.py) ------------ */
+/* The reference runs its heads in fp32 (autocast disabled, worldmirror.py:146): activations are NHWC fp32
+ * [n, H, W, C], weights fp32 [Cout, taps * Cin] with taps ordered (ky, kx, ci); the tensor cores run kind::tf32
+ * with fp32 accumulation (bf16 activations measured 1.5e-2 relative error on pts3d, above the stated 1e-2).
+ * nn.Conv2d(Cin, Cout, 1 | 3, stride 1, padding 0 | 1) as an implicit GEMM on tcgen05 with its neighbours fused:
+ * out = [relu](conv(in) + bias + res1 + res2); bias / res1 / res2 may be NULL; res1_bcast: res1 is [H, W, Cout]
+ * (the positional table of _apply_pos_embed, dense_head.py:262-271).  Cin % 32 == 0; Cout 128 or a multiple of 256.
+ * ConvTranspose2d(k == stride) is this with taps = 1 and Cout = k*k*C followed by wm_pixel_shuffle; the stride-2
+ * convolution is wm_im2col_s2 followed by this with taps = 1.
+ * Fuses: projects[i] + pos embed (:212-215), scratch.layer*_rn (:278-281), ResidualConvUnit (:436-457, whose in-place
+ * ReLU makes the skip relu(x)), FeatureFusionBlock.out_conv and skip_add (:518-534), scratch.output_conv1 (:293). */
+wm_status wm_conv2d_nhwc(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* weight, int taps, int Cout,
+                         const float* bias, const void* res1, int res1_bcast, const void* res2, int relu, void* out);
+/* scratch.output_conv2 + activate_head (dense_head.py:85-89, 297-344): conv3x3(Cin -> 32) + ReLU + conv1x1(32 -> od) +
+ * activations; act 0 = exp (depth), 1 = inv_log (points), 2 = norm (normals); confidence = 1 + exp.
+ * w1 [32, 9*Cin], b1 [32], w2 [od, 32], b2 [od] fp32; pred [n, H, W, od-1], conf [n, H, W] fp32; od = 2 or 4. */
+wm_status wm_conv2d_final(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
+                          const float* w2, const float* b2, int od, int act, float* pred, float* conf);
+/* nn.LayerNorm(C) of gathered rows (dense_head.py:203-211): output row g * rows_per_group + i = LN(input row
+ * g * in_group_rows + in_offset + i), fp32 in, fp32 out; C = 1024 or 2048. */
+wm_status wm_layernorm_rows(wm_stream stream, const float* x, const float* w, const float* b, float eps, long long rows,
+                            int rows_per_group, int in_group_rows, int in_offset, int C, void* y);
+/* F.interpolate(bilinear, align_corners=True) (dense_head.py:216-226, 529) on NHWC fp32, optionally followed by the
+ * separable UV positional embedding: + pos_u[x][c] for c < C/2, + pos_v[y][c - C/2] otherwise (fp32 tables). */
+wm_status wm_bilinear_nhwc(wm_stream stream, const void* in, int n, int Hi, int Wi, int C, int Ho, int Wo, const float* pos_u,
+                           const float* pos_v, void* out);
+/* Scatter of nn.ConvTranspose2d(C, C, k, stride k) (dense_head.py:57-64): [n*Hi*Wi, k*k*C] -> [n, Hi*k, Wi*k, C]. */
+wm_status wm_pixel_shuffle(wm_stream stream, const void* in, int n, int Hi, int Wi, int C, int k, void* out);
+/* im2col of nn.Conv2d(C, C, 3, stride 2, padding 1) (dense_head.py:66-68): -> [n*Ho*Wo, 9*C], Ho = (Hi-1)/2 + 1. */
+wm_status wm_im2col_s2(wm_stream stream, const void* in, int n, int Hi, int Wi, int C, void* out);
+
 #ifdef __cplusplus
 }
 #endif

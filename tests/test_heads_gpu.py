@@ -1,0 +1,180 @@
+"""GPU parity of the prediction-head kernels: each op against plain torch fp32 on the same
+operands (convolutions run on the tensor cores at kind::tf32 on operands already rounded to TF32, fp32 accumulation,
+outputs rounded to TF32 = 2^-11 relative: tolerance 2^-10 of the output scale; same for the bandwidth kernels), and the whole
+B200DPTHead against the fixture the REFERENCE heads produced (tests/golden/c1_heads.npz)."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+pkg = importlib.import_module("hunyuanworld-mirror_b200")
+capi, W = pkg.capi, pkg.weights
+heads = importlib.import_module("hunyuanworld-mirror_b200.heads")
+from oracle import aggregator_oracle as O  # noqa: E402
+from oracle import heads_oracle as HO  # noqa: E402
+
+
+def _rand(shape, seed, scale=1.0):
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed)
+    return torch.randn(shape, generator=g) * scale
+
+
+def _tf(x):
+    """Operands as the kernels see them: rounded to TF32 (producers and the weight loader do this)."""
+    return heads.round_tf32(x)
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _close(got, ref, what, rel=2.0 ** -10):
+    err = (got - ref).abs().max().item()
+    tol = rel * ref.abs().max().item() + 1e-6
+    print(f"{what}: max abs err {err:.3e} (ref max {ref.abs().max().item():.3f})")
+    assert torch.isfinite(got).all() and err <= tol, (what, err, tol)
+
+
+@pytest.mark.parametrize("n,H,Wd,cin,cout,taps,res,relu", [
+    (2, 18, 18, 256, 256, 9, 2, 1),    # C1 grid, two residual inputs + ReLU (RCU1.conv2 of a fusion block)
+    (1, 37, 37, 1024, 256, 9, 0, 1),   # layer3_rn at 518 px
+    (2, 9, 11, 2048, 512, 1, 1, 0),    # projects[1] + positional table (broadcast residual), two Cout tiles
+    (1, 40, 23, 256, 128, 9, 0, 0),    # output_conv1 shape class (Cout 128), ragged tiles in x and y
+    (3, 5, 70, 128, 256, 1, 1, 1),     # image narrower than a tile row block
+])
+def test_conv2d_nhwc(n, H, Wd, cin, cout, taps, res, relu):
+    k = 3 if taps == 9 else 1
+    x = _tf(_rand((n, cin, H, Wd), 1))
+    w = _tf(_rand((cout, cin, k, k), 2, 1.0 / (cin * taps) ** 0.5))
+    b = _rand((cout,), 3, 0.1)
+    bc = res == 1
+    r1 = _rand((1 if bc else n, cout, H, Wd), 4) if res >= 1 else None
+    r2 = _rand((n, cout, H, Wd), 5) if res >= 2 else None
+    ref = F.conv2d(x, w, b, padding=k // 2)
+    if r1 is not None:
+        ref = ref + r1
+    if r2 is not None:
+        ref = ref + r2
+    if relu:
+        ref = F.relu(ref)
+    nhwc = lambda t: None if t is None else t.permute(0, 2, 3, 1).contiguous().cuda()
+    xd, r1d, r2d = nhwc(x), nhwc(r1), nhwc(r2)
+    wd = w.permute(0, 2, 3, 1).reshape(cout, taps * cin).contiguous().cuda()
+    bd = b.cuda()
+    out = torch.zeros(n, H, Wd, cout, dtype=torch.float32, device="cuda")
+    capi.check(capi.lib().wm_conv2d_nhwc(_st(), xd.data_ptr(), n, H, Wd, cin, wd.data_ptr(), taps, cout, bd.data_ptr(),
+                                         None if r1d is None else r1d.data_ptr(), int(bc), None if r2d is None else r2d.data_ptr(),
+                                         relu, out.data_ptr()))
+    torch.cuda.synchronize()
+    _close(out.cpu().permute(0, 3, 1, 2), ref, f"conv {taps} taps {cin}->{cout} {H}x{Wd}")
+
+
+@pytest.mark.parametrize("od,act", [(2, "exp"), (4, "inv_log"), (4, "norm")])
+def test_conv2d_final(od, act):
+    n, H, Wd, cin = 2, 21, 35, 128
+    x = _tf(_rand((n, cin, H, Wd), 1))
+    w1 = _tf(_rand((32, cin, 3, 3), 2, 1.0 / (cin * 9) ** 0.5))
+    b1, w2, b2 = _rand((32,), 3, 0.1), _rand((od, 32, 1, 1), 4, 32 ** -0.5), _rand((od,), 5, 0.1)
+    o = F.conv2d(F.relu(F.conv2d(x, w1, b1, padding=1)), w2, b2)
+    pr, cr = HO.activate(o, act + "+expp1")
+    xd = x.permute(0, 2, 3, 1).contiguous().cuda()
+    w1d = w1.permute(0, 2, 3, 1).reshape(32, 9 * cin).contiguous().cuda()
+    b1d, w2d, b2d = b1.cuda(), w2.reshape(od, 32).contiguous().cuda(), b2.cuda()
+    pred = torch.zeros(n, H, Wd, od - 1, device="cuda")
+    conf = torch.zeros(n, H, Wd, device="cuda")
+    capi.check(capi.lib().wm_conv2d_final(_st(), xd.data_ptr(), n, H, Wd, cin, w1d.data_ptr(), b1d.data_ptr(), w2d.data_ptr(),
+                                          b2d.data_ptr(), od, {"exp": 0, "inv_log": 1, "norm": 2}[act], pred.data_ptr(),
+                                          conf.data_ptr()))
+    torch.cuda.synchronize()
+    _close(pred.cpu(), pr, f"final conv {act} pred", rel=1e-4)
+    _close(conf.cpu(), cr, f"final conv {act} conf", rel=1e-4)
+
+
+def test_bilinear_pixel_shuffle_im2col_ln():
+    lib = capi.lib()
+    n, Hi, Wi, c = 2, 19, 23, 256
+    x = _tf(_rand((n, c, Hi, Wi), 1))
+    xd = x.permute(0, 2, 3, 1).contiguous().cuda()
+    for Ho, Wo, pos in ((37, 40, False), (38, 46, False), (60, 51, True)):
+        ref = F.interpolate(x, size=(Ho, Wo), mode="bilinear", align_corners=True)
+        pu = pv = None
+        if pos:
+            pu, pv = heads.uv_tables(Wo, Ho, c, Wo / Ho)
+            ref = ref + HO.uv_pos_embed(Wo, Ho, c, Wo / Ho)[None]
+            pu, pv = pu.cuda(), pv.cuda()
+        out = torch.zeros(n, Ho, Wo, c, dtype=torch.float32, device="cuda")
+        capi.check(lib.wm_bilinear_nhwc(_st(), xd.data_ptr(), n, Hi, Wi, c, Ho, Wo, None if pu is None else pu.data_ptr(),
+                                        None if pv is None else pv.data_ptr(), out.data_ptr()))
+        torch.cuda.synchronize()
+        _close(out.cpu().permute(0, 3, 1, 2), ref, f"bilinear {Hi}x{Wi}->{Ho}x{Wo} pos={pos}")
+    # ConvTranspose2d(k == stride) = 1x1 convolution to k*k*c channels + scatter
+    for k in (4, 2):
+        wt = _tf(_rand((c, c, k, k), 2, c ** -0.5))
+        b = _rand((c,), 3, 0.1)
+        ref = F.conv_transpose2d(x, wt, b, stride=k)
+        wd = wt.permute(2, 3, 1, 0).reshape(k * k * c, c).contiguous().cuda()
+        bd = b.repeat(k * k).contiguous().cuda()
+        tmp = torch.zeros(n, Hi, Wi, k * k * c, dtype=torch.float32, device="cuda")
+        capi.check(lib.wm_conv2d_nhwc(_st(), xd.data_ptr(), n, Hi, Wi, c, wd.data_ptr(), 1, k * k * c, bd.data_ptr(), None, 0, None, 0,
+                                      tmp.data_ptr()))
+        out = torch.zeros(n, Hi * k, Wi * k, c, dtype=torch.float32, device="cuda")
+        capi.check(lib.wm_pixel_shuffle(_st(), tmp.data_ptr(), n, Hi, Wi, c, k, out.data_ptr()))
+        torch.cuda.synchronize()
+        _close(out.cpu().permute(0, 3, 1, 2), ref, f"conv_transpose k={k}")
+    # stride-2 3x3 = im2col + 1x1 convolution
+    w3 = _tf(_rand((c, c, 3, 3), 4, (9 * c) ** -0.5))
+    b3 = _rand((c,), 5, 0.1)
+    ref = F.conv2d(x, w3, b3, stride=2, padding=1)
+    Ho, Wo = ref.shape[-2:]
+    col = torch.zeros(n, Ho, Wo, 9 * c, dtype=torch.float32, device="cuda")
+    capi.check(lib.wm_im2col_s2(_st(), xd.data_ptr(), n, Hi, Wi, c, col.data_ptr()))
+    w3d = w3.permute(0, 2, 3, 1).reshape(c, 9 * c).contiguous().cuda()
+    b3d = b3.cuda()
+    out = torch.zeros(n, Ho, Wo, c, dtype=torch.float32, device="cuda")
+    capi.check(lib.wm_conv2d_nhwc(_st(), col.data_ptr(), n, Ho, Wo, 9 * c, w3d.data_ptr(), 1, c, b3d.data_ptr(), None, 0, None, 0,
+                                  out.data_ptr()))
+    torch.cuda.synchronize()
+    _close(out.cpu().permute(0, 3, 1, 2), ref, "conv3x3 stride 2")
+    # LayerNorm(2048) of gathered rows
+    S, P, psi, Cd = 3, 40, 7, 2048
+    t = _rand((S, P, Cd), 6)
+    lw, lb = 1 + _rand((Cd,), 7, 0.1), _rand((Cd,), 8, 0.1)
+    ref = O.layer_norm(t[:, psi:], lw, lb, 1e-5)
+    td, lwd, lbd = t.cuda(), lw.cuda(), lb.cuda()
+    y = torch.zeros(S, P - psi, Cd, dtype=torch.float32, device="cuda")
+    capi.check(lib.wm_layernorm_rows(_st(), td.data_ptr(), lwd.data_ptr(), lbd.data_ptr(), 1e-5, S * (P - psi), P - psi, P, psi,
+                                     Cd, y.data_ptr()))
+    torch.cuda.synchronize()
+    _close(y.cpu(), ref, "layernorm rows 2048")
+
+
+@pytest.mark.parametrize("name,pre,od", [("depth", "depth_head.", 2), ("pts3d", "pts_head.", 4), ("normals", "norm_head.", 4)])
+def test_dpt_head_matches_reference_golden(name, pre, od, state_dict_full):
+    """B200DPTHead on the fp32 oracle aggregator's tokens (pinned to the reference) against what the REFERENCE DPTHead
+    produced from the reference tokens.  Gate: rel. Frobenius <= 2e-3 (tf32 operands, fp32 accumulation and storage)."""
+    fx = np.load(os.path.join(GOLDEN, "c1_heads.npz"))
+    st = int(fx["stride"])
+    hsd = W.synthetic_heads_state_dict(seed=0)
+    imgs = W.synthetic_images(2, 252, 252, seed=1)
+    with torch.no_grad():
+        toks, psi = O.aggregator_forward(imgs, state_dict_full)
+    head = heads.B200DPTHead(dim_in=2048, output_dim=od, activation=HO.HEAD_ACTIVATIONS[pre])
+    head.load_state_dict({k[len(pre):]: v for k, v in hsd.items() if k.startswith(pre)})
+    pred, conf = head([t.cuda() for t in toks], imgs.cuda(), psi)
+    torch.cuda.synchronize()
+    assert tuple(pred.shape) == (1, 2, 252, 252, od - 1) and tuple(conf.shape) == (1, 2, 252, 252)
+    got, ref = pred[0, :, ::st, ::st].cpu().numpy(), fx[name + "_sub"]
+    gc, rc = conf[0, :, ::st, ::st].cpu().numpy(), fx[name + "_conf_sub"]
+    e = np.linalg.norm(got - ref) / np.linalg.norm(ref)
+    ec = np.linalg.norm(gc - rc) / np.linalg.norm(rc)
+    rs = np.abs(pred[0].sum(dim=2).cpu().numpy() - fx[name + "_rowsum"]).max() / (252 * float(fx[name + "_absmean"]))
+    print(f"{name}: rel fro {e:.3e}, conf rel fro {ec:.3e}, row-sum dev {rs:.3e}")
+    assert np.isfinite(got).all() and e <= 2e-3 and ec <= 2e-3 and rs <= 5e-3
