@@ -72,6 +72,11 @@ SIGNATURES = {
     "wm_bilinear_nhwc": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _i, _fp, _fp, _vp]),
     "wm_pixel_shuffle": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "wm_im2col_s2": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "wm_skinny_linear": (C.c_int, [_vp, _fp, _i, _fp, _fp, _i, _i, _i, _i, _i, _fp, _fp, _fp, _i]),
+    "wm_cam_layernorm": (C.c_int, [_vp, _fp, C.c_longlong, _fp, _fp, _f, _i, _fp, _fp]),
+    "wm_cam_attention": (C.c_int, [_vp, _fp, _i, _fp]),
+    "wm_cam_embed": (C.c_int, [_vp, _fp, _i, _i, _fp, _fp, _i, _i, _fp]),
+    "wm_cam_predict": (C.c_int, [_vp, _fp, _i, _fp, _fp, _i, _i, _fp, _fp]),
     "wm_pack_bf16": (C.c_int, [_vp, _fp, C.c_longlong, _i, _i, _vp]),
 }
 

@@ -965,6 +965,40 @@ wm_status wm_im2col_s2(wm_stream stream, const void* in, int n, int Hi, int Wi, 
   return im2col_s2(static_cast<cudaStream_t>(stream), in, n, Hi, Wi, C, out);
 }
 
+wm_status wm_skinny_linear(wm_stream stream, const float* A, int lda, const float* W, const float* bias, int M, int N, int K,
+                           int silu_in, int act, const float* resid, const float* gamma, float* out, int ldo) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return skinny_linear(static_cast<cudaStream_t>(stream), A, lda, W, bias, M, N, K, silu_in, act, resid, gamma, out, ldo);
+}
+
+wm_status wm_cam_layernorm(wm_stream stream, const float* x, long long in_stride, const float* w, const float* b, float eps, int M,
+                           const float* mod, float* y) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return cam_layernorm(static_cast<cudaStream_t>(stream), x, in_stride, w, b, eps, M, mod, y);
+}
+
+wm_status wm_cam_attention(wm_stream stream, const float* qkv, int S, float* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return cam_attention(static_cast<cudaStream_t>(stream), qkv, S, out);
+}
+
+wm_status wm_cam_embed(wm_stream stream, const float* in, int in_bcast, int K, const float* W, const float* bias, int M, int N,
+                       float* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return cam_embed(static_cast<cudaStream_t>(stream), in, in_bcast, K, W, bias, M, N, out);
+}
+
+wm_status wm_cam_predict(wm_stream stream, const float* h, int K, const float* W, const float* bias, int M, int first, float* pred,
+                         float* act) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return cam_predict(static_cast<cudaStream_t>(stream), h, K, W, bias, M, first, pred, act);
+}
+
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
   int sms;
   WM_TRY(require_sm100(&sms));

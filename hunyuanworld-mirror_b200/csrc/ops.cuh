@@ -40,6 +40,15 @@ wm_status bilinear_nhwc(cudaStream_t st, const void* in, int n, int Hi, int Wi, 
                         const float* pos_v, void* out);
 wm_status pixel_shuffle(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, int k, void* out);
 wm_status im2col_s2(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, void* out);
+// camera head (camhead.cu)
+wm_status skinny_linear(cudaStream_t st, const float* A, int lda, const float* W, const float* bias, int M, int N, int K, int silu_in,
+                        int act, const float* resid, const float* gamma, float* out, int ldo);
+wm_status cam_layernorm(cudaStream_t st, const float* x, long long in_stride, const float* w, const float* b, float eps, int M,
+                        const float* mod, float* y);
+wm_status cam_attention(cudaStream_t st, const float* qkv, int S, float* out);
+wm_status cam_embed(cudaStream_t st, const float* in, int in_bcast, int K, const float* W, const float* bias, int M, int N, float* out);
+wm_status cam_predict(cudaStream_t st, const float* h, int K, const float* W, const float* bias, int M, int first, float* pred,
+                      float* act);
 wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);
 
 }  // namespace wm

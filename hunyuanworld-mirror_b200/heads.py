@@ -217,3 +217,142 @@ class B200DPTHead(torch.nn.Module):
         capi.check(lib.wm_conv2d_final(_st(), fused.data_ptr(), n, H, W, 128, w["oc2.w"].data_ptr(), w["oc2.b"].data_ptr(),
                                        w["oc3.w"].data_ptr(), w["oc3.b"].data_ptr(), self.output_dim, self.act, pred.data_ptr(),
                                        conf.data_ptr()))
+
+
+class B200CameraHead(torch.nn.Module):
+    """Mirror of `CameraHead` (src/models/heads/camera_head.py:10-104): same constructor keywords, `state_dict` keys and
+    `forward(feat_seq, steps=4) -> list of [B, S, 9]` (activated [t(3), quat xyzw(4), fov(2)] of every refinement step).
+    fp32 throughout, like the reference (worldmirror.py:146); every linear layer is a weight-streaming skinny GEMM
+    (csrc/camhead.cu).  Under sequence parallelism pass the camera tokens of ALL views (the trunk attends across views,
+    camera_head.py:73,92): `hunyuanworld-mirror_b200.parallel.gather_outputs`."""
+
+    def __init__(self, dim_in: int = 2048, trunk_depth: int = 4, num_heads: int = 16, mlp_ratio: int = 4, init_values: float = 0.01,
+                 trans_act: str = "linear", quat_act: str = "linear", fl_act: str = "relu"):
+        super().__init__()
+        if (dim_in, num_heads, mlp_ratio) != (2048, 16, 4) or (trans_act, quat_act, fl_act) != ("linear", "linear", "relu"):
+            raise NotImplementedError("B200CameraHead is built for WorldMirror's configuration (dim 2048, 16 heads, linear/linear/relu)")
+        self.dim, self.depth = dim_in, trunk_depth
+        self.w: Dict[str, torch.Tensor] = {}
+        self._loaded = False
+
+    def load_state_dict(self, sd, strict: bool = True, device=None):
+        capi.lib()
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        need = ["init_token", "token_norm.weight", "token_norm.bias", "out_norm.weight", "out_norm.bias", "param_embed.weight",
+                "param_embed.bias", "adapt_norm_gen.1.weight", "adapt_norm_gen.1.bias", "param_predictor.fc1.weight",
+                "param_predictor.fc1.bias", "param_predictor.fc2.weight", "param_predictor.fc2.bias"]
+        for i in range(self.depth):
+            need += [f"refine_net.{i}.{k}" for k in ("norm1.weight", "norm1.bias", "attn.qkv.weight", "attn.qkv.bias", "attn.proj.weight",
+                                                     "attn.proj.bias", "ls1.gamma", "norm2.weight", "norm2.bias", "mlp.fc1.weight",
+                                                     "mlp.fc1.bias", "mlp.fc2.weight", "mlp.fc2.bias", "ls2.gamma")]
+        missing = [k for k in need if k not in sd]
+        if missing:
+            raise RuntimeError(f"Missing key(s) in state_dict: {missing[:4]}...")
+        self.w = {k: sd[k].detach().to(dev, torch.float32).contiguous() for k in need}
+        self._loaded = True
+        return torch.nn.modules.module._IncompatibleKeys([], [k for k in sd if k not in need])
+
+    def _linear(self, x, key, M, silu_in=0, act=0, resid=None, gamma=None, out=None):
+        W, b = self.w[key + ".weight"], self.w[key + ".bias"]
+        N, K = W.shape
+        if out is None:
+            out = torch.empty(M, N, dtype=torch.float32, device=x.device)
+        capi.check(capi.lib().wm_skinny_linear(_st(), x.data_ptr(), K, W.data_ptr(), b.data_ptr(), M, N, K, silu_in, act, _p(resid),
+                                               _p(gamma), out.data_ptr(), N))
+        return out
+
+    def _ln(self, x, stride, key, eps, M, mod=None):
+        y = torch.empty(M, self.dim, dtype=torch.float32, device=x.device)
+        w = self.w[key + ".weight"] if key else None
+        b = self.w[key + ".bias"] if key else None
+        capi.check(capi.lib().wm_cam_layernorm(_st(), x.data_ptr(), stride, _p(w), _p(b), eps, M, _p(mod), y.data_ptr()))
+        return y
+
+    @torch.no_grad()
+    def forward(self, feat_seq: list, steps: int = 4) -> list:
+        if not self._loaded:
+            raise RuntimeError("B200CameraHead: load_state_dict() has not been called")
+        latest = feat_seq[-1]
+        if not latest.is_cuda:
+            raise RuntimeError("B200CameraHead needs CUDA tensors (there is no CPU path)")
+        B, S, P, Cd = latest.shape
+        assert Cd == self.dim
+        lib, w, dev = capi.lib(), self.w, latest.device
+        outs = [torch.empty(B, S, 9, dtype=torch.float32, device=dev) for _ in range(steps)]
+        with torch.cuda.device(dev):
+            for bi in range(B):
+                feat = latest[bi].to(torch.float32)
+                if not feat.is_contiguous():
+                    feat = feat.contiguous()
+                tok = self._ln(feat, P * Cd, "token_norm", 1e-5, S)  # camera token = row 0 of every view
+                pred = torch.empty(S, 9, dtype=torch.float32, device=dev)
+                emb = torch.empty(S, Cd, dtype=torch.float32, device=dev)
+                for step in range(steps):
+                    src = w["init_token"] if step == 0 else pred
+                    capi.check(lib.wm_cam_embed(_st(), src.data_ptr(), int(step == 0), 9, w["param_embed.weight"].data_ptr(),
+                                                w["param_embed.bias"].data_ptr(), S, Cd, emb.data_ptr()))
+                    mod = self._linear(emb, "adapt_norm_gen.1", S, silu_in=1)
+                    x = self._ln(tok, Cd, None, 1e-6, S, mod=mod)
+                    for i in range(self.depth):
+                        p = f"refine_net.{i}."
+                        n1 = self._ln(x, Cd, p + "norm1", 1e-5, S)
+                        qkv = self._linear(n1, p + "attn.qkv", S)
+                        att = torch.empty(S, Cd, dtype=torch.float32, device=dev)
+                        capi.check(lib.wm_cam_attention(_st(), qkv.data_ptr(), S, att.data_ptr()))
+                        self._linear(att, p + "attn.proj", S, resid=x, gamma=w[p + "ls1.gamma"], out=x)
+                        n2 = self._ln(x, Cd, p + "norm2", 1e-5, S)
+                        hid = self._linear(n2, p + "mlp.fc1", S, act=1)
+                        self._linear(hid, p + "mlp.fc2", S, resid=x, gamma=w[p + "ls2.gamma"], out=x)
+                    xo = self._ln(x, Cd, "out_norm", 1e-5, S)
+                    hid = self._linear(xo, "param_predictor.fc1", S, act=1)
+                    capi.check(lib.wm_cam_predict(_st(), hid.data_ptr(), hid.shape[1], w["param_predictor.fc2.weight"].data_ptr(),
+                                                  w["param_predictor.fc2.bias"].data_ptr(), S, int(step == 0), pred.data_ptr(),
+                                                  outs[step][bi].data_ptr()))
+        return outs
+
+
+class B200WorldMirror(torch.nn.Module):
+    """`WorldMirror.forward` (src/models/models/worldmirror.py:120-196) on the B200 path: aggregator, camera head and the
+    depth / points / normals DPT heads, same `views` dictionary in, same prediction keys out (`camera_params`, `depth`,
+    `depth_conf`, `pts3d`, `pts3d_conf`, `normals`, `normals_conf`).  `priors` are the already normalised tensors
+    (depth, rays, poses) that `extract_priors` (worldmirror.py:218-251) produces; the Gaussian branch is not part of this
+    path."""
+
+    def __init__(self, aggregator, cam_head=None, depth_head=None, pts_head=None, norm_head=None):
+        super().__init__()
+        self.visual_geometry_transformer = aggregator
+        self.cam_head, self.depth_head, self.pts_head, self.norm_head = cam_head, depth_head, pts_head, norm_head
+
+    @classmethod
+    def from_state_dicts(cls, aggregator_sd, heads_sd, **agg_kwargs):
+        from .aggregator import B200VisualGeometryTransformer
+
+        agg = B200VisualGeometryTransformer(**agg_kwargs)
+        agg.load_state_dict(aggregator_sd)
+
+        def sub(p):
+            return {k[len(p):]: v for k, v in heads_sd.items() if k.startswith(p)}
+
+        cam = B200CameraHead(dim_in=2048)
+        cam.load_state_dict(sub("cam_head."))
+        heads = {}
+        for name, od, act in (("depth_head", 2, "exp+expp1"), ("pts_head", 4, "inv_log+expp1"), ("norm_head", 4, "norm+expp1")):
+            h = B200DPTHead(dim_in=2048, output_dim=od, activation=act)
+            h.load_state_dict(sub(name + "."))
+            heads[name] = h
+        return cls(agg, cam, heads["depth_head"], heads["pts_head"], heads["norm_head"])
+
+    @torch.no_grad()
+    def forward(self, views, cond_flags=(0, 0, 0), priors=None):
+        imgs = views["img"]
+        if sum(cond_flags) > 0 and priors is not None:
+            token_list, psi = self.visual_geometry_transformer(imgs, priors, cond_flags=list(cond_flags))
+        else:
+            token_list, psi = self.visual_geometry_transformer(imgs)
+        preds = {}
+        if self.cam_head is not None:
+            preds["camera_params"] = self.cam_head(token_list)[-1]
+        for name, head in (("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head)):
+            if head is not None:
+                preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
+        return preds

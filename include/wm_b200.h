@@ -219,6 +219,26 @@ wm_status wm_pixel_shuffle(wm_stream stream, const void* in, int n, int Hi, int 
 /* im2col of nn.Conv2d(C, C, 3, stride 2, padding 1) (dense_head.py:66-68): -> [n*Ho*Wo, 9*C], Ho = (Hi-1)/2 + 1. */
 wm_status wm_im2col_s2(wm_stream stream, const void* in, int n, int Hi, int Wi, int C, void* out);
 
+/* ---- camera head: CameraHead (src/models/heads/camera_head.py:58-104), fp32 ---- */
+/* nn.Linear on M = views rows (HBM-bound: streams W [N, K] once): out = epi(f(A) W^T + bias); silu_in: f = SiLU
+ * (adapt_norm_gen, :49); act 1: exact-erf GELU (Mlp.fc1); resid/gamma non-NULL: out = resid + gamma * (.)
+ * (LayerScale + residual of Block, block.py:91-92; out may alias resid).  K % 128 == 0. */
+wm_status wm_skinny_linear(wm_stream stream, const float* A, int lda, const float* W, const float* bias, int M, int N, int K,
+                           int silu_in, int act, const float* resid, const float* gamma, float* out, int ldo);
+/* nn.LayerNorm(2048) fp32 of rows `in_stride` floats apart (the camera token of each view, :72-73); w/b NULL: no affine
+ * (adapt_norm, :52); mod [M, 3*2048] = [shift | scale | gate] non-NULL: y = gate * (LN(x) * (1 + scale) + shift) + x (:81-83). */
+wm_status wm_cam_layernorm(wm_stream stream, const float* x, long long in_stride, const float* w, const float* b, float eps, int M,
+                           const float* mod, float* y);
+/* Attention.forward over the S camera tokens, 16 heads of 128, no QK-norm / RoPE: qkv [S, 6144] -> out [S, 2048]. */
+wm_status wm_cam_attention(wm_stream stream, const float* qkv, int S, float* out);
+/* param_embed = nn.Linear(9, 2048) (:47, 77-80); in_bcast: `in` is the shared init_token [K]. */
+wm_status wm_cam_embed(wm_stream stream, const float* in, int in_bcast, int K, const float* W, const float* bias, int M, int N,
+                       float* out);
+/* param_predictor.fc2 (1024 -> 9) + running sum + activations (:88-99, 106-126): pred [M, 9] is updated in place (set
+ * when first != 0), act [M, 9] = [t(3), quat(4), relu(fov)(2)]. */
+wm_status wm_cam_predict(wm_stream stream, const float* h, int K, const float* W, const float* bias, int M, int first, float* pred,
+                         float* act);
+
 #ifdef __cplusplus
 }
 #endif

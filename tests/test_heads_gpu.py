@@ -178,3 +178,59 @@ def test_dpt_head_matches_reference_golden(name, pre, od, state_dict_full):
     rs = np.abs(pred[0].sum(dim=2).cpu().numpy() - fx[name + "_rowsum"]).max() / (252 * float(fx[name + "_absmean"]))
     print(f"{name}: rel fro {e:.3e}, conf rel fro {ec:.3e}, row-sum dev {rs:.3e}")
     assert np.isfinite(got).all() and e <= 2e-3 and ec <= 2e-3 and rs <= 5e-3
+
+
+def test_camera_head_matches_reference_golden():
+    """B200CameraHead (fp32 SIMT) on the reference's own camera tokens against the reference CameraHead's four
+    refinement steps: fp32 vs fp32, different summation order only."""
+    fx = np.load(os.path.join(GOLDEN, "c1_heads.npz"))
+    hsd = W.synthetic_heads_state_dict(seed=0)
+    cam = heads.B200CameraHead(dim_in=2048)
+    cam.load_state_dict({k[len("cam_head."):]: v for k, v in hsd.items() if k.startswith("cam_head.")})
+    S = fx["cam_tokens"].shape[1]
+    feat = torch.zeros(1, S, 5, 2048)  # the camera token is row 0 of every view; other rows must not matter
+    feat[:, :, 0] = torch.from_numpy(fx["cam_tokens"])
+    feat[:, :, 1:] = 7.0
+    seq = cam([feat.cuda()])
+    torch.cuda.synchronize()
+    got = torch.stack(seq, 0).cpu().numpy()
+    np.testing.assert_allclose(got, fx["camera_params_steps"], atol=3e-4, rtol=2e-4)
+    ang = HO.quat_angle(torch.from_numpy(got[-1][..., 3:7]), torch.from_numpy(fx["camera_params_steps"][-1][..., 3:7])).max().item()
+    print(f"camera head vs reference: max abs {np.abs(got - fx['camera_params_steps']).max():.3e}, rotation {ang:.3e} rad")
+    assert ang < 1e-4
+
+
+def test_camera_head_many_views_matches_oracle():
+    """S = 21 views (three row tiles of the skinny GEMM, a ragged last one) against the fp32 oracle."""
+    hsd = W.synthetic_heads_state_dict(seed=0)
+    cam = heads.B200CameraHead(dim_in=2048)
+    cam.load_state_dict({k[len("cam_head."):]: v for k, v in hsd.items() if k.startswith("cam_head.")})
+    toks = _rand((1, 21, 2048), 11)
+    with torch.no_grad():
+        ref = HO.camera_head(toks, hsd)
+    seq = cam([toks[:, :, None].contiguous().cuda()])
+    torch.cuda.synchronize()
+    for a, b in zip(seq, ref):
+        np.testing.assert_allclose(a.cpu().numpy(), b.numpy(), atol=3e-4, rtol=2e-4)
+
+
+def test_worldmirror_forward_end_to_end(state_dict_full):
+    """The whole B200 path (bf16 aggregator, fp32 camera head, tf32 DPT heads) against the REFERENCE aggregator +
+    REFERENCE heads (tests/golden/c1_heads.npz), BASELINE.json config 1 shapes.  Gates as in
+    tests/test_parity_gpu.py::test_north_star_tolerances_end_to_end."""
+    fx = np.load(os.path.join(GOLDEN, "c1_heads.npz"))
+    st = int(fx["stride"])
+    model = heads.B200WorldMirror.from_state_dicts(state_dict_full, W.synthetic_heads_state_dict(seed=0))
+    preds = model({"img": W.synthetic_images(2, 252, 252, seed=1).cuda()})
+    torch.cuda.synchronize()
+    for name in ("depth", "pts3d", "normals"):
+        got, ref = preds[name][0, :, ::st, ::st].cpu().numpy(), fx[name + "_sub"]
+        e = np.linalg.norm(got - ref) / np.linalg.norm(ref)
+        eps = 1e-2 * np.median(np.abs(ref))
+        mr = (np.abs(got - ref) / np.maximum(np.abs(ref), eps)).max()
+        print(f"e2e {name}: rel fro {e:.3e} max-rel {mr:.3e}")
+        assert np.isfinite(got).all() and e <= 1e-2
+    cam_ref = torch.from_numpy(fx["camera_params_steps"][-1])
+    ang = HO.quat_angle(preds["camera_params"].cpu()[..., 3:7], cam_ref[..., 3:7]).max().item()
+    print(f"e2e camera rotation {ang:.3e} rad")
+    assert ang <= 1e-3
