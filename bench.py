@@ -5,13 +5,14 @@
     torchrun ... bench.py --gpus N --steps K --warmup W      # N ranks: views sharded, K|V all-gather (NCCL)
     python bench.py --impl reference --steps K --warmup W    # the reference algorithm on the host cores
 
-A step is one forward of the aggregator (DINOv2 patch embedding, token assembly, 24 x (frame block, global
-block), four [S,P,2048] fp32 outputs) on synthetic images with seeded random weights of the reference schema.
-N = 1 runs BASELINE.json configs[1]'s aggregator workload (8 views, 518x518, no priors); N > 1 keeps 8 views
-per rank (one scene of 8N views; frame attention local, global attention over all ranks' K|V).
+A step is one WorldMirror forward (worldmirror.py:120-196 without the Gaussian branch): the aggregator (DINOv2 patch
+embedding, token assembly, 24 x (frame block, global block)), the camera head and the depth / points / normals DPT
+heads, on synthetic images with seeded random weights of the reference schema.  `--no-heads` times the aggregator alone.
+N = 1 runs BASELINE.json configs[1] (8 views, 518x518, no priors, all heads); N > 1 keeps 8 views
+per rank (one scene of 8N views; frame attention and DPT heads local, global attention over all ranks' K|V).
 `value` times the forward with the images already in HBM (CUDA events, max over ranks); `e2e` times the same
-forward through the module's public call with images in pinned host memory and a device->host read of the
-camera tokens inside the timed region.  One JSON line on stdout (rank 0).
+forward through the module's public call with images in pinned host memory and a device->host read of every
+prediction inside the timed region.  One JSON line on stdout (rank 0).
 """
 import argparse
 import importlib
@@ -27,7 +28,7 @@ sys.path.insert(0, ROOT)
 
 VIEWS_PER_RANK = 8
 SIZE = 518
-METRIC = "views/sec, WorldMirror aggregator fwd 518px"
+METRIC = "views/sec, WorldMirror fwd 518px"
 
 
 def flops_aggregator(n_local, n_total, P=1376):
@@ -92,7 +93,7 @@ class ClockSampler:
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def cpu_reference_steps(n_views, steps, warmup):
+def cpu_reference_steps(n_views, steps, warmup, with_heads=True):
     """The reference algorithm on the host cores: oracle/aggregator_oracle.py (a restatement pinned against
     the reference's own outputs, tests/golden/) -- /root/reference is Python and does not travel to the GPU box."""
     import torch
@@ -102,13 +103,18 @@ def cpu_reference_steps(n_views, steps, warmup):
     W = importlib.import_module("hunyuanworld-mirror_b200.weights")
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    from oracle import heads_oracle as HO
+
     sd = W.synthetic_state_dict(seed=0)
+    hsd = W.synthetic_heads_state_dict(seed=0) if with_heads else None
     imgs = W.synthetic_images(n_views, SIZE, SIZE, seed=1)
     times = []
     with torch.no_grad():
         for i in range(warmup + steps):
             t0 = time.perf_counter()
-            O.aggregator_forward(imgs, sd)
+            toks, _ = O.aggregator_forward(imgs, sd)
+            if with_heads:
+                HO.all_heads(toks, SIZE, SIZE, hsd)
             if i >= warmup:
                 times.append(time.perf_counter() - t0)
     return times, cores
@@ -120,15 +126,15 @@ def run_reference(args):
         return
     # bounded sample of the 8-view workload so that warmup + steps stay within a few minutes (~7 s / view here)
     sample_views = 2 if (args.steps + args.warmup) <= 14 else 1
-    times, cores = cpu_reference_steps(sample_views, args.steps, args.warmup)
+    times, cores = cpu_reference_steps(sample_views, args.steps, args.warmup, not args.no_heads)
     total = sum(times)
     value = sample_views * len(times) / total
-    sample = (f"{sample_views} of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth (24 DINOv2 + 24x2 blocks), fp32, "
+    sample = (f"{sample_views} of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth (24 DINOv2 + 24x2 blocks{'' if args.no_heads else ' + camera and 3 DPT heads'}), fp32, "
               f"{len(times)} timed forwards; global attention spans the sampled views only")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "views/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"aggregator fwd, {VIEWS_PER_RANK} views {SIZE}x{SIZE}, no priors (BASELINE configs[1])",
+            "config": {"workload": f"WorldMirror fwd, {VIEWS_PER_RANK} views {SIZE}x{SIZE}, no priors (BASELINE configs[1])",
                        "views_per_gpu": VIEWS_PER_RANK, "size": SIZE},
             "cpu_baseline": {"value": value, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -152,8 +158,11 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
+    heads_on = not args.no_heads
     model = pkg.B200VisualGeometryTransformer()
     model.load_state_dict(W.synthetic_state_dict(seed=0))
+    full = pkg.B200WorldMirror.from_state_dicts(None, W.synthetic_heads_state_dict(seed=0), aggregator=model) if heads_on else None
+    H = pkg.heads
     if world > 1:
         model.init_sequence_parallel()
     for kv in args.set:  # library tuning knobs (wm_set_int), e.g. --set attn_bounded_variant=10
@@ -187,11 +196,18 @@ def run_b200(args):
 
     # ---- value: images resident in HBM
     def step_resident():
-        model(imgs_dev)
+        if heads_on:
+            full({"img": imgs_dev})
+        else:
+            model(imgs_dev)
 
     with ClockSampler(local_rank) as clocks:
         total_ms = timed(step_resident, args.steps, max(args.warmup, 3), prof_mask=1 << 3)
-    launches = lib.wm_launch_count(model._handle) // args.steps
+    head_launches = H.LAUNCHES[0]
+    H.LAUNCHES[0] = 0
+    step_resident()
+    head_launches = H.LAUNCHES[0]  # per step, counted on one extra forward
+    launches = lib.wm_launch_count(model._handle) // (args.steps + 1) + head_launches
     attn_ms, attn_n = capi.C.c_float(), capi.C.c_int()
     capi.check(lib.wm_profile_read(model._handle, 3, capi.C.byref(attn_ms), capi.C.byref(attn_n)))
     ms_per_step = total_ms / args.steps
@@ -209,19 +225,45 @@ def run_b200(args):
         if cnt.value:
             breakdown[name] = {"ms": round(ms.value, 4), "launches": cnt.value}
     capi.check(lib.wm_profile(model._handle, 0))
+    if heads_on:  # heads are launched from Python: time them with events on the same stream
+        toks, psi = model(imgs_dev)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        ev[0].record()
+        full.cam_head(toks)
+        ev[1].record()
+        for i, hd in enumerate((full.depth_head, full.pts_head, full.norm_head)):
+            hd(toks, images=imgs_dev, patch_start_idx=psi)
+            ev[2 + i].record()
+        torch.cuda.synchronize()
+        breakdown["camera_head"] = {"ms": round(ev[0].elapsed_time(ev[1]), 4), "launches": None}
+        for i, nm in enumerate(("dpt_depth", "dpt_points", "dpt_normals")):
+            breakdown[nm] = {"ms": round(ev[1 + i].elapsed_time(ev[2 + i]), 4), "launches": None}
+        del toks
 
     # ---- e2e: pinned host images -> device every step, camera tokens read back every step
-    cam_host = torch.empty(1, n_local, 2048, dtype=torch.float32).pin_memory()
+    if heads_on:
+        shapes = {"camera_params": (1, n_local, 9), "depth": (1, n_local, SIZE, SIZE, 1), "depth_conf": (1, n_local, SIZE, SIZE),
+                  "pts3d": (1, n_local, SIZE, SIZE, 3), "pts3d_conf": (1, n_local, SIZE, SIZE),
+                  "normals": (1, n_local, SIZE, SIZE, 3), "normals_conf": (1, n_local, SIZE, SIZE)}
+    else:
+        shapes = {"cam_tokens": (1, n_local, 2048)}
+    host_out = {k: torch.empty(v, dtype=torch.float32).pin_memory() for k, v in shapes.items()}
+    d2h_bytes = sum(t.numel() * 4 for t in host_out.values())
 
     def step_e2e():
         x = imgs_host.to(dev, non_blocking=True)
-        outs, _ = model(x)
-        cam_host.copy_(outs[-1][:, :, 0], non_blocking=True)
+        if heads_on:
+            preds = full({"img": x})
+            for k, t in host_out.items():
+                t.copy_(preds[k], non_blocking=True)
+        else:
+            outs, _ = model(x)
+            host_out["cam_tokens"].copy_(outs[-1][:, :, 0], non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
     e2e_ms = timed(step_e2e, args.steps, 3) / args.steps
     e2e = {"value": n_total / (e2e_ms * 1e-3), "unit": "views/s", "h2d_bytes_per_step": imgs_host.numel() * 4,
-           "d2h_bytes_per_step": cam_host.numel() * 4, "ms_per_step": e2e_ms}
+           "d2h_bytes_per_step": d2h_bytes, "ms_per_step": e2e_ms}
 
     sp_exchange = None
     if world > 1:
@@ -254,17 +296,21 @@ def run_b200(args):
                     "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
                     "traffic": traffic, "peak_source": peak_src, "avg_launch_ms": attn_avg_ms, "launches_timed": attn_n.value,
                     "share_of_step": attn_ms.value / total_ms,
-                    "whole_step_tflops": fl["total"] / (ms_per_step * 1e-3) / 1e12}
+                    "whole_step_tflops": None if heads_on else fl["total"] / (ms_per_step * 1e-3) / 1e12}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            t, cores = cpu_reference_steps(2, 1, 0)
+            t, cores = cpu_reference_steps(2, 1, 0, heads_on)
             cpu = {"value": 2 / t[0], "unit": "views/s", "cores": cores, "kind": "port",
-                   "sample": f"2 of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth, fp32, one forward ({t[0]:.1f} s); oracle/aggregator_oracle.py"}
+                   "sample": f"2 of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth{' + camera and 3 DPT heads' if heads_on else ''}, fp32, "
+                             f"one forward ({t[0]:.1f} s); oracle/aggregator_oracle.py{' + oracle/heads_oracle.py' if heads_on else ''}"}
         line = {"metric": METRIC, "value": value, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic",
-                "config": {"workload": f"aggregator fwd (DINOv2 ViT-L/14 + 24x(frame,global) blocks), {n_local} views/GPU x {world} GPU = "
-                                       f"{n_total} views {SIZE}x{SIZE}, no priors (BASELINE configs[1] at N=1; heads out of scope, SURVEY 8f)",
+                "config": {"workload": f"WorldMirror fwd: aggregator (DINOv2 ViT-L/14 + 24x(frame,global) blocks)"
+                                       f"{' + camera head + depth/points/normals DPT heads' if heads_on else ' only (--no-heads)'}, "
+                                       f"{n_local} views/GPU x {world} GPU = {n_total} views {SIZE}x{SIZE}, no priors "
+                                       f"(BASELINE configs[1] at N=1; Gaussian head not built, SURVEY 8f row 3)",
+                           "heads": heads_on, "head_dtype": "camera fp32, DPT tf32 (fp32 accumulate)" if heads_on else None,
                            "views_per_gpu": n_local, "views_total": n_total, "size": SIZE, "tokens_per_view": 1376,
                            "parallelism": f"views sharded; global attention: {sp_exchange}" if world > 1 else "single GPU",
                            "l2": "per-step working set (1.8 GB bf16 weights + activations) exceeds the 126 MB L2; no flush needed"},
@@ -285,6 +331,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--views", type=int, default=VIEWS_PER_RANK, help="views per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-heads", action="store_true", help="time the aggregator alone (the round-1 workload before the heads existed)")
     ap.add_argument("--set", action="append", default=[], metavar="KNOB=INT", help="wm_set_int tuning knob (repeatable)")
     args = ap.parse_args()
     if args.impl == "reference":

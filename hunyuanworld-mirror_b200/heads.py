@@ -26,6 +26,13 @@ from . import capi
 
 PATCH = 14
 _ACT = {"exp": 0, "inv_log": 1, "norm": 2}
+LAUNCHES = [0]  # kernels launched by the heads since the caller last reset it (bench.py: gpu_launches)
+
+
+def _k(status: int) -> None:
+    """Check the status of one kernel-launching library call and count it."""
+    capi.check(status)
+    LAUNCHES[0] += 1
 
 
 def _st():
@@ -132,13 +139,13 @@ class B200DPTHead(torch.nn.Module):
     # ------------------------------------------------------------------ ops
     def _conv(self, x, n, H, W, cin, wkey, taps, cout, bias=None, res1=None, bcast=0, res2=None, relu=0):
         out = torch.empty(n, H, W, cout, dtype=torch.float32, device=x.device)
-        capi.check(capi.lib().wm_conv2d_nhwc(_st(), x.data_ptr(), n, H, W, cin, self.w[wkey].data_ptr(), taps, cout, _p(bias),
+        _k(capi.lib().wm_conv2d_nhwc(_st(), x.data_ptr(), n, H, W, cin, self.w[wkey].data_ptr(), taps, cout, _p(bias),
                                              _p(res1), bcast, _p(res2), relu, out.data_ptr()))
         return out
 
     def _resize(self, x, n, Hi, Wi, c, Ho, Wo, pu=None, pv=None):
         out = torch.empty(n, Ho, Wo, c, dtype=torch.float32, device=x.device)
-        capi.check(capi.lib().wm_bilinear_nhwc(_st(), x.data_ptr(), n, Hi, Wi, c, Ho, Wo, _p(pu), _p(pv), out.data_ptr()))
+        _k(capi.lib().wm_bilinear_nhwc(_st(), x.data_ptr(), n, Hi, Wi, c, Ho, Wo, _p(pu), _p(pv), out.data_ptr()))
         return out
 
     def _rcu(self, r, unit, x, n, H, W, extra=None, relu_out=0):
@@ -180,7 +187,7 @@ class B200DPTHead(torch.nn.Module):
         for i, t in enumerate(toks):
             t = t.to(torch.float32).contiguous()
             ln = torch.empty(n, gh, gw, Cd, dtype=torch.float32, device=dev)
-            capi.check(lib.wm_layernorm_rows(_st(), t.data_ptr(), w["norm.w"].data_ptr(), w["norm.b"].data_ptr(), 1e-5, n * g, g, P,
+            _k(lib.wm_layernorm_rows(_st(), t.data_ptr(), w["norm.w"].data_ptr(), w["norm.b"].data_ptr(), 1e-5, n * g, g, P,
                                              psi, Cd, ln.data_ptr()))
             c = self.oc[i]
             f = self._conv(ln, n, gh, gw, Cd, f"proj{i}.w", 1, c, w[f"proj{i}.b"], res1=tabs[i], bcast=1)
@@ -189,12 +196,12 @@ class B200DPTHead(torch.nn.Module):
                 k = 4 if i == 0 else 2
                 tmp = self._conv(f, n, gh, gw, c, f"up{i}.w", 1, k * k * c, w[f"up{i}.b"])
                 f = torch.empty(n, gh * k, gw * k, c, dtype=torch.float32, device=dev)
-                capi.check(lib.wm_pixel_shuffle(_st(), tmp.data_ptr(), n, gh, gw, c, k, f.data_ptr()))
+                _k(lib.wm_pixel_shuffle(_st(), tmp.data_ptr(), n, gh, gw, c, k, f.data_ptr()))
                 h_, w_ = gh * k, gw * k
             elif i == 3:  # Conv2d(c, c, 3, stride 2, padding 1) = im2col + 1x1 convolution over 9c channels
                 h_, w_ = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
                 col = torch.empty(n, h_, w_, 9 * c, dtype=torch.float32, device=dev)
-                capi.check(lib.wm_im2col_s2(_st(), f.data_ptr(), n, gh, gw, c, col.data_ptr()))
+                _k(lib.wm_im2col_s2(_st(), f.data_ptr(), n, gh, gw, c, col.data_ptr()))
                 f = self._conv(col, n, h_, w_, 9 * c, "down3.w", 1, c, w["down3.b"])
             # scratch.layer{i}_rn (no bias); only relu(rn) is ever read (in-place ReLU of the consuming RCU)
             rn.append(self._conv(f, n, h_, w_, c, f"rn{i}.w", 9, 256, relu=1))
@@ -214,7 +221,7 @@ class B200DPTHead(torch.nn.Module):
             hp, wp = ho, wo
         o1 = self._conv(path, n, hp, wp, 256, "oc1.w", 9, 128, w["oc1.b"])
         fused = self._resize(o1, n, hp, wp, 128, gh * PATCH, gw * PATCH, pu, pv)
-        capi.check(lib.wm_conv2d_final(_st(), fused.data_ptr(), n, H, W, 128, w["oc2.w"].data_ptr(), w["oc2.b"].data_ptr(),
+        _k(lib.wm_conv2d_final(_st(), fused.data_ptr(), n, H, W, 128, w["oc2.w"].data_ptr(), w["oc2.b"].data_ptr(),
                                        w["oc3.w"].data_ptr(), w["oc3.b"].data_ptr(), self.output_dim, self.act, pred.data_ptr(),
                                        conf.data_ptr()))
 
@@ -257,7 +264,7 @@ class B200CameraHead(torch.nn.Module):
         N, K = W.shape
         if out is None:
             out = torch.empty(M, N, dtype=torch.float32, device=x.device)
-        capi.check(capi.lib().wm_skinny_linear(_st(), x.data_ptr(), K, W.data_ptr(), b.data_ptr(), M, N, K, silu_in, act, _p(resid),
+        _k(capi.lib().wm_skinny_linear(_st(), x.data_ptr(), K, W.data_ptr(), b.data_ptr(), M, N, K, silu_in, act, _p(resid),
                                                _p(gamma), out.data_ptr(), N))
         return out
 
@@ -265,7 +272,7 @@ class B200CameraHead(torch.nn.Module):
         y = torch.empty(M, self.dim, dtype=torch.float32, device=x.device)
         w = self.w[key + ".weight"] if key else None
         b = self.w[key + ".bias"] if key else None
-        capi.check(capi.lib().wm_cam_layernorm(_st(), x.data_ptr(), stride, _p(w), _p(b), eps, M, _p(mod), y.data_ptr()))
+        _k(capi.lib().wm_cam_layernorm(_st(), x.data_ptr(), stride, _p(w), _p(b), eps, M, _p(mod), y.data_ptr()))
         return y
 
     @torch.no_grad()
@@ -289,7 +296,7 @@ class B200CameraHead(torch.nn.Module):
                 emb = torch.empty(S, Cd, dtype=torch.float32, device=dev)
                 for step in range(steps):
                     src = w["init_token"] if step == 0 else pred
-                    capi.check(lib.wm_cam_embed(_st(), src.data_ptr(), int(step == 0), 9, w["param_embed.weight"].data_ptr(),
+                    _k(lib.wm_cam_embed(_st(), src.data_ptr(), int(step == 0), 9, w["param_embed.weight"].data_ptr(),
                                                 w["param_embed.bias"].data_ptr(), S, Cd, emb.data_ptr()))
                     mod = self._linear(emb, "adapt_norm_gen.1", S, silu_in=1)
                     x = self._ln(tok, Cd, None, 1e-6, S, mod=mod)
@@ -298,14 +305,14 @@ class B200CameraHead(torch.nn.Module):
                         n1 = self._ln(x, Cd, p + "norm1", 1e-5, S)
                         qkv = self._linear(n1, p + "attn.qkv", S)
                         att = torch.empty(S, Cd, dtype=torch.float32, device=dev)
-                        capi.check(lib.wm_cam_attention(_st(), qkv.data_ptr(), S, att.data_ptr()))
+                        _k(lib.wm_cam_attention(_st(), qkv.data_ptr(), S, att.data_ptr()))
                         self._linear(att, p + "attn.proj", S, resid=x, gamma=w[p + "ls1.gamma"], out=x)
                         n2 = self._ln(x, Cd, p + "norm2", 1e-5, S)
                         hid = self._linear(n2, p + "mlp.fc1", S, act=1)
                         self._linear(hid, p + "mlp.fc2", S, resid=x, gamma=w[p + "ls2.gamma"], out=x)
                     xo = self._ln(x, Cd, "out_norm", 1e-5, S)
                     hid = self._linear(xo, "param_predictor.fc1", S, act=1)
-                    capi.check(lib.wm_cam_predict(_st(), hid.data_ptr(), hid.shape[1], w["param_predictor.fc2.weight"].data_ptr(),
+                    _k(lib.wm_cam_predict(_st(), hid.data_ptr(), hid.shape[1], w["param_predictor.fc2.weight"].data_ptr(),
                                                   w["param_predictor.fc2.bias"].data_ptr(), S, int(step == 0), pred.data_ptr(),
                                                   outs[step][bi].data_ptr()))
         return outs
@@ -324,11 +331,13 @@ class B200WorldMirror(torch.nn.Module):
         self.cam_head, self.depth_head, self.pts_head, self.norm_head = cam_head, depth_head, pts_head, norm_head
 
     @classmethod
-    def from_state_dicts(cls, aggregator_sd, heads_sd, **agg_kwargs):
+    def from_state_dicts(cls, aggregator_sd, heads_sd, aggregator=None, **agg_kwargs):
         from .aggregator import B200VisualGeometryTransformer
 
-        agg = B200VisualGeometryTransformer(**agg_kwargs)
-        agg.load_state_dict(aggregator_sd)
+        agg = aggregator
+        if agg is None:
+            agg = B200VisualGeometryTransformer(**agg_kwargs)
+            agg.load_state_dict(aggregator_sd)
 
         def sub(p):
             return {k[len(p):]: v for k, v in heads_sd.items() if k.startswith(p)}
@@ -351,7 +360,19 @@ class B200WorldMirror(torch.nn.Module):
             token_list, psi = self.visual_geometry_transformer(imgs)
         preds = {}
         if self.cam_head is not None:
-            preds["camera_params"] = self.cam_head(token_list)[-1]
+            agg = self.visual_geometry_transformer
+            if getattr(agg, "world", 1) > 1:
+                # the trunk attends across views (camera_head.py:73,92): gather every rank's camera tokens [S_local, 2048]
+                import torch.distributed as dist
+
+                mine = token_list[-1][:, :, :1].contiguous()
+                parts = [torch.empty_like(mine) for _ in range(agg.world)]
+                dist.all_gather(parts, mine, group=agg._sp_group)
+                s_loc = mine.shape[1]
+                cam = self.cam_head([torch.cat(parts, dim=1)])[-1]
+                preds["camera_params"] = cam[:, agg.rank * s_loc:(agg.rank + 1) * s_loc].contiguous()
+            else:
+                preds["camera_params"] = self.cam_head(token_list)[-1]
         for name, head in (("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head)):
             if head is not None:
                 preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
