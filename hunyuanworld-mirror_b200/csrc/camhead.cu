@@ -11,15 +11,23 @@ namespace wm {
 
 enum : int { CAM_ACT_NONE = 0, CAM_ACT_GELU = 1 };
 
+// weights are read exactly once per call: bypass L1 allocation
+__device__ __forceinline__ float4 ld_stream(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
 __device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
 __device__ __forceinline__ float gelu_exact(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
 
 // out[m, n] = epi( sum_k f(A[m, k]) * W[n, k] + bias[n] ),  f = SiLU when silu_in (adapt_norm_gen = Sequential(SiLU, Linear),
 // camera_head.py:49), epi = GELU (Mlp.fc1, mlp.py:30-31) or, with resid != null, resid[m, n] + gamma[n] * (.)
 // (LayerScale + residual, block.py:91-92; in place when out == resid).
-// CTA = 8 warps x 2 output columns = 16 columns of W, 8 rows of A; lane l covers k = 128 i + 4 l .. + 3 (512 B coalesced
-// per W row per step); grid = (N / 16, ceil(M / 8)).  A is re-read from L1/L2 by the 8 warps (8 x K fp32 <= 256 KB).
-constexpr int SK_ROWS = 8, SK_COLS = 2, SK_WARPS = 8;
+// CTA = 4 warps x 2 output columns = 8 columns of W, 8 rows of A; lane l covers k = 128 i + 4 l .. + 3 (512 B coalesced
+// per W row per step); grid = (N / 8, ceil(M / 8)).  A is re-read from L1/L2 by the warps (8 x K fp32 <= 256 KB).
+// The k loop is unrolled 4x so that every lane has 8 independent 16-byte weight loads in flight (Little: 6.5 TB/s x
+// ~1 us needs ~44 KB outstanding per SM; the first version kept 8 KB in flight and measured 1.45 TB/s).
+constexpr int SK_ROWS = 8, SK_COLS = 2, SK_WARPS = 4, SK_UNROLL = 4;
 __global__ void __launch_bounds__(32 * SK_WARPS) skinny_linear_kernel(const float* __restrict__ A, int lda, const float* __restrict__ W,
                                                                       const float* __restrict__ bias, int M, int N, int K, int silu_in,
                                                                       int act, const float* resid, const float* __restrict__ gamma,
@@ -38,18 +46,28 @@ __global__ void __launch_bounds__(32 * SK_WARPS) skinny_linear_kernel(const floa
   const float4* w4[SK_COLS];
 #pragma unroll
   for (int c = 0; c < SK_COLS; ++c) w4[c] = reinterpret_cast<const float4*>(W + (size_t)min(n0 + c, N - 1) * K);
-  for (int k4 = lane; k4 < K / 4; k4 += 32) {
-    float4 wv[SK_COLS];
+  for (int kb = lane; kb < K / 4; kb += 32 * SK_UNROLL) {  // K % 128 == 0; chunks past the end are skipped below
+    float4 wv[SK_UNROLL][SK_COLS];
 #pragma unroll
-    for (int c = 0; c < SK_COLS; ++c) wv[c] = __ldg(w4[c] + k4);
+    for (int u = 0; u < SK_UNROLL; ++u) {
+      const int k4 = min(kb + 32 * u, K / 4 - 1);
 #pragma unroll
-    for (int r = 0; r < SK_ROWS; ++r) {
-      const int m = min(m0 + r, M - 1);
-      float4 a = __ldg(reinterpret_cast<const float4*>(A + (size_t)m * lda) + k4);
-      if (silu_in) a = make_float4(silu(a.x), silu(a.y), silu(a.z), silu(a.w));
+      for (int c = 0; c < SK_COLS; ++c) wv[u][c] = ld_stream(w4[c] + k4);
+    }
 #pragma unroll
-      for (int c = 0; c < SK_COLS; ++c)
-        acc[r][c] = fmaf(a.x, wv[c].x, fmaf(a.y, wv[c].y, fmaf(a.z, wv[c].z, fmaf(a.w, wv[c].w, acc[r][c]))));
+    for (int u = 0; u < SK_UNROLL; ++u) {
+      const int k4 = kb + 32 * u;
+      if (k4 < K / 4) {
+#pragma unroll
+        for (int r = 0; r < SK_ROWS; ++r) {
+          const int m = min(m0 + r, M - 1);
+          float4 a = __ldg(reinterpret_cast<const float4*>(A + (size_t)m * lda) + k4);
+          if (silu_in) a = make_float4(silu(a.x), silu(a.y), silu(a.z), silu(a.w));
+#pragma unroll
+          for (int c = 0; c < SK_COLS; ++c)
+            acc[r][c] = fmaf(a.x, wv[u][c].x, fmaf(a.y, wv[u][c].y, fmaf(a.z, wv[u][c].z, fmaf(a.w, wv[u][c].w, acc[r][c]))));
+        }
+      }
     }
   }
 #pragma unroll

@@ -74,37 +74,40 @@ wm_status ln_rows(cudaStream_t st, const float* x, const float* w, const float* 
 __global__ void __launch_bounds__(256) bilinear_kernel(const float* __restrict__ in, int n, int Hi, int Wi, int C,
                                                        int Ho, int Wo, float sy, float sx, const float* __restrict__ pos_u,
                                                        const float* __restrict__ pos_v, float* __restrict__ out) {
+  // blockIdx.y = (image, output row): the row interpolation is uniform per block; threads run over (x, 4-channel chunk)
+  // with 32-bit index arithmetic only
   pdl_launch_dependents();
   pdl_wait();
   const int c4 = C >> 2;
-  const long long total = (long long)n * Ho * Wo * c4;
-  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(t % c4);
-    long long p = t / c4;
-    const int xo = (int)(p % Wo);
-    p /= Wo;
-    const int yo = (int)(p % Ho), img = (int)(p / Ho);
-    const float fy = yo * sy, fx = xo * sx;
-    const int y0 = min((int)fy, Hi - 1), x0 = min((int)fx, Wi - 1);
-    const int y1 = min(y0 + 1, Hi - 1), x1 = min(x0 + 1, Wi - 1);
-    const float ly = fy - y0, lx = fx - x0;
-    const float4* base = reinterpret_cast<const float4*>(in + (size_t)img * Hi * Wi * C) + c;
-    const float4 a = __ldg(base + ((size_t)y0 * Wi + x0) * c4), b = __ldg(base + ((size_t)y0 * Wi + x1) * c4);
-    const float4 d = __ldg(base + ((size_t)y1 * Wi + x0) * c4), e = __ldg(base + ((size_t)y1 * Wi + x1) * c4);
+  const int img = blockIdx.y / Ho, yo = blockIdx.y - img * Ho;
+  const float fy = yo * sy;
+  const int y0 = min((int)fy, Hi - 1), y1 = min(y0 + 1, Hi - 1);
+  const float ly = fy - y0, hy0 = 1.f - ly;
+  const float4* row0 = reinterpret_cast<const float4*>(in + ((size_t)img * Hi + y0) * Wi * C);
+  const float4* row1 = reinterpret_cast<const float4*>(in + ((size_t)img * Hi + y1) * Wi * C);
+  float4* orow = reinterpret_cast<float4*>(out + ((size_t)img * Ho + yo) * Wo * C);
+  const int half = C >> 1;
+  const int total = Wo * c4;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+    const int xo = t / c4, c = t - xo * c4;
+    const float fx = xo * sx;
+    const int x0 = min((int)fx, Wi - 1), x1 = min(x0 + 1, Wi - 1);
+    const float lx = fx - x0, hx0 = 1.f - lx;
+    const float4 a = __ldg(row0 + x0 * c4 + c), b = __ldg(row0 + x1 * c4 + c);
+    const float4 d = __ldg(row1 + x0 * c4 + c), e = __ldg(row1 + x1 * c4 + c);
     // the order PyTorch's upsample_bilinear2d kernel uses: h0 * (w0 * a + w1 * b) + h1 * (w0 * d + w1 * e)
-    const float hy0 = 1.f - ly, hx0 = 1.f - lx;
     float4 r;
     r.x = hy0 * (hx0 * a.x + lx * b.x) + ly * (hx0 * d.x + lx * e.x);
     r.y = hy0 * (hx0 * a.y + lx * b.y) + ly * (hx0 * d.y + lx * e.y);
     r.z = hy0 * (hx0 * a.z + lx * b.z) + ly * (hx0 * d.z + lx * e.z);
     r.w = hy0 * (hx0 * a.w + lx * b.w) + ly * (hx0 * d.w + lx * e.w);
     if (pos_u != nullptr) {
-      const int half = C >> 1, ch = c * 4;
-      const float* pp = ch < half ? pos_u + (size_t)xo * half + ch : pos_v + (size_t)yo * half + (ch - half);
+      const int ch = c * 4;
+      const float* pp = ch < half ? pos_u + xo * half + ch : pos_v + yo * half + (ch - half);
       const float4 p0 = __ldg(reinterpret_cast<const float4*>(pp));
       r.x += p0.x, r.y += p0.y, r.z += p0.z, r.w += p0.w;
     }
-    reinterpret_cast<float4*>(out)[t] = make_float4(tf32_rn(r.x), tf32_rn(r.y), tf32_rn(r.z), tf32_rn(r.w));
+    __stcs(orow + t, make_float4(tf32_rn(r.x), tf32_rn(r.y), tf32_rn(r.z), tf32_rn(r.w)));
   }
 }
 
@@ -113,10 +116,11 @@ wm_status bilinear_nhwc(cudaStream_t st, const void* in, int n, int Hi, int Wi, 
   WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && Ho > 0 && Wo > 0 && C > 0 && C % 8 == 0, "bilinear: bad geometry");
   WM_CHECK((pos_u == nullptr) == (pos_v == nullptr), "bilinear: pos_u and pos_v go together");
   const float sy = Ho > 1 ? (float)(Hi - 1) / (float)(Ho - 1) : 0.f, sx = Wo > 1 ? (float)(Wi - 1) / (float)(Wo - 1) : 0.f;
-  const long long total = (long long)n * Ho * Wo * (C / 4);
-  const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, 148LL * 32);
-  return launch_pdl(bilinear_kernel, dim3(grid), dim3(256), 0, st, static_cast<const float*>(in), n, Hi, Wi, C, Ho, Wo, sy, sx,
-                    pos_u, pos_v, static_cast<float*>(out));
+  WM_CHECK((long long)n * Ho <= 65535 && (long long)Wo * C < (1LL << 31), "bilinear: n * Ho must fit a grid dimension");
+  const int row_work = Wo * (C / 4);
+  const unsigned gx = (unsigned)std::min((row_work + 255) / 256, 8);
+  return launch_pdl(bilinear_kernel, dim3(gx, (unsigned)(n * Ho)), dim3(256), 0, st, static_cast<const float*>(in), n, Hi, Wi, C,
+                    Ho, Wo, sy, sx, pos_u, pos_v, static_cast<float*>(out));
 }
 
 // nn.ConvTranspose2d(C, C, k, stride=k) (dense_head.py:57-64) = GEMM [pixels, Cin] x [Cin, (ky, kx, co)] followed by

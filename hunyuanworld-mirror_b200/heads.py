@@ -240,6 +240,7 @@ class B200CameraHead(torch.nn.Module):
             raise NotImplementedError("B200CameraHead is built for WorldMirror's configuration (dim 2048, 16 heads, linear/linear/relu)")
         self.dim, self.depth = dim_in, trunk_depth
         self.w: Dict[str, torch.Tensor] = {}
+        self._graphs: Dict[tuple, object] = {}
         self._loaded = False
 
     def load_state_dict(self, sd, strict: bool = True, device=None):
@@ -256,6 +257,7 @@ class B200CameraHead(torch.nn.Module):
         if missing:
             raise RuntimeError(f"Missing key(s) in state_dict: {missing[:4]}...")
         self.w = {k: sd[k].detach().to(dev, torch.float32).contiguous() for k in need}
+        self._graphs = {}
         self._loaded = True
         return torch.nn.modules.module._IncompatibleKeys([], [k for k in sd if k not in need])
 
@@ -275,6 +277,55 @@ class B200CameraHead(torch.nn.Module):
         _k(capi.lib().wm_cam_layernorm(_st(), x.data_ptr(), stride, _p(w), _p(b), eps, M, _p(mod), y.data_ptr()))
         return y
 
+    def _run(self, feat, stride, S, steps, outs):
+        """One sample: `feat` holds the camera tokens, rows `stride` floats apart; outs[step] is a [S, 9] tensor."""
+        lib, w, dev, Cd = capi.lib(), self.w, feat.device, self.dim
+        tok = self._ln(feat, stride, "token_norm", 1e-5, S)
+        pred = torch.empty(S, 9, dtype=torch.float32, device=dev)
+        emb = torch.empty(S, Cd, dtype=torch.float32, device=dev)
+        for step in range(steps):
+            src = w["init_token"] if step == 0 else pred
+            _k(lib.wm_cam_embed(_st(), src.data_ptr(), int(step == 0), 9, w["param_embed.weight"].data_ptr(),
+                                w["param_embed.bias"].data_ptr(), S, Cd, emb.data_ptr()))
+            mod = self._linear(emb, "adapt_norm_gen.1", S, silu_in=1)
+            x = self._ln(tok, Cd, None, 1e-6, S, mod=mod)
+            for i in range(self.depth):
+                p = f"refine_net.{i}."
+                n1 = self._ln(x, Cd, p + "norm1", 1e-5, S)
+                qkv = self._linear(n1, p + "attn.qkv", S)
+                att = torch.empty(S, Cd, dtype=torch.float32, device=dev)
+                _k(lib.wm_cam_attention(_st(), qkv.data_ptr(), S, att.data_ptr()))
+                self._linear(att, p + "attn.proj", S, resid=x, gamma=w[p + "ls1.gamma"], out=x)
+                n2 = self._ln(x, Cd, p + "norm2", 1e-5, S)
+                hid = self._linear(n2, p + "mlp.fc1", S, act=1)
+                self._linear(hid, p + "mlp.fc2", S, resid=x, gamma=w[p + "ls2.gamma"], out=x)
+            xo = self._ln(x, Cd, "out_norm", 1e-5, S)
+            hid = self._linear(xo, "param_predictor.fc1", S, act=1)
+            _k(lib.wm_cam_predict(_st(), hid.data_ptr(), hid.shape[1], w["param_predictor.fc2.weight"].data_ptr(),
+                                  w["param_predictor.fc2.bias"].data_ptr(), S, int(step == 0), pred.data_ptr(), outs[step].data_ptr()))
+
+    def _graph_for(self, S, steps, dev):
+        """The head is ~137 launches of a few microseconds each: captured once per (views, steps) into a CUDA graph so
+        that the launch latency of issuing them from Python does not bound it.  WM_CAM_GRAPH=0 keeps eager launches."""
+        import os
+
+        key = (S, steps, dev.index)
+        if key in self._graphs:
+            return self._graphs[key]
+        entry = None
+        if os.environ.get("WM_CAM_GRAPH", "1") != "0":
+            tok_in = torch.zeros(S, self.dim, dtype=torch.float32, device=dev)
+            outs = [torch.zeros(S, 9, dtype=torch.float32, device=dev) for _ in range(steps)]
+            self._run(tok_in, self.dim, S, steps, outs)  # warm-up outside capture
+            torch.cuda.synchronize(dev)
+            before = LAUNCHES[0]
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self._run(tok_in, self.dim, S, steps, outs)
+            entry = (graph, tok_in, outs, LAUNCHES[0] - before)
+        self._graphs[key] = entry
+        return entry
+
     @torch.no_grad()
     def forward(self, feat_seq: list, steps: int = 4) -> list:
         if not self._loaded:
@@ -284,37 +335,23 @@ class B200CameraHead(torch.nn.Module):
             raise RuntimeError("B200CameraHead needs CUDA tensors (there is no CPU path)")
         B, S, P, Cd = latest.shape
         assert Cd == self.dim
-        lib, w, dev = capi.lib(), self.w, latest.device
+        dev = latest.device
         outs = [torch.empty(B, S, 9, dtype=torch.float32, device=dev) for _ in range(steps)]
         with torch.cuda.device(dev):
+            g = self._graph_for(S, steps, dev)
             for bi in range(B):
                 feat = latest[bi].to(torch.float32)
-                if not feat.is_contiguous():
-                    feat = feat.contiguous()
-                tok = self._ln(feat, P * Cd, "token_norm", 1e-5, S)  # camera token = row 0 of every view
-                pred = torch.empty(S, 9, dtype=torch.float32, device=dev)
-                emb = torch.empty(S, Cd, dtype=torch.float32, device=dev)
-                for step in range(steps):
-                    src = w["init_token"] if step == 0 else pred
-                    _k(lib.wm_cam_embed(_st(), src.data_ptr(), int(step == 0), 9, w["param_embed.weight"].data_ptr(),
-                                                w["param_embed.bias"].data_ptr(), S, Cd, emb.data_ptr()))
-                    mod = self._linear(emb, "adapt_norm_gen.1", S, silu_in=1)
-                    x = self._ln(tok, Cd, None, 1e-6, S, mod=mod)
-                    for i in range(self.depth):
-                        p = f"refine_net.{i}."
-                        n1 = self._ln(x, Cd, p + "norm1", 1e-5, S)
-                        qkv = self._linear(n1, p + "attn.qkv", S)
-                        att = torch.empty(S, Cd, dtype=torch.float32, device=dev)
-                        _k(lib.wm_cam_attention(_st(), qkv.data_ptr(), S, att.data_ptr()))
-                        self._linear(att, p + "attn.proj", S, resid=x, gamma=w[p + "ls1.gamma"], out=x)
-                        n2 = self._ln(x, Cd, p + "norm2", 1e-5, S)
-                        hid = self._linear(n2, p + "mlp.fc1", S, act=1)
-                        self._linear(hid, p + "mlp.fc2", S, resid=x, gamma=w[p + "ls2.gamma"], out=x)
-                    xo = self._ln(x, Cd, "out_norm", 1e-5, S)
-                    hid = self._linear(xo, "param_predictor.fc1", S, act=1)
-                    _k(lib.wm_cam_predict(_st(), hid.data_ptr(), hid.shape[1], w["param_predictor.fc2.weight"].data_ptr(),
-                                                  w["param_predictor.fc2.bias"].data_ptr(), S, int(step == 0), pred.data_ptr(),
-                                                  outs[step][bi].data_ptr()))
+                if g is not None:
+                    graph, tok_in, gouts, n_launch = g
+                    tok_in.copy_(feat[:, 0])  # camera token = row 0 of every view
+                    graph.replay()
+                    LAUNCHES[0] += n_launch
+                    for step in range(steps):
+                        outs[step][bi].copy_(gouts[step])
+                else:
+                    if not feat.is_contiguous():
+                        feat = feat.contiguous()
+                    self._run(feat, P * Cd, S, steps, [o[bi] for o in outs])
         return outs
 
 
