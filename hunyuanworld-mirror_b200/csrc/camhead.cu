@@ -24,7 +24,7 @@ __device__ __forceinline__ float gelu_exact(float x) { return 0.5f * x * (1.0f +
 // camera_head.py:49), epi = GELU (Mlp.fc1, mlp.py:30-31) or, with resid != null, resid[m, n] + gamma[n] * (.)
 // (LayerScale + residual, block.py:91-92; in place when out == resid).
 // CTA = 4 warps x 2 output columns = 8 columns of W, 8 rows of A; lane l covers k = 128 i + 4 l .. + 3 (512 B coalesced
-// per W row per step); grid = (N / 8, ceil(M / 8)).  A is re-read from L1/L2 by the warps (8 x K fp32 <= 256 KB).
+// per W row per step); grid = (ceil(M / 8), N / 8).  A is re-read from L1/L2 by the warps (8 x K fp32 <= 256 KB).
 // The k loop is unrolled 4x so that every lane has 8 independent 16-byte weight loads in flight (Little: 6.5 TB/s x
 // ~1 us needs ~44 KB outstanding per SM; the first version kept 8 KB in flight and measured 1.45 TB/s).
 constexpr int SK_ROWS = 8, SK_COLS = 2, SK_WARPS = 4, SK_UNROLL = 4;
@@ -35,8 +35,10 @@ __global__ void __launch_bounds__(32 * SK_WARPS) skinny_linear_kernel(const floa
   pdl_launch_dependents();
   pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = (blockIdx.x * SK_WARPS + warp) * SK_COLS;
-  const int m0 = blockIdx.y * SK_ROWS;
+  // blockIdx.x (fastest in launch order) = row tile: the CTAs that share a set of weight rows run together, so W comes
+  // from HBM once and from L2 for the other row tiles (M = 64 views: 8 row tiles)
+  const int n0 = (blockIdx.y * SK_WARPS + warp) * SK_COLS;
+  const int m0 = blockIdx.x * SK_ROWS;
   if (n0 >= N) return;
   float acc[SK_ROWS][SK_COLS];
 #pragma unroll
@@ -103,7 +105,8 @@ wm_status skinny_linear(cudaStream_t st, const float* A, int lda, const float* W
   WM_CHECK(A && W && out && M > 0 && N > 0 && K > 0 && K % 128 == 0 && lda % 4 == 0 && lda >= K && ldo >= N,
            "skinny_linear: bad argument (M=%d N=%d K=%d)", M, N, K);
   WM_CHECK((resid == nullptr) == (gamma == nullptr), "skinny_linear: resid and gamma go together");
-  const dim3 grid((N + SK_WARPS * SK_COLS - 1) / (SK_WARPS * SK_COLS), (M + SK_ROWS - 1) / SK_ROWS);
+  const dim3 grid((M + SK_ROWS - 1) / SK_ROWS, (N + SK_WARPS * SK_COLS - 1) / (SK_WARPS * SK_COLS));
+  WM_CHECK(grid.y <= 65535, "skinny_linear: N too large");
   return launch_pdl(skinny_linear_kernel, grid, dim3(32 * SK_WARPS), 0, st, A, lda, W, bias, M, N, K, silu_in, act, resid, gamma, out, ldo);
 }
 

@@ -366,6 +366,21 @@ class B200WorldMirror(torch.nn.Module):
         super().__init__()
         self.visual_geometry_transformer = aggregator
         self.cam_head, self.depth_head, self.pts_head, self.norm_head = cam_head, depth_head, pts_head, norm_head
+        self._side = None
+
+    def _camera(self, token_list):
+        agg = self.visual_geometry_transformer
+        if getattr(agg, "world", 1) > 1:
+            # the trunk attends across views (camera_head.py:73,92): gather every rank's camera tokens [S_local, 2048]
+            import torch.distributed as dist
+
+            mine = token_list[-1][:, :, :1].contiguous()
+            parts = [torch.empty_like(mine) for _ in range(agg.world)]
+            dist.all_gather(parts, mine, group=agg._sp_group)
+            s_loc = mine.shape[1]
+            cam = self.cam_head([torch.cat(parts, dim=1)])[-1]
+            return cam[:, agg.rank * s_loc:(agg.rank + 1) * s_loc].contiguous()
+        return self.cam_head(token_list)[-1]
 
     @classmethod
     def from_state_dicts(cls, aggregator_sd, heads_sd, aggregator=None, **agg_kwargs):
@@ -396,21 +411,21 @@ class B200WorldMirror(torch.nn.Module):
         else:
             token_list, psi = self.visual_geometry_transformer(imgs)
         preds = {}
+        main = torch.cuda.current_stream(imgs.device)
+        side = None
         if self.cam_head is not None:
-            agg = self.visual_geometry_transformer
-            if getattr(agg, "world", 1) > 1:
-                # the trunk attends across views (camera_head.py:73,92): gather every rank's camera tokens [S_local, 2048]
-                import torch.distributed as dist
-
-                mine = token_list[-1][:, :, :1].contiguous()
-                parts = [torch.empty_like(mine) for _ in range(agg.world)]
-                dist.all_gather(parts, mine, group=agg._sp_group)
-                s_loc = mine.shape[1]
-                cam = self.cam_head([torch.cat(parts, dim=1)])[-1]
-                preds["camera_params"] = cam[:, agg.rank * s_loc:(agg.rank + 1) * s_loc].contiguous()
-            else:
-                preds["camera_params"] = self.cam_head(token_list)[-1]
+            # The camera head is a chain of ~137 tiny kernels (latency-bound), the DPT heads are throughput-bound: run the
+            # camera head on a high-priority side stream underneath them.
+            if self._side is None or self._side.device != imgs.device:
+                self._side = torch.cuda.Stream(device=imgs.device, priority=-1)
+            side = self._side
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                preds["camera_params"] = self._camera(token_list)
         for name, head in (("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head)):
             if head is not None:
                 preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
+        if side is not None:
+            main.wait_stream(side)
+            preds["camera_params"].record_stream(main)
         return preds
