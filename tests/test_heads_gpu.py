@@ -234,3 +234,23 @@ def test_worldmirror_forward_end_to_end(state_dict_full):
     ang = HO.quat_angle(preds["camera_params"].cpu()[..., 3:7], cam_ref[..., 3:7]).max().item()
     print(f"e2e camera rotation {ang:.3e} rad")
     assert ang <= 1e-3
+
+
+def test_dpt_head_518_matches_oracle():
+    """BASELINE.json's image size (518 x 518: 37 x 37 patch grid, maps of 19 / 37 / 74 / 148 / 296 / 518 pixels, every
+    border-tile case of the convolution kernel) on one view of synthetic tokens against the fp32 oracle head."""
+    hsd = W.synthetic_heads_state_dict(seed=0)
+    pre = "pts_head."
+    P = 7 + 37 * 37
+    toks = [_rand((1, 1, P, 2048), 20 + i, 0.8) for i in range(4)]
+    with torch.no_grad():
+        ref_p, ref_c = HO.dpt_head(toks, 518, 518, hsd, pre, "inv_log+expp1")
+    head = heads.B200DPTHead(dim_in=2048, output_dim=4, activation="inv_log+expp1")
+    head.load_state_dict({k[len(pre):]: v for k, v in hsd.items() if k.startswith(pre)})
+    pred, conf = head([t.cuda() for t in toks], torch.zeros(1, 1, 3, 518, 518, device="cuda"), 7)
+    torch.cuda.synchronize()
+    e = ((pred.cpu() - ref_p).norm() / ref_p.norm()).item()
+    ec = ((conf.cpu() - ref_c).norm() / ref_c.norm()).item()
+    border = (pred.cpu() - ref_p)[0, 0, [0, -1]].abs().max().item() / ref_p.abs().max().item()
+    print(f"DPT 518: rel fro {e:.3e}, conf {ec:.3e}, border rows max err / max {border:.3e}")
+    assert torch.isfinite(pred).all() and e <= 2e-3 and ec <= 2e-3 and border <= 5e-3
