@@ -999,6 +999,13 @@ wm_status wm_cam_predict(wm_stream stream, const float* h, int K, const float* W
   return cam_predict(static_cast<cudaStream_t>(stream), h, K, W, bias, M, first, pred, act);
 }
 
+wm_status wm_normalize_depth(wm_stream stream, const float* depth, int n_views, int hw, double eps, int min_percentile,
+                             int max_percentile, float* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return normalize_depth(static_cast<cudaStream_t>(stream), depth, n_views, hw, eps, min_percentile, max_percentile, out);
+}
+
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
   int sms;
   WM_TRY(require_sm100(&sms));

@@ -49,6 +49,9 @@ wm_status cam_attention(cudaStream_t st, const float* qkv, int S, float* out);
 wm_status cam_embed(cudaStream_t st, const float* in, int in_bcast, int K, const float* W, const float* bias, int M, int N, float* out);
 wm_status cam_predict(cudaStream_t st, const float* h, int K, const float* W, const float* bias, int M, int first, float* pred,
                       float* act);
+// prior preparation (priors.cu)
+wm_status normalize_depth(cudaStream_t st, const float* depth, int n_views, int hw, double eps, int min_percentile,
+                          int max_percentile, float* out);
 wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);
 
 }  // namespace wm

@@ -239,6 +239,13 @@ wm_status wm_cam_embed(wm_stream stream, const float* in, int in_bcast, int K, c
 wm_status wm_cam_predict(wm_stream stream, const float* h, int K, const float* W, const float* bias, int M, int first, float* pred,
                          float* act);
 
+/* ---- prior preparation ------------------------------------------------------- */
+/* normalize_depth (src/models/utils/priors.py:107-167) for all views in one launch, no host round trip: per view
+ * nan_to_num, percentiles (torch.quantile semantics, exact radix select) over the positive values, rescale, clamp.
+ * depth, out: [n_views, hw] fp32, distinct buffers. */
+wm_status wm_normalize_depth(wm_stream stream, const float* depth, int n_views, int hw, double eps, int min_percentile,
+                             int max_percentile, float* out);
+
 #ifdef __cplusplus
 }
 #endif
