@@ -78,6 +78,7 @@ SIGNATURES = {
     "wm_cam_embed": (C.c_int, [_vp, _fp, _i, _i, _fp, _fp, _i, _i, _fp]),
     "wm_cam_predict": (C.c_int, [_vp, _fp, _i, _fp, _fp, _i, _i, _fp, _fp]),
     "wm_normalize_depth": (C.c_int, [_vp, _fp, _i, _i, C.c_double, _i, _i, _fp]),
+    "wm_pose_prior": (C.c_int, [_vp, _fp, _i, _fp, _i, _i, _i, C.c_double, _fp, _fp]),
     "wm_pack_bf16": (C.c_int, [_vp, _fp, C.c_longlong, _i, _i, _vp]),
 }
 

@@ -1006,6 +1006,13 @@ wm_status wm_normalize_depth(wm_stream stream, const float* depth, int n_views, 
   return normalize_depth(static_cast<cudaStream_t>(stream), depth, n_views, hw, eps, min_percentile, max_percentile, out);
 }
 
+wm_status wm_pose_prior(wm_stream stream, const float* extrinsics, int extr_stride, const float* intrinsics, int n_views, int H, int W,
+                        double padding, float* poses, float* rays) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return pose_prior(static_cast<cudaStream_t>(stream), extrinsics, extr_stride, intrinsics, n_views, H, W, padding, poses, rays);
+}
+
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
   int sms;
   WM_TRY(require_sm100(&sms));

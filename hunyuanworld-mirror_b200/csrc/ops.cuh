@@ -52,6 +52,8 @@ wm_status cam_predict(cudaStream_t st, const float* h, int K, const float* W, co
 // prior preparation (priors.cu)
 wm_status normalize_depth(cudaStream_t st, const float* depth, int n_views, int hw, double eps, int min_percentile,
                           int max_percentile, float* out);
+wm_status pose_prior(cudaStream_t st, const float* extr, int extr_stride, const float* intr, int S, int H, int W, double padding,
+                     float* poses, float* rays);
 wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);
 
 }  // namespace wm

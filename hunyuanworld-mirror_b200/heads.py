@@ -358,9 +358,10 @@ class B200CameraHead(torch.nn.Module):
 class B200WorldMirror(torch.nn.Module):
     """`WorldMirror.forward` (src/models/models/worldmirror.py:120-196) on the B200 path: aggregator, camera head and the
     depth / points / normals DPT heads, same `views` dictionary in, same prediction keys out (`camera_params`, `depth`,
-    `depth_conf`, `pts3d`, `pts3d_conf`, `normals`, `normals_conf`).  `priors` are the already normalised tensors
-    (depth, rays, poses) that `extract_priors` (worldmirror.py:218-251) produces; the Gaussian branch is not part of this
-    path."""
+    `depth_conf`, `pts3d`, `pts3d_conf`, `normals`, `normals_conf`).  With any cond_flag set the priors are extracted
+    from `views` (`camera_pose`, `depthmap`, `camera_intrinsics`) by `priors.extract_priors`, as `WorldMirror.forward`
+    does (worldmirror.py:133-143); `priors` may instead pass the already normalised (depth, rays, poses).  The Gaussian
+    branch is not part of this path."""
 
     def __init__(self, aggregator, cam_head=None, depth_head=None, pts_head=None, norm_head=None):
         super().__init__()
@@ -406,7 +407,11 @@ class B200WorldMirror(torch.nn.Module):
     @torch.no_grad()
     def forward(self, views, cond_flags=(0, 0, 0), priors=None):
         imgs = views["img"]
-        if sum(cond_flags) > 0 and priors is not None:
+        if sum(cond_flags) > 0:
+            if priors is None:  # worldmirror.py:136-138: priors come from the views dictionary
+                from .priors import extract_priors
+
+                priors = extract_priors(views)
             token_list, psi = self.visual_geometry_transformer(imgs, priors, cond_flags=list(cond_flags))
         else:
             token_list, psi = self.visual_geometry_transformer(imgs)

@@ -25,3 +25,36 @@ def normalize_depth(depth: torch.Tensor, eps: float = 1e-6, min_percentile: int 
         capi.check(capi.lib().wm_normalize_depth(torch.cuda.current_stream().cuda_stream, src.data_ptr(), B * S, H * W, float(eps),
                                                  int(min_percentile), int(max_percentile), out.data_ptr()))
     return out
+
+
+@torch.no_grad()
+def extract_priors(views: dict):
+    """`WorldMirror.extract_priors` (worldmirror.py:218-251): views -> (depths [B,S,H,W] | None, rays [B,S,4] | None,
+    poses [B,S,7] | None), the tuple `VisualGeometryTransformer.forward` takes.  Two kernel launches per scene instead of
+    the reference's per-view Python loops; nothing is read back to the host."""
+    h, w = views["img"].shape[-2:]
+    depths = rays = poses = None
+    lib = capi.lib()
+    if "camera_pose" in views:
+        cp = views["camera_pose"]
+        if not cp.is_cuda:
+            raise RuntimeError("extract_priors needs CUDA tensors (there is no CPU path)")
+        ext = cp.to(torch.float32).contiguous()  # [B, S, 4, 4] (or [B, S, 3, 4])
+        B, S = ext.shape[:2]
+        stride = ext.shape[-2] * ext.shape[-1]
+        intr = None
+        if "camera_intrinsics" in views:
+            intr = views["camera_intrinsics"][:, :, :3, :3].to(torch.float32).contiguous()
+            rays = torch.empty(B, S, 4, dtype=torch.float32, device=ext.device)
+        poses = torch.empty(B, S, 7, dtype=torch.float32, device=ext.device)
+        with torch.cuda.device(ext.device):
+            st = torch.cuda.current_stream().cuda_stream
+            for b in range(B):
+                capi.check(lib.wm_pose_prior(st, ext[b].data_ptr(), stride, None if intr is None else intr[b].data_ptr(), S, h, w, 0.1,
+                                             poses[b].data_ptr(), None if rays is None else rays[b].data_ptr()))
+    elif "camera_intrinsics" in views:
+        k = views["camera_intrinsics"][:, :, :3, :3].to(torch.float32)
+        rays = torch.stack([k[:, :, 0, 0] / w, k[:, :, 1, 1] / h, k[:, :, 0, 2] / w, k[:, :, 1, 2] / h], dim=-1)
+    if "depthmap" in views:
+        depths = normalize_depth(views["depthmap"])
+    return depths, rays, poses

@@ -245,6 +245,13 @@ wm_status wm_cam_predict(wm_stream stream, const float* h, int K, const float* W
  * depth, out: [n_views, hw] fp32, distinct buffers. */
 wm_status wm_normalize_depth(wm_stream stream, const float* depth, int n_views, int hw, double eps, int min_percentile,
                              int max_percentile, float* out);
+/* The pose and ray priors of one scene (worldmirror.py:228-249): poses [n_views, 7] = extrinsics_to_vector(
+ * normalize_poses(extrinsics)) = [t in the unit cube (5 % / 95 % percentile box, padding), quaternion xyzw]
+ * (utils/priors.py:4-104, utils/camera_utils.py:25-35, utils/rotation.py:41-97); rays [n_views, 4] =
+ * [fx/W, fy/H, cx/W, cy/H].  extrinsics: rows of a [3,4] (or the top of a [4,4]) matrix per view, `extr_stride` floats
+ * apart (12 or 16); intrinsics [n_views, 3, 3] and rays may both be NULL.  At most 1024 views. */
+wm_status wm_pose_prior(wm_stream stream, const float* extrinsics, int extr_stride, const float* intrinsics, int n_views, int H, int W,
+                        double padding, float* poses, float* rays);
 
 #ifdef __cplusplus
 }

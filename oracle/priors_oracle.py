@@ -67,3 +67,80 @@ def synthetic_depth_cases(seed: int = 0):
     f = np.full((H, W), 2.5, f32)
     h = (g.uniform(0.0, 1.0, size=(H, W)) ** 8 * 100).astype(f32)  # heavy tail: percentiles far from min / max
     return np.stack([a, b, c, d, e, f, h])[None]  # [1, 7, H, W]
+
+
+# --------------------------------------------------------------------------------------
+# Pose / ray priors (worldmirror.py:228-249)
+# --------------------------------------------------------------------------------------
+def _rotmat_to_quat(m: np.ndarray) -> np.ndarray:
+    """utils/rotation.py:41-97 for one 3x3 fp32 matrix -> quaternion xyzw with w >= 0."""
+    m00, m01, m02, m10, m11, m12, m20, m21, m22 = [f32(v) for v in m.reshape(9)]
+    one = f32(1.0)
+    t = np.array([one + m00 + m11 + m22, one + m00 - m11 - m22, one - m00 + m11 - m22, one - m00 - m11 + m22], dtype=f32)
+    q_abs = np.where(t > 0, np.sqrt(np.maximum(t, f32(0))), f32(0)).astype(f32)
+    cand = np.array([[q_abs[0] * q_abs[0], m21 - m12, m02 - m20, m10 - m01],
+                     [m21 - m12, q_abs[1] * q_abs[1], m10 + m01, m02 + m20],
+                     [m02 - m20, m10 + m01, q_abs[2] * q_abs[2], m12 + m21],
+                     [m10 - m01, m20 + m02, m21 + m12, q_abs[3] * q_abs[3]]], dtype=f32)
+    best = int(np.argmax(q_abs))
+    q = (cand[best] / (f32(2.0) * np.maximum(q_abs[best], f32(0.1)))).astype(f32)  # r, i, j, k
+    q = q[[1, 2, 3, 0]]
+    return -q if q[3] < 0 else q
+
+
+def pose_ray_priors(camera_pose: np.ndarray, intrinsics, H: int, W: int, padding: float = 0.1):
+    """extract_priors' pose and ray branches (worldmirror.py:228-249) for one scene: camera_pose [S, 4, 4] (or [S, 3, 4]),
+    intrinsics [S, 3, 3] | None -> (poses [S, 7], rays [S, 4] | None), fp32.
+    normalize_poses: utils/priors.py:4-104; extrinsics_to_vector: utils/camera_utils.py:25-35."""
+    ext = camera_pose[:, :3].astype(f32).copy()
+    S = ext.shape[0]
+    if not np.isfinite(ext).all():                                                     # priors.py:21-27
+        ext = np.nan_to_num(ext, nan=0.0, posinf=1e6, neginf=-1e6).astype(f32)
+    pos = ext[:, :3, 3]
+    if S > 10:                                                                         # :56-63
+        srt = np.sort(pos, axis=0)
+        mn = np.array([_quantile(srt[:, a], 0.05) for a in range(3)], dtype=f32)
+        mx = np.array([_quantile(srt[:, a], 0.95) for a in range(3)], dtype=f32)
+    else:
+        mn, mx = pos.min(axis=0), pos.max(axis=0)
+    eps = np.maximum(f32(1e-6), np.abs(mx) * f32(1e-6)).astype(f32)                    # :69-73
+    rng = np.maximum((mx - mn).astype(f32), eps)
+    scale = f32(np.clip(rng.max(), f32(1e-6), f32(1e6)))                               # :77-78
+    center = ((mn + mx) / f32(2.0)).astype(f32)                                        # :81
+    actual = f32(scale / f32(1 - 2 * padding))                                         # :84
+    t = np.clip(((pos - center) / actual + f32(0.5)).astype(f32), 0.0, 1.0)            # :85-88
+    q = np.stack([_rotmat_to_quat(ext[s, :3, :3]) for s in range(S)])
+    poses = np.concatenate([t, q], axis=1).astype(f32)
+    rays = None
+    if intrinsics is not None:                                                         # worldmirror.py:243-249
+        k = intrinsics[:, :3, :3].astype(f32)
+        rays = np.stack([k[:, 0, 0] / f32(W), k[:, 1, 1] / f32(H), k[:, 0, 2] / f32(W), k[:, 1, 2] / f32(H)], axis=1).astype(f32)
+    return poses, rays
+
+
+def synthetic_pose_cases(seed: int = 0):
+    """[(camera_pose [S,4,4], intrinsics [S,3,3])]: 32 views (percentile branch), 5 views (min/max branch), 12 views with a
+    NaN and an inf (nan_to_num branch), rotations with every quaternion component dominant once."""
+    g = np.random.default_rng(seed)
+
+    def rot(v):
+        th = np.linalg.norm(v)
+        k = v / th
+        K = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+        return np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * K @ K
+
+    cases = []
+    for S, big in ((32, False), (5, True), (12, True)):
+        pose = np.tile(np.eye(4, dtype=np.float64), (S, 1, 1))
+        for s in range(S):
+            ang = g.uniform(2.5, 3.1) if (big and s % 2) else g.uniform(0.01, 0.5)
+            axis = g.normal(size=3)
+            pose[s, :3, :3] = rot(axis / np.linalg.norm(axis) * ang)
+            pose[s, :3, 3] = g.uniform(-1, 1, 3) * (5.0 if s == 3 else 1.0)
+        intr = np.tile(np.array([[0.8 * 518, 0, 259.0], [0, 0.8 * 518, 259.0], [0, 0, 1.0]]), (S, 1, 1))
+        intr[:, 0, 0] += g.uniform(-20, 20, S)
+        intr[:, 1, 2] += g.uniform(-5, 5, S)
+        cases.append((pose.astype(f32), intr.astype(f32)))
+    cases[2][0][4, 1, 3] = np.nan
+    cases[2][0][7, 0, 3] = np.inf
+    return cases

@@ -388,6 +388,12 @@ def test_gathered_attention_scan_order_and_flags(variant, self_rank, late):
     main, side = torch.cuda.Stream(), torch.cuda.Stream()
     if not late:
         words[:world] = epoch
+    # With lazy module loading the FIRST launch of a kernel loads it, and loading waits for running kernels: a flag kernel
+    # first launched while the attention kernel is already spinning on that flag would deadlock.  (The forward pass
+    # launches its flag kernels before the attention kernel that waits on them, capi.cu run_block.)  Load both here.
+    with torch.cuda.stream(side):
+        torch.cuda._sleep(1)
+        capi.check(lib.wm_p2p_raise_flag(side.cuda_stream, words.data_ptr() + 100 * 4, 1))
     torch.cuda.synchronize()
     capi.check(lib.wm_flash_attn_gathered(main.cuda_stream, q.data_ptr(), heads * 64, k_ptr, v_ptr, 2 * heads * 64, o.data_ptr(),
                                           heads * 64, Lq, Lkv, heads, scale, variant, ws.data_ptr(), ws.numel(), shard,

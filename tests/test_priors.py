@@ -60,3 +60,33 @@ def test_cuda_normalize_depth_full_size_properties():
     assert 0.005 < frac0 < 0.015 and 0.005 < frac1 < 0.015
     y2 = pkg.priors.normalize_depth(xd * 8.0)  # power of two: exact rescaling
     assert float((y2 - y).abs().max()) <= 1e-6
+
+
+def test_pose_oracle_matches_reference_fixture():
+    fx = np.load(os.path.join(GOLDEN, "priors_pose.npz"))
+    for i, (pose, intr) in enumerate(PO.synthetic_pose_cases(seed=0)):
+        p, r = PO.pose_ray_priors(pose, intr, 518, 518)
+        np.testing.assert_array_equal(p, fx[f"poses{i}"])
+        np.testing.assert_array_equal(r, fx[f"rays{i}"])
+
+
+@pytest.mark.gpu
+def test_cuda_extract_priors_matches_reference_fixture():
+    """`extract_priors` (worldmirror.py:218-251) on the GPU: poses, rays and depth of every fixture case."""
+    pkg = importlib.import_module("hunyuanworld-mirror_b200")
+    fx = np.load(os.path.join(GOLDEN, "priors_pose.npz"))
+    dref = np.load(os.path.join(GOLDEN, "priors_depth.npz"))["out"]
+    for i, (pose, intr) in enumerate(PO.synthetic_pose_cases(seed=0)):
+        S = pose.shape[0]
+        views = {"img": torch.zeros(1, S, 3, 518, 518, device="cuda"), "camera_pose": torch.from_numpy(pose)[None].cuda(),
+                 "camera_intrinsics": torch.from_numpy(intr)[None].cuda()}
+        depths, rays, poses = pkg.priors.extract_priors(views)
+        torch.cuda.synchronize()
+        assert depths is None and tuple(poses.shape) == (1, S, 7) and tuple(rays.shape) == (1, S, 4)
+        dp = np.abs(poses[0].cpu().numpy() - fx[f"poses{i}"]).max()
+        dr = np.abs(rays[0].cpu().numpy() - fx[f"rays{i}"]).max()
+        print(f"pose case {i} ({S} views): poses max abs diff {dp:.2e}, rays {dr:.2e}")
+        assert dp <= 1.2e-7 and dr == 0.0
+    x = torch.from_numpy(PO.synthetic_depth_cases(seed=0)).cuda()
+    d, r, p = pkg.priors.extract_priors({"img": torch.zeros(1, 7, 3, 70, 84, device="cuda"), "depthmap": x})
+    assert r is None and p is None and np.abs(d.cpu().numpy() - dref).max() <= 2.4e-7
