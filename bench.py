@@ -171,6 +171,20 @@ def run_b200(args):
     n_local, n_total = args.views, args.views * world
     imgs_host = W.synthetic_images(n_total, SIZE, SIZE, seed=1)[:, rank * n_local:(rank + 1) * n_local].contiguous().pin_memory()
     imgs_dev = imgs_host.to(dev)
+    prior_in = None
+    if args.priors:  # BASELINE.json configs[2]: camera-pose + depth + intrinsics prior tokens (SURVEY.md section 8d inputs)
+        pose_all, depth_all, intr_all = W.synthetic_scene(n_total, SIZE, SIZE, seed=2)
+        sl = slice(rank * n_local, (rank + 1) * n_local)
+        prior_in = {"camera_pose": pose_all.to(dev), "camera_intrinsics": intr_all.to(dev), "depthmap": depth_all[:, sl].contiguous().to(dev)}
+        del depth_all
+
+    def priors_now():
+        """extract_priors on the GPU inside the timed step: the pose box needs every view of the scene (S x 16 numbers,
+        replicated on all ranks), depth is per view (this rank's views only)."""
+        d, r, p = pkg.priors.extract_priors({"img": imgs_dev, **prior_in})
+        return d, r[:, sl].contiguous(), p[:, sl].contiguous()
+
+    flags = [1, 1, 1] if args.priors else [0, 0, 0]
     lib = capi.lib()
 
     def barrier():
@@ -196,10 +210,11 @@ def run_b200(args):
 
     # ---- value: images resident in HBM
     def step_resident():
+        pri = priors_now() if args.priors else None
         if heads_on:
-            full({"img": imgs_dev})
+            full({"img": imgs_dev}, cond_flags=flags, priors=pri)
         else:
-            model(imgs_dev)
+            model(imgs_dev, pri, cond_flags=flags)
 
     with ClockSampler(local_rank) as clocks:
         total_ms = timed(step_resident, args.steps, max(args.warmup, 3), prof_mask=1 << 3)
@@ -255,12 +270,13 @@ def run_b200(args):
 
     def step_e2e():
         x = imgs_host.to(dev, non_blocking=True)
+        pri = priors_now() if args.priors else None
         if heads_on:
-            preds = full({"img": x})
+            preds = full({"img": x}, cond_flags=flags, priors=pri)
             for k, t in host_out.items():
                 t.copy_(preds[k], non_blocking=True)
         else:
-            outs, _ = model(x)
+            outs, _ = model(x, pri, cond_flags=flags)
             host_out["cam_tokens"].copy_(outs[-1][:, :, 0], non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
@@ -311,8 +327,10 @@ def run_b200(args):
                 "data": "synthetic",
                 "config": {"workload": f"WorldMirror fwd: aggregator (DINOv2 ViT-L/14 + 24x(frame,global) blocks)"
                                        f"{' + camera head + depth/points/normals DPT heads' if heads_on else ' only (--no-heads)'}, "
-                                       f"{n_local} views/GPU x {world} GPU = {n_total} views {SIZE}x{SIZE}, no priors "
-                                       f"(BASELINE configs[1] at N=1; Gaussian head not built, SURVEY 8f row 3)",
+                                       f"{n_local} views/GPU x {world} GPU = {n_total} views {SIZE}x{SIZE}, "
+                                       f"{'camera-pose + depth + intrinsics priors extracted on the GPU inside the step (BASELINE configs[2])' if args.priors else 'no priors (BASELINE configs[1] at N=1)'}"
+                                       f"; Gaussian head not built, SURVEY 8f row 3",
+                           "priors": bool(args.priors),
                            "heads": heads_on, "head_dtype": "camera fp32, DPT tf32 (fp32 accumulate)" if heads_on else None,
                            "views_per_gpu": n_local, "views_total": n_total, "size": SIZE, "tokens_per_view": 1376,
                            "parallelism": f"views sharded; global attention: {sp_exchange}" if world > 1 else "single GPU",
@@ -335,6 +353,7 @@ def main():
     ap.add_argument("--views", type=int, default=VIEWS_PER_RANK, help="views per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-heads", action="store_true", help="time the aggregator alone (the round-1 workload before the heads existed)")
+    ap.add_argument("--priors", action="store_true", help="BASELINE configs[2]: pose + depth + intrinsics priors, cond_flags [1,1,1]")
     ap.add_argument("--set", action="append", default=[], metavar="KNOB=INT", help="wm_set_int tuning knob (repeatable)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -244,3 +244,25 @@ def synthetic_priors(n_views: int, h: int, w: int, seed: int = 2):
     q = torch.randn(1, n_views, 4, generator=g)
     q = q / q.norm(dim=-1, keepdim=True)
     return depth, rays, torch.cat([t, q], dim=-1)
+
+
+def synthetic_scene(n_views: int, h: int, w: int, seed: int = 2):
+    """Raw geometric inputs of `WorldMirror.forward` as SURVEY.md section 8d specifies them for the benchmark:
+    camera_pose [1,N,4,4] = random small-rotation SE(3) (axis-angle <= 0.5 rad, t ~ U(-1,1)^3), depthmap [1,N,H,W] ~
+    U(0.5, 4.5), camera_intrinsics [1,N,3,3] = pinhole fx = fy = 0.8 W, cx = W/2, cy = H/2.  `extract_priors` turns them
+    into the (depth, rays, poses) tensors the aggregator takes."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed)
+    axis = torch.randn(n_views, 3, generator=g)
+    axis = axis / axis.norm(dim=-1, keepdim=True)
+    ang = torch.rand(n_views, 1, generator=g) * 0.5
+    k = axis
+    K = torch.zeros(n_views, 3, 3)
+    K[:, 0, 1], K[:, 0, 2], K[:, 1, 0], K[:, 1, 2], K[:, 2, 0], K[:, 2, 1] = -k[:, 2], k[:, 1], k[:, 2], -k[:, 0], -k[:, 1], k[:, 0]
+    R = torch.eye(3)[None] + torch.sin(ang)[:, :, None] * K + (1 - torch.cos(ang))[:, :, None] * (K @ K)
+    pose = torch.eye(4).repeat(n_views, 1, 1)
+    pose[:, :3, :3] = R
+    pose[:, :3, 3] = torch.rand(n_views, 3, generator=g) * 2 - 1
+    depth = torch.rand(1, n_views, h, w, generator=g) * 4.0 + 0.5
+    intr = torch.tensor([[0.8 * w, 0.0, w / 2.0], [0.0, 0.8 * w, h / 2.0], [0.0, 0.0, 1.0]]).repeat(1, n_views, 1, 1)
+    return pose[None].contiguous(), depth, intr.contiguous()
