@@ -79,6 +79,13 @@ SIGNATURES = {
     "wm_cam_predict": (C.c_int, [_vp, _fp, _i, _fp, _fp, _i, _i, _fp, _fp]),
     "wm_normalize_depth": (C.c_int, [_vp, _fp, _i, _i, C.c_double, _i, _i, _fp]),
     "wm_pose_prior": (C.c_int, [_vp, _fp, _i, _fp, _i, _i, _i, C.c_double, _fp, _fp]),
+    "wm_im2row7": (C.c_int, [_vp, _fp, _i, _i, _i, _vp]),
+    "wm_conv2d_project": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _vp, _fp, _fp, _fp, _i, _fp]),
+    "wm_splat_cameras": (C.c_int, [_vp, _fp, _i, _i, _i, _fp]),
+    "wm_splat_prepare": (C.c_int, [_vp, _fp, _fp, _fp, _fp, _i, _i, _i, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "wm_prune_workspace_bytes": (C.c_int, [C.c_longlong, C.POINTER(C.c_size_t)]),
+    "wm_prune_splats": (C.c_int, [_vp, C.c_longlong, _fp, _fp, _fp, _fp, _fp, _fp, C.c_double, _vp, C.c_size_t, _fp, _fp, _fp,
+                                  _fp, _fp, _vp]),
     "wm_pack_bf16": (C.c_int, [_vp, _fp, C.c_longlong, _i, _i, _vp]),
 }
 

@@ -1013,6 +1013,43 @@ wm_status wm_pose_prior(wm_stream stream, const float* extrinsics, int extr_stri
   return pose_prior(static_cast<cudaStream_t>(stream), extrinsics, extr_stride, intrinsics, n_views, H, W, padding, poses, rays);
 }
 
+wm_status wm_im2row7(wm_stream stream, const float* images, int n, int H, int W, void* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return im2row7(static_cast<cudaStream_t>(stream), images, n, H, W, out);
+}
+
+wm_status wm_conv2d_project(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
+                            const float* w2, const float* b2, int od, float* out) {
+  return conv2d_project(static_cast<cudaStream_t>(stream), in, n, H, W, Cin, w1, b1, w2, b2, od, out);
+}
+
+wm_status wm_splat_cameras(wm_stream stream, const float* camera_params, int n, int H, int W, float* cam) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return splat_cameras(static_cast<cudaStream_t>(stream), camera_params, n, H, W, cam);
+}
+
+wm_status wm_splat_prepare(wm_stream stream, const float* raw, const float* images, const float* gs_depth, const float* cam, int n,
+                           int H, int W, float* means, float* quats, float* scales, float* opacities, float* sh, float* weights) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return splat_prepare(static_cast<cudaStream_t>(stream), raw, images, gs_depth, cam, n, H, W, means, quats, scales, opacities, sh,
+                       weights);
+}
+
+wm_status wm_prune_workspace_bytes(long long N, size_t* bytes) { return prune_workspace_bytes(N, bytes); }
+
+wm_status wm_prune_splats(wm_stream stream, long long N, const float* means, const float* quats, const float* scales,
+                          const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
+                          size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
+                          float* out_sh, unsigned* count) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return prune_splats(static_cast<cudaStream_t>(stream), N, means, quats, scales, opacities, sh, weights, voxel_size, workspace,
+                      workspace_bytes, out_means, out_quats, out_scales, out_opacities, out_sh, count);
+}
+
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
   int sms;
   WM_TRY(require_sm100(&sms));

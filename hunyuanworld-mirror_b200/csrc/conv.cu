@@ -17,7 +17,9 @@
 // Epilogues (the reference's module boundaries they fuse are cited at the launchers):
 //   NT = 128 / 256:  out fp32 = [relu]( acc + bias + res1 + res2 ), written as NHWC through a 4D TMA store (pixels of a
 //                    border tile that fall outside the image are clipped by the store);
-//   NT = 32 (final): relu(acc + bias) -> 1x1 conv (32 -> od) -> activate_head -> fp32 prediction + confidence.
+//   NT = 32 (final): relu(acc + bias) -> 1x1 conv (32 -> od) -> activate_head -> fp32 prediction + confidence;
+//   NT = 256 (project): relu(acc + bias) -> 1x1 conv (256 -> od <= 16) + bias, raw fp32 [pixels, od]: the Gaussian
+//                    parameter head `gs_renderer.gs_head` (models/rasterization.py:149-153), hidden map never stored.
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -35,27 +37,32 @@ constexpr int cv_smem() {
 }
 
 enum : int { ACT_EXP = 0, ACT_INV_LOG = 1, ACT_NORM = 2 };
+enum : int { EPI_STORE = 0, EPI_FINAL = 1, EPI_PROJECT = 2 };
+constexpr int CV_PROJ_MAX = 16;  // output channels of the projecting epilogue (its weights live in the staging tile)
 
 struct ConvArgs {
-  int n, H, W, Cin, Cout, taps;  // taps: 1 (1x1) or 9 (3x3, stride 1, pad 1)
+  int n, H, W, Cin, Cout, taps;  // taps: 1 (1x1), 9 (3x3, stride 1, pad 1) or 7 (7x1 vertical, stride 1, pad 3)
   int tiles_x, tiles_y, n_tiles, total_tiles, kblocks;  // kblocks = taps * Cin / 32
   const float* bias;            // [Cout] or null
   const float* res1;            // [n or 1, H, W, Cout] or null
   const float* res2;            // [n, H, W, Cout] or null
   int res1_bcast;               // res1 has no image axis (positional table)
-  int relu;
-  // final epilogue
-  const float *w2, *b2;         // [od, 32], [od]
+  int relu;                     // 1: on the whole sum; 2: on acc + bias only, before the residuals are added
+  // final / projecting epilogue
+  const float *w2, *b2;         // [od, NT], [od]
   int od, act;
-  float *pred, *conf;           // [n, H, W, od - 1], [n, H, W]
+  float *pred, *conf;           // final: [n, H, W, od - 1], [n, H, W]; project: pred = [n, H, W, od]
 };
 
-template <int NT>
+template <int NT, int EPI>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const ConvArgs g) {
   constexpr int B_BYTES = NT * 128;
-  constexpr bool FINAL = NT == 32;
+  constexpr bool FINAL = EPI == EPI_FINAL;
+  constexpr bool STORE = EPI == EPI_STORE;
+  static_assert(!FINAL || NT == 32, "final epilogue: 32 hidden channels");
+  static_assert(EPI != EPI_PROJECT || CV_PROJ_MAX * NT * 4 <= CV_STG_BYTES, "projection weights must fit the staging tile");
   constexpr uint32_t TMEM_COLS = 2 * NT < 32 ? 32 : 2 * NT;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -73,7 +80,7 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 0 && elect_one()) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (!FINAL) tma_prefetch_desc(&tmC);
+    if (STORE) tma_prefetch_desc(&tmC);
   }
   if (warp == 1 && elect_one()) {
     for (int i = 0; i < CV_STAGES; ++i) {
@@ -116,7 +123,7 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int kb = 0; kb < g.kblocks; ++kb, ++it) {
           const uint32_t s = it % CV_STAGES, ph = (it / CV_STAGES) & 1;
           const int tap = kb / cblocks, cb = kb - tap * cblocks;
-          const int dy = g.taps == 9 ? tap / 3 - 1 : 0, dx = g.taps == 9 ? tap % 3 - 1 : 0;
+          const int dy = g.taps == 9 ? tap / 3 - 1 : (g.taps == 7 ? tap - 3 : 0), dx = g.taps == 9 ? tap % 3 - 1 : 0;
           mbar_wait(&empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&full[s], CV_A_BYTES + B_BYTES);
           tma_load_4d(sA + s * CV_A_BYTES, &tmA, &full[s], cb * CV_KE, x0 + dx, y0 + dy, img, kEvictNormal);
@@ -154,6 +161,15 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const uint32_t stg = smem_u32(sC);
     uint32_t tcount = 0;
+    if constexpr (EPI == EPI_PROJECT) {
+      // w2 [od, NT] -> smem [(c / 4), j, (c % 4)]: one broadcast 16-byte load feeds four FMAs of output j
+      float* ws = reinterpret_cast<float*>(sC);
+      for (int i = et; i < g.od * NT; i += 128) {
+        const int j = i / NT, c = i - j * NT;
+        ws[((c >> 2) * g.od + j) * 4 + (c & 3)] = __ldg(g.w2 + i);
+      }
+      named_bar_sync(1, 128);
+    }
     for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++tcount) {
       int n0, x0, y0, img;
       decode(tile, n0, x0, y0, img);
@@ -207,6 +223,49 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
           }
         }
+      } else if constexpr (EPI == EPI_PROJECT) {
+        float o[CV_PROJ_MAX];
+#pragma unroll
+        for (int j = 0; j < CV_PROJ_MAX; ++j) o[j] = j < g.od ? __ldg(g.b2 + j) : 0.f;
+#pragma unroll 1
+        for (int grp = 0; grp < NT / 32; ++grp) {
+          uint32_t v[32];
+          tmem_ld_x32(taddr + grp * 32, v);
+          tmem_wait_ld();
+          if (grp == NT / 32 - 1) {
+            tcgen05_fence_before();
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive(&tempty[acc]);
+          }
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            float h[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              float a = __uint_as_float(v[4 * c4 + i]);
+              if (g.bias != nullptr) a += __ldg(g.bias + grp * 32 + 4 * c4 + i);
+              h[i] = fmaxf(a, 0.f);
+            }
+            const uint32_t wrow = stg + static_cast<uint32_t>(((grp * 8 + c4) * g.od) * 16);
+#pragma unroll
+            for (int j = 0; j < CV_PROJ_MAX; ++j) {
+              if (j < g.od) {
+                uint32_t w0, w1, w2, w3;
+                ld_shared_v4(wrow + j * 16, w0, w1, w2, w3);
+                o[j] = fmaf(__uint_as_float(w0), h[0], o[j]);
+                o[j] = fmaf(__uint_as_float(w1), h[1], o[j]);
+                o[j] = fmaf(__uint_as_float(w2), h[2], o[j]);
+                o[j] = fmaf(__uint_as_float(w3), h[3], o[j]);
+              }
+            }
+          }
+        }
+        if (valid) {
+          float* pr = g.pred + pix * g.od;
+#pragma unroll
+          for (int j = 0; j < CV_PROJ_MAX; ++j)
+            if (j < g.od) pr[j] = o[j];
+        }
       } else {
 #pragma unroll 1
         for (int grp = 0; grp < NT / 32; ++grp) {
@@ -232,6 +291,10 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               xv[4 * i] += b.x, xv[4 * i + 1] += b.y, xv[4 * i + 2] += b.z, xv[4 * i + 3] += b.w;
             }
           }
+          if (g.relu == 2) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) xv[i] = fmaxf(xv[i], 0.f);
+          }
           if (valid) {
 #pragma unroll
             for (int rsel = 0; rsel < 2; ++rsel) {
@@ -246,7 +309,7 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
           }
-          if (g.relu) {
+          if (g.relu == 1) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) xv[i] = fmaxf(xv[i], 0.f);
           }
@@ -267,7 +330,7 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       }
     }
-    if (!FINAL && et == 0) tma_store_wait<0>();
+    if (STORE && et == 0) tma_store_wait<0>();
   }
 
   tcgen05_fence_before();
@@ -279,13 +342,13 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 }
 
 // ------------------------------------------------------------------------------------------------ host
-template <int NT>
+template <int NT, int EPI>
 static wm_status launch_conv(cudaStream_t st, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, ConvArgs g) {
   int sms = 0;
   WM_TRY(require_sm100(&sms));
   static bool configured = false;
   if (!configured) {
-    WM_CUDA(cudaFuncSetAttribute(conv_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, cv_smem<NT>()));
+    WM_CUDA(cudaFuncSetAttribute(conv_kernel<NT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, cv_smem<NT>()));
     configured = true;
   }
   g.tiles_x = (g.W + CV_TW - 1) / CV_TW;
@@ -294,14 +357,14 @@ static wm_status launch_conv(cudaStream_t st, const CUtensorMap& ta, const CUten
   g.total_tiles = g.n * g.tiles_x * g.tiles_y * g.n_tiles;
   g.kblocks = g.taps * (g.Cin / CV_KE);
   const int grid = g.total_tiles < sms ? g.total_tiles : sms;
-  return launch_pdl(conv_kernel<NT>, dim3(grid), dim3(CV_THREADS), cv_smem<NT>(), st, ta, tb, tc, g);
+  return launch_pdl(conv_kernel<NT, EPI>, dim3(grid), dim3(CV_THREADS), cv_smem<NT>(), st, ta, tb, tc, g);
 }
 
 static wm_status conv_check(const void* in, const void* w, int n, int H, int W, int Cin, int Cout, int taps) {
   WM_CHECK(in && w, "conv2d: null operand");
   WM_CHECK(n > 0 && H > 0 && W > 0 && Cin > 0 && Cin % CV_KE == 0 && Cout > 0, "conv2d: bad geometry n=%d H=%d W=%d Cin=%d Cout=%d", n,
            H, W, Cin, Cout);
-  WM_CHECK(taps == 1 || taps == 9, "conv2d: taps must be 1 (1x1) or 9 (3x3, stride 1, pad 1)");
+  WM_CHECK(taps == 1 || taps == 9 || taps == 7, "conv2d: taps must be 1 (1x1), 9 (3x3, pad 1) or 7 (7x1 vertical, pad 3)");
   WM_CHECK((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0, "conv2d: operands must be 16-byte aligned");
   return WM_OK;
 }
@@ -322,7 +385,7 @@ wm_status conv2d_nhwc(cudaStream_t st, const void* in, int n, int H, int W, int 
   g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = Cout, g.taps = taps;
   g.bias = bias, g.res1 = static_cast<const float*>(res1), g.res1_bcast = res1_bcast;
   g.res2 = static_cast<const float*>(res2), g.relu = relu;
-  return NT == 128 ? launch_conv<128>(st, ta, tb, tc, g) : launch_conv<256>(st, ta, tb, tc, g);
+  return NT == 128 ? launch_conv<128, EPI_STORE>(st, ta, tb, tc, g) : launch_conv<256, EPI_STORE>(st, ta, tb, tc, g);
 }
 
 // scratch.output_conv2 + activate_head (dense_head.py:85-89, 297-344): conv3x3(Cin -> 32) + ReLU + conv1x1(32 -> od)
@@ -338,7 +401,23 @@ wm_status conv2d_final(cudaStream_t st, const void* in, int n, int H, int W, int
   ConvArgs g{};
   g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = 32, g.taps = 9;
   g.bias = b1, g.w2 = w2, g.b2 = b2, g.od = od, g.act = act, g.pred = pred, g.conf = conf;
-  return launch_conv<32>(st, ta, tb, ta, g);
+  return launch_conv<32, EPI_FINAL>(st, ta, tb, ta, g);
+}
+
+// gs_renderer.gs_head (models/rasterization.py:149-153): conv3x3(Cin -> 256, bias optional) + ReLU + conv1x1(256 -> od) + b2,
+// raw fp32 [n, H, W, od]; the 256-channel hidden map stays in TMEM.  w1: fp32 [256, 9 * Cin] tap-major; w2: fp32 [od, 256].
+wm_status conv2d_project(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
+                         const float* w2, const float* b2, int od, float* out) {
+  WM_TRY(conv_check(in, w1, n, H, W, Cin, 256, 9));
+  WM_CHECK(w2 && b2 && out && od > 0 && od <= CV_PROJ_MAX, "conv2d_project: bad argument (od=%d, at most %d)", od, CV_PROJ_MAX);
+  const CUtensorMapDataType f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  CUtensorMap ta, tb;
+  WM_TRY(tmap_nhwc(&ta, f32, 4, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
+  WM_TRY(tmap_2d(&tb, f32, 4, w1, 256, (uint64_t)9 * Cin, (uint64_t)9 * Cin, CV_KE, 256));
+  ConvArgs g{};
+  g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = 256, g.taps = 9;
+  g.bias = b1, g.w2 = w2, g.b2 = b2, g.od = od, g.pred = out;
+  return launch_conv<256, EPI_PROJECT>(st, ta, tb, ta, g);
 }
 
 }  // namespace wm

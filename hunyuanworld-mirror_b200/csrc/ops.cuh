@@ -54,6 +54,18 @@ wm_status normalize_depth(cudaStream_t st, const float* depth, int n_views, int 
                           int max_percentile, float* out);
 wm_status pose_prior(cudaStream_t st, const float* extr, int extr_stride, const float* intr, int S, int H, int W, double padding,
                      float* poses, float* rays);
+// Gaussian path (conv.cu, splat.cu)
+wm_status conv2d_project(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
+                         const float* w2, const float* b2, int od, float* out);
+wm_status im2row7(cudaStream_t st, const float* img, int n, int H, int W, void* out);
+wm_status splat_cameras(cudaStream_t st, const float* params, int n, int H, int W, float* cam);
+wm_status splat_prepare(cudaStream_t st, const float* raw, const float* img, const float* depth, const float* cam, int n, int H,
+                        int W, float* means, float* quats, float* scales, float* opacities, float* sh, float* weights);
+wm_status prune_workspace_bytes(long long N, size_t* bytes);
+wm_status prune_splats(cudaStream_t st, long long N, const float* means, const float* quats, const float* scales,
+                       const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
+                       size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities, float* out_sh,
+                       unsigned* count);
 wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);
 
 }  // namespace wm

@@ -1,0 +1,330 @@
+// Gaussian path of WorldMirror.forward (reference: src/models/models/rasterization.py).
+// What `GaussianSplatRenderer.render` leaves in the predictions is `splats` only (the rasterised images are dropped,
+// rasterization.py:239-246), so the path is: gs DPT head (conv.cu / headops.cu, plus the 7x7 image branch prepared
+// here) -> gs_head parameter convolution (conv.cu, projecting epilogue) -> prepare_splats (:389-498) -> prune_gs (:301-387).
+// Everything in this file is HBM-bound elementwise / integer work, written for coalesced access, no tensor cores:
+//   im2row7_kernel        images NCHW -> NHWC rows of the 7 horizontal taps (21 of 32 channels), so the 7x7 convolution
+//                         of `input_merger` (dense_head.py:91-94) becomes a 7-tap vertical implicit GEMM of conv.cu;
+//   splat_camera_kernel   camera_params [S, 9] -> camera-to-world rotation / translation and pinhole intrinsics
+//                         (utils/camera_utils.py:46-75, utils/rotation.py:8-38, utils/geometry.py:92-111);
+//   splat_prepare_kernel  activations of act_gs.py, RGB2SH, depth un-projection (utils/geometry.py:5-89);
+//   prune: voxel index bounds -> flat voxel key -> stable radix sort (CUB, library) -> segment heads -> scan -> one
+//                         thread per voxel merges its splats IN ORIGINAL INDEX ORDER, which is the order the reference's
+//                         CPU scatter_add_ accumulates in, so the merge is deterministic (the reference on CUDA is not).
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace wm {
+
+constexpr int SP_THREADS = 256;
+constexpr int SP_RAW = 12;  // quats 4 | scales 3 | opacity 1 | residual SH (degree 0) 3 | weight 1  (rasterization.py:131-138)
+
+// ------------------------------------------------------------------------------------------------ 7x7 image branch
+__global__ void __launch_bounds__(SP_THREADS) im2row7_kernel(const float* __restrict__ img, int n, int H, int W, float4* __restrict__ out) {
+  const size_t total = (size_t)n * H * W * 8;
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+    const int grp = (int)(t & 7);
+    const size_t pix = t >> 3;
+    const int x = (int)(pix % W);
+    const int y = (int)((pix / W) % H);
+    const size_t im = pix / ((size_t)W * H);
+    float v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int k = grp * 4 + i, kx = k / 3, c = k - kx * 3, xs = x + kx - 3;
+      v[i] = (k < 21 && xs >= 0 && xs < W) ? tf32_rn(__ldg(img + ((im * 3 + c) * H + y) * W + xs)) : 0.f;
+    }
+    out[t] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
+wm_status im2row7(cudaStream_t st, const float* img, int n, int H, int W, void* out) {
+  WM_CHECK(img && out && n > 0 && H > 0 && W > 0, "im2row7: bad argument");
+  const size_t total = (size_t)n * H * W * 8;
+  const int grid = (int)std::min<size_t>((total + SP_THREADS - 1) / SP_THREADS, 148 * 32);
+  im2row7_kernel<<<grid, SP_THREADS, 0, st>>>(img, n, H, W, static_cast<float4*>(out));
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ cameras
+// cam[v] = { R_c2w (9, row major), t_c2w (3), fx, fy, cx, cy }.  fp32, operations in the reference's order.
+__global__ void splat_camera_kernel(const float* __restrict__ params, int n, int H, int W, float* __restrict__ cam) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n) return;
+  const float* p = params + (size_t)v * 9;
+  const float t0 = p[0], t1 = p[1], t2 = p[2], i = p[3], j = p[4], k = p[5], r = p[6];
+  const float ss = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(i, i), __fmul_rn(j, j)), __fmul_rn(k, k)), __fmul_rn(r, r));
+  const float two_s = __fdiv_rn(2.0f, ss);
+  auto a = [](float x, float y) { return __fadd_rn(x, y); };
+  auto s = [](float x, float y) { return __fsub_rn(x, y); };
+  auto m = [](float x, float y) { return __fmul_rn(x, y); };
+  float R[9];  // world-to-camera rotation (quat_to_rotmat)
+  R[0] = s(1.f, m(two_s, a(m(j, j), m(k, k))));
+  R[1] = m(two_s, s(m(i, j), m(k, r)));
+  R[2] = m(two_s, a(m(i, k), m(j, r)));
+  R[3] = m(two_s, a(m(i, j), m(k, r)));
+  R[4] = s(1.f, m(two_s, a(m(i, i), m(k, k))));
+  R[5] = m(two_s, s(m(j, k), m(i, r)));
+  R[6] = m(two_s, s(m(i, k), m(j, r)));
+  R[7] = m(two_s, a(m(j, k), m(i, r)));
+  R[8] = s(1.f, m(two_s, a(m(i, i), m(j, j))));
+  float* o = cam + (size_t)v * 16;
+  // closed_form_inverse_se3: R^T, -R^T t
+#pragma unroll
+  for (int rr = 0; rr < 3; ++rr) {
+#pragma unroll
+    for (int cc = 0; cc < 3; ++cc) o[rr * 3 + cc] = R[cc * 3 + rr];
+    o[9 + rr] = -a(a(m(R[rr], t0), m(R[3 + rr], t1)), m(R[6 + rr], t2));
+  }
+  o[12] = __fdiv_rn(m((float)W, 0.5f), tanf(m(p[8], 0.5f)));  // fx from fov_u
+  o[13] = __fdiv_rn(m((float)H, 0.5f), tanf(m(p[7], 0.5f)));  // fy from fov_v
+  o[14] = m((float)W, 0.5f);
+  o[15] = m((float)H, 0.5f);
+}
+
+wm_status splat_cameras(cudaStream_t st, const float* params, int n, int H, int W, float* cam) {
+  WM_CHECK(params && cam && n > 0 && H > 0 && W > 0, "splat_cameras: bad argument");
+  splat_camera_kernel<<<(n + 127) / 128, 128, 0, st>>>(params, n, H, W, cam);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ prepare_splats
+__device__ __forceinline__ float sp_sigmoid(float x) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x))); }
+
+struct SplatOut {
+  float *means, *quats, *scales, *opacities, *sh, *weights;  // [N,3] [N,4] [N,3] [N] [N,3] [N]
+};
+
+__global__ void __launch_bounds__(SP_THREADS)
+splat_prepare_kernel(const float* __restrict__ raw, const float* __restrict__ img, const float* __restrict__ depth,
+                     const float* __restrict__ cam, int n, int H, int W, SplatOut o) {
+  const size_t hw = (size_t)H * W, total = (size_t)n * hw;
+  for (size_t pix = blockIdx.x * (size_t)blockDim.x + threadIdx.x; pix < total; pix += (size_t)gridDim.x * blockDim.x) {
+    const size_t v = pix / hw, rem = pix - v * hw;
+    const int y = (int)(rem / W), x = (int)(rem - (size_t)y * W);
+    float p[SP_RAW];
+    const float4* r4 = reinterpret_cast<const float4*>(raw + pix * SP_RAW);
+#pragma unroll
+    for (int i = 0; i < SP_RAW / 4; ++i) {
+      const float4 t = __ldg(r4 + i);
+      p[4 * i] = t.x, p[4 * i + 1] = t.y, p[4 * i + 2] = t.z, p[4 * i + 3] = t.w;
+    }
+    // reg_dense_rotation: q / (|q| + 1e-8)
+    const float qn = __fadd_rn(__fsqrt_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(p[0], p[0]), __fmul_rn(p[1], p[1])), __fmul_rn(p[2], p[2])),
+                                                    __fmul_rn(p[3], p[3]))), 1e-8f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o.quats[pix * 4 + i] = __fdiv_rn(p[i], qn);
+    // reg_dense_scales (exp) clamped at 0.3; sigmoid opacity and weight
+#pragma unroll
+    for (int i = 0; i < 3; ++i) o.scales[pix * 3 + i] = fminf(expf(p[4 + i]), 0.3f);
+    o.opacities[pix] = sp_sigmoid(p[7]);
+    o.weights[pix] = sp_sigmoid(p[11]);
+    // sh = RGB2SH(image) + residual  (utils/sh_utils.py:112-113, C0 as an fp32 divisor)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float rgb = __ldg(img + (v * 3 + c) * hw + rem);
+      o.sh[pix * 3 + c] = __fadd_rn(__fdiv_rn(__fsub_rn(rgb, 0.5f), 0.28209479177387814f), p[8 + c]);
+    }
+    // means: depth_to_world_coords_points(gs_depth, camera-to-world, intrinsics)
+    const float* cv = cam + v * 16;
+    const float z = __ldg(depth + pix);
+    const float xc = __fdiv_rn(__fmul_rn(__fsub_rn((float)x, cv[14]), z), cv[12]);
+    const float yc = __fdiv_rn(__fmul_rn(__fsub_rn((float)y, cv[15]), z), cv[13]);
+#pragma unroll
+    for (int jx = 0; jx < 3; ++jx)
+      o.means[pix * 3 + jx] = fmaf(cv[jx * 3 + 2], z, fmaf(cv[jx * 3 + 1], yc, cv[jx * 3] * xc)) + cv[9 + jx];
+  }
+}
+
+wm_status splat_prepare(cudaStream_t st, const float* raw, const float* img, const float* depth, const float* cam, int n, int H,
+                        int W, float* means, float* quats, float* scales, float* opacities, float* sh, float* weights) {
+  WM_CHECK(raw && img && depth && cam && means && quats && scales && opacities && sh && weights && n > 0 && H > 0 && W > 0,
+           "splat_prepare: bad argument");
+  const size_t total = (size_t)n * H * W;
+  const int grid = (int)std::min<size_t>((total + SP_THREADS - 1) / SP_THREADS, 148 * 16);
+  splat_prepare_kernel<<<grid, SP_THREADS, 0, st>>>(raw, img, depth, cam, n, H, W, SplatOut{means, quats, scales, opacities, sh, weights});
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+}  // namespace wm
+
+// ------------------------------------------------------------------------------------------------ prune_gs
+namespace wm {
+
+struct PruneWs {
+  long long* bounds;  // [6] = min xyz, max xyz of the voxel indices
+  long long *keys_in, *keys_out;
+  unsigned *vals_in, *vals_out, *flags, *segid;
+  void* cub_tmp;
+  size_t cub_bytes;
+};
+
+__device__ __forceinline__ long long sp_voxel(float m, float vs) { return (long long)floorf(__fdiv_rn(m, vs)); }
+
+__global__ void prune_init_kernel(long long* bounds) {
+  if (threadIdx.x < 3) bounds[threadIdx.x] = LLONG_MAX;
+  else if (threadIdx.x < 6) bounds[threadIdx.x] = LLONG_MIN;
+}
+
+__global__ void __launch_bounds__(SP_THREADS) prune_bounds_kernel(const float* __restrict__ means, unsigned N, float vs, long long* bounds) {
+  long long lo[3] = {LLONG_MAX, LLONG_MAX, LLONG_MAX}, hi[3] = {LLONG_MIN, LLONG_MIN, LLONG_MIN};
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const long long v = sp_voxel(__ldg(means + (size_t)i * 3 + d), vs);
+      lo[d] = v < lo[d] ? v : lo[d];
+      hi[d] = v > hi[d] ? v : hi[d];
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const long long a = __shfl_xor_sync(0xffffffffu, lo[d], off), b = __shfl_xor_sync(0xffffffffu, hi[d], off);
+      lo[d] = a < lo[d] ? a : lo[d];
+      hi[d] = b > hi[d] ? b : hi[d];
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(bounds + d, lo[d]);
+      atomicMax(bounds + 3 + d, hi[d]);
+    }
+  }
+}
+
+// flat = (vx - minx) * dimy * dimz + (vy - miny) * dimz + (vz - minz), int64 as torch computes it (rasterization.py:322-331)
+__global__ void __launch_bounds__(SP_THREADS)
+prune_keys_kernel(const float* __restrict__ means, unsigned N, float vs, const long long* __restrict__ bounds, long long* __restrict__ keys,
+                  unsigned* __restrict__ vals) {
+  const long long mx = bounds[0], my = bounds[1], mz = bounds[2];
+  const long long dy = bounds[4] - my + 1, dz = bounds[5] - mz + 1;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const long long vx = sp_voxel(__ldg(means + (size_t)i * 3), vs) - mx;
+    const long long vy = sp_voxel(__ldg(means + (size_t)i * 3 + 1), vs) - my;
+    const long long vz = sp_voxel(__ldg(means + (size_t)i * 3 + 2), vs) - mz;
+    keys[i] = vx * dy * dz + vy * dz + vz;
+    vals[i] = i;
+  }
+}
+
+__global__ void __launch_bounds__(SP_THREADS) prune_flags_kernel(const long long* __restrict__ keys, unsigned N, unsigned* __restrict__ flags) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x)
+    flags[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u;
+}
+
+// One thread per voxel (= per segment head of the sorted keys).  The sort is stable, so a segment lists its splats in
+// ascending original index: the order torch's CPU scatter_add_ adds them in.  Products are rounded before they are added
+// (no fused multiply-add), as `x * weights` followed by scatter_add_ does.
+__global__ void __launch_bounds__(SP_THREADS)
+prune_merge_kernel(const long long* __restrict__ keys, const unsigned* __restrict__ vals, const unsigned* __restrict__ segid, unsigned N,
+                   SplatOut in, SplatOut out, unsigned* __restrict__ count) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    if (i == N - 1) *count = segid[i];
+    const long long key = keys[i];
+    if (i != 0 && keys[i - 1] == key) continue;
+    const unsigned s = segid[i] - 1;
+    float wsum = 0.f, op = 0.f, m[3] = {0.f, 0.f, 0.f}, sh[3] = {0.f, 0.f, 0.f}, sc[3] = {0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
+    unsigned j = i;
+    do {
+      const size_t idx = vals[j];
+      const float w = __ldg(in.weights + idx);
+      wsum = __fadd_rn(wsum, w);
+      op = __fadd_rn(op, __fmul_rn(w, w));
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        m[d] = __fadd_rn(m[d], __fmul_rn(__ldg(in.means + idx * 3 + d), w));
+        sh[d] = __fadd_rn(sh[d], __fmul_rn(__ldg(in.sh + idx * 3 + d), w));
+        sc[d] = __fadd_rn(sc[d], __fmul_rn(__ldg(in.scales + idx * 3 + d), w));
+      }
+#pragma unroll
+      for (int d = 0; d < 4; ++d) q[d] = __fadd_rn(q[d], __fmul_rn(__ldg(in.quats + idx * 4 + d), w));
+      ++j;
+    } while (j < N && keys[j] == key);
+    wsum = fmaxf(wsum, 1e-8f);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      out.means[(size_t)s * 3 + d] = __fdiv_rn(m[d], wsum);
+      out.sh[(size_t)s * 3 + d] = __fdiv_rn(sh[d], wsum);
+      out.scales[(size_t)s * 3 + d] = __fdiv_rn(sc[d], wsum);
+    }
+    out.opacities[s] = __fdiv_rn(op, wsum);
+    const float qn = fmaxf(__fsqrt_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q[0], q[0]), __fmul_rn(q[1], q[1])), __fmul_rn(q[2], q[2])),
+                                                 __fmul_rn(q[3], q[3]))), 1e-8f);
+#pragma unroll
+    for (int d = 0; d < 4; ++d) out.quats[(size_t)s * 4 + d] = __fdiv_rn(q[d], qn);
+  }
+}
+
+static size_t sp_align(size_t x) { return (x + 255) & ~size_t(255); }
+
+static wm_status prune_layout(unsigned N, void* base, size_t* total, PruneWs* ws) {
+  size_t sort_bytes = 0, scan_bytes = 0;
+  WM_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const long long*)nullptr, (long long*)nullptr, (const unsigned*)nullptr,
+                                          (unsigned*)nullptr, (int)N, 0, 64, (cudaStream_t)0));
+  WM_CUDA(cub::DeviceScan::InclusiveSum(nullptr, scan_bytes, (const unsigned*)nullptr, (unsigned*)nullptr, (int)N, (cudaStream_t)0));
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? static_cast<char*>(base) + off : nullptr;
+    off += sp_align(bytes);
+    return p;
+  };
+  PruneWs w{};
+  w.bounds = static_cast<long long*>(take(6 * sizeof(long long)));
+  w.keys_in = static_cast<long long*>(take((size_t)N * 8));
+  w.keys_out = static_cast<long long*>(take((size_t)N * 8));
+  w.vals_in = static_cast<unsigned*>(take((size_t)N * 4));
+  w.vals_out = static_cast<unsigned*>(take((size_t)N * 4));
+  w.flags = static_cast<unsigned*>(take((size_t)N * 4));
+  w.segid = static_cast<unsigned*>(take((size_t)N * 4));
+  w.cub_bytes = std::max(sort_bytes, scan_bytes);
+  w.cub_tmp = take(w.cub_bytes);
+  *total = off;
+  if (ws) *ws = w;
+  return WM_OK;
+}
+
+wm_status prune_workspace_bytes(long long N, size_t* bytes) {
+  WM_CHECK(N > 0 && N < (1ll << 31) && bytes, "prune_workspace_bytes: bad argument");
+  return prune_layout((unsigned)N, nullptr, bytes, nullptr);
+}
+
+// prune_gs (rasterization.py:301-387) for one scene: N splats -> *count voxels (device word), outputs sized for N rows.
+wm_status prune_splats(cudaStream_t st, long long N, const float* means, const float* quats, const float* scales,
+                       const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
+                       size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities, float* out_sh,
+                       unsigned* count) {
+  WM_CHECK(N > 0 && N < (1ll << 31) && means && quats && scales && opacities && sh && weights && workspace && out_means && out_quats &&
+               out_scales && out_opacities && out_sh && count && voxel_size > 0,
+           "prune_splats: bad argument");
+  PruneWs w{};
+  size_t need = 0;
+  WM_TRY(prune_layout((unsigned)N, workspace, &need, &w));
+  WM_CHECK(workspace_bytes >= need, "prune_splats: workspace of %zu bytes, %zu needed", workspace_bytes, need);
+  const unsigned n = (unsigned)N;
+  const float vs = (float)voxel_size;  // the Python float becomes an fp32 divisor
+  const int grid = (int)std::min<size_t>(((size_t)n + SP_THREADS - 1) / SP_THREADS, 148 * 16);
+  prune_init_kernel<<<1, 32, 0, st>>>(w.bounds);
+  prune_bounds_kernel<<<grid, SP_THREADS, 0, st>>>(means, n, vs, w.bounds);
+  prune_keys_kernel<<<grid, SP_THREADS, 0, st>>>(means, n, vs, w.bounds, w.keys_in, w.vals_in);
+  WM_LAUNCH_CHECK();
+  size_t tmp = w.cub_bytes;
+  WM_CUDA(cub::DeviceRadixSort::SortPairs(w.cub_tmp, tmp, (const long long*)w.keys_in, w.keys_out, (const unsigned*)w.vals_in, w.vals_out,
+                                          (int)n, 0, 64, st));
+  prune_flags_kernel<<<grid, SP_THREADS, 0, st>>>(w.keys_out, n, w.flags);
+  WM_LAUNCH_CHECK();
+  tmp = w.cub_bytes;
+  WM_CUDA(cub::DeviceScan::InclusiveSum(w.cub_tmp, tmp, (const unsigned*)w.flags, w.segid, (int)n, st));
+  SplatOut in{const_cast<float*>(means), const_cast<float*>(quats), const_cast<float*>(scales), const_cast<float*>(opacities),
+              const_cast<float*>(sh), const_cast<float*>(weights)};
+  SplatOut out{out_means, out_quats, out_scales, out_opacities, out_sh, nullptr};
+  prune_merge_kernel<<<grid, SP_THREADS, 0, st>>>(w.keys_out, w.vals_out, w.segid, n, in, out, count);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+}  // namespace wm

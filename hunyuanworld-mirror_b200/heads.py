@@ -70,14 +70,15 @@ class B200DPTHead(torch.nn.Module):
                  features: int = 256, out_channels: Sequence[int] = (256, 512, 1024, 1024), pos_embed: bool = True,
                  down_ratio: int = 1, is_gsdpt: bool = False):
         super().__init__()
-        if is_gsdpt or down_ratio != 1 or not pos_embed or patch_size != PATCH:
-            raise NotImplementedError("B200DPTHead covers the depth / points / normals configuration of WorldMirror")
+        if down_ratio != 1 or not pos_embed or patch_size != PATCH:
+            raise NotImplementedError("B200DPTHead covers the configurations WorldMirror constructs (down_ratio 1, pos_embed)")
         if dim_in not in (1024, 2048) or features != 256 or tuple(out_channels) != (256, 512, 1024, 1024):
             raise NotImplementedError("B200DPTHead is built for dim_in 2048, features 256, out_channels (256,512,1024,1024)")
         act, conf = activation.split("+") if "+" in activation else (activation, "expp1")
         if act not in _ACT or conf != "expp1" or output_dim not in (2, 4):
             raise ValueError(f"Unknown attribute activation: {activation}")
         self.dim_in, self.output_dim, self.activation, self.act = dim_in, output_dim, activation, _ACT[act]
+        self.is_gsdpt = bool(is_gsdpt)
         self.oc = tuple(out_channels)
         self.w: Dict[str, torch.Tensor] = {}
         self._pos: Dict[tuple, tuple] = {}
@@ -120,6 +121,12 @@ class B200DPTHead(torch.nn.Module):
         w["oc2.w"], w["oc2.b"] = conv("scratch.output_conv2.0.weight"), vec("scratch.output_conv2.0.bias")
         w["oc3.w"] = sd["scratch.output_conv2.2.weight"].detach().to(dev, torch.float32).reshape(self.output_dim, 32).contiguous()
         w["oc3.b"] = vec("scratch.output_conv2.2.bias")
+        if self.is_gsdpt:  # input_merger = Conv2d(3, 128, 7, 1, 3): [co, ci, ky, kx] -> [co, ky, (kx, ci) padded 21 -> 32]
+            t = sd["input_merger.0.weight"].detach().to(dev, torch.float32)
+            co = t.shape[0]
+            rows = torch.zeros(co, 7, 32, dtype=torch.float32, device=dev)
+            rows[:, :, :21] = t.permute(0, 2, 3, 1).reshape(co, 7, 21)
+            w["im.w"], w["im.b"] = round_tf32(rows.reshape(co, 7 * 32).contiguous()), vec("input_merger.0.bias")
         assert tuple(w["proj0.w"].shape) == (self.oc[0], self.dim_in)
         self.w, self._loaded, self._dev = w, True, dev
         return torch.nn.modules.module._IncompatibleKeys([], [])
@@ -168,14 +175,20 @@ class B200DPTHead(torch.nn.Module):
         na = self.output_dim - 1
         pred = torch.empty(B, S, H, W, na, dtype=torch.float32, device=dev)
         conf = torch.empty(B, S, H, W, dtype=torch.float32, device=dev)
+        feat = torch.empty(B, S, H, W, 128, dtype=torch.float32, device=dev) if self.is_gsdpt else None
+        if self.is_gsdpt:
+            images = images.to(dev, torch.float32).contiguous()
         with torch.cuda.device(dev):
             for b in range(B):
                 for f0 in range(0, S, chunk):
                     f1 = min(f0 + chunk, S)
-                    self._forward_chunk([t[b, f0:f1] for t in token_list], H, W, patch_start_idx, pred[b, f0:f1], conf[b, f0:f1])
+                    self._forward_chunk([t[b, f0:f1] for t in token_list], H, W, patch_start_idx, pred[b, f0:f1], conf[b, f0:f1],
+                                        images[b, f0:f1] if self.is_gsdpt else None, feat[b, f0:f1] if self.is_gsdpt else None)
+        if self.is_gsdpt:  # (features [B, S, 128, H, W], predictions, confidence) as dense_head.py:232-245; channels-last memory
+            return feat.permute(0, 1, 4, 2, 3), pred, conf
         return pred, conf
 
-    def _forward_chunk(self, toks, H, W, psi, pred, conf):
+    def _forward_chunk(self, toks, H, W, psi, pred, conf, images=None, feat=None):
         lib, w = capi.lib(), self.w
         n, P, Cd = toks[0].shape
         gh, gw = H // PATCH, W // PATCH
@@ -224,6 +237,14 @@ class B200DPTHead(torch.nn.Module):
         _k(lib.wm_conv2d_final(_st(), fused.data_ptr(), n, H, W, 128, w["oc2.w"].data_ptr(), w["oc2.b"].data_ptr(),
                                        w["oc3.w"].data_ptr(), w["oc3.b"].data_ptr(), self.output_dim, self.act, pred.data_ptr(),
                                        conf.data_ptr()))
+        if self.is_gsdpt:
+            # fused + relu(input_merger(images)) (dense_head.py:239-242): the 7 horizontal taps of the 3-channel image become
+            # 21 (of 32) channels of an NHWC map, the 7 vertical taps run as an implicit GEMM with ReLU before the residual
+            assert H == gh * PATCH and W == gw * PATCH
+            rows = torch.empty(n, H, W, 32, dtype=torch.float32, device=dev)
+            _k(lib.wm_im2row7(_st(), images.data_ptr(), n, H, W, rows.data_ptr()))
+            _k(lib.wm_conv2d_nhwc(_st(), rows.data_ptr(), n, H, W, 32, w["im.w"].data_ptr(), 7, 128, w["im.b"].data_ptr(),
+                                  fused.data_ptr(), 0, None, 2, feat.data_ptr()))
 
 
 class B200CameraHead(torch.nn.Module):
@@ -355,18 +376,147 @@ class B200CameraHead(torch.nn.Module):
         return outs
 
 
+class B200GaussianSplatRenderer(torch.nn.Module):
+    """`GaussianSplatRenderer` (src/models/models/rasterization.py:97-246) as far as `WorldMirror.forward` observes it:
+    `render` fills `predictions["splats"]`.  The reference also rasterises every view with gsplat and then drops the
+    images (rasterization.py:221-246); that dead compute is not reproduced.  Built for the configuration WorldMirror
+    constructs (worldmirror.py:110-118): sh_degree 0, no offsets, residual SH, position from gs_depth + predicted camera.
+    `enable_conf_filter` (off in that configuration) is not implemented."""
+
+    SPLAT_KEYS = ("means", "quats", "scales", "opacities", "sh", "weights")
+
+    def __init__(self, feature_dim: int = 256, sh_degree: int = 0, predict_offset: bool = False, predict_residual_sh: bool = True,
+                 enable_prune: bool = True, voxel_size: float = 0.002, using_gtcamera_splat: bool = False,
+                 render_novel_views: bool = False, enable_conf_filter: bool = False, conf_threshold_percent: float = 30.0,
+                 max_gaussians: int = 5000000, debug=False, group=None):
+        super().__init__()
+        if feature_dim != 256 or sh_degree != 0 or predict_offset or not predict_residual_sh or enable_conf_filter:
+            raise NotImplementedError("B200GaussianSplatRenderer covers WorldMirror's configuration: feature_dim 256, "
+                                      "sh_degree 0, no offsets, residual SH, no confidence filter")
+        self.feature_dim, self.sh_degree, self.nums_sh = feature_dim, sh_degree, 1
+        self.enable_prune, self.voxel_size = enable_prune, voxel_size
+        self.group = group  # process group the views are sharded over (None: single process)
+        self.w: Dict[str, torch.Tensor] = {}
+        self._loaded = False
+        self._ws = None
+
+    def load_state_dict(self, sd, strict: bool = True, device=None):
+        """Reference keys: gs_head.0.weight [256, 128, 3, 3] (no bias), gs_head.2.weight [12, 256, 1, 1], gs_head.2.bias [12]."""
+        capi.lib()
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        t = sd["gs_head.0.weight"].detach().to(dev, torch.float32)
+        co, ci, kh, kw = t.shape
+        self.w = {"w1": round_tf32(t.permute(0, 2, 3, 1).reshape(co, kh * kw * ci).contiguous()),
+                  "w2": sd["gs_head.2.weight"].detach().to(dev, torch.float32).reshape(-1, co).contiguous(),
+                  "b2": sd["gs_head.2.bias"].detach().to(dev, torch.float32).contiguous()}
+        assert (co, ci) == (256, 128) and self.w["w2"].shape[0] == 12
+        self._loaded, self._dev = True, dev
+        return torch.nn.modules.module._IncompatibleKeys([], [])
+
+    # ------------------------------------------------------------------ pieces
+    def gs_head(self, feat_nhwc: torch.Tensor) -> torch.Tensor:
+        """[n, H, W, 128] fp32 channels-last -> raw Gaussian parameters [n, H, W, 12] (rasterization.py:149-153, 196-197)."""
+        n, H, W, c = feat_nhwc.shape
+        raw = torch.empty(n, H, W, 12, dtype=torch.float32, device=feat_nhwc.device)
+        _k(capi.lib().wm_conv2d_project(_st(), feat_nhwc.data_ptr(), n, H, W, c, self.w["w1"].data_ptr(), None,
+                                        self.w["w2"].data_ptr(), self.w["b2"].data_ptr(), 12, raw.data_ptr()))
+        return raw
+
+    def prepare_splats(self, raw, images, gs_depth, camera_params):
+        """rasterization.py:389-498 for one scene: raw [n, H, W, 12], images [n, 3, H, W], gs_depth [n, H, W(, 1)],
+        camera_params [n, 9] -> dict of fp32 tensors over N = n*H*W splats."""
+        lib = capi.lib()
+        n, H, W, _ = raw.shape
+        N, dev = n * H * W, raw.device
+        cam = torch.empty(n, 16, dtype=torch.float32, device=dev)
+        cp = camera_params.to(dev, torch.float32).contiguous()
+        _k(lib.wm_splat_cameras(_st(), cp.data_ptr(), n, H, W, cam.data_ptr()))
+        out = {k: torch.empty((N, d) if d > 1 else (N,), dtype=torch.float32, device=dev)
+               for k, d in (("means", 3), ("quats", 4), ("scales", 3), ("opacities", 1), ("sh", 3), ("weights", 1))}
+        images, gs_depth = images.to(dev, torch.float32).contiguous(), gs_depth.contiguous()
+        _k(lib.wm_splat_prepare(_st(), raw.data_ptr(), images.data_ptr(), gs_depth.data_ptr(), cam.data_ptr(), n, H, W,
+                                out["means"].data_ptr(), out["quats"].data_ptr(), out["scales"].data_ptr(),
+                                out["opacities"].data_ptr(), out["sh"].data_ptr(), out["weights"].data_ptr()))
+        return out
+
+    def prune_gs(self, splats, voxel_size=None):
+        """rasterization.py:301-387 for one scene (tensors over N splats) -> tensors over the K occupied voxels, ascending
+        flat voxel index.  One host read (K) at the end, as the reference's `len(unique_voxels)`."""
+        lib = capi.lib()
+        vs = self.voxel_size if voxel_size is None else voxel_size
+        m = splats["means"]
+        N, dev = m.shape[0], m.device
+        need = C.c_size_t(0)
+        capi.check(lib.wm_prune_workspace_bytes(N, C.byref(need)))
+        if self._ws is None or self._ws.numel() < need.value or self._ws.device != dev:
+            self._ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
+        out = {k: torch.empty_like(splats[k]) for k in ("means", "quats", "scales", "opacities", "sh")}
+        count = torch.zeros(1, dtype=torch.int32, device=dev)
+        LAUNCHES[0] += 6  # bounds, keys, sort (several CUB kernels, counted once), flags, scan, merge
+        capi.check(lib.wm_prune_splats(_st(), N, m.data_ptr(), splats["quats"].data_ptr(), splats["scales"].data_ptr(),
+                                       splats["opacities"].data_ptr(), splats["sh"].reshape(N, 3).data_ptr(),
+                                       splats["weights"].data_ptr(), float(vs), self._ws.data_ptr(), self._ws.numel(),
+                                       out["means"].data_ptr(), out["quats"].data_ptr(), out["scales"].data_ptr(),
+                                       out["opacities"].data_ptr(), out["sh"].data_ptr(), count.data_ptr()))
+        K = int(count.item())
+        res = {k: v[:K] for k, v in out.items()}
+        res["sh"] = res["sh"].reshape(K, 1, 3)
+        return res
+
+    # ------------------------------------------------------------------ reference entry point
+    @torch.no_grad()
+    def render(self, gs_feats, images, predictions, views=None, context_predictions=None):
+        """gs_feats [B, S, 128, H, W] (as B200DPTHead(is_gsdpt=True) returns it), images [B, S, 3, H, W], predictions with
+        `camera_params` [B, S, 9] and `gs_depth` [B, S, H, W, 1].  Adds predictions["splats"]: with pruning a dict of
+        per-scene lists (means [K,3], sh [K,1,3], opacities [K], scales [K,3], quats [K,4]), as rasterization.py:381-386;
+        without, the prepare_splats dict batched over B."""
+        if not self._loaded:
+            raise RuntimeError("B200GaussianSplatRenderer: load_state_dict() has not been called")
+        if context_predictions is not None:
+            raise NotImplementedError("context_predictions (training-time scale alignment) is not part of the inference path")
+        B, S_all = images.shape[:2]
+        S = int(views["context_nums"]) if views is not None and "context_nums" in views else S_all
+        feat = gs_feats.permute(0, 1, 3, 4, 2)  # back to channels-last: a view when it came from B200DPTHead
+        scenes = []
+        for b in range(B):
+            raw = self.gs_head(feat[b, :S].contiguous())
+            sp = self.prepare_splats(raw, images[b, :S], predictions["gs_depth"][b, :S], predictions["camera_params"][b, :S])
+            if self.group is not None:  # views are sharded over ranks: every rank needs all splats of the scene
+                import torch.distributed as dist
+
+                world = dist.get_world_size(self.group)
+                for k in self.SPLAT_KEYS:
+                    parts = [torch.empty_like(sp[k]) for _ in range(world)]
+                    dist.all_gather(parts, sp[k], group=self.group)
+                    sp[k] = torch.cat(parts, dim=0)
+            sp["gs_feats"] = raw.reshape(-1, 12)
+            scenes.append(sp)
+        if self.enable_prune:
+            merged = [self.prune_gs(sp) for sp in scenes]
+            predictions["splats"] = {k: [m[k] for m in merged] for k in ("means", "sh", "opacities", "scales", "quats")}
+        else:
+            spl = {k: torch.stack([sp[k] for sp in scenes], dim=0) for k in self.SPLAT_KEYS + ("gs_feats",)}
+            spl["sh"] = spl["sh"].reshape(B, -1, 1, 3)
+            spl["residual_sh"] = spl["gs_feats"][..., 8:11].reshape(B, -1, 1, 3)
+            predictions["splats"] = spl
+        return predictions
+
+
 class B200WorldMirror(torch.nn.Module):
     """`WorldMirror.forward` (src/models/models/worldmirror.py:120-196) on the B200 path: aggregator, camera head and the
     depth / points / normals DPT heads, same `views` dictionary in, same prediction keys out (`camera_params`, `depth`,
     `depth_conf`, `pts3d`, `pts3d_conf`, `normals`, `normals_conf`).  With any cond_flag set the priors are extracted
     from `views` (`camera_pose`, `depthmap`, `camera_intrinsics`) by `priors.extract_priors`, as `WorldMirror.forward`
-    does (worldmirror.py:133-143); `priors` may instead pass the already normalised (depth, rays, poses).  The Gaussian
-    branch is not part of this path."""
+    does (worldmirror.py:133-143); `priors` may instead pass the already normalised (depth, rays, poses).  With the
+    Gaussian branch (`gs_head`, `gs_renderer`; worldmirror.py:202-217) the predictions also carry `gs_depth`,
+    `gs_depth_conf` and `splats`."""
 
-    def __init__(self, aggregator, cam_head=None, depth_head=None, pts_head=None, norm_head=None):
+    def __init__(self, aggregator, cam_head=None, depth_head=None, pts_head=None, norm_head=None, gs_head=None, gs_renderer=None):
         super().__init__()
         self.visual_geometry_transformer = aggregator
         self.cam_head, self.depth_head, self.pts_head, self.norm_head = cam_head, depth_head, pts_head, norm_head
+        self.gs_head, self.gs_renderer = gs_head, gs_renderer
+        self.enable_gs = gs_head is not None and gs_renderer is not None
         self._side = None
 
     def _camera(self, token_list):
@@ -402,7 +552,15 @@ class B200WorldMirror(torch.nn.Module):
             h = B200DPTHead(dim_in=2048, output_dim=od, activation=act)
             h.load_state_dict(sub(name + "."))
             heads[name] = h
-        return cls(agg, cam, heads["depth_head"], heads["pts_head"], heads["norm_head"])
+        gs_head = gs_renderer = None
+        if any(k.startswith("gs_renderer.") for k in heads_sd):  # enable_gs (worldmirror.py:101-118)
+            gs_head = B200DPTHead(dim_in=2048, output_dim=2, activation="exp+expp1", features=256, is_gsdpt=True)
+            gs_head.load_state_dict(sub("gs_head."))
+            gs_renderer = B200GaussianSplatRenderer(sh_degree=0, predict_offset=False, predict_residual_sh=True, enable_prune=True,
+                                                    voxel_size=0.002, using_gtcamera_splat=True, render_novel_views=True,
+                                                    group=getattr(agg, "_sp_group", None) if getattr(agg, "world", 1) > 1 else None)
+            gs_renderer.load_state_dict(sub("gs_renderer."))
+        return cls(agg, cam, heads["depth_head"], heads["pts_head"], heads["norm_head"], gs_head, gs_renderer)
 
     @torch.no_grad()
     def forward(self, views, cond_flags=(0, 0, 0), priors=None):
@@ -430,7 +588,14 @@ class B200WorldMirror(torch.nn.Module):
         for name, head in (("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head)):
             if head is not None:
                 preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
+        gs_feat = None
+        if self.enable_gs:
+            gs_feat, preds["gs_depth"], preds["gs_depth_conf"] = self.gs_head(token_list, images=imgs, patch_start_idx=psi)
         if side is not None:
             main.wait_stream(side)
             preds["camera_params"].record_stream(main)
+        if self.enable_gs:
+            if self.cam_head is None:
+                raise RuntimeError("the Gaussian branch positions its splats with the predicted cameras: cam_head is required")
+            preds = self.gs_renderer.render(gs_feats=gs_feat, images=imgs, predictions=preds, views=views)
         return preds

@@ -164,9 +164,33 @@ def heads_schema() -> "OrderedDict[str, Tuple[int, ...]]":
     return s
 
 
-def synthetic_heads_state_dict(seed: int = 0) -> Dict[str, torch.Tensor]:
-    """Deterministic head weights under the reference keys (same recipe as `synthetic_state_dict`)."""
-    return OrderedDict((k, synthetic_tensor(k, shp, seed)) for k, shp in heads_schema().items())
+def gs_schema(features: int = 256, raw_channels: int = 12) -> "OrderedDict[str, Tuple[int, ...]]":
+    """Key -> shape of the Gaussian branch (worldmirror.py:101-118): gs_head = DPTHead(is_gsdpt=True, output_dim=2), whose
+    extra module is input_merger = Conv2d(3, 128, 7, 1, 3) (dense_head.py:91-94), and gs_renderer.gs_head =
+    Conv2d(128, 256, 3, bias=False) / ReLU / Conv2d(256, 12, 1) (rasterization.py:149-153; sh_degree 0, no offsets)."""
+    s: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    s.update(_dpt_shapes("gs_head.", 2))
+    s["gs_head.input_merger.0.weight"] = (features // 2, 3, 7, 7)
+    s["gs_head.input_merger.0.bias"] = (features // 2,)
+    s["gs_renderer.gs_head.0.weight"] = (features, features // 2, 3, 3)
+    s["gs_renderer.gs_head.2.weight"] = (raw_channels, features, 1, 1)
+    s["gs_renderer.gs_head.2.bias"] = (raw_channels,)
+    return s
+
+
+# constant_ initialisation of the parameter head's bias (rasterization.py:139-147): scales -7, opacities -2, weights -2
+GS_BIAS_INIT = (0.0, 0.0, 0.0, 0.0, -7.0, -7.0, -7.0, -2.0, 0.0, 0.0, 0.0, -2.0)
+
+
+def synthetic_heads_state_dict(seed: int = 0, gs: bool = False) -> Dict[str, torch.Tensor]:
+    """Deterministic head weights under the reference keys (same recipe as `synthetic_state_dict`); gs: with the
+    Gaussian branch (gs_head.*, gs_renderer.*)."""
+    sd = OrderedDict((k, synthetic_tensor(k, shp, seed)) for k, shp in heads_schema().items())
+    if gs:
+        for k, shp in gs_schema().items():
+            sd[k] = synthetic_tensor(k, shp, seed)
+        sd["gs_renderer.gs_head.2.bias"] += torch.tensor(GS_BIAS_INIT)
+    return sd
 
 
 def _role(key: str, shape: Tuple[int, ...]) -> Tuple[float, float]:

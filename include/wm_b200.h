@@ -253,6 +253,37 @@ wm_status wm_normalize_depth(wm_stream stream, const float* depth, int n_views, 
 wm_status wm_pose_prior(wm_stream stream, const float* extrinsics, int extr_stride, const float* intrinsics, int n_views, int H, int W,
                         double padding, float* poses, float* rays);
 
+/* ---- Gaussian path: what WorldMirror.forward keeps of it is `splats` ------------- */
+/* (the rasterised images are discarded, src/models/models/rasterization.py:239-246).  wm_conv2d_nhwc additionally takes
+ * taps = 7 (a 7x1 vertical convolution, padding 3) and relu = 2 (ReLU on conv + bias BEFORE res1 / res2 are added): with
+ * wm_im2row7 that is DPTHead's `input_merger` = Conv2d(3, 128, 7, 1, 3) + ReLU added to the fused map
+ * (heads/dense_head.py:91-94, 239-242). */
+/* images NCHW fp32 [n, 3, H, W] -> NHWC fp32 [n, H, W, 32]: channel kx * 3 + c = image[c][y][x + kx - 3] (zero outside),
+ * channels 21..31 zero, TF32-rounded.  The matching weight is [128, 7 (ky), 32]. */
+wm_status wm_im2row7(wm_stream stream, const float* images, int n, int H, int W, void* out);
+/* gs_renderer.gs_head (rasterization.py:149-153): conv3x3(Cin -> 256) [+ b1] + ReLU + conv1x1(256 -> od) + b2 in one
+ * kernel, the hidden map stays in tensor memory.  w1 [256, 9*Cin] tap-major, w2 [od, 256], out [n, H, W, od] fp32; od <= 16. */
+wm_status wm_conv2d_project(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
+                            const float* w2, const float* b2, int od, float* out);
+/* camera_params [n, 9] -> cam [n, 16] = camera-to-world R (9, row major), t (3), fx, fy, cx, cy: vector_to_camera_matrices
+ * + closed_form_inverse_se3 as prepare_splats uses them (rasterization.py:459-468; utils/camera_utils.py:46-75). */
+wm_status wm_splat_cameras(wm_stream stream, const float* camera_params, int n, int H, int W, float* cam);
+/* prepare_splats, position_from = "gsdepth+predcamera", sh_degree 0, no offsets (rasterization.py:389-498; utils/act_gs.py):
+ * raw [n, H, W, 12] = quats 4 | scales 3 | opacity 1 | residual SH 3 | weight 1; images NCHW [n, 3, H, W]; gs_depth
+ * [n, H, W]; cam from wm_splat_cameras.  Outputs over N = n*H*W splats: means [N,3], quats [N,4], scales [N,3] (clamped
+ * at 0.3), opacities [N], sh [N,3] (= RGB2SH(image) + residual), weights [N]. */
+wm_status wm_splat_prepare(wm_stream stream, const float* raw, const float* images, const float* gs_depth, const float* cam, int n,
+                           int H, int W, float* means, float* quats, float* scales, float* opacities, float* sh, float* weights);
+/* prune_gs (rasterization.py:301-387) for one scene: splats falling into the same voxel are merged (weighted means,
+ * scales, SH; opacity = sum w^2 / sum w; normalised weighted quaternion).  Voxels come out in ascending flat index,
+ * as torch.unique orders them; a voxel's splats are accumulated in ascending original index (the CPU scatter_add_ order).
+ * Outputs are sized for N rows, the first *count (a device word) are valid.  workspace: wm_prune_workspace_bytes(N). */
+wm_status wm_prune_workspace_bytes(long long N, size_t* bytes);
+wm_status wm_prune_splats(wm_stream stream, long long N, const float* means, const float* quats, const float* scales,
+                          const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
+                          size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
+                          float* out_sh, unsigned* count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -31,3 +31,14 @@ def wmpkg():
 def state_dict_full():
     w = importlib.import_module("hunyuanworld-mirror_b200.weights")
     return w.synthetic_state_dict(seed=0)
+
+
+@pytest.fixture(scope="session")
+def c1_tokens(state_dict_full):
+    """token_list of the oracle aggregator on config C1 (2 views 252 x 252, no priors); shared by the head oracles' tests."""
+    import torch
+    from oracle import aggregator_oracle as O
+    w = importlib.import_module("hunyuanworld-mirror_b200.weights")
+    with torch.no_grad():
+        outs, _ = O.aggregator_forward(w.synthetic_images(2, 252, 252, seed=1), state_dict_full)
+    return outs

@@ -1,0 +1,257 @@
+"""GPU parity of the Gaussian path: the new convolution forms against torch fp32, the
+elementwise splat preparation against the oracle, the voxel merge BIT-EXACT against the oracle and against the fixture
+the REFERENCE `prune_gs` produced, and the whole branch against what the reference modules produced on config C1
+(tests/golden/gs_c1.npz)."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+pkg = importlib.import_module("hunyuanworld-mirror_b200")
+capi, W = pkg.capi, pkg.weights
+heads = importlib.import_module("hunyuanworld-mirror_b200.heads")
+from oracle import aggregator_oracle as O  # noqa: E402
+from oracle import gs_oracle as G  # noqa: E402
+
+KEYS = ("means", "quats", "scales", "opacities", "sh")
+
+
+def _rand(shape, seed, scale=1.0):
+    g = torch.Generator(device="cpu")
+    g.manual_seed(seed)
+    return torch.randn(shape, generator=g) * scale
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _close(got, ref, what, rel=2.0 ** -10):
+    err = (got - ref).abs().max().item()
+    tol = rel * ref.abs().max().item() + 1e-6
+    print(f"{what}: max abs err {err:.3e} (ref max {ref.abs().max().item():.3f})")
+    assert torch.isfinite(got).all() and err <= tol, (what, err, tol)
+
+
+def _renderer(sd=None):
+    r = heads.B200GaussianSplatRenderer(sh_degree=0, predict_offset=False, predict_residual_sh=True, enable_prune=True, voxel_size=0.002)
+    if sd is not None:
+        r.load_state_dict({k[len("gs_renderer."):]: v for k, v in sd.items() if k.startswith("gs_renderer.")})
+    return r
+
+
+@pytest.mark.parametrize("n,H,Wd", [(2, 40, 23), (1, 70, 84)])
+def test_input_merger_conv(n, H, Wd):
+    """Conv2d(3, 128, 7, 1, 3) + ReLU, added to a feature map: wm_im2row7 + the 7-tap vertical implicit GEMM with
+    ReLU before the residual, against torch fp32 on TF32-rounded operands."""
+    lib = capi.lib()
+    img = heads.round_tf32(torch.rand(n, 3, H, Wd, generator=torch.Generator().manual_seed(1)))
+    w = heads.round_tf32(_rand((128, 3, 7, 7), 2, 1.0 / 147 ** 0.5))
+    b = _rand((128,), 3, 0.1)
+    res = _rand((n, 128, H, Wd), 4)
+    ref = res + F.relu(F.conv2d(img, w, b, padding=3))
+    rows_w = torch.zeros(128, 7, 32)
+    rows_w[:, :, :21] = w.permute(0, 2, 3, 1).reshape(128, 7, 21)
+    d = {k: v.cuda().contiguous() for k, v in dict(img=img, w=rows_w.reshape(128, 224), b=b, res=res.permute(0, 2, 3, 1)).items()}
+    rows = torch.empty(n, H, Wd, 32, device="cuda")
+    out = torch.empty(n, H, Wd, 128, device="cuda")
+    capi.check(lib.wm_im2row7(_st(), d["img"].data_ptr(), n, H, Wd, rows.data_ptr()))
+    capi.check(lib.wm_conv2d_nhwc(_st(), rows.data_ptr(), n, H, Wd, 32, d["w"].data_ptr(), 7, 128, d["b"].data_ptr(),
+                                  d["res"].data_ptr(), 0, None, 2, out.data_ptr()))
+    torch.cuda.synchronize()
+    _close(out.cpu().permute(0, 3, 1, 2), ref, f"input_merger {n}x{H}x{Wd}")
+
+
+@pytest.mark.parametrize("n,H,Wd", [(2, 18, 18), (1, 41, 55)])
+def test_conv2d_project(n, H, Wd):
+    """gs_renderer.gs_head: conv3x3(128 -> 256, no bias) + ReLU + conv1x1(256 -> 12) + bias in one kernel."""
+    lib = capi.lib()
+    x = heads.round_tf32(_rand((n, 128, H, Wd), 1))
+    w1 = heads.round_tf32(_rand((256, 128, 3, 3), 2, 1.0 / (128 * 9) ** 0.5))
+    w2 = _rand((12, 256, 1, 1), 3, 1.0 / 16)
+    b2 = _rand((12,), 4)
+    ref = F.conv2d(F.relu(F.conv2d(x, w1, None, padding=1)), w2, b2).permute(0, 2, 3, 1)
+    d = {k: v.cuda().contiguous() for k, v in dict(x=x.permute(0, 2, 3, 1), w1=w1.permute(0, 2, 3, 1).reshape(256, -1),
+                                                   w2=w2.reshape(12, 256), b2=b2).items()}
+    out = torch.full((n, H, Wd, 12), float("nan"), device="cuda")
+    capi.check(lib.wm_conv2d_project(_st(), d["x"].data_ptr(), n, H, Wd, 128, d["w1"].data_ptr(), None, d["w2"].data_ptr(),
+                                     d["b2"].data_ptr(), 12, out.data_ptr()))
+    torch.cuda.synchronize()
+    _close(out.cpu(), ref, f"conv2d_project {n}x{H}x{Wd}", rel=2.0 ** -11)
+
+
+def test_prepare_splats_matches_oracle():
+    """Activations, RGB2SH and depth un-projection with predicted cameras: fp32 vs fp32 (libm exp / tan differ by ulps)."""
+    n, H, Wd = 3, 28, 42
+    raw = _rand((n, H, Wd, 12), 1)
+    raw[..., 4:7] = raw[..., 4:7] * 2 - 5  # log-scales around the 0.3 clamp too
+    raw[0, 0, 0, 4] = 3.0
+    img = torch.rand(n, 3, H, Wd, generator=torch.Generator().manual_seed(2))
+    depth = torch.rand(n, H, Wd, generator=torch.Generator().manual_seed(3)) * 3 + 0.2
+    cp = _rand((n, 9), 4)
+    cp[:, 3:7] = cp[:, 3:7] * 0.7  # the camera head does not normalise its quaternion
+    cp[:, 7:] = cp[:, 7:].abs() * 0.3 + 0.6
+    ref = G.prepare_splats(raw, img, depth, cp)
+    got = _renderer().prepare_splats(raw.cuda(), img.cuda(), depth.cuda(), cp.cuda())
+    torch.cuda.synchronize()
+    for k in KEYS + ("weights",):
+        r = ref[k].reshape(n * H * Wd, -1)
+        g = got[k].cpu().reshape(n * H * Wd, -1)
+        err = ((g - r).abs() / (r.abs() + 1e-3 * r.abs().mean())).max().item()
+        print(f"prepare_splats {k}: max rel err {err:.2e}")
+        assert torch.isfinite(g).all() and err < 2e-5, (k, err)
+
+
+@pytest.mark.parametrize("vs", G.PRUNE_VOXELS)
+def test_prune_bit_exact(vs):
+    """Same voxels, same order, same bits as the numpy oracle AND as the reference's torch prune_gs (fixture) on the
+    seeded clustered splats (quaternion norm: 2 ulp, as in tests/test_gs_oracle.py)."""
+    fx = np.load(os.path.join(GOLDEN, "gs_c1.npz"))
+    syn = G.synthetic_splats(int(fx["n_syn"]))
+    ref = G.prune_gs(syn, voxel_size=vs)
+    out = _renderer().prune_gs({k: torch.from_numpy(v).cuda() for k, v in syn.items()}, voxel_size=vs)
+    torch.cuda.synchronize()
+    for k in KEYS:
+        g = out[k].cpu().numpy()
+        golden = fx[f"syn{vs}_{k}"]
+        g = g.reshape(golden.shape) if g.size == golden.size else g
+        assert g.shape == golden.shape, (k, g.shape, golden.shape)
+        if k == "quats":
+            np.testing.assert_allclose(g, golden, rtol=3e-7, atol=1e-9)
+            np.testing.assert_allclose(g, ref[k].reshape(golden.shape), rtol=3e-7, atol=1e-9)
+        else:
+            assert np.array_equal(g, golden), (k, np.abs(g - golden).max())
+            assert np.array_equal(g, ref[k].reshape(golden.shape)), k
+
+
+def test_prune_large_properties():
+    """BASELINE-sized scene (8 views of 518 x 518 = 2.1 M splats) through size-independent properties: voxel keys strictly
+    ascending, total weight conserved, weighted centroid conserved, idempotent on its own output with unit weights."""
+    N = 8 * 518 * 518
+    g = torch.Generator(device="cuda").manual_seed(7)
+    means = torch.rand(N, 3, device="cuda", generator=g) * 0.4 - 0.2
+    sp = {"means": means, "quats": F.normalize(torch.randn(N, 4, device="cuda", generator=g), dim=1),
+          "scales": torch.rand(N, 3, device="cuda", generator=g) * 0.01, "opacities": torch.rand(N, device="cuda", generator=g),
+          "sh": torch.randn(N, 3, device="cuda", generator=g), "weights": torch.rand(N, device="cuda", generator=g) * 0.5 + 0.1}
+    r = _renderer()
+    vs = 0.004
+    out = r.prune_gs(sp, voxel_size=vs)
+    K = out["means"].shape[0]
+    vst = torch.full((1,), vs, device="cuda")  # a tensor divisor: true fp32 division as on the CPU (tensor / python float on
+    vox = torch.floor(means / vst).long()      # CUDA multiplies by the reciprocal and moves a few boundary points)
+    vox = vox - vox.min(dim=0)[0]
+    dims = vox.max(dim=0)[0] + 1
+    flat = vox[:, 0] * dims[1] * dims[2] + vox[:, 1] * dims[2] + vox[:, 2]
+    uniq = torch.unique(flat)
+    assert K == uniq.numel(), (K, uniq.numel())
+    print(f"prune 2.1 M splats -> {K} voxels")
+    # merged means stay inside their voxel, and the voxels come out in ascending flat order
+    ov = torch.floor(out["means"] / vst).long() - torch.floor(means / vst).long().min(dim=0)[0]
+    oflat = ov[:, 0] * dims[1] * dims[2] + ov[:, 1] * dims[2] + ov[:, 2]
+    inside = (oflat == uniq).float().mean().item()
+    assert inside > 0.999, inside  # a weighted mean can round onto a voxel face
+    # conservation: sum_k wsum_k * mean_k = sum_i w_i * mean_i, with wsum recomputed by torch
+    inv = torch.searchsorted(uniq, flat)
+    wsum = torch.zeros(K, device="cuda", dtype=torch.float64).index_add_(0, inv, sp["weights"].double())
+    lhs = (out["means"].double() * wsum[:, None]).sum(dim=0)
+    rhs = (means.double() * sp["weights"].double()[:, None]).sum(dim=0)
+    assert torch.allclose(lhs, rhs, rtol=1e-5, atol=1e-3), (lhs, rhs)
+    op = torch.zeros(K, device="cuda", dtype=torch.float64).index_add_(0, inv, (sp["weights"].double()) ** 2) / wsum
+    assert torch.allclose(out["opacities"].double(), op, rtol=1e-5)
+    assert torch.allclose(out["quats"].norm(dim=1), torch.ones(K, device="cuda"), atol=1e-5)
+    # idempotence: one splat per voxel in, the same splats out
+    again = r.prune_gs({**{k: out[k] for k in ("means", "quats", "scales")}, "sh": out["sh"].reshape(K, 3),
+                        "opacities": torch.ones(K, device="cuda"), "weights": torch.ones(K, device="cuda")}, voxel_size=vs)
+    assert again["means"].shape[0] >= int(0.999 * K)
+    if again["means"].shape[0] == K:
+        assert torch.equal(again["means"], out["means"]) and torch.equal(again["scales"], out["scales"])
+
+
+def test_gs_branch_matches_reference_golden(state_dict_full):
+    """B200DPTHead(is_gsdpt) + B200GaussianSplatRenderer on the fp32 oracle aggregator's tokens and the REFERENCE camera
+    against what the reference modules produced.  tf32 convolutions: rel. Frobenius <= 2e-3 on the dense maps."""
+    fx = np.load(os.path.join(GOLDEN, "gs_c1.npz"))
+    n, h, w, st = int(fx["n_views"]), int(fx["H"]), int(fx["W"]), int(fx["stride"])
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    imgs = W.synthetic_images(n, h, w, seed=1)
+    with torch.no_grad():
+        toks, psi = O.aggregator_forward(imgs, state_dict_full)
+    head = heads.B200DPTHead(dim_in=2048, output_dim=2, activation="exp+expp1", is_gsdpt=True)
+    head.load_state_dict({k[len("gs_head."):]: v for k, v in hsd.items() if k.startswith("gs_head.")})
+    feat, depth, conf = head([t.cuda() for t in toks], imgs.cuda(), psi)
+    torch.cuda.synchronize()
+    assert tuple(feat.shape) == (1, n, 128, h, w) and tuple(depth.shape) == (1, n, h, w, 1) and tuple(conf.shape) == (1, n, h, w)
+
+    def fro(a, b):
+        return float(np.linalg.norm(a - b) / np.linalg.norm(b))
+
+    e_d = fro(depth[0, :, ::st, ::st, 0].cpu().numpy(), fx["gs_depth_sub"])
+    e_c = fro(conf[0, :, ::st, ::st].cpu().numpy(), fx["gs_conf_sub"])
+    e_f = fro(feat[0, :, :, ::12, ::12].cpu().numpy(), fx["gs_feat_sub"])
+    rs = np.abs(feat[0].sum(dim=3).cpu().numpy() - fx["gs_feat_rowsum"]).max() / (w * float(fx["gs_feat_absmean"]))
+    print(f"gs head: depth {e_d:.3e} conf {e_c:.3e} features {e_f:.3e} feature row-sum dev {rs:.3e}")
+    assert e_d <= 2e-3 and e_c <= 2e-3 and e_f <= 2e-3 and rs <= 5e-3
+    rend = _renderer(hsd)
+    rend.enable_prune = False
+    preds = {"camera_params": torch.from_numpy(fx["camera_params"])[None].cuda(), "gs_depth": depth}
+    sp = rend.render(feat, imgs.cuda(), preds, {"img": imgs})["splats"]
+    torch.cuda.synchronize()
+    e_r = fro(sp["gs_feats"][0].reshape(n, h, w, 12)[:, ::st, ::st].cpu().numpy(), fx["raw_sub"])
+    print(f"raw Gaussian parameters: rel fro {e_r:.3e}")
+    assert e_r <= 2e-3
+    N = n * h * w
+    for k in KEYS + ("weights",):
+        got = sp[k][0].reshape(N, -1).cpu().numpy()
+        ref = fx["pre_" + k]
+        e = fro(got[::7], ref)
+        sums = np.abs(got.astype(np.float64).sum(axis=0) - fx["pre_" + k + "_sum"]).max() / (N * float(np.abs(ref).mean()))
+        print(f"splats before pruning, {k}: rel fro {e:.3e}, column-sum dev {sums:.3e}")
+        assert np.isfinite(got).all() and e <= (1e-2 if k == "scales" else 5e-3) and sums <= 2e-3, k
+    rend.enable_prune = True
+    out = rend.render(feat, imgs.cuda(), dict(preds), {"img": imgs})["splats"]
+    K, Kref = out["means"][0].shape[0], int(fx["pruned_K"])
+    print(f"pruned: {K} voxels (reference {Kref})")
+    assert abs(K - Kref) <= 0.003 * Kref
+    assert tuple(out["sh"][0].shape) == (K, 1, 3) and tuple(out["quats"][0].shape) == (K, 4)
+    for k in KEYS:
+        got = out[k][0].reshape(K, -1).double().sum(dim=0).cpu().numpy()
+        ref = fx["pruned_" + k + "_sum"]
+        np.testing.assert_allclose(got, ref, rtol=1e-2, atol=1e-2 * float(np.abs(fx["pruned_" + k]).mean()) * K)
+
+
+def test_worldmirror_forward_with_gaussians(state_dict_full):
+    """`B200WorldMirror.forward` with the Gaussian branch: the reference's prediction keys, splats consistent with the
+    oracle's voxel merge of the un-pruned splats of the same forward."""
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    model = heads.B200WorldMirror.from_state_dicts(state_dict_full, hsd)
+    assert model.enable_gs
+    imgs = W.synthetic_images(2, 252, 252, seed=1).cuda()
+    preds = model({"img": imgs})
+    torch.cuda.synchronize()
+    for k in ("camera_params", "depth", "depth_conf", "pts3d", "pts3d_conf", "normals", "normals_conf", "gs_depth", "gs_depth_conf", "splats"):
+        assert k in preds, k
+    fx = np.load(os.path.join(GOLDEN, "gs_c1.npz"))
+    st = int(fx["stride"])
+    e = np.linalg.norm(preds["gs_depth"][0, :, ::st, ::st, 0].cpu().numpy() - fx["gs_depth_sub"]) / np.linalg.norm(fx["gs_depth_sub"])
+    K, Kref = preds["splats"]["means"][0].shape[0], int(fx["pruned_K"])
+    print(f"e2e gs_depth rel fro {e:.3e}; {K} voxels (reference {Kref})")
+    assert e <= 1e-2 and abs(K - Kref) <= 0.01 * Kref
+    # same forward without pruning -> oracle prune == GPU prune, bit for bit (quaternions 2 ulp)
+    model.gs_renderer.enable_prune = False
+    raw = model({"img": imgs})["splats"]
+    torch.cuda.synchronize()
+    ref = G.prune_gs({k: raw[k][0].reshape(raw[k].shape[1], -1).squeeze(-1).cpu().numpy() for k in KEYS + ("weights",)}, 0.002)
+    assert ref["means"].shape[0] == K
+    for k in KEYS:
+        g = preds["splats"][k][0].reshape(K, -1).cpu().numpy()
+        if k == "quats":
+            np.testing.assert_allclose(g, ref[k], rtol=3e-7, atol=1e-9)
+        else:
+            assert np.array_equal(g, ref[k].reshape(K, -1)), k

@@ -19,13 +19,6 @@ def heads_sd():
     return W.synthetic_heads_state_dict(seed=0)
 
 
-@pytest.fixture(scope="module")
-def c1_tokens(state_dict_full):
-    with torch.no_grad():
-        outs, psi = O.aggregator_forward(W.synthetic_images(2, 252, 252, seed=1), state_dict_full)
-    return outs
-
-
 def test_camera_head_matches_reference(heads_sd, c1_tokens):
     fx = np.load(os.path.join(GOLDEN, "c1_heads.npz"))
     # from the reference's own camera tokens: fp32 vs fp32
