@@ -93,7 +93,7 @@ class ClockSampler:
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def cpu_reference_steps(n_views, steps, warmup, with_heads=True):
+def cpu_reference_steps(n_views, steps, warmup, with_heads=True, with_gs=True):
     """The reference algorithm on the host cores: oracle/aggregator_oracle.py (a restatement pinned against
     the reference's own outputs, tests/golden/) -- /root/reference is Python and does not travel to the GPU box."""
     import torch
@@ -106,7 +106,10 @@ def cpu_reference_steps(n_views, steps, warmup, with_heads=True):
     from oracle import heads_oracle as HO
 
     sd = W.synthetic_state_dict(seed=0)
-    hsd = W.synthetic_heads_state_dict(seed=0) if with_heads else None
+    with_gs = with_gs and with_heads
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=with_gs) if with_heads else None
+    if with_gs:
+        from oracle import gs_oracle as GO
     imgs = W.synthetic_images(n_views, SIZE, SIZE, seed=1)
     times = []
     with torch.no_grad():
@@ -114,7 +117,9 @@ def cpu_reference_steps(n_views, steps, warmup, with_heads=True):
             t0 = time.perf_counter()
             toks, _ = O.aggregator_forward(imgs, sd)
             if with_heads:
-                HO.all_heads(toks, SIZE, SIZE, hsd)
+                preds = HO.all_heads(toks, SIZE, SIZE, hsd)
+                if with_gs:
+                    GO.gs_branch(toks, imgs, preds["camera_params"], hsd)
             if i >= warmup:
                 times.append(time.perf_counter() - t0)
     return times, cores
@@ -126,10 +131,10 @@ def run_reference(args):
         return
     # bounded sample of the 8-view workload so that warmup + steps stay within a few minutes (~7 s / view here)
     sample_views = 2 if (args.steps + args.warmup) <= 14 else 1
-    times, cores = cpu_reference_steps(sample_views, args.steps, args.warmup, not args.no_heads)
+    times, cores = cpu_reference_steps(sample_views, args.steps, args.warmup, not args.no_heads, not args.no_gs)
     total = sum(times)
     value = sample_views * len(times) / total
-    sample = (f"{sample_views} of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth (24 DINOv2 + 24x2 blocks{'' if args.no_heads else ' + camera and 3 DPT heads'}), fp32, "
+    sample = (f"{sample_views} of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth (24 DINOv2 + 24x2 blocks{'' if args.no_heads else ' + camera and 3 DPT heads' + ('' if args.no_gs else ' + Gaussian branch')}), fp32, "
               f"{len(times)} timed forwards; global attention spans the sampled views only")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "views/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
@@ -159,12 +164,15 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
 
     heads_on = not args.no_heads
+    gs_on = heads_on and not args.no_gs
     model = pkg.B200VisualGeometryTransformer()
     model.load_state_dict(W.synthetic_state_dict(seed=0))
-    full = pkg.B200WorldMirror.from_state_dicts(None, W.synthetic_heads_state_dict(seed=0), aggregator=model) if heads_on else None
+    full = pkg.B200WorldMirror.from_state_dicts(None, W.synthetic_heads_state_dict(seed=0, gs=gs_on), aggregator=model) if heads_on else None
     H = pkg.heads
     if world > 1:
         model.init_sequence_parallel()
+        if gs_on:  # the voxel merge spans the views of the scene: every rank gathers the splats of the others
+            full.gs_renderer.sharded, full.gs_renderer.group = True, model._sp_group
     for kv in args.set:  # library tuning knobs (wm_set_int), e.g. --set attn_bounded_variant=10
         k, v = kv.split("=")
         capi.check(capi.lib().wm_set_int(model._handle, k.encode(), int(v)))
@@ -244,18 +252,28 @@ def run_b200(args):
         toks, psi = model(imgs_dev)
         full._camera(toks)  # warm-up (graph capture for this view count)
         torch.cuda.synchronize()
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(7)]
         ev[0].record()
-        full._camera(toks)
+        cam_now = full._camera(toks)
         ev[1].record()
         for i, hd in enumerate((full.depth_head, full.pts_head, full.norm_head)):
             hd(toks, images=imgs_dev, patch_start_idx=psi)
             ev[2 + i].record()
+        if gs_on:
+            gfeat, gdepth, gconf = full.gs_head(toks, images=imgs_dev, patch_start_idx=psi)
+            ev[5].record()
+            full.gs_renderer.render(gfeat, imgs_dev, {"camera_params": cam_now, "gs_depth": gdepth})
+            ev[6].record()
         torch.cuda.synchronize()
         breakdown["camera_head"] = {"ms": round(ev[0].elapsed_time(ev[1]), 4), "launches": None,
                                     "note": "timed alone; inside the step it runs on a side stream underneath the DPT heads"}
         for i, nm in enumerate(("dpt_depth", "dpt_points", "dpt_normals")):
             breakdown[nm] = {"ms": round(ev[1 + i].elapsed_time(ev[2 + i]), 4), "launches": None}
+        if gs_on:
+            breakdown["dpt_gaussian"] = {"ms": round(ev[4].elapsed_time(ev[5]), 4), "launches": None}
+            breakdown["splats"] = {"ms": round(ev[5].elapsed_time(ev[6]), 4), "launches": None,
+                                   "note": "parameter convolution, prepare_splats, voxel merge (incl. one host read of the voxel count)"}
+            del gfeat, gdepth, gconf
         del toks
 
     # ---- e2e: pinned host images -> device every step, camera tokens read back every step
@@ -265,8 +283,16 @@ def run_b200(args):
                   "normals": (1, n_local, SIZE, SIZE, 3), "normals_conf": (1, n_local, SIZE, SIZE)}
     else:
         shapes = {"cam_tokens": (1, n_local, 2048)}
+    if gs_on:
+        shapes.update({"gs_depth": (1, n_local, SIZE, SIZE, 1), "gs_depth_conf": (1, n_local, SIZE, SIZE)})
     host_out = {k: torch.empty(v, dtype=torch.float32).pin_memory() for k, v in shapes.items()}
     d2h_bytes = sum(t.numel() * 4 for t in host_out.values())
+    # the merged splats of the scene (one result, identical on every rank): rank 0 reads them back, K rows of 14 floats
+    splat_rows = n_total * SIZE * SIZE
+    splat_host = ({k: torch.empty((splat_rows,) + shp, dtype=torch.float32).pin_memory()
+                   for k, shp in (("means", (3,)), ("sh", (1, 3)), ("opacities", ()), ("scales", (3,)), ("quats", (4,)))}
+                  if gs_on and rank == 0 else None)
+    splat_bytes = [0]
 
     def step_e2e():
         x = imgs_host.to(dev, non_blocking=True)
@@ -275,6 +301,11 @@ def run_b200(args):
             preds = full({"img": x}, cond_flags=flags, priors=pri)
             for k, t in host_out.items():
                 t.copy_(preds[k], non_blocking=True)
+            if splat_host is not None:
+                K = preds["splats"]["means"][0].shape[0]
+                for k, t in splat_host.items():
+                    t[:K].copy_(preds["splats"][k][0], non_blocking=True)
+                splat_bytes[0] = K * 14 * 4
         else:
             outs, _ = model(x, pri, cond_flags=flags)
             host_out["cam_tokens"].copy_(outs[-1][:, :, 0], non_blocking=True)
@@ -282,7 +313,7 @@ def run_b200(args):
 
     e2e_ms = timed(step_e2e, args.steps, 3) / args.steps
     e2e = {"value": n_total / (e2e_ms * 1e-3), "unit": "views/s", "h2d_bytes_per_step": imgs_host.numel() * 4,
-           "d2h_bytes_per_step": d2h_bytes, "ms_per_step": e2e_ms}
+           "d2h_bytes_per_step": d2h_bytes + splat_bytes[0], "ms_per_step": e2e_ms}
 
     sp_exchange = None
     if world > 1:
@@ -318,20 +349,21 @@ def run_b200(args):
                     "whole_step_tflops": None if heads_on else fl["total"] / (ms_per_step * 1e-3) / 1e12}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            t, cores = cpu_reference_steps(2, 1, 0, heads_on)
+            t, cores = cpu_reference_steps(2, 1, 0, heads_on, gs_on)
             cpu = {"value": 2 / t[0], "unit": "views/s", "cores": cores, "kind": "port",
-                   "sample": f"2 of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth{' + camera and 3 DPT heads' if heads_on else ''}, fp32, "
-                             f"one forward ({t[0]:.1f} s); oracle/aggregator_oracle.py{' + oracle/heads_oracle.py' if heads_on else ''}"}
+                   "sample": f"2 of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth{' + camera and 3 DPT heads' if heads_on else ''}{' + Gaussian branch' if gs_on else ''}, fp32, "
+                             f"one forward ({t[0]:.1f} s); oracle/aggregator_oracle.py{' + oracle/heads_oracle.py' if heads_on else ''}{' + oracle/gs_oracle.py' if gs_on else ''}"}
         line = {"metric": METRIC, "value": value, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic",
                 "config": {"workload": f"WorldMirror fwd: aggregator (DINOv2 ViT-L/14 + 24x(frame,global) blocks)"
-                                       f"{' + camera head + depth/points/normals DPT heads' if heads_on else ' only (--no-heads)'}, "
+                                       f"{' + camera head + depth/points/normals DPT heads' if heads_on else ' only (--no-heads)'}"
+                                       f"{' + Gaussian branch (gs DPT head, parameter head, prepare_splats, voxel merge -> splats)' if gs_on else ''}, "
                                        f"{n_local} views/GPU x {world} GPU = {n_total} views {SIZE}x{SIZE}, "
                                        f"{'camera-pose + depth + intrinsics priors extracted on the GPU inside the step (BASELINE configs[2])' if args.priors else 'no priors (BASELINE configs[1] at N=1)'}"
-                                       f"; Gaussian head not built, SURVEY 8f row 3",
+                                       f"{'' if gs_on or not heads_on else '; Gaussian branch off (--no-gs)'}",
                            "priors": bool(args.priors),
-                           "heads": heads_on, "head_dtype": "camera fp32, DPT tf32 (fp32 accumulate)" if heads_on else None,
+                           "heads": heads_on, "gaussians": gs_on, "head_dtype": "camera fp32, DPT tf32 (fp32 accumulate)" if heads_on else None,
                            "views_per_gpu": n_local, "views_total": n_total, "size": SIZE, "tokens_per_view": 1376,
                            "parallelism": f"views sharded; global attention: {sp_exchange}" if world > 1 else "single GPU",
                            "l2": "per-step working set (1.8 GB bf16 weights + activations) exceeds the 126 MB L2; no flush needed"},
@@ -353,6 +385,7 @@ def main():
     ap.add_argument("--views", type=int, default=VIEWS_PER_RANK, help="views per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-heads", action="store_true", help="time the aggregator alone (the round-1 workload before the heads existed)")
+    ap.add_argument("--no-gs", action="store_true", help="leave the Gaussian branch (gs_depth, splats) out of the step")
     ap.add_argument("--priors", action="store_true", help="BASELINE configs[2]: pose + depth + intrinsics priors, cond_flags [1,1,1]")
     ap.add_argument("--set", action="append", default=[], metavar="KNOB=INT", help="wm_set_int tuning knob (repeatable)")
     args = ap.parse_args()

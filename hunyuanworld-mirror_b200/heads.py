@@ -388,14 +388,14 @@ class B200GaussianSplatRenderer(torch.nn.Module):
     def __init__(self, feature_dim: int = 256, sh_degree: int = 0, predict_offset: bool = False, predict_residual_sh: bool = True,
                  enable_prune: bool = True, voxel_size: float = 0.002, using_gtcamera_splat: bool = False,
                  render_novel_views: bool = False, enable_conf_filter: bool = False, conf_threshold_percent: float = 30.0,
-                 max_gaussians: int = 5000000, debug=False, group=None):
+                 max_gaussians: int = 5000000, debug=False, sharded: bool = False, group=None):
         super().__init__()
         if feature_dim != 256 or sh_degree != 0 or predict_offset or not predict_residual_sh or enable_conf_filter:
             raise NotImplementedError("B200GaussianSplatRenderer covers WorldMirror's configuration: feature_dim 256, "
                                       "sh_degree 0, no offsets, residual SH, no confidence filter")
         self.feature_dim, self.sh_degree, self.nums_sh = feature_dim, sh_degree, 1
         self.enable_prune, self.voxel_size = enable_prune, voxel_size
-        self.group = group  # process group the views are sharded over (None: single process)
+        self.sharded, self.group = sharded, group  # views sharded over the ranks of `group` (None: the default group)
         self.w: Dict[str, torch.Tensor] = {}
         self._loaded = False
         self._ws = None
@@ -481,7 +481,7 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         for b in range(B):
             raw = self.gs_head(feat[b, :S].contiguous())
             sp = self.prepare_splats(raw, images[b, :S], predictions["gs_depth"][b, :S], predictions["camera_params"][b, :S])
-            if self.group is not None:  # views are sharded over ranks: every rank needs all splats of the scene
+            if self.sharded:  # views are sharded over ranks: every rank needs all splats of the scene
                 import torch.distributed as dist
 
                 world = dist.get_world_size(self.group)
@@ -558,7 +558,7 @@ class B200WorldMirror(torch.nn.Module):
             gs_head.load_state_dict(sub("gs_head."))
             gs_renderer = B200GaussianSplatRenderer(sh_degree=0, predict_offset=False, predict_residual_sh=True, enable_prune=True,
                                                     voxel_size=0.002, using_gtcamera_splat=True, render_novel_views=True,
-                                                    group=getattr(agg, "_sp_group", None) if getattr(agg, "world", 1) > 1 else None)
+                                                    sharded=getattr(agg, "world", 1) > 1, group=getattr(agg, "_sp_group", None))
             gs_renderer.load_state_dict(sub("gs_renderer."))
         return cls(agg, cam, heads["depth_head"], heads["pts_head"], heads["norm_head"], gs_head, gs_renderer)
 

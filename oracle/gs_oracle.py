@@ -149,3 +149,12 @@ def synthetic_splats(n: int = 20000, seed: int = 5) -> Dict[str, np.ndarray]:
 
 
 PRUNE_VOXELS = (0.002, 0.01, 0.05)
+
+
+def gs_branch(token_list: Sequence[Tensor], images: Tensor, camera_params: Tensor, sd: Dict[str, Tensor],
+              voxel_size: float = 0.002) -> Dict[str, object]:
+    """What `_gen_all_preds` adds with enable_gs (worldmirror.py:202-217): gs_depth, gs_depth_conf and the pruned splats of
+    one scene.  images [1, S, 3, H, W], camera_params [1, S, 9]."""
+    feat, depth, conf = gs_dpt_head(token_list, images, sd)
+    sp = prepare_splats(gs_params(feat, sd), images[0], depth[0, ..., 0], camera_params[0])
+    return {"gs_depth": depth, "gs_depth_conf": conf, "splats": prune_gs({k: v.numpy() for k, v in sp.items()}, voxel_size)}

@@ -51,6 +51,29 @@ def main():
         e = ((a - f[:, sl]).norm() / f[:, sl].norm()).item()
         ok &= e < 2e-3
         print(f"rank {rank}: p2p (world {world}) vs single GPU rel fro {e:.3e}", flush=True)
+    # Gaussian branch with the views sharded: every rank gathers the other ranks' splats and merges the whole scene;
+    # the result must equal, bit for bit, the merge of all views done on one GPU (same splats, same order)
+    H2 = pkg.heads
+    gsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    g = torch.Generator().manual_seed(3)
+    S, h, w = per * world, 28, 42
+    feat = torch.randn(1, S, h, w, 128, generator=g).to(dev)
+    im = torch.rand(1, S, 3, h, w, generator=g).to(dev)
+    cp = torch.randn(1, S, 9, generator=g)
+    cp[..., 7:] = cp[..., 7:].abs() * 0.3 + 0.6
+    preds = {"camera_params": cp.to(dev), "gs_depth": (torch.rand(1, S, h, w, 1, generator=g) * 0.05 + 0.2).to(dev)}
+    outs = []
+    for sharded in (True, False):
+        r = H2.B200GaussianSplatRenderer(voxel_size=0.01, sharded=sharded)
+        r.load_state_dict({k[len("gs_renderer."):]: v for k, v in gsd.items() if k.startswith("gs_renderer.")})
+        v = sl if sharded else slice(0, S)
+        p = {k: t[:, v].contiguous() for k, t in preds.items()}
+        outs.append(r.render(feat[:, v].permute(0, 1, 4, 2, 3), im[:, v].contiguous(), p)["splats"])
+    torch.cuda.synchronize()
+    K = outs[1]["means"][0].shape[0]
+    same = all(torch.equal(outs[0][k][0], outs[1][k][0]) for k in ("means", "sh", "opacities", "scales", "quats"))
+    print(f"rank {rank}: sharded voxel merge == single-GPU merge: {same} ({S * h * w} splats -> {K} voxels)", flush=True)
+    ok &= same and 0 < K < S * h * w
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
