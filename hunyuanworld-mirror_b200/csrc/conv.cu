@@ -1,13 +1,15 @@
 // Implicit-GEMM convolution on tcgen05 for the DPT prediction heads (SURVEY.md section 8f row 1;
 // reference: src/models/heads/dense_head.py:164-344).  The reference runs its heads with autocast disabled
-// (worldmirror.py:146), i.e. in fp32; bf16 activations measured 1.5e-2 relative error on pts3d (the inv_log output
-// amplifies), above the stated 1e-2, so activations and weights stay fp32 in memory and the tensor cores run
-// kind::tf32 (10-bit mantissa operands, fp32 accumulation).  Every producer rounds what it stores to TF32 (nearest),
-// weights are rounded at load time: the MMA's own operand truncation is then exact and no bias accumulates.  Activations are NHWC, so a 3x3 convolution is a GEMM
+// (worldmirror.py:146), i.e. in fp32; bf16 activations (8-bit mantissa) measured 1.5e-2 relative error on pts3d (the
+// inv_log output amplifies), above the stated 1e-2.  A 10-bit mantissa passes (1.2e-3): the first version of this file ran
+// kind::tf32 on fp32 maps rounded to TF32; the same 10 bits fit fp16, which the tensor cores read at TWICE the tf32 rate
+// and which halves every map in HBM.  So activations and weights are fp16 in memory (round to nearest, saturating: the
+// maps of these heads are O(1), fp16 reaches 65504), the MMA is kind::f16 with fp32 accumulation, and every epilogue does
+// its bias / residual / activation arithmetic in fp32 before rounding once.  Activations are NHWC, so a 3x3 convolution is a GEMM
 //     acc[pixel, co] (fp32, TMEM) = sum over (tap, ci) of  in[pixel + tap offset, ci] * w[co, tap, ci]
 // whose A operand needs no im2col buffer: the producer issues one 4D TMA tile load per (tap, 32-channel block) with
 // the tile origin shifted by the tap offset, and TMA's out-of-bounds zero fill IS the convolution's zero padding.
-// A tile = 8 x 16 pixels x 32 channels (fp32) = 128 rows of 128 B in the SWIZZLE_128B layout the UMMA descriptors expect.
+// A tile = 8 x 16 pixels x 64 channels (fp16) = 128 rows of 128 B in the SWIZZLE_128B layout the UMMA descriptors expect.
 //
 // One CTA per SM, persistent over (image, tile row, tile column, Cout tile), 256 threads:
 //   warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (one elected lane), warp 2 = TMEM allocator, warp 3 idle,
@@ -15,11 +17,13 @@
 // 4-stage smem ring; two TMEM accumulators of NT columns so the epilogue of tile i overlaps the main loop of i+1.
 //
 // Epilogues (the reference's module boundaries they fuse are cited at the launchers):
-//   NT = 128 / 256:  out fp32 = [relu]( acc + bias + res1 + res2 ), written as NHWC through a 4D TMA store (pixels of a
+//   NT = 128 / 256:  out fp16 = [relu]( acc + bias + res1 + res2 ), written as NHWC through a 4D TMA store (pixels of a
 //                    border tile that fall outside the image are clipped by the store);
 //   NT = 32 (final): relu(acc + bias) -> 1x1 conv (32 -> od) -> activate_head -> fp32 prediction + confidence;
 //   NT = 256 (project): relu(acc + bias) -> 1x1 conv (256 -> od <= 16) + bias, raw fp32 [pixels, od]: the Gaussian
 //                    parameter head `gs_renderer.gs_head` (models/rasterization.py:149-153), hidden map never stored.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -27,8 +31,8 @@ namespace wm {
 
 constexpr int CV_TW = 16, CV_TH = 8;   // tile = 8 rows x 16 columns of pixels
 constexpr int CV_STAGES = 4;
-constexpr int CV_KE = 32;              // fp32 elements per k-block (one 128-byte swizzle row)
-constexpr int CV_A_BYTES = 128 * CV_KE * 4;
+constexpr int CV_KE = 64;              // fp16 elements per k-block (one 128-byte swizzle row)
+constexpr int CV_A_BYTES = 128 * CV_KE * 2;
 constexpr int CV_THREADS = 256;
 constexpr int CV_STG_BYTES = 128 * 128;
 template <int NT>
@@ -42,11 +46,11 @@ constexpr int CV_PROJ_MAX = 16;  // output channels of the projecting epilogue (
 
 struct ConvArgs {
   int n, H, W, Cin, Cout, taps;  // taps: 1 (1x1), 9 (3x3, stride 1, pad 1) or 7 (7x1 vertical, stride 1, pad 3)
-  int tiles_x, tiles_y, n_tiles, total_tiles, kblocks;  // kblocks = taps * Cin / 32
+  int tiles_x, tiles_y, n_tiles, total_tiles, kblocks;  // kblocks = taps * Cin / 64
   const float* bias;            // [Cout] or null
-  const float* res1;            // [n or 1, H, W, Cout] or null
-  const float* res2;            // [n, H, W, Cout] or null
-  int res1_bcast;               // res1 has no image axis (positional table)
+  const void* res1;             // fp16 [n, H, W, Cout], or fp32 [H, W, Cout] when res1_bcast, or null
+  const __half* res2;           // fp16 [n, H, W, Cout] or null
+  int res1_bcast;               // res1 is the fp32 positional table, shared by all images
   int relu;                     // 1: on the whole sum; 2: on acc + bias only, before the residuals are added
   // final / projecting epilogue
   const float *w2, *b2;         // [od, NT], [od]
@@ -134,7 +138,7 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     __syncwarp();
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_tf32(128, NT);
+      constexpr uint32_t idesc = umma_idesc_f16(128, NT);
       uint32_t it = 0, tcount = 0;
       for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++tcount) {
         const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
@@ -148,8 +152,8 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const uint64_t adesc = umma_desc_sw128(smem_u32(sA + s * CV_A_BYTES), 16, 1024);
           const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + s * B_BYTES), 16, 1024);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)  // K = 8 fp32 = 32 bytes (>> 4 = 2) per instruction inside the swizzle row
-            umma_ss_tf32(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          for (int k = 0; k < 4; ++k)  // K = 16 fp16 = 32 bytes (>> 4 = 2) per instruction inside the swizzle row
+            umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
           umma_commit(&empty[s]);
         }
         umma_commit(&tfull[acc]);
@@ -296,16 +300,28 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             for (int i = 0; i < 32; ++i) xv[i] = fmaxf(xv[i], 0.f);
           }
           if (valid) {
-#pragma unroll
-            for (int rsel = 0; rsel < 2; ++rsel) {
-              const float* rp = rsel == 0 ? g.res1 : g.res2;
-              if (rp == nullptr) continue;
-              const size_t rpix = (rsel == 0 && g.res1_bcast) ? (size_t)y * g.W + x : pix;
-              const float4* r4 = reinterpret_cast<const float4*>(rp + rpix * g.Cout + col0);
+            if (g.res1 != nullptr && g.res1_bcast) {  // fp32 positional table [H, W, Cout]
+              const float4* r4 = reinterpret_cast<const float4*>(static_cast<const float*>(g.res1) + ((size_t)y * g.W + x) * g.Cout + col0);
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
                 const float4 r = __ldg(r4 + i);
                 xv[4 * i] += r.x, xv[4 * i + 1] += r.y, xv[4 * i + 2] += r.z, xv[4 * i + 3] += r.w;
+              }
+            }
+#pragma unroll
+            for (int rsel = 0; rsel < 2; ++rsel) {
+              const __half* rp = rsel == 0 ? (g.res1_bcast ? nullptr : static_cast<const __half*>(g.res1)) : g.res2;
+              if (rp == nullptr) continue;
+              const uint4* r4 = reinterpret_cast<const uint4*>(rp + pix * g.Cout + col0);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 r = __ldg(r4 + i);
+                const uint32_t u[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&u[k]));
+                  xv[8 * i + 2 * k] += f.x, xv[8 * i + 2 * k + 1] += f.y;
+                }
               }
             }
           }
@@ -313,19 +329,24 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
             for (int i = 0; i < 32; ++i) xv[i] = fmaxf(xv[i], 0.f);
           }
+          // two 32-column groups fill one 128-byte staging row (64 fp16 channels) per pixel
+          const int half = grp & 1;
+          if (half == 0) {
+            if (et == 0) tma_store_wait_read<0>();  // the previous store has drained the staging tile
+            named_bar_sync(1, 128);
+          }
 #pragma unroll
-          for (int i = 0; i < 32; ++i) xv[i] = tf32_rn(xv[i]);  // the next convolution's operand: round once, here
-          if (et == 0) tma_store_wait_read<0>();  // the previous store has drained the staging tile
-          named_bar_sync(1, 128);
-#pragma unroll
-          for (int c = 0; c < 8; ++c)
-            st_shared_v4(stg + sw128_offset(et, c), __float_as_uint(xv[4 * c]), __float_as_uint(xv[4 * c + 1]),
-                         __float_as_uint(xv[4 * c + 2]), __float_as_uint(xv[4 * c + 3]));
-          fence_proxy_async_smem();
-          named_bar_sync(1, 128);
-          if (et == 0) {
-            tma_store_4d(&tmC, sC, col0, x0, y0, img);
-            tma_store_commit();
+          for (int c = 0; c < 4; ++c)
+            st_shared_v4(stg + sw128_offset(et, half * 4 + c), pack_half2_sat(xv[8 * c], xv[8 * c + 1]),
+                         pack_half2_sat(xv[8 * c + 2], xv[8 * c + 3]), pack_half2_sat(xv[8 * c + 4], xv[8 * c + 5]),
+                         pack_half2_sat(xv[8 * c + 6], xv[8 * c + 7]));
+          if (half == 1) {
+            fence_proxy_async_smem();
+            named_bar_sync(1, 128);
+            if (et == 0) {
+              tma_store_4d(&tmC, sC, col0 - 32, x0, y0, img);
+              tma_store_commit();
+            }
           }
         }
       }
@@ -369,35 +390,35 @@ static wm_status conv_check(const void* in, const void* w, int n, int H, int W, 
   return WM_OK;
 }
 
-// nn.Conv2d(Cin, Cout, 1 | 3, stride 1, padding 0 | 1) on NHWC fp32 with the surrounding elementwise work fused:
-// out = [relu](conv(in) + bias + res1 + res2).  weight: fp32 [Cout, taps * Cin], tap-major (ky, kx, ci).
+// nn.Conv2d(Cin, Cout, 1 | 3, stride 1, padding 0 | 1) on NHWC fp16 with the surrounding elementwise work fused:
+// out = [relu](conv(in) + bias + res1 + res2).  weight: fp16 [Cout, taps * Cin], tap-major (ky, kx, ci).
 wm_status conv2d_nhwc(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* weight, int taps, int Cout,
                       const float* bias, const void* res1, int res1_bcast, const void* res2, int relu, void* out) {
   WM_TRY(conv_check(in, weight, n, H, W, Cin, Cout, taps));
   WM_CHECK(out && (Cout % 256 == 0 || Cout == 128), "conv2d: Cout must be 128 or a multiple of 256 (got %d)", Cout);
-  const CUtensorMapDataType f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  const CUtensorMapDataType f16 = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   const int NT = Cout == 128 ? 128 : 256;
   CUtensorMap ta, tb, tc;
-  WM_TRY(tmap_nhwc(&ta, f32, 4, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
-  WM_TRY(tmap_2d(&tb, f32, 4, weight, Cout, (uint64_t)taps * Cin, (uint64_t)taps * Cin, CV_KE, NT));
-  WM_TRY(tmap_nhwc(&tc, f32, 4, out, n, H, W, Cout, 32, CV_TW, CV_TH));
+  WM_TRY(tmap_nhwc(&ta, f16, 2, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
+  WM_TRY(tmap_2d(&tb, f16, 2, weight, Cout, (uint64_t)taps * Cin, (uint64_t)taps * Cin, CV_KE, NT));
+  WM_TRY(tmap_nhwc(&tc, f16, 2, out, n, H, W, Cout, 64, CV_TW, CV_TH));
   ConvArgs g{};
   g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = Cout, g.taps = taps;
-  g.bias = bias, g.res1 = static_cast<const float*>(res1), g.res1_bcast = res1_bcast;
-  g.res2 = static_cast<const float*>(res2), g.relu = relu;
+  g.bias = bias, g.res1 = res1, g.res1_bcast = res1_bcast;
+  g.res2 = static_cast<const __half*>(res2), g.relu = relu;
   return NT == 128 ? launch_conv<128, EPI_STORE>(st, ta, tb, tc, g) : launch_conv<256, EPI_STORE>(st, ta, tb, tc, g);
 }
 
 // scratch.output_conv2 + activate_head (dense_head.py:85-89, 297-344): conv3x3(Cin -> 32) + ReLU + conv1x1(32 -> od)
-// + attribute / confidence activations, fp32 out.  w1: fp32 [32, 9 * Cin] tap-major; w2: fp32 [od, 32].
+// + attribute / confidence activations, fp32 out.  in, w1: fp16 (w1 [32, 9 * Cin] tap-major); w2: fp32 [od, 32].
 wm_status conv2d_final(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
                        const float* w2, const float* b2, int od, int act, float* pred, float* conf) {
   WM_TRY(conv_check(in, w1, n, H, W, Cin, 32, 9));
   WM_CHECK(b1 && w2 && b2 && pred && conf && (od == 2 || od == 4) && act >= ACT_EXP && act <= ACT_NORM, "conv2d_final: bad argument");
-  const CUtensorMapDataType f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  const CUtensorMapDataType f16 = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   CUtensorMap ta, tb;
-  WM_TRY(tmap_nhwc(&ta, f32, 4, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
-  WM_TRY(tmap_2d(&tb, f32, 4, w1, 32, (uint64_t)9 * Cin, (uint64_t)9 * Cin, CV_KE, 32));
+  WM_TRY(tmap_nhwc(&ta, f16, 2, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
+  WM_TRY(tmap_2d(&tb, f16, 2, w1, 32, (uint64_t)9 * Cin, (uint64_t)9 * Cin, CV_KE, 32));
   ConvArgs g{};
   g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = 32, g.taps = 9;
   g.bias = b1, g.w2 = w2, g.b2 = b2, g.od = od, g.act = act, g.pred = pred, g.conf = conf;
@@ -405,15 +426,15 @@ wm_status conv2d_final(cudaStream_t st, const void* in, int n, int H, int W, int
 }
 
 // gs_renderer.gs_head (models/rasterization.py:149-153): conv3x3(Cin -> 256, bias optional) + ReLU + conv1x1(256 -> od) + b2,
-// raw fp32 [n, H, W, od]; the 256-channel hidden map stays in TMEM.  w1: fp32 [256, 9 * Cin] tap-major; w2: fp32 [od, 256].
+// raw fp32 [n, H, W, od]; the 256-channel hidden map stays in TMEM.  in, w1: fp16 (w1 [256, 9 * Cin] tap-major); w2: fp32 [od, 256].
 wm_status conv2d_project(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
                          const float* w2, const float* b2, int od, float* out) {
   WM_TRY(conv_check(in, w1, n, H, W, Cin, 256, 9));
   WM_CHECK(w2 && b2 && out && od > 0 && od <= CV_PROJ_MAX, "conv2d_project: bad argument (od=%d, at most %d)", od, CV_PROJ_MAX);
-  const CUtensorMapDataType f32 = CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  const CUtensorMapDataType f16 = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   CUtensorMap ta, tb;
-  WM_TRY(tmap_nhwc(&ta, f32, 4, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
-  WM_TRY(tmap_2d(&tb, f32, 4, w1, 256, (uint64_t)9 * Cin, (uint64_t)9 * Cin, CV_KE, 256));
+  WM_TRY(tmap_nhwc(&ta, f16, 2, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
+  WM_TRY(tmap_2d(&tb, f16, 2, w1, 256, (uint64_t)9 * Cin, (uint64_t)9 * Cin, CV_KE, 256));
   ConvArgs g{};
   g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = 256, g.taps = 9;
   g.bias = b1, g.w2 = w2, g.b2 = b2, g.od = od, g.pred = out;

@@ -1,7 +1,10 @@
 // HBM-bound kernels around the DPT heads' convolutions: LayerNorm of the 2048-wide
-// patch tokens, bilinear resampling (align_corners=True) of NHWC fp32 maps with the optional sinusoidal UV
+// patch tokens, bilinear resampling (align_corners=True) of NHWC fp16 maps with the optional sinusoidal UV
 // positional embedding, the ConvTranspose2d(k == stride) scatter, and the im2col of the one stride-2 convolution.
-// Activations are fp32 (see conv.cu); every kernel moves 16 bytes per thread per access along the contiguous channel axis.
+// Activations are fp16 with fp32 arithmetic (see conv.cu); every kernel moves 16 bytes (8 channels) per thread per access
+// along the contiguous channel axis.
+#include <cuda_fp16.h>
+
 #include <algorithm>
 
 #include "common.cuh"
@@ -11,12 +14,12 @@ namespace wm {
 
 // nn.LayerNorm(C) over rows gathered from a strided token tensor: output row r = group g * rows_per_group + i reads
 // input row g * in_group_rows + in_offset + i (DPTHead: tokens[:, :, patch_start:], dense_head.py:203-211).
-// One warp per row, the row lives in registers (C <= 2048), two-pass variance, fp32 out rounded to TF32 (conv.cu).
+// One warp per row, the row lives in registers (C <= 2048), two-pass variance, fp32 in, fp16 out (conv.cu).
 template <int C>
 __global__ void __launch_bounds__(256) ln_rows_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                       const float* __restrict__ b, float eps, long long rows,
                                                       int rows_per_group, int in_group_rows, int in_offset,
-                                                      float* __restrict__ y) {
+                                                      __half* __restrict__ y) {
   constexpr int V = C / 128;  // float4 per lane
   pdl_launch_dependents();
   pdl_wait();
@@ -44,14 +47,14 @@ __global__ void __launch_bounds__(256) ln_rows_kernel(const float* __restrict__ 
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
   const float rstd = rsqrtf(q * (1.0f / C) + eps);
-  float4* yr = reinterpret_cast<float4*>(y + r * C);
+  uint2* yr = reinterpret_cast<uint2*>(y + r * C);
   const float4* w4 = reinterpret_cast<const float4*>(w);
   const float4* b4 = reinterpret_cast<const float4*>(b);
 #pragma unroll
   for (int k = 0; k < V; ++k) {
     const float4 ww = __ldg(w4 + k * 32 + lane), bb = __ldg(b4 + k * 32 + lane);
-    yr[k * 32 + lane] = make_float4(tf32_rn((v[k].x - mu) * rstd * ww.x + bb.x), tf32_rn((v[k].y - mu) * rstd * ww.y + bb.y),
-                                    tf32_rn((v[k].z - mu) * rstd * ww.z + bb.z), tf32_rn((v[k].w - mu) * rstd * ww.w + bb.w));
+    yr[k * 32 + lane] = make_uint2(pack_half2_sat((v[k].x - mu) * rstd * ww.x + bb.x, (v[k].y - mu) * rstd * ww.y + bb.y),
+                                   pack_half2_sat((v[k].z - mu) * rstd * ww.z + bb.z, (v[k].w - mu) * rstd * ww.w + bb.w));
   }
 }
 
@@ -59,7 +62,7 @@ wm_status ln_rows(cudaStream_t st, const float* x, const float* w, const float* 
                   int rows_per_group, int in_group_rows, int in_offset, int C, void* y) {
   WM_CHECK(x && w && b && y && rows > 0 && rows_per_group > 0, "ln_rows: bad argument");
   const unsigned grid = (unsigned)((rows + 7) / 8);
-  float* yo = static_cast<float*>(y);
+  __half* yo = static_cast<__half*>(y);
   if (C == 2048)
     return launch_pdl(ln_rows_kernel<2048>, dim3(grid), dim3(256), 0, st, x, w, b, eps, rows, rows_per_group, in_group_rows, in_offset, yo);
   if (C == 1024)
@@ -67,60 +70,70 @@ wm_status ln_rows(cudaStream_t st, const float* x, const float* w, const float* 
   return fail(WM_ERR_INVALID, "ln_rows: C must be 1024 or 2048 (got %d)", C);
 }
 
-// F.interpolate(mode="bilinear", align_corners=True) on NHWC fp32 (dense_head.py:216-226, 529 via custom_interpolate
+// F.interpolate(mode="bilinear", align_corners=True) on NHWC fp16 (fp32 arithmetic) (dense_head.py:216-226, 529 via custom_interpolate
 // :539-579): src = dst * (in - 1) / (out - 1).  Optional positional embedding added after resampling
 // (_apply_pos_embed, dense_head.py:262-271): channel c < C/2 takes pos_u[x][c], c >= C/2 takes pos_v[y][c - C/2]
 // (the UV embedding is separable: utils/grid.py:4-42).  One thread per 4 channels of one output pixel.
-__global__ void __launch_bounds__(256) bilinear_kernel(const float* __restrict__ in, int n, int Hi, int Wi, int C,
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&w[k]));
+    f[2 * k] = t.x, f[2 * k + 1] = t.y;
+  }
+}
+
+__global__ void __launch_bounds__(256) bilinear_kernel(const __half* __restrict__ in, int n, int Hi, int Wi, int C,
                                                        int Ho, int Wo, float sy, float sx, const float* __restrict__ pos_u,
-                                                       const float* __restrict__ pos_v, float* __restrict__ out) {
-  // blockIdx.y = (image, output row): the row interpolation is uniform per block; threads run over (x, 4-channel chunk)
+                                                       const float* __restrict__ pos_v, __half* __restrict__ out) {
+  // blockIdx.y = (image, output row): the row interpolation is uniform per block; threads run over (x, 8-channel chunk)
   // with 32-bit index arithmetic only
   pdl_launch_dependents();
   pdl_wait();
-  const int c4 = C >> 2;
+  const int c8 = C >> 3;
   const int img = blockIdx.y / Ho, yo = blockIdx.y - img * Ho;
   const float fy = yo * sy;
   const int y0 = min((int)fy, Hi - 1), y1 = min(y0 + 1, Hi - 1);
   const float ly = fy - y0, hy0 = 1.f - ly;
-  const float4* row0 = reinterpret_cast<const float4*>(in + ((size_t)img * Hi + y0) * Wi * C);
-  const float4* row1 = reinterpret_cast<const float4*>(in + ((size_t)img * Hi + y1) * Wi * C);
-  float4* orow = reinterpret_cast<float4*>(out + ((size_t)img * Ho + yo) * Wo * C);
+  const uint4* row0 = reinterpret_cast<const uint4*>(in + ((size_t)img * Hi + y0) * Wi * C);
+  const uint4* row1 = reinterpret_cast<const uint4*>(in + ((size_t)img * Hi + y1) * Wi * C);
+  uint4* orow = reinterpret_cast<uint4*>(out + ((size_t)img * Ho + yo) * Wo * C);
   const int half = C >> 1;
-  const int total = Wo * c4;
+  const int total = Wo * c8;
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
-    const int xo = t / c4, c = t - xo * c4;
+    const int xo = t / c8, c = t - xo * c8;
     const float fx = xo * sx;
     const int x0 = min((int)fx, Wi - 1), x1 = min(x0 + 1, Wi - 1);
     const float lx = fx - x0, hx0 = 1.f - lx;
-    const float4 a = __ldg(row0 + x0 * c4 + c), b = __ldg(row0 + x1 * c4 + c);
-    const float4 d = __ldg(row1 + x0 * c4 + c), e = __ldg(row1 + x1 * c4 + c);
+    float a[8], b[8], d[8], e[8], r[8];
+    unpack8(__ldg(row0 + x0 * c8 + c), a);
+    unpack8(__ldg(row0 + x1 * c8 + c), b);
+    unpack8(__ldg(row1 + x0 * c8 + c), d);
+    unpack8(__ldg(row1 + x1 * c8 + c), e);
     // the order PyTorch's upsample_bilinear2d kernel uses: h0 * (w0 * a + w1 * b) + h1 * (w0 * d + w1 * e)
-    float4 r;
-    r.x = hy0 * (hx0 * a.x + lx * b.x) + ly * (hx0 * d.x + lx * e.x);
-    r.y = hy0 * (hx0 * a.y + lx * b.y) + ly * (hx0 * d.y + lx * e.y);
-    r.z = hy0 * (hx0 * a.z + lx * b.z) + ly * (hx0 * d.z + lx * e.z);
-    r.w = hy0 * (hx0 * a.w + lx * b.w) + ly * (hx0 * d.w + lx * e.w);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = hy0 * (hx0 * a[i] + lx * b[i]) + ly * (hx0 * d[i] + lx * e[i]);
     if (pos_u != nullptr) {
-      const int ch = c * 4;
+      const int ch = c * 8;
       const float* pp = ch < half ? pos_u + xo * half + ch : pos_v + yo * half + (ch - half);
-      const float4 p0 = __ldg(reinterpret_cast<const float4*>(pp));
-      r.x += p0.x, r.y += p0.y, r.z += p0.z, r.w += p0.w;
+      const float4 p0 = __ldg(reinterpret_cast<const float4*>(pp)), p1 = __ldg(reinterpret_cast<const float4*>(pp) + 1);
+      r[0] += p0.x, r[1] += p0.y, r[2] += p0.z, r[3] += p0.w, r[4] += p1.x, r[5] += p1.y, r[6] += p1.z, r[7] += p1.w;
     }
-    __stcs(orow + t, make_float4(tf32_rn(r.x), tf32_rn(r.y), tf32_rn(r.z), tf32_rn(r.w)));
+    __stcs(orow + t, make_uint4(pack_half2_sat(r[0], r[1]), pack_half2_sat(r[2], r[3]), pack_half2_sat(r[4], r[5]),
+                                pack_half2_sat(r[6], r[7])));
   }
 }
 
 wm_status bilinear_nhwc(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, int Ho, int Wo, const float* pos_u,
                         const float* pos_v, void* out) {
-  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && Ho > 0 && Wo > 0 && C > 0 && C % 8 == 0, "bilinear: bad geometry");
+  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && Ho > 0 && Wo > 0 && C > 0 && C % 16 == 0, "bilinear: bad geometry");
   WM_CHECK((pos_u == nullptr) == (pos_v == nullptr), "bilinear: pos_u and pos_v go together");
   const float sy = Ho > 1 ? (float)(Hi - 1) / (float)(Ho - 1) : 0.f, sx = Wo > 1 ? (float)(Wi - 1) / (float)(Wo - 1) : 0.f;
   WM_CHECK((long long)n * Ho <= 65535 && (long long)Wo * C < (1LL << 31), "bilinear: n * Ho must fit a grid dimension");
-  const int row_work = Wo * (C / 4);
+  const int row_work = Wo * (C / 8);
   const unsigned gx = (unsigned)std::min((row_work + 255) / 256, 8);
-  return launch_pdl(bilinear_kernel, dim3(gx, (unsigned)(n * Ho)), dim3(256), 0, st, static_cast<const float*>(in), n, Hi, Wi, C,
-                    Ho, Wo, sy, sx, pos_u, pos_v, static_cast<float*>(out));
+  return launch_pdl(bilinear_kernel, dim3(gx, (unsigned)(n * Ho)), dim3(256), 0, st, static_cast<const __half*>(in), n, Hi, Wi, C,
+                    Ho, Wo, sy, sx, pos_u, pos_v, static_cast<__half*>(out));
 }
 
 // nn.ConvTranspose2d(C, C, k, stride=k) (dense_head.py:57-64) = GEMM [pixels, Cin] x [Cin, (ky, kx, co)] followed by
@@ -129,7 +142,7 @@ __global__ void __launch_bounds__(256) pixel_shuffle_kernel(const uint4* __restr
                                                             uint4* __restrict__ out) {
   pdl_launch_dependents();
   pdl_wait();
-  const int c8 = C >> 2;  // 16-byte chunks (4 fp32) per pixel
+  const int c8 = C >> 3;  // 16-byte chunks (8 fp16) per pixel
   const long long total = (long long)n * Hi * k * Wi * k * c8;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(t % c8);
@@ -143,8 +156,8 @@ __global__ void __launch_bounds__(256) pixel_shuffle_kernel(const uint4* __restr
 }
 
 wm_status pixel_shuffle(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, int k, void* out) {
-  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && C > 0 && C % 4 == 0 && k > 0, "pixel_shuffle: bad geometry");
-  const long long total = (long long)n * Hi * k * Wi * k * (C / 4);
+  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && C > 0 && C % 8 == 0 && k > 0, "pixel_shuffle: bad geometry");
+  const long long total = (long long)n * Hi * k * Wi * k * (C / 8);
   const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, 148LL * 32);
   return launch_pdl(pixel_shuffle_kernel, dim3(grid), dim3(256), 0, st, static_cast<const uint4*>(in), n, Hi, Wi, C, k,
                     static_cast<uint4*>(out));
@@ -155,7 +168,7 @@ __global__ void __launch_bounds__(256) im2col_s2_kernel(const uint4* __restrict_
                                                         uint4* __restrict__ out) {
   pdl_launch_dependents();
   pdl_wait();
-  const int c8 = C >> 2;  // 16-byte chunks (4 fp32) per pixel
+  const int c8 = C >> 3;  // 16-byte chunks (8 fp16) per pixel
   const long long total = (long long)n * Ho * Wo * 9 * c8;
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(t % c8);
@@ -173,9 +186,9 @@ __global__ void __launch_bounds__(256) im2col_s2_kernel(const uint4* __restrict_
 }
 
 wm_status im2col_s2(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, void* out) {
-  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && C > 0 && C % 4 == 0, "im2col_s2: bad geometry");
+  WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && C > 0 && C % 8 == 0, "im2col_s2: bad geometry");
   const int Ho = (Hi - 1) / 2 + 1, Wo = (Wi - 1) / 2 + 1;
-  const long long total = (long long)n * Ho * Wo * 9 * (C / 4);
+  const long long total = (long long)n * Ho * Wo * 9 * (C / 8);
   const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, 148LL * 32);
   return launch_pdl(im2col_s2_kernel, dim3(grid), dim3(256), 0, st, static_cast<const uint4*>(in), n, Hi, Wi, C, Ho, Wo,
                     static_cast<uint4*>(out));

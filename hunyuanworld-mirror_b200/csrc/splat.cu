@@ -3,7 +3,7 @@
 // rasterization.py:239-246), so the path is: gs DPT head (conv.cu / headops.cu, plus the 7x7 image branch prepared
 // here) -> gs_head parameter convolution (conv.cu, projecting epilogue) -> prepare_splats (:389-498) -> prune_gs (:301-387).
 // Everything in this file is HBM-bound elementwise / integer work, written for coalesced access, no tensor cores:
-//   im2row7_kernel        images NCHW -> NHWC rows of the 7 horizontal taps (21 of 32 channels), so the 7x7 convolution
+//   im2row7_kernel        images NCHW -> NHWC fp16 rows of the 7 horizontal taps (21 of 64 channels), so the 7x7 convolution
 //                         of `input_merger` (dense_head.py:91-94) becomes a 7-tap vertical implicit GEMM of conv.cu;
 //   splat_camera_kernel   camera_params [S, 9] -> camera-to-world rotation / translation and pinhole intrinsics
 //                         (utils/camera_utils.py:46-75, utils/rotation.py:8-38, utils/geometry.py:92-111);
@@ -23,21 +23,25 @@ constexpr int SP_THREADS = 256;
 constexpr int SP_RAW = 12;  // quats 4 | scales 3 | opacity 1 | residual SH (degree 0) 3 | weight 1  (rasterization.py:131-138)
 
 // ------------------------------------------------------------------------------------------------ 7x7 image branch
-__global__ void __launch_bounds__(SP_THREADS) im2row7_kernel(const float* __restrict__ img, int n, int H, int W, float4* __restrict__ out) {
-  const size_t total = (size_t)n * H * W * 8;
+__global__ void __launch_bounds__(SP_THREADS) im2row7_kernel(const float* __restrict__ img, int n, int H, int W, uint4* __restrict__ out) {
+  const size_t total = (size_t)n * H * W * 8;  // 8 chunks of 8 fp16 channels per pixel
   for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
     const int grp = (int)(t & 7);
-    const size_t pix = t >> 3;
-    const int x = (int)(pix % W);
-    const int y = (int)((pix / W) % H);
-    const size_t im = pix / ((size_t)W * H);
-    float v[4];
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (grp < 3) {  // channels 0..20 carry data
+      const size_t pix = t >> 3;
+      const int x = (int)(pix % W);
+      const int y = (int)((pix / W) % H);
+      const size_t im = pix / ((size_t)W * H);
+      float v[8];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int k = grp * 4 + i, kx = k / 3, c = k - kx * 3, xs = x + kx - 3;
-      v[i] = (k < 21 && xs >= 0 && xs < W) ? tf32_rn(__ldg(img + ((im * 3 + c) * H + y) * W + xs)) : 0.f;
+      for (int i = 0; i < 8; ++i) {
+        const int k = grp * 8 + i, kx = k / 3, c = k - kx * 3, xs = x + kx - 3;
+        v[i] = (k < 21 && xs >= 0 && xs < W) ? __ldg(img + ((im * 3 + c) * H + y) * W + xs) : 0.f;
+      }
+      o = make_uint4(pack_half2_sat(v[0], v[1]), pack_half2_sat(v[2], v[3]), pack_half2_sat(v[4], v[5]), pack_half2_sat(v[6], v[7]));
     }
-    out[t] = make_float4(v[0], v[1], v[2], v[3]);
+    out[t] = o;
   }
 }
 
@@ -45,7 +49,7 @@ wm_status im2row7(cudaStream_t st, const float* img, int n, int H, int W, void* 
   WM_CHECK(img && out && n > 0 && H > 0 && W > 0, "im2row7: bad argument");
   const size_t total = (size_t)n * H * W * 8;
   const int grid = (int)std::min<size_t>((total + SP_THREADS - 1) / SP_THREADS, 148 * 32);
-  im2row7_kernel<<<grid, SP_THREADS, 0, st>>>(img, n, H, W, static_cast<float4*>(out));
+  im2row7_kernel<<<grid, SP_THREADS, 0, st>>>(img, n, H, W, static_cast<uint4*>(out));
   WM_LAUNCH_CHECK();
   return WM_OK;
 }

@@ -3,8 +3,9 @@
 `B200DPTHead` mirrors `DPTHead` (src/models/heads/dense_head.py:11-260, is_gsdpt=False): same constructor keywords,
 same `state_dict` keys on the way in, same `forward(token_list, images, patch_start_idx, frames_chunk_size)` and the
 same return value `(pred [B,S,H,W,C-1], conf [B,S,H,W])` in fp32.  Every convolution runs as an implicit GEMM on
-tcgen05 (csrc/conv.cu) over NHWC fp32 activations at kind::tf32 with fp32 accumulation (the reference runs its heads
-in fp32, worldmirror.py:146; bf16 activations measured 1.5e-2 on pts3d); bias, ReLU, the residual adds of
+tcgen05 (csrc/conv.cu) over NHWC fp16 activations (10-bit mantissa, as TF32) with fp32 accumulation and fp32 epilogue
+arithmetic (the reference runs its heads in fp32, worldmirror.py:146; bf16 activations measured 1.5e-2 on pts3d, a
+10-bit mantissa 1.2e-3); bias, ReLU, the residual adds of
 ResidualConvUnit / FeatureFusionBlock, the positional embedding and the output activations are fused into the
 epilogues; LayerNorm, bilinear resampling and the ConvTranspose scatter are bandwidth kernels (csrc/headops.cu).
 Two algebraic rewrites, both exact in real arithmetic:
@@ -25,6 +26,7 @@ import torch
 from . import capi
 
 PATCH = 14
+ACT = torch.float16  # storage type of every activation map and convolution weight of the DPT heads (csrc/conv.cu)
 _ACT = {"exp": 0, "inv_log": 1, "norm": 2}
 LAUNCHES = [0]  # kernels launched by the heads since the caller last reset it (bench.py: gpu_launches)
 
@@ -44,8 +46,8 @@ def _p(t):
 
 
 def round_tf32(t: torch.Tensor) -> torch.Tensor:
-    """Round fp32 to TF32 (10-bit mantissa), nearest with ties away from zero = PTX cvt.rna.tf32.f32.  The tensor
-    cores truncate fp32 operands; rounding once at load time makes that truncation exact (csrc/conv.cu)."""
+    """Round fp32 to TF32 (10-bit mantissa), nearest with ties away from zero = PTX cvt.rna.tf32.f32.  Kept for tests
+    that want operands exactly representable in the heads' fp16 storage (same mantissa width)."""
     i = t.contiguous().view(torch.int32)
     return ((i + 0x1000) & ~0x1FFF).view(torch.float32)
 
@@ -86,7 +88,7 @@ class B200DPTHead(torch.nn.Module):
 
     # ------------------------------------------------------------------ weights
     def load_state_dict(self, sd, strict: bool = True, device=None):
-        """Reference keys and shapes (DPTHead.state_dict()).  Convolution weights are repacked to fp32
+        """Reference keys and shapes (DPTHead.state_dict()).  Convolution weights are repacked to fp16
         [Cout, (ky, kx, ci)]; ConvTranspose2d weights [ci, co, ky, kx] to [(ky, kx, co), ci] with the bias tiled."""
         capi.lib()  # raises if the CUDA library is missing: no fallback
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
@@ -95,7 +97,7 @@ class B200DPTHead(torch.nn.Module):
         def conv(key):
             t = sd[key].detach().to(dev, torch.float32)
             co, ci, kh, kw = t.shape
-            return round_tf32(t.permute(0, 2, 3, 1).reshape(co, kh * kw * ci).contiguous())
+            return t.permute(0, 2, 3, 1).reshape(co, kh * kw * ci).to(ACT).contiguous()
 
         def vec(key):
             return sd[key].detach().to(dev, torch.float32).contiguous()
@@ -107,7 +109,7 @@ class B200DPTHead(torch.nn.Module):
         for i, k in ((0, 4), (1, 2)):
             t = sd[f"resize_layers.{i}.weight"].detach().to(dev, torch.float32)  # [ci, co, k, k]
             ci, co = t.shape[0], t.shape[1]
-            w[f"up{i}.w"] = round_tf32(t.permute(2, 3, 1, 0).reshape(k * k * co, ci).contiguous())
+            w[f"up{i}.w"] = t.permute(2, 3, 1, 0).reshape(k * k * co, ci).to(ACT).contiguous()
             w[f"up{i}.b"] = vec(f"resize_layers.{i}.bias").repeat(k * k).contiguous()
         w["down3.w"], w["down3.b"] = conv("resize_layers.3.weight"), vec("resize_layers.3.bias")
         for r in (1, 2, 3, 4):
@@ -121,12 +123,12 @@ class B200DPTHead(torch.nn.Module):
         w["oc2.w"], w["oc2.b"] = conv("scratch.output_conv2.0.weight"), vec("scratch.output_conv2.0.bias")
         w["oc3.w"] = sd["scratch.output_conv2.2.weight"].detach().to(dev, torch.float32).reshape(self.output_dim, 32).contiguous()
         w["oc3.b"] = vec("scratch.output_conv2.2.bias")
-        if self.is_gsdpt:  # input_merger = Conv2d(3, 128, 7, 1, 3): [co, ci, ky, kx] -> [co, ky, (kx, ci) padded 21 -> 32]
+        if self.is_gsdpt:  # input_merger = Conv2d(3, 128, 7, 1, 3): [co, ci, ky, kx] -> [co, ky, (kx, ci) padded 21 -> 64]
             t = sd["input_merger.0.weight"].detach().to(dev, torch.float32)
             co = t.shape[0]
-            rows = torch.zeros(co, 7, 32, dtype=torch.float32, device=dev)
+            rows = torch.zeros(co, 7, 64, dtype=torch.float32, device=dev)
             rows[:, :, :21] = t.permute(0, 2, 3, 1).reshape(co, 7, 21)
-            w["im.w"], w["im.b"] = round_tf32(rows.reshape(co, 7 * 32).contiguous()), vec("input_merger.0.bias")
+            w["im.w"], w["im.b"] = rows.reshape(co, 7 * 64).to(ACT).contiguous(), vec("input_merger.0.bias")
         assert tuple(w["proj0.w"].shape) == (self.oc[0], self.dim_in)
         self.w, self._loaded, self._dev = w, True, dev
         return torch.nn.modules.module._IncompatibleKeys([], [])
@@ -145,13 +147,13 @@ class B200DPTHead(torch.nn.Module):
 
     # ------------------------------------------------------------------ ops
     def _conv(self, x, n, H, W, cin, wkey, taps, cout, bias=None, res1=None, bcast=0, res2=None, relu=0):
-        out = torch.empty(n, H, W, cout, dtype=torch.float32, device=x.device)
+        out = torch.empty(n, H, W, cout, dtype=ACT, device=x.device)
         _k(capi.lib().wm_conv2d_nhwc(_st(), x.data_ptr(), n, H, W, cin, self.w[wkey].data_ptr(), taps, cout, _p(bias),
                                              _p(res1), bcast, _p(res2), relu, out.data_ptr()))
         return out
 
     def _resize(self, x, n, Hi, Wi, c, Ho, Wo, pu=None, pv=None):
-        out = torch.empty(n, Ho, Wo, c, dtype=torch.float32, device=x.device)
+        out = torch.empty(n, Ho, Wo, c, dtype=ACT, device=x.device)
         _k(capi.lib().wm_bilinear_nhwc(_st(), x.data_ptr(), n, Hi, Wi, c, Ho, Wo, _p(pu), _p(pv), out.data_ptr()))
         return out
 
@@ -175,7 +177,7 @@ class B200DPTHead(torch.nn.Module):
         na = self.output_dim - 1
         pred = torch.empty(B, S, H, W, na, dtype=torch.float32, device=dev)
         conf = torch.empty(B, S, H, W, dtype=torch.float32, device=dev)
-        feat = torch.empty(B, S, H, W, 128, dtype=torch.float32, device=dev) if self.is_gsdpt else None
+        feat = torch.empty(B, S, H, W, 128, dtype=ACT, device=dev) if self.is_gsdpt else None
         if self.is_gsdpt:
             images = images.to(dev, torch.float32).contiguous()
         with torch.cuda.device(dev):
@@ -199,7 +201,7 @@ class B200DPTHead(torch.nn.Module):
         rn, sizes = [], []
         for i, t in enumerate(toks):
             t = t.to(torch.float32).contiguous()
-            ln = torch.empty(n, gh, gw, Cd, dtype=torch.float32, device=dev)
+            ln = torch.empty(n, gh, gw, Cd, dtype=ACT, device=dev)
             _k(lib.wm_layernorm_rows(_st(), t.data_ptr(), w["norm.w"].data_ptr(), w["norm.b"].data_ptr(), 1e-5, n * g, g, P,
                                              psi, Cd, ln.data_ptr()))
             c = self.oc[i]
@@ -208,12 +210,12 @@ class B200DPTHead(torch.nn.Module):
             if i in (0, 1):  # ConvTranspose2d(c, c, k, stride k) = 1x1 convolution to k*k*c channels + scatter
                 k = 4 if i == 0 else 2
                 tmp = self._conv(f, n, gh, gw, c, f"up{i}.w", 1, k * k * c, w[f"up{i}.b"])
-                f = torch.empty(n, gh * k, gw * k, c, dtype=torch.float32, device=dev)
+                f = torch.empty(n, gh * k, gw * k, c, dtype=ACT, device=dev)
                 _k(lib.wm_pixel_shuffle(_st(), tmp.data_ptr(), n, gh, gw, c, k, f.data_ptr()))
                 h_, w_ = gh * k, gw * k
             elif i == 3:  # Conv2d(c, c, 3, stride 2, padding 1) = im2col + 1x1 convolution over 9c channels
                 h_, w_ = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
-                col = torch.empty(n, h_, w_, 9 * c, dtype=torch.float32, device=dev)
+                col = torch.empty(n, h_, w_, 9 * c, dtype=ACT, device=dev)
                 _k(lib.wm_im2col_s2(_st(), f.data_ptr(), n, gh, gw, c, col.data_ptr()))
                 f = self._conv(col, n, h_, w_, 9 * c, "down3.w", 1, c, w["down3.b"])
             # scratch.layer{i}_rn (no bias); only relu(rn) is ever read (in-place ReLU of the consuming RCU)
@@ -239,11 +241,11 @@ class B200DPTHead(torch.nn.Module):
                                        conf.data_ptr()))
         if self.is_gsdpt:
             # fused + relu(input_merger(images)) (dense_head.py:239-242): the 7 horizontal taps of the 3-channel image become
-            # 21 (of 32) channels of an NHWC map, the 7 vertical taps run as an implicit GEMM with ReLU before the residual
+            # 21 (of 64) channels of an NHWC map, the 7 vertical taps run as an implicit GEMM with ReLU before the residual
             assert H == gh * PATCH and W == gw * PATCH
-            rows = torch.empty(n, H, W, 32, dtype=torch.float32, device=dev)
+            rows = torch.empty(n, H, W, 64, dtype=ACT, device=dev)
             _k(lib.wm_im2row7(_st(), images.data_ptr(), n, H, W, rows.data_ptr()))
-            _k(lib.wm_conv2d_nhwc(_st(), rows.data_ptr(), n, H, W, 32, w["im.w"].data_ptr(), 7, 128, w["im.b"].data_ptr(),
+            _k(lib.wm_conv2d_nhwc(_st(), rows.data_ptr(), n, H, W, 64, w["im.w"].data_ptr(), 7, 128, w["im.b"].data_ptr(),
                                   fused.data_ptr(), 0, None, 2, feat.data_ptr()))
 
 
@@ -406,7 +408,7 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
         t = sd["gs_head.0.weight"].detach().to(dev, torch.float32)
         co, ci, kh, kw = t.shape
-        self.w = {"w1": round_tf32(t.permute(0, 2, 3, 1).reshape(co, kh * kw * ci).contiguous()),
+        self.w = {"w1": t.permute(0, 2, 3, 1).reshape(co, kh * kw * ci).to(ACT).contiguous(),
                   "w2": sd["gs_head.2.weight"].detach().to(dev, torch.float32).reshape(-1, co).contiguous(),
                   "b2": sd["gs_head.2.bias"].detach().to(dev, torch.float32).contiguous()}
         assert (co, ci) == (256, 128) and self.w["w2"].shape[0] == 12
@@ -415,8 +417,9 @@ class B200GaussianSplatRenderer(torch.nn.Module):
 
     # ------------------------------------------------------------------ pieces
     def gs_head(self, feat_nhwc: torch.Tensor) -> torch.Tensor:
-        """[n, H, W, 128] fp32 channels-last -> raw Gaussian parameters [n, H, W, 12] (rasterization.py:149-153, 196-197)."""
+        """[n, H, W, 128] fp16 channels-last -> raw Gaussian parameters [n, H, W, 12] fp32 (rasterization.py:149-153, 196-197)."""
         n, H, W, c = feat_nhwc.shape
+        feat_nhwc = feat_nhwc.to(ACT).contiguous()  # no copy when it comes from B200DPTHead
         raw = torch.empty(n, H, W, 12, dtype=torch.float32, device=feat_nhwc.device)
         _k(capi.lib().wm_conv2d_project(_st(), feat_nhwc.data_ptr(), n, H, W, c, self.w["w1"].data_ptr(), None,
                                         self.w["w2"].data_ptr(), self.w["b2"].data_ptr(), 12, raw.data_ptr()))
@@ -479,7 +482,7 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         feat = gs_feats.permute(0, 1, 3, 4, 2)  # back to channels-last: a view when it came from B200DPTHead
         scenes = []
         for b in range(B):
-            raw = self.gs_head(feat[b, :S].contiguous())
+            raw = self.gs_head(feat[b, :S])
             sp = self.prepare_splats(raw, images[b, :S], predictions["gs_depth"][b, :S], predictions["camera_params"][b, :S])
             if self.sharded:  # views are sharded over ranks: every rank needs all splats of the scene
                 import torch.distributed as dist

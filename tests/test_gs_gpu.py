@@ -50,23 +50,24 @@ def _renderer(sd=None):
 @pytest.mark.parametrize("n,H,Wd", [(2, 40, 23), (1, 70, 84)])
 def test_input_merger_conv(n, H, Wd):
     """Conv2d(3, 128, 7, 1, 3) + ReLU, added to a feature map: wm_im2row7 + the 7-tap vertical implicit GEMM with
-    ReLU before the residual, against torch fp32 on TF32-rounded operands."""
+    ReLU before the residual, against torch fp32 on operands representable in fp16."""
     lib = capi.lib()
     img = heads.round_tf32(torch.rand(n, 3, H, Wd, generator=torch.Generator().manual_seed(1)))
     w = heads.round_tf32(_rand((128, 3, 7, 7), 2, 1.0 / 147 ** 0.5))
     b = _rand((128,), 3, 0.1)
-    res = _rand((n, 128, H, Wd), 4)
+    res = heads.round_tf32(_rand((n, 128, H, Wd), 4))
     ref = res + F.relu(F.conv2d(img, w, b, padding=3))
-    rows_w = torch.zeros(128, 7, 32)
+    rows_w = torch.zeros(128, 7, 64)
     rows_w[:, :, :21] = w.permute(0, 2, 3, 1).reshape(128, 7, 21)
-    d = {k: v.cuda().contiguous() for k, v in dict(img=img, w=rows_w.reshape(128, 224), b=b, res=res.permute(0, 2, 3, 1)).items()}
-    rows = torch.empty(n, H, Wd, 32, device="cuda")
-    out = torch.empty(n, H, Wd, 128, device="cuda")
+    d = {k: v.cuda().contiguous() for k, v in dict(img=img, w=rows_w.reshape(128, 448).half(), b=b,
+                                                   res=res.permute(0, 2, 3, 1).half()).items()}
+    rows = torch.empty(n, H, Wd, 64, device="cuda", dtype=torch.float16)
+    out = torch.empty(n, H, Wd, 128, device="cuda", dtype=torch.float16)
     capi.check(lib.wm_im2row7(_st(), d["img"].data_ptr(), n, H, Wd, rows.data_ptr()))
-    capi.check(lib.wm_conv2d_nhwc(_st(), rows.data_ptr(), n, H, Wd, 32, d["w"].data_ptr(), 7, 128, d["b"].data_ptr(),
+    capi.check(lib.wm_conv2d_nhwc(_st(), rows.data_ptr(), n, H, Wd, 64, d["w"].data_ptr(), 7, 128, d["b"].data_ptr(),
                                   d["res"].data_ptr(), 0, None, 2, out.data_ptr()))
     torch.cuda.synchronize()
-    _close(out.cpu().permute(0, 3, 1, 2), ref, f"input_merger {n}x{H}x{Wd}")
+    _close(out.float().cpu().permute(0, 3, 1, 2), ref, f"input_merger {n}x{H}x{Wd}")
 
 
 @pytest.mark.parametrize("n,H,Wd", [(2, 18, 18), (1, 41, 55)])
@@ -78,7 +79,7 @@ def test_conv2d_project(n, H, Wd):
     w2 = _rand((12, 256, 1, 1), 3, 1.0 / 16)
     b2 = _rand((12,), 4)
     ref = F.conv2d(F.relu(F.conv2d(x, w1, None, padding=1)), w2, b2).permute(0, 2, 3, 1)
-    d = {k: v.cuda().contiguous() for k, v in dict(x=x.permute(0, 2, 3, 1), w1=w1.permute(0, 2, 3, 1).reshape(256, -1),
+    d = {k: v.cuda().contiguous() for k, v in dict(x=x.permute(0, 2, 3, 1).half(), w1=w1.permute(0, 2, 3, 1).reshape(256, -1).half(),
                                                    w2=w2.reshape(12, 256), b2=b2).items()}
     out = torch.full((n, H, Wd, 12), float("nan"), device="cuda")
     capi.check(lib.wm_conv2d_project(_st(), d["x"].data_ptr(), n, H, Wd, 128, d["w1"].data_ptr(), None, d["w2"].data_ptr(),
@@ -194,8 +195,8 @@ def test_gs_branch_matches_reference_golden(state_dict_full):
 
     e_d = fro(depth[0, :, ::st, ::st, 0].cpu().numpy(), fx["gs_depth_sub"])
     e_c = fro(conf[0, :, ::st, ::st].cpu().numpy(), fx["gs_conf_sub"])
-    e_f = fro(feat[0, :, :, ::12, ::12].cpu().numpy(), fx["gs_feat_sub"])
-    rs = np.abs(feat[0].sum(dim=3).cpu().numpy() - fx["gs_feat_rowsum"]).max() / (w * float(fx["gs_feat_absmean"]))
+    e_f = fro(feat[0, :, :, ::12, ::12].float().cpu().numpy(), fx["gs_feat_sub"])
+    rs = np.abs(feat[0].float().sum(dim=3).cpu().numpy() - fx["gs_feat_rowsum"]).max() / (w * float(fx["gs_feat_absmean"]))
     print(f"gs head: depth {e_d:.3e} conf {e_c:.3e} features {e_f:.3e} feature row-sum dev {rs:.3e}")
     assert e_d <= 2e-3 and e_c <= 2e-3 and e_f <= 2e-3 and rs <= 5e-3
     rend = _renderer(hsd)

@@ -1,6 +1,6 @@
 """GPU parity of the prediction-head kernels: each op against plain torch fp32 on the same
-operands (convolutions run on the tensor cores at kind::tf32 on operands already rounded to TF32, fp32 accumulation,
-outputs rounded to TF32 = 2^-11 relative: tolerance 2^-10 of the output scale; same for the bandwidth kernels), and the whole
+operands (convolutions run on the tensor cores at kind::f16 on fp16 operands, 10-bit mantissa like TF32, fp32 accumulation,
+outputs rounded to fp16 = 2^-11 relative: tolerance 2^-10 of the output scale; same for the bandwidth kernels), and the whole
 B200DPTHead against the fixture the REFERENCE heads produced (tests/golden/c1_heads.npz)."""
 import importlib
 import os
@@ -28,7 +28,7 @@ def _rand(shape, seed, scale=1.0):
 
 
 def _tf(x):
-    """Operands as the kernels see them: rounded to TF32 (producers and the weight loader do this)."""
+    """Operands exactly representable in the kernels' fp16 storage (10-bit mantissa)."""
     return heads.round_tf32(x)
 
 
@@ -58,23 +58,26 @@ def test_conv2d_nhwc(n, H, Wd, cin, cout, taps, res, relu):
     bc = res == 1
     r1 = _rand((1 if bc else n, cout, H, Wd), 4) if res >= 1 else None
     r2 = _rand((n, cout, H, Wd), 5) if res >= 2 else None
-    ref = F.conv2d(x, w, b, padding=k // 2)
-    if r1 is not None:
-        ref = ref + r1
+    if r1 is not None and not bc:
+        r1 = _tf(r1)
     if r2 is not None:
-        ref = ref + r2
+        r2 = _tf(r2)
+    ref = F.conv2d(x, w, b, padding=k // 2)
+    for r in (r1, r2):
+        if r is not None:
+            ref = ref + r
     if relu:
         ref = F.relu(ref)
-    nhwc = lambda t: None if t is None else t.permute(0, 2, 3, 1).contiguous().cuda()
-    xd, r1d, r2d = nhwc(x), nhwc(r1), nhwc(r2)
-    wd = w.permute(0, 2, 3, 1).reshape(cout, taps * cin).contiguous().cuda()
+    nhwc = lambda t, dt=torch.float16: None if t is None else t.permute(0, 2, 3, 1).contiguous().cuda().to(dt)
+    xd, r1d, r2d = nhwc(x), nhwc(r1, torch.float32 if bc else torch.float16), nhwc(r2)
+    wd = w.permute(0, 2, 3, 1).reshape(cout, taps * cin).contiguous().cuda().half()
     bd = b.cuda()
-    out = torch.zeros(n, H, Wd, cout, dtype=torch.float32, device="cuda")
+    out = torch.zeros(n, H, Wd, cout, dtype=torch.float16, device="cuda")
     capi.check(capi.lib().wm_conv2d_nhwc(_st(), xd.data_ptr(), n, H, Wd, cin, wd.data_ptr(), taps, cout, bd.data_ptr(),
                                          None if r1d is None else r1d.data_ptr(), int(bc), None if r2d is None else r2d.data_ptr(),
                                          relu, out.data_ptr()))
     torch.cuda.synchronize()
-    _close(out.cpu().permute(0, 3, 1, 2), ref, f"conv {taps} taps {cin}->{cout} {H}x{Wd}")
+    _close(out.float().cpu().permute(0, 3, 1, 2), ref, f"conv {taps} taps {cin}->{cout} {H}x{Wd}")
 
 
 @pytest.mark.parametrize("od,act", [(2, "exp"), (4, "inv_log"), (4, "norm")])
@@ -85,8 +88,8 @@ def test_conv2d_final(od, act):
     b1, w2, b2 = _rand((32,), 3, 0.1), _rand((od, 32, 1, 1), 4, 32 ** -0.5), _rand((od,), 5, 0.1)
     o = F.conv2d(F.relu(F.conv2d(x, w1, b1, padding=1)), w2, b2)
     pr, cr = HO.activate(o, act + "+expp1")
-    xd = x.permute(0, 2, 3, 1).contiguous().cuda()
-    w1d = w1.permute(0, 2, 3, 1).reshape(32, 9 * cin).contiguous().cuda()
+    xd = x.permute(0, 2, 3, 1).contiguous().cuda().half()
+    w1d = w1.permute(0, 2, 3, 1).reshape(32, 9 * cin).contiguous().cuda().half()
     b1d, w2d, b2d = b1.cuda(), w2.reshape(od, 32).contiguous().cuda(), b2.cuda()
     pred = torch.zeros(n, H, Wd, od - 1, device="cuda")
     conf = torch.zeros(n, H, Wd, device="cuda")
@@ -102,7 +105,7 @@ def test_bilinear_pixel_shuffle_im2col_ln():
     lib = capi.lib()
     n, Hi, Wi, c = 2, 19, 23, 256
     x = _tf(_rand((n, c, Hi, Wi), 1))
-    xd = x.permute(0, 2, 3, 1).contiguous().cuda()
+    xd = x.permute(0, 2, 3, 1).contiguous().cuda().half()
     for Ho, Wo, pos in ((37, 40, False), (38, 46, False), (60, 51, True)):
         ref = F.interpolate(x, size=(Ho, Wo), mode="bilinear", align_corners=True)
         pu = pv = None
@@ -110,50 +113,50 @@ def test_bilinear_pixel_shuffle_im2col_ln():
             pu, pv = heads.uv_tables(Wo, Ho, c, Wo / Ho)
             ref = ref + HO.uv_pos_embed(Wo, Ho, c, Wo / Ho)[None]
             pu, pv = pu.cuda(), pv.cuda()
-        out = torch.zeros(n, Ho, Wo, c, dtype=torch.float32, device="cuda")
+        out = torch.zeros(n, Ho, Wo, c, dtype=torch.float16, device="cuda")
         capi.check(lib.wm_bilinear_nhwc(_st(), xd.data_ptr(), n, Hi, Wi, c, Ho, Wo, None if pu is None else pu.data_ptr(),
                                         None if pv is None else pv.data_ptr(), out.data_ptr()))
         torch.cuda.synchronize()
-        _close(out.cpu().permute(0, 3, 1, 2), ref, f"bilinear {Hi}x{Wi}->{Ho}x{Wo} pos={pos}")
+        _close(out.float().cpu().permute(0, 3, 1, 2), ref, f"bilinear {Hi}x{Wi}->{Ho}x{Wo} pos={pos}")
     # ConvTranspose2d(k == stride) = 1x1 convolution to k*k*c channels + scatter
     for k in (4, 2):
         wt = _tf(_rand((c, c, k, k), 2, c ** -0.5))
         b = _rand((c,), 3, 0.1)
         ref = F.conv_transpose2d(x, wt, b, stride=k)
-        wd = wt.permute(2, 3, 1, 0).reshape(k * k * c, c).contiguous().cuda()
+        wd = wt.permute(2, 3, 1, 0).reshape(k * k * c, c).contiguous().cuda().half()
         bd = b.repeat(k * k).contiguous().cuda()
-        tmp = torch.zeros(n, Hi, Wi, k * k * c, dtype=torch.float32, device="cuda")
+        tmp = torch.zeros(n, Hi, Wi, k * k * c, dtype=torch.float16, device="cuda")
         capi.check(lib.wm_conv2d_nhwc(_st(), xd.data_ptr(), n, Hi, Wi, c, wd.data_ptr(), 1, k * k * c, bd.data_ptr(), None, 0, None, 0,
                                       tmp.data_ptr()))
-        out = torch.zeros(n, Hi * k, Wi * k, c, dtype=torch.float32, device="cuda")
+        out = torch.zeros(n, Hi * k, Wi * k, c, dtype=torch.float16, device="cuda")
         capi.check(lib.wm_pixel_shuffle(_st(), tmp.data_ptr(), n, Hi, Wi, c, k, out.data_ptr()))
         torch.cuda.synchronize()
-        _close(out.cpu().permute(0, 3, 1, 2), ref, f"conv_transpose k={k}")
+        _close(out.float().cpu().permute(0, 3, 1, 2), ref, f"conv_transpose k={k}")
     # stride-2 3x3 = im2col + 1x1 convolution
     w3 = _tf(_rand((c, c, 3, 3), 4, (9 * c) ** -0.5))
     b3 = _rand((c,), 5, 0.1)
     ref = F.conv2d(x, w3, b3, stride=2, padding=1)
     Ho, Wo = ref.shape[-2:]
-    col = torch.zeros(n, Ho, Wo, 9 * c, dtype=torch.float32, device="cuda")
+    col = torch.zeros(n, Ho, Wo, 9 * c, dtype=torch.float16, device="cuda")
     capi.check(lib.wm_im2col_s2(_st(), xd.data_ptr(), n, Hi, Wi, c, col.data_ptr()))
-    w3d = w3.permute(0, 2, 3, 1).reshape(c, 9 * c).contiguous().cuda()
+    w3d = w3.permute(0, 2, 3, 1).reshape(c, 9 * c).contiguous().cuda().half()
     b3d = b3.cuda()
-    out = torch.zeros(n, Ho, Wo, c, dtype=torch.float32, device="cuda")
+    out = torch.zeros(n, Ho, Wo, c, dtype=torch.float16, device="cuda")
     capi.check(lib.wm_conv2d_nhwc(_st(), col.data_ptr(), n, Ho, Wo, 9 * c, w3d.data_ptr(), 1, c, b3d.data_ptr(), None, 0, None, 0,
                                   out.data_ptr()))
     torch.cuda.synchronize()
-    _close(out.cpu().permute(0, 3, 1, 2), ref, "conv3x3 stride 2")
+    _close(out.float().cpu().permute(0, 3, 1, 2), ref, "conv3x3 stride 2")
     # LayerNorm(2048) of gathered rows
     S, P, psi, Cd = 3, 40, 7, 2048
     t = _rand((S, P, Cd), 6)
     lw, lb = 1 + _rand((Cd,), 7, 0.1), _rand((Cd,), 8, 0.1)
     ref = O.layer_norm(t[:, psi:], lw, lb, 1e-5)
     td, lwd, lbd = t.cuda(), lw.cuda(), lb.cuda()
-    y = torch.zeros(S, P - psi, Cd, dtype=torch.float32, device="cuda")
+    y = torch.zeros(S, P - psi, Cd, dtype=torch.float16, device="cuda")
     capi.check(lib.wm_layernorm_rows(_st(), td.data_ptr(), lwd.data_ptr(), lbd.data_ptr(), 1e-5, S * (P - psi), P - psi, P, psi,
                                      Cd, y.data_ptr()))
     torch.cuda.synchronize()
-    _close(y.cpu(), ref, "layernorm rows 2048")
+    _close(y.float().cpu(), ref, "layernorm rows 2048")
 
 
 @pytest.mark.parametrize("name,pre,od", [("depth", "depth_head.", 2), ("pts3d", "pts_head.", 4), ("normals", "norm_head.", 4)])

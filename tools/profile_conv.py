@@ -11,10 +11,10 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 pkg = importlib.import_module("hunyuanworld-mirror_b200")
 capi, H = pkg.capi, pkg.heads
 n, hw, cin, cout = 8, int(os.environ.get("HW", 148)), 256, int(os.environ.get("COUT", 256))
-x = H.round_tf32(torch.randn(n, hw, hw, cin, device="cuda"))
-w = H.round_tf32(torch.randn(cout, 9 * cin, device="cuda") * 0.02)
+x = torch.randn(n, hw, hw, cin, device="cuda").half()
+w = (torch.randn(cout, 9 * cin, device="cuda") * 0.02).half()
 b = torch.zeros(cout, device="cuda")
-out = torch.empty(n, hw, hw, cout, device="cuda")
+out = torch.empty(n, hw, hw, cout, device="cuda", dtype=torch.float16)
 st = torch.cuda.current_stream().cuda_stream
 run = lambda: capi.check(capi.lib().wm_conv2d_nhwc(st, x.data_ptr(), n, hw, hw, cin, w.data_ptr(), 9, cout, b.data_ptr(), None, 0, None, 1, out.data_ptr()))
 for _ in range(3):
@@ -26,4 +26,4 @@ for _ in range(10):
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 10
-print(f"conv3x3 {cin}->{cout} on {n} x {hw}x{hw}: {ms:.4f} ms, {2.0 * n * hw * hw * 9 * cin * cout / ms * 1e-9:.1f} TFLOP/s (tf32)")
+print(f"conv3x3 {cin}->{cout} on {n} x {hw}x{hw}: {ms:.4f} ms, {2.0 * n * hw * hw * 9 * cin * cout / ms * 1e-9:.1f} TFLOP/s (fp16 operands, fp32 accumulation)")
