@@ -363,7 +363,7 @@ def run_b200(args):
                                        f"{'camera-pose + depth + intrinsics priors extracted on the GPU inside the step (BASELINE configs[2])' if args.priors else 'no priors (BASELINE configs[1] at N=1)'}"
                                        f"{'' if gs_on or not heads_on else '; Gaussian branch off (--no-gs)'}",
                            "priors": bool(args.priors),
-                           "heads": heads_on, "gaussians": gs_on, "head_dtype": "camera fp32, DPT tf32 (fp32 accumulate)" if heads_on else None,
+                           "heads": heads_on, "gaussians": gs_on, "head_dtype": "camera fp32, DPT fp16 maps and weights with fp32 accumulation and fp32 epilogues" if heads_on else None,
                            "views_per_gpu": n_local, "views_total": n_total, "size": SIZE, "tokens_per_view": 1376,
                            "parallelism": f"views sharded; global attention: {sp_exchange}" if world > 1 else "single GPU",
                            "l2": "per-step working set (1.8 GB bf16 weights + activations) exceeds the 126 MB L2; no flush needed"},

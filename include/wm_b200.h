@@ -189,12 +189,14 @@ void wm_rope_tables(int max_pos, float* cos_host, float* sin_host);
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst);
 
 /* ---- prediction heads: DPTHead (src/models/heads/dense_head.py) ------------ */
-/* The reference runs its heads in fp32 (autocast disabled, worldmirror.py:146): activations are NHWC fp32
- * [n, H, W, C], weights fp32 [Cout, taps * Cin] with taps ordered (ky, kx, ci); the tensor cores run kind::tf32
- * with fp32 accumulation (bf16 activations measured 1.5e-2 relative error on pts3d, above the stated 1e-2).
+/* The reference runs its heads in fp32 (autocast disabled, worldmirror.py:146).  Here activation maps are NHWC fp16
+ * [n, H, W, C] and convolution weights fp16 [Cout, taps * Cin] with taps ordered (ky, kx, ci): a 10-bit mantissa, like
+ * TF32, at twice the tensor rate; accumulation and all epilogue arithmetic are fp32; biases, positional tables and the
+ * final predictions are fp32 (bf16 maps measured 1.5e-2 relative error on pts3d, above the stated 1e-2; 10 bits: 1.2e-3).
  * nn.Conv2d(Cin, Cout, 1 | 3, stride 1, padding 0 | 1) as an implicit GEMM on tcgen05 with its neighbours fused:
- * out = [relu](conv(in) + bias + res1 + res2); bias / res1 / res2 may be NULL; res1_bcast: res1 is [H, W, Cout]
- * (the positional table of _apply_pos_embed, dense_head.py:262-271).  Cin % 32 == 0; Cout 128 or a multiple of 256.
+ * out = [relu](conv(in) + bias + res1 + res2); bias (fp32) / res1 / res2 (fp16 maps) may be NULL; res1_bcast: res1 is the
+ * fp32 table [H, W, Cout] (the positional table of _apply_pos_embed, dense_head.py:262-271).  Cin % 64 == 0; Cout 128
+ * or a multiple of 256.
  * ConvTranspose2d(k == stride) is this with taps = 1 and Cout = k*k*C followed by wm_pixel_shuffle; the stride-2
  * convolution is wm_im2col_s2 followed by this with taps = 1.
  * Fuses: projects[i] + pos embed (:212-215), scratch.layer*_rn (:278-281), ResidualConvUnit (:436-457, whose in-place
@@ -203,14 +205,14 @@ wm_status wm_conv2d_nhwc(wm_stream stream, const void* in, int n, int H, int W, 
                          const float* bias, const void* res1, int res1_bcast, const void* res2, int relu, void* out);
 /* scratch.output_conv2 + activate_head (dense_head.py:85-89, 297-344): conv3x3(Cin -> 32) + ReLU + conv1x1(32 -> od) +
  * activations; act 0 = exp (depth), 1 = inv_log (points), 2 = norm (normals); confidence = 1 + exp.
- * w1 [32, 9*Cin], b1 [32], w2 [od, 32], b2 [od] fp32; pred [n, H, W, od-1], conf [n, H, W] fp32; od = 2 or 4. */
+ * in, w1 [32, 9*Cin] fp16; b1 [32], w2 [od, 32], b2 [od] fp32; pred [n, H, W, od-1], conf [n, H, W] fp32; od = 2 or 4. */
 wm_status wm_conv2d_final(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
                           const float* w2, const float* b2, int od, int act, float* pred, float* conf);
 /* nn.LayerNorm(C) of gathered rows (dense_head.py:203-211): output row g * rows_per_group + i = LN(input row
- * g * in_group_rows + in_offset + i), fp32 in, fp32 out; C = 1024 or 2048. */
+ * g * in_group_rows + in_offset + i), fp32 in, fp16 out; C = 1024 or 2048. */
 wm_status wm_layernorm_rows(wm_stream stream, const float* x, const float* w, const float* b, float eps, long long rows,
                             int rows_per_group, int in_group_rows, int in_offset, int C, void* y);
-/* F.interpolate(bilinear, align_corners=True) (dense_head.py:216-226, 529) on NHWC fp32, optionally followed by the
+/* F.interpolate(bilinear, align_corners=True) (dense_head.py:216-226, 529) on NHWC fp16 (fp32 arithmetic), optionally followed by the
  * separable UV positional embedding: + pos_u[x][c] for c < C/2, + pos_v[y][c - C/2] otherwise (fp32 tables). */
 wm_status wm_bilinear_nhwc(wm_stream stream, const void* in, int n, int Hi, int Wi, int C, int Ho, int Wo, const float* pos_u,
                            const float* pos_v, void* out);
@@ -258,11 +260,11 @@ wm_status wm_pose_prior(wm_stream stream, const float* extrinsics, int extr_stri
  * taps = 7 (a 7x1 vertical convolution, padding 3) and relu = 2 (ReLU on conv + bias BEFORE res1 / res2 are added): with
  * wm_im2row7 that is DPTHead's `input_merger` = Conv2d(3, 128, 7, 1, 3) + ReLU added to the fused map
  * (heads/dense_head.py:91-94, 239-242). */
-/* images NCHW fp32 [n, 3, H, W] -> NHWC fp32 [n, H, W, 32]: channel kx * 3 + c = image[c][y][x + kx - 3] (zero outside),
- * channels 21..31 zero, TF32-rounded.  The matching weight is [128, 7 (ky), 32]. */
+/* images NCHW fp32 [n, 3, H, W] -> NHWC fp16 [n, H, W, 64]: channel kx * 3 + c = image[c][y][x + kx - 3] (zero outside),
+ * channels 21..63 zero.  The matching weight is fp16 [128, 7 (ky), 64]. */
 wm_status wm_im2row7(wm_stream stream, const float* images, int n, int H, int W, void* out);
 /* gs_renderer.gs_head (rasterization.py:149-153): conv3x3(Cin -> 256) [+ b1] + ReLU + conv1x1(256 -> od) + b2 in one
- * kernel, the hidden map stays in tensor memory.  w1 [256, 9*Cin] tap-major, w2 [od, 256], out [n, H, W, od] fp32; od <= 16. */
+ * kernel, the hidden map stays in tensor memory.  in, w1 [256, 9*Cin] (tap-major) fp16; w2 [od, 256], b2 fp32; out [n, H, W, od] fp32; od <= 16. */
 wm_status wm_conv2d_project(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
                             const float* w2, const float* b2, int od, float* out);
 /* camera_params [n, 9] -> cam [n, 16] = camera-to-world R (9, row major), t (3), fx, fy, cx, cy: vector_to_camera_matrices
