@@ -194,10 +194,24 @@ __global__ void __launch_bounds__(SP_THREADS) prune_bounds_kernel(const float* _
       lo[d] = a < lo[d] ? a : lo[d];
       hi[d] = b > hi[d] ? b : hi[d];
     }
-    if ((threadIdx.x & 31) == 0) {
-      atomicMin(bounds + d, lo[d]);
-      atomicMax(bounds + 3 + d, hi[d]);
+  }
+  // warp results -> block result in shared memory -> six global atomics per block
+  __shared__ long long s_lo[3][SP_THREADS / 32], s_hi[3][SP_THREADS / 32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+#pragma unroll
+    for (int d = 0; d < 3; ++d) s_lo[d][warp] = lo[d], s_hi[d][warp] = hi[d];
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int d = threadIdx.x;
+    long long a = s_lo[d][0], b2 = s_hi[d][0];
+    for (int w = 1; w < SP_THREADS / 32; ++w) {
+      a = s_lo[d][w] < a ? s_lo[d][w] : a;
+      b2 = s_hi[d][w] > b2 ? s_hi[d][w] : b2;
     }
+    atomicMin(bounds + d, a);
+    atomicMax(bounds + 3 + d, b2);
   }
 }
 

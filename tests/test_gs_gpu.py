@@ -256,3 +256,55 @@ def test_worldmirror_forward_with_gaussians(state_dict_full):
             np.testing.assert_allclose(g, ref[k], rtol=3e-7, atol=1e-9)
         else:
             assert np.array_equal(g, ref[k].reshape(K, -1)), k
+
+
+def test_gs_head_rectangular_and_chunked():
+    """Rectangular views (56 x 84: ragged convolution tiles everywhere), three views processed in chunks of two: equal,
+    bit for bit, to the unchunked call (dense_head.py:141-156), and within the 10-bit-operand tolerance of the oracle."""
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    S, h, w = 3, 56, 84
+    P = 7 + (h // 14) * (w // 14)
+    toks = [_rand((1, S, P, 2048), 30 + i, 0.8) for i in range(4)]
+    imgs = torch.rand(1, S, 3, h, w, generator=torch.Generator().manual_seed(9))
+    head = heads.B200DPTHead(dim_in=2048, output_dim=2, activation="exp+expp1", is_gsdpt=True)
+    head.load_state_dict({k[len("gs_head."):]: v for k, v in hsd.items() if k.startswith("gs_head.")})
+    dt = [t.cuda() for t in toks]
+    f1, d1, c1 = head(dt, imgs.cuda(), 7, frames_chunk_size=2)
+    f2, d2, c2 = head(dt, imgs.cuda(), 7, frames_chunk_size=None)
+    torch.cuda.synchronize()
+    assert torch.equal(f1, f2) and torch.equal(d1, d2) and torch.equal(c1, c2)
+    with torch.no_grad():
+        rf, rd, rc = G.gs_dpt_head(toks, imgs, hsd)
+    e_f = ((f1[0].float().cpu() - rf).norm() / rf.norm()).item()
+    e_d = ((d1.cpu() - rd).norm() / rd.norm()).item()
+    e_c = ((c1.cpu() - rc).norm() / rc.norm()).item()
+    print(f"gs head 56x84, chunks of 2: features {e_f:.3e} depth {e_d:.3e} conf {e_c:.3e}")
+    assert e_f <= 2e-3 and e_d <= 2e-3 and e_c <= 2e-3
+
+
+def test_renderer_context_views_and_errors():
+    """`views["context_nums"]` restricts the splats to the first S views (rasterization.py:183, 401); unsupported
+    configurations and a missing load raise instead of falling back."""
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    g = torch.Generator().manual_seed(4)
+    S, h, w = 3, 28, 42
+    feat = torch.randn(1, S, h, w, 128, generator=g).cuda().half().permute(0, 1, 4, 2, 3)
+    imgs = torch.rand(1, S, 3, h, w, generator=g).cuda()
+    cp = torch.randn(1, S, 9, generator=g)
+    cp[..., 7:] = cp[..., 7:].abs() * 0.3 + 0.6
+    preds = {"camera_params": cp.cuda(), "gs_depth": (torch.rand(1, S, h, w, 1, generator=g) + 0.2).cuda()}
+    r = _renderer(hsd)
+    r.enable_prune = False
+    two = r.render(feat, imgs, dict(preds), {"img": imgs, "context_nums": 2})["splats"]
+    ref = r.render(feat[:, :2], imgs[:, :2].contiguous(), {k: v[:, :2].contiguous() for k, v in preds.items()})["splats"]
+    assert two["means"].shape == (1, 2 * h * w, 3)
+    for k in ("means", "quats", "scales", "opacities", "sh", "weights", "gs_feats", "residual_sh"):
+        assert torch.equal(two[k], ref[k]), k
+    with pytest.raises(NotImplementedError):
+        heads.B200GaussianSplatRenderer(sh_degree=1)
+    with pytest.raises(NotImplementedError):
+        heads.B200GaussianSplatRenderer(predict_offset=True)
+    with pytest.raises(RuntimeError):
+        heads.B200GaussianSplatRenderer().render(feat, imgs, dict(preds))
+    with pytest.raises(capi.WmError):
+        r.prune_gs({k: v[0] for k, v in ref.items()}, voxel_size=0.0)
