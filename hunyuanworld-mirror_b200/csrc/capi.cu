@@ -1050,6 +1050,30 @@ wm_status wm_prune_splats(wm_stream stream, long long N, const float* means, con
                       workspace_bytes, out_means, out_quats, out_scales, out_opacities, out_sh, count);
 }
 
+wm_status wm_raster_project(wm_stream stream, const float* means, const float* quats, const float* scales, const float* opacities,
+                            const float* viewmats, const float* Ks, int C, long long N, int W, int H, float near_plane,
+                            float far_plane, float eps2d, float* means2d, float* conics, float* depths, int* radii, unsigned* tiles,
+                            unsigned* cum, void* scan_tmp, size_t scan_tmp_bytes) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return raster_project(static_cast<cudaStream_t>(stream), means, quats, scales, opacities, viewmats, Ks, C, N, W, H, near_plane,
+                        far_plane, eps2d, means2d, conics, depths, radii, tiles, cum, scan_tmp, scan_tmp_bytes);
+}
+
+wm_status wm_raster_workspace_bytes(long long elems, long long n_isects, size_t* scan_bytes, size_t* render_bytes) {
+  return raster_workspace_bytes(elems, n_isects, scan_bytes, render_bytes);
+}
+
+wm_status wm_raster_render(wm_stream stream, const float* means2d, const float* conics, const float* depths, const int* radii,
+                           const unsigned* cum, const float* opacities, const float* sh, int C, long long N, int W, int H,
+                           long long n_isects, void* workspace, size_t workspace_bytes, unsigned* offsets, float* out_rgb,
+                           float* out_depth, float* out_alpha) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return raster_render(static_cast<cudaStream_t>(stream), means2d, conics, depths, radii, cum, opacities, sh, C, N, W, H, n_isects,
+                       workspace, workspace_bytes, offsets, out_rgb, out_depth, out_alpha);
+}
+
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
   int sms;
   WM_TRY(require_sm100(&sms));

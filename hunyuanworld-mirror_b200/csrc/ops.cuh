@@ -66,6 +66,16 @@ wm_status prune_splats(cudaStream_t st, long long N, const float* means, const f
                        const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
                        size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities, float* out_sh,
                        unsigned* count);
+// splat rasterisation (raster.cu)
+wm_status raster_project(cudaStream_t st, const float* means, const float* quats, const float* scales, const float* opacities,
+                         const float* viewmats, const float* Ks, int C, long long N, int W, int H, float near_plane, float far_plane,
+                         float eps2d, float* means2d, float* conics, float* depths, int* radii, unsigned* tiles, unsigned* cum,
+                         void* scan_tmp, size_t scan_tmp_bytes);
+wm_status raster_workspace_bytes(long long elems, long long n_isects, size_t* scan_bytes, size_t* render_bytes);
+wm_status raster_render(cudaStream_t st, const float* means2d, const float* conics, const float* depths, const int* radii,
+                        const unsigned* cum, const float* opacities, const float* sh, int C, long long N, int W, int H,
+                        long long n_isects, void* workspace, size_t workspace_bytes, unsigned* offsets, float* out_rgb,
+                        float* out_depth, float* out_alpha);
 wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);
 
 }  // namespace wm

@@ -286,6 +286,27 @@ wm_status wm_prune_splats(wm_stream stream, long long N, const float* means, con
                           size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
                           float* out_sh, unsigned* count);
 
+/* ---- forward splat rasterisation: gsplat 1.5.3's rasterization() as the reference ---- */
+/* calls it (src/models/models/rasterization.py:29-66: pinhole, classic mode, tile 16, eps2d 0.3, SH degree 0,
+ * render_mode "RGB+ED"), restated from submodules/gsplat/gsplat/cuda/csrc/{ProjectionEWA3DGSPacked,IntersectTile,
+ * RasterizeToPixels3DGSFwd}.cu.  Three calls, one host read between the first two:
+ *   wm_raster_project: per (camera, gaussian) 2D mean, conic, depth, integer radii (0 = culled), tile count, and the
+ *     inclusive scan `cum` of the tile counts (cum[C*N - 1] = number of intersections); quats are (w, x, y, z);
+ *     viewmats [C, 4, 4] world-to-camera row major, Ks [C, 3, 3];
+ *   wm_raster_workspace_bytes: scratch sizes for the scan (first call) and for sort + binning (second call);
+ *   wm_raster_render: emit (image | tile | depth) keys, stable radix sort, tile offsets, front-to-back compositing;
+ *     sh [N, 3] degree-0 coefficients (colour = max(C0 sh + 0.5, 0)); offsets: scratch of C * tiles + 1 words;
+ *     out_rgb [C, H, W, 3], out_depth [C, H, W] = expected depth, out_alpha [C, H, W]. */
+wm_status wm_raster_project(wm_stream stream, const float* means, const float* quats, const float* scales, const float* opacities,
+                            const float* viewmats, const float* Ks, int C, long long N, int W, int H, float near_plane,
+                            float far_plane, float eps2d, float* means2d, float* conics, float* depths, int* radii, unsigned* tiles,
+                            unsigned* cum, void* scan_tmp, size_t scan_tmp_bytes);
+wm_status wm_raster_workspace_bytes(long long elems, long long n_isects, size_t* scan_bytes, size_t* render_bytes);
+wm_status wm_raster_render(wm_stream stream, const float* means2d, const float* conics, const float* depths, const int* radii,
+                           const unsigned* cum, const float* opacities, const float* sh, int C, long long N, int W, int H,
+                           long long n_isects, void* workspace, size_t workspace_bytes, unsigned* offsets, float* out_rgb,
+                           float* out_depth, float* out_alpha);
+
 #ifdef __cplusplus
 }
 #endif
