@@ -401,6 +401,21 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         self.w: Dict[str, torch.Tensor] = {}
         self._loaded = False
         self._ws = None
+        from .raster import B200Rasterizer
+
+        self.rasterizer = B200Rasterizer()  # rasterization.py:163; only used when render(..., rasterize=True)
+
+    def prediction_cameras(self, camera_params, H: int, W: int):
+        """prepare_prediction_cameras (rasterization.py:506-530): camera_params [S, 9] -> camera-to-world [S, 4, 4], K [S, 3, 3]."""
+        S, dev = camera_params.shape[0], camera_params.device
+        cam = torch.empty(S, 16, dtype=torch.float32, device=dev)
+        cp = camera_params.to(torch.float32).contiguous()
+        _k(capi.lib().wm_splat_cameras(_st(), cp.data_ptr(), S, H, W, cam.data_ptr()))
+        c2w = torch.zeros(S, 4, 4, dtype=torch.float32, device=dev)
+        c2w[:, :3, :3], c2w[:, :3, 3], c2w[:, 3, 3] = cam[:, :9].reshape(S, 3, 3), cam[:, 9:12], 1.0
+        K = torch.zeros(S, 3, 3, dtype=torch.float32, device=dev)
+        K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2], K[:, 2, 2] = cam[:, 12], cam[:, 13], cam[:, 14], cam[:, 15], 1.0
+        return c2w, K
 
     def load_state_dict(self, sd, strict: bool = True, device=None):
         """Reference keys: gs_head.0.weight [256, 128, 3, 3] (no bias), gs_head.2.weight [12, 256, 1, 1], gs_head.2.bias [12]."""
@@ -468,11 +483,13 @@ class B200GaussianSplatRenderer(torch.nn.Module):
 
     # ------------------------------------------------------------------ reference entry point
     @torch.no_grad()
-    def render(self, gs_feats, images, predictions, views=None, context_predictions=None):
+    def render(self, gs_feats, images, predictions, views=None, context_predictions=None, rasterize: bool = False):
         """gs_feats [B, S, 128, H, W] (as B200DPTHead(is_gsdpt=True) returns it), images [B, S, 3, H, W], predictions with
         `camera_params` [B, S, 9] and `gs_depth` [B, S, H, W, 1].  Adds predictions["splats"]: with pruning a dict of
         per-scene lists (means [K,3], sh [K,1,3], opacities [K], scales [K,3], quats [K,4]), as rasterization.py:381-386;
-        without, the prepare_splats dict batched over B."""
+        without, the prepare_splats dict batched over B.  rasterize=True additionally renders every view from its predicted
+        camera in chunks of four, as the reference does before it drops the images (rasterization.py:221-241), and keeps
+        them as predictions["rendered_colors" | "rendered_depths" | "rendered_alphas"] [B, S, H, W, 3 | 1 | 1]."""
         if not self._loaded:
             raise RuntimeError("B200GaussianSplatRenderer: load_state_dict() has not been called")
         if context_predictions is not None:
@@ -497,6 +514,19 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         if self.enable_prune:
             merged = [self.prune_gs(sp) for sp in scenes]
             predictions["splats"] = {k: [m[k] for m in merged] for k in ("means", "sh", "opacities", "scales", "quats")}
+            if rasterize:
+                if self.sharded:
+                    raise NotImplementedError("rasterize=True with views sharded over ranks")
+                H, W = images.shape[-2:]
+                outs = [[], [], []]
+                for b, m in enumerate(merged):
+                    c2w, K = self.prediction_cameras(predictions["camera_params"][b], H, W)
+                    parts = [self.rasterizer.rasterize_splats(m["means"], m["quats"], m["scales"], m["opacities"], m["sh"], c2w[i:i + 4],
+                                                              K[i:i + 4], W, H, sh_degree=0) for i in range(0, c2w.shape[0], 4)]
+                    for k in range(3):
+                        outs[k].append(torch.cat([p[k] for p in parts], dim=0))
+                for k, name in enumerate(("rendered_colors", "rendered_depths", "rendered_alphas")):
+                    predictions[name] = torch.stack(outs[k], dim=0)
         else:
             spl = {k: torch.stack([sp[k] for sp in scenes], dim=0) for k in self.SPLAT_KEYS + ("gs_feats",)}
             spl["sh"] = spl["sh"].reshape(B, -1, 1, 3)

@@ -308,3 +308,32 @@ def test_renderer_context_views_and_errors():
         heads.B200GaussianSplatRenderer().render(feat, imgs, dict(preds))
     with pytest.raises(capi.WmError):
         r.prune_gs({k: v[0] for k, v in ref.items()}, voxel_size=0.0)
+
+
+def test_render_with_rasterisation_matches_oracle(state_dict_full):
+    """render(..., rasterize=True): the chunked rendering of every view from its predicted camera, which the reference
+    performs and discards (rasterization.py:221-241), against the numpy rasteriser oracle on the same merged splats."""
+    from oracle import raster_oracle as RO
+
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    fx = np.load(os.path.join(GOLDEN, "gs_c1.npz"))
+    g = torch.Generator().manual_seed(8)
+    S, h, w = 2, 56, 70
+    feat = torch.randn(1, S, h, w, 128, generator=g).cuda().half().permute(0, 1, 4, 2, 3)
+    imgs = torch.rand(1, S, 3, h, w, generator=g).cuda()
+    preds = {"camera_params": torch.from_numpy(fx["camera_params"])[None].cuda(), "gs_depth": (torch.rand(1, S, h, w, 1, generator=g) * 0.5 + 0.5).cuda()}
+    r = _renderer(hsd)
+    r.voxel_size = 0.01
+    out = r.render(feat, imgs, preds, rasterize=True)
+    torch.cuda.synchronize()
+    sp = {k: v[0].cpu().numpy() for k, v in out["splats"].items()}
+    c2w, K = r.prediction_cameras(preds["camera_params"][0], h, w)
+    ref = RO.rasterize(sp["means"], sp["quats"], sp["scales"], sp["opacities"], sp["sh"].reshape(-1, 3), c2w.cpu().numpy(), K.cpu().numpy(), w, h)
+    for name, refimg in zip(("rendered_colors", "rendered_depths", "rendered_alphas"), ref):
+        got = out[name][0].cpu().numpy()
+        assert got.shape == refimg.shape, (name, got.shape, refimg.shape)
+        d = np.abs(got - refimg)
+        scale = max(float(np.abs(refimg).mean()), 1e-3)
+        print(f"{name}: mean abs diff {d.mean():.2e} (mean |ref| {scale:.3f}), pixels off by > 1e-3: {100 * (d > 1e-3 * max(scale, 1)).mean():.3f} %")
+        assert d.mean() < 1e-4 * max(scale, 1) and (d > 1e-3 * max(scale, 1)).mean() < 1e-2
+    assert out["rendered_alphas"].max().item() > 0.1

@@ -34,5 +34,15 @@ for it in range(2):
     out = rend.render(feat, imgs, {"camera_params": cp, "gs_depth": depth})["splats"]
     ev[2].record()
     torch.cuda.synchronize()
+    sp = {k: v[0] for k, v in out.items()}
+    c2w, K = rend.prediction_cameras(cp[0], size, size)
+    ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev2[0].record()
+    for i in range(0, n, 4):  # chunks of four views, as rasterization.py:223-236
+        rend.rasterizer.rasterize_splats(sp["means"], sp["quats"], sp["scales"], sp["opacities"], sp["sh"], c2w[i:i + 4], K[i:i + 4], size, size, sh_degree=0)
+    ev2[1].record()
+    torch.cuda.synchronize()
+    print(f"pass {it}: rasterising {n} views of {size}x{size} from {sp['means'].shape[0]} splats: {ev2[0].elapsed_time(ev2[1]):.3f} ms "
+          f"({rend.rasterizer.last['n_isects']} tile intersections in the last chunk)", flush=True)
     print(f"pass {it}: gs DPT head {ev[0].elapsed_time(ev[1]):.3f} ms, parameter head + prepare + merge {ev[1].elapsed_time(ev[2]):.3f} ms, "
           f"{n * size * size} splats -> {out['means'][0].shape[0]} voxels", flush=True)
