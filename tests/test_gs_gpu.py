@@ -337,3 +337,23 @@ def test_render_with_rasterisation_matches_oracle(state_dict_full):
         print(f"{name}: mean abs diff {d.mean():.2e} (mean |ref| {scale:.3f}), pixels off by > 1e-3: {100 * (d > 1e-3 * max(scale, 1)).mean():.3f} %")
         assert d.mean() < 1e-4 * max(scale, 1) and (d > 1e-3 * max(scale, 1)).mean() < 1e-2
     assert out["rendered_alphas"].max().item() > 0.1
+
+
+def test_worldmirror_batch_of_scenes(state_dict_full):
+    """B = 2 scenes in one call = the two scenes called one by one, bit for bit, for every prediction including the
+    per-scene splat lists (the reference's forward is batched over B, worldmirror.py:120-152)."""
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    model = heads.B200WorldMirror.from_state_dicts(state_dict_full, hsd)
+    imgs = torch.rand(2, 2, 3, 56, 70, generator=torch.Generator().manual_seed(12)).cuda()
+    both = model({"img": imgs})
+    singles = [model({"img": imgs[b:b + 1]}) for b in range(2)]
+    torch.cuda.synchronize()
+    for k in ("camera_params", "depth", "depth_conf", "pts3d", "pts3d_conf", "normals", "normals_conf", "gs_depth", "gs_depth_conf"):
+        assert both[k].shape[0] == 2
+        for b in range(2):
+            assert torch.equal(both[k][b], singles[b][k][0]), (k, b)
+    for k in KEYS:
+        assert len(both["splats"][k]) == 2
+        for b in range(2):
+            assert torch.equal(both["splats"][k][b], singles[b]["splats"][k][0]), (k, b)
+    assert not torch.equal(both["depth"][0], both["depth"][1])
