@@ -35,9 +35,22 @@ constexpr int CV_KE = 64;              // fp16 elements per k-block (one 128-byt
 constexpr int CV_A_BYTES = 128 * CV_KE * 2;
 constexpr int CV_THREADS = 256;
 constexpr int CV_STG_BYTES = 128 * 128;
-template <int NT>
+// "Tall" mode (3x3 convolutions with Cout tiles of 32 / 128): the narrow Cout tiles are bound by the nine-fold re-read of
+// their input tile from L2, so the producer loads ONE box of (8 + 2) x 16 pixels per (dx, channel block) and the three dy taps
+// read it through descriptors that start 0 / 1 / 2 pixel rows (2048 B, a multiple of the 1024-byte swizzle atom) into it:
+// three times fewer input bytes.  A stage then holds that box and the three weight tiles of the taps (dy, dx).
+constexpr int CV_TALL_A_BYTES = (CV_TH + 2) * CV_TW * 128;
+template <int NT, bool TALL>
+constexpr int cv_stages() {
+  return TALL && NT >= 128 ? 3 : CV_STAGES;
+}
+template <int NT, bool TALL>
+constexpr int cv_stage_bytes() {
+  return TALL ? CV_TALL_A_BYTES + 3 * NT * 128 : CV_A_BYTES + NT * 128;
+}
+template <int NT, bool TALL = false>
 constexpr int cv_smem() {
-  return CV_STAGES * (CV_A_BYTES + NT * 128) + CV_STG_BYTES + 256 + 1024;
+  return cv_stages<NT, TALL>() * cv_stage_bytes<NT, TALL>() + CV_STG_BYTES + 256 + 1024;
 }
 
 enum : int { ACT_EXP = 0, ACT_INV_LOG = 1, ACT_NORM = 2 };
@@ -58,7 +71,7 @@ struct ConvArgs {
   float *pred, *conf;           // final: [n, H, W, od - 1], [n, H, W]; project: pred = [n, H, W, od]
 };
 
-template <int NT, int EPI>
+template <int NT, int EPI, bool TALL>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const ConvArgs g) {
@@ -70,9 +83,12 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   constexpr uint32_t TMEM_COLS = 2 * NT < 32 ? 32 : 2 * NT;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  constexpr int STAGES = TALL && NT >= 128 ? 3 : CV_STAGES;  // = cv_stages<NT, TALL>()
+  constexpr int A_STAGE = TALL ? CV_TALL_A_BYTES : CV_A_BYTES;
+  constexpr int B_STAGE = TALL ? 3 * B_BYTES : B_BYTES;
   uint8_t* sA = smem;
-  uint8_t* sB = sA + CV_STAGES * CV_A_BYTES;
-  uint8_t* sC = sB + CV_STAGES * B_BYTES;
+  uint8_t* sB = sA + STAGES * A_STAGE;
+  uint8_t* sC = sB + STAGES * B_STAGE;
   uint64_t* full = reinterpret_cast<uint64_t*>(sC + CV_STG_BYTES);
   uint64_t* empty = full + CV_STAGES;
   uint64_t* tfull = empty + CV_STAGES;
@@ -87,7 +103,7 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (STORE) tma_prefetch_desc(&tmC);
   }
   if (warp == 1 && elect_one()) {
-    for (int i = 0; i < CV_STAGES; ++i) {
+    for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
     }
@@ -125,13 +141,20 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         int n0, x0, y0, img;
         decode(tile, n0, x0, y0, img);
         for (int kb = 0; kb < g.kblocks; ++kb, ++it) {
-          const uint32_t s = it % CV_STAGES, ph = (it / CV_STAGES) & 1;
+          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
           const int tap = kb / cblocks, cb = kb - tap * cblocks;
-          const int dy = g.taps == 9 ? tap / 3 - 1 : (g.taps == 7 ? tap - 3 : 0), dx = g.taps == 9 ? tap % 3 - 1 : 0;
           mbar_wait(&empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full[s], CV_A_BYTES + B_BYTES);
-          tma_load_4d(sA + s * CV_A_BYTES, &tmA, &full[s], cb * CV_KE, x0 + dx, y0 + dy, img, kEvictNormal);
-          tma_load_2d(sB + s * B_BYTES, &tmB, &full[s], kb * CV_KE, n0, kEvictLast);
+          mbar_arrive_expect_tx(&full[s], A_STAGE + B_STAGE);
+          if constexpr (TALL) {  // tap = dx index: one box of 10 pixel rows, the weight tiles of (dy = -1, 0, 1; dx)
+            tma_load_4d(sA + s * A_STAGE, &tmA, &full[s], cb * CV_KE, x0 + tap - 1, y0 - 1, img, kEvictNormal);
+#pragma unroll
+            for (int dyi = 0; dyi < 3; ++dyi)
+              tma_load_2d(sB + s * B_STAGE + dyi * B_BYTES, &tmB, &full[s], ((dyi * 3 + tap) * cblocks + cb) * CV_KE, n0, kEvictLast);
+          } else {
+            const int dy = g.taps == 9 ? tap / 3 - 1 : (g.taps == 7 ? tap - 3 : 0), dx = g.taps == 9 ? tap % 3 - 1 : 0;
+            tma_load_4d(sA + s * A_STAGE, &tmA, &full[s], cb * CV_KE, x0 + dx, y0 + dy, img, kEvictNormal);
+            tma_load_2d(sB + s * B_STAGE, &tmB, &full[s], kb * CV_KE, n0, kEvictLast);
+          }
         }
       }
     }
@@ -146,14 +169,18 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tcgen05_fence_after();
         const uint32_t d_tmem = tmem_base + acc * NT;
         for (int kb = 0; kb < g.kblocks; ++kb, ++it) {
-          const uint32_t s = it % CV_STAGES, ph = (it / CV_STAGES) & 1;
+          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
           mbar_wait(&full[s], ph);
           tcgen05_fence_after();
-          const uint64_t adesc = umma_desc_sw128(smem_u32(sA + s * CV_A_BYTES), 16, 1024);
-          const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + s * B_BYTES), 16, 1024);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)  // K = 16 fp16 = 32 bytes (>> 4 = 2) per instruction inside the swizzle row
-            umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          for (int dyi = 0; dyi < (TALL ? 3 : 1); ++dyi) {
+            // tall mode: the tile of tap dy starts dyi pixel rows (16 pixels x 128 B) into the box
+            const uint64_t adesc = umma_desc_sw128(smem_u32(sA + s * A_STAGE + dyi * (CV_TW * 128)), 16, 1024);
+            const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + s * B_STAGE + dyi * B_BYTES), 16, 1024);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)  // K = 16 fp16 = 32 bytes (>> 4 = 2) per instruction inside the swizzle row
+              umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | dyi | k) != 0);
+          }
           umma_commit(&empty[s]);
         }
         umma_commit(&tfull[acc]);
@@ -363,22 +390,22 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 }
 
 // ------------------------------------------------------------------------------------------------ host
-template <int NT, int EPI>
+template <int NT, int EPI, bool TALL = false>
 static wm_status launch_conv(cudaStream_t st, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, ConvArgs g) {
   int sms = 0;
   WM_TRY(require_sm100(&sms));
   static bool configured = false;
   if (!configured) {
-    WM_CUDA(cudaFuncSetAttribute(conv_kernel<NT, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, cv_smem<NT>()));
+    WM_CUDA(cudaFuncSetAttribute(conv_kernel<NT, EPI, TALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, cv_smem<NT, TALL>()));
     configured = true;
   }
   g.tiles_x = (g.W + CV_TW - 1) / CV_TW;
   g.tiles_y = (g.H + CV_TH - 1) / CV_TH;
   g.n_tiles = g.Cout / NT;
   g.total_tiles = g.n * g.tiles_x * g.tiles_y * g.n_tiles;
-  g.kblocks = g.taps * (g.Cin / CV_KE);
+  g.kblocks = (TALL ? 3 : g.taps) * (g.Cin / CV_KE);
   const int grid = g.total_tiles < sms ? g.total_tiles : sms;
-  return launch_pdl(conv_kernel<NT, EPI>, dim3(grid), dim3(CV_THREADS), cv_smem<NT>(), st, ta, tb, tc, g);
+  return launch_pdl(conv_kernel<NT, EPI, TALL>, dim3(grid), dim3(CV_THREADS), cv_smem<NT, TALL>(), st, ta, tb, tc, g);
 }
 
 static wm_status conv_check(const void* in, const void* w, int n, int H, int W, int Cin, int Cout, int taps) {
@@ -399,13 +426,15 @@ wm_status conv2d_nhwc(cudaStream_t st, const void* in, int n, int H, int W, int 
   const CUtensorMapDataType f16 = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   const int NT = Cout == 128 ? 128 : 256;
   CUtensorMap ta, tb, tc;
-  WM_TRY(tmap_nhwc(&ta, f16, 2, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
+  const bool tall = NT == 128 && taps == 9;
+  WM_TRY(tmap_nhwc(&ta, f16, 2, in, n, H, W, Cin, CV_KE, CV_TW, tall ? CV_TH + 2 : CV_TH));
   WM_TRY(tmap_2d(&tb, f16, 2, weight, Cout, (uint64_t)taps * Cin, (uint64_t)taps * Cin, CV_KE, NT));
   WM_TRY(tmap_nhwc(&tc, f16, 2, out, n, H, W, Cout, 64, CV_TW, CV_TH));
   ConvArgs g{};
   g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = Cout, g.taps = taps;
   g.bias = bias, g.res1 = res1, g.res1_bcast = res1_bcast;
   g.res2 = static_cast<const __half*>(res2), g.relu = relu;
+  if (tall) return launch_conv<128, EPI_STORE, true>(st, ta, tb, tc, g);
   return NT == 128 ? launch_conv<128, EPI_STORE>(st, ta, tb, tc, g) : launch_conv<256, EPI_STORE>(st, ta, tb, tc, g);
 }
 
@@ -417,12 +446,12 @@ wm_status conv2d_final(cudaStream_t st, const void* in, int n, int H, int W, int
   WM_CHECK(b1 && w2 && b2 && pred && conf && (od == 2 || od == 4) && act >= ACT_EXP && act <= ACT_NORM, "conv2d_final: bad argument");
   const CUtensorMapDataType f16 = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   CUtensorMap ta, tb;
-  WM_TRY(tmap_nhwc(&ta, f16, 2, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH));
+  WM_TRY(tmap_nhwc(&ta, f16, 2, in, n, H, W, Cin, CV_KE, CV_TW, CV_TH + 2));
   WM_TRY(tmap_2d(&tb, f16, 2, w1, 32, (uint64_t)9 * Cin, (uint64_t)9 * Cin, CV_KE, 32));
   ConvArgs g{};
   g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = 32, g.taps = 9;
   g.bias = b1, g.w2 = w2, g.b2 = b2, g.od = od, g.act = act, g.pred = pred, g.conf = conf;
-  return launch_conv<32, EPI_FINAL>(st, ta, tb, ta, g);
+  return launch_conv<32, EPI_FINAL, true>(st, ta, tb, ta, g);
 }
 
 // gs_renderer.gs_head (models/rasterization.py:149-153): conv3x3(Cin -> 256, bias optional) + ReLU + conv1x1(256 -> od) + b2,
