@@ -287,25 +287,26 @@ def run_b200(args):
         shapes.update({"gs_depth": (1, n_local, SIZE, SIZE, 1), "gs_depth_conf": (1, n_local, SIZE, SIZE)})
     host_out = {k: torch.empty(v, dtype=torch.float32).pin_memory() for k, v in shapes.items()}
     d2h_bytes = sum(t.numel() * 4 for t in host_out.values())
-    # the merged splats of the scene (one result, identical on every rank): rank 0 reads them back, K rows of 14 floats
+    # the merged splats of the scene (one result, identical on every rank): rank 0 reads them back (N-row buffers of 14
+    # floats per row, the first K rows valid)
     splat_rows = n_total * SIZE * SIZE
     splat_host = ({k: torch.empty((splat_rows,) + shp, dtype=torch.float32).pin_memory()
                    for k, shp in (("means", (3,)), ("sh", (1, 3)), ("opacities", ()), ("scales", (3,)), ("quats", (4,)))}
                   if gs_on and rank == 0 else None)
     splat_bytes = [0]
+    all_host = dict(host_out)
+    if splat_host is not None:
+        all_host.update({"splats." + k: t for k, t in splat_host.items()})
 
     def step_e2e():
         x = imgs_host.to(dev, non_blocking=True)
         pri = priors_now() if args.priors else None
         if heads_on:
-            preds = full({"img": x}, cond_flags=flags, priors=pri)
-            for k, t in host_out.items():
-                t.copy_(preds[k], non_blocking=True)
+            # every prediction goes to its pinned buffer on a copy stream as soon as its head has finished; the merged
+            # splats are read back as N-row buffers (the voxel count K is known on the host only at the end)
+            preds = full({"img": x}, cond_flags=flags, priors=pri, host_out=all_host)
             if splat_host is not None:
-                K = preds["splats"]["means"][0].shape[0]
-                for k, t in splat_host.items():
-                    t[:K].copy_(preds["splats"][k][0], non_blocking=True)
-                splat_bytes[0] = K * 14 * 4
+                splat_bytes[0] = sum(t.numel() * 4 for t in splat_host.values())
         else:
             outs, _ = model(x, pri, cond_flags=flags)
             host_out["cam_tokens"].copy_(outs[-1][:, :, 0], non_blocking=True)

@@ -457,9 +457,11 @@ class B200GaussianSplatRenderer(torch.nn.Module):
                                 out["opacities"].data_ptr(), out["sh"].data_ptr(), out["weights"].data_ptr()))
         return out
 
-    def prune_gs(self, splats, voxel_size=None):
+    def prune_gs(self, splats, voxel_size=None, defer: bool = False):
         """rasterization.py:301-387 for one scene (tensors over N splats) -> tensors over the K occupied voxels, ascending
-        flat voxel index.  One host read (K) at the end, as the reference's `len(unique_voxels)`."""
+        flat voxel index.  One host read (K) at the end, as the reference's `len(unique_voxels)`; defer=True returns the
+        N-row buffers and the device-side count instead, so that the caller can keep launching work and read K later
+        (`finish_prune`)."""
         lib = capi.lib()
         vs = self.voxel_size if voxel_size is None else voxel_size
         m = splats["means"]
@@ -476,20 +478,35 @@ class B200GaussianSplatRenderer(torch.nn.Module):
                                        splats["weights"].data_ptr(), float(vs), self._ws.data_ptr(), self._ws.numel(),
                                        out["means"].data_ptr(), out["quats"].data_ptr(), out["scales"].data_ptr(),
                                        out["opacities"].data_ptr(), out["sh"].data_ptr(), count.data_ptr()))
+        return (out, count) if defer else self.finish_prune(out, count)
+
+    @staticmethod
+    def finish_prune(out, count):
         K = int(count.item())
         res = {k: v[:K] for k, v in out.items()}
         res["sh"] = res["sh"].reshape(K, 1, 3)
         return res
 
+    def finish(self, predictions):
+        """Second half of render(..., defer=True): read the voxel counts (host sync) and slice the merged splats."""
+        pending = predictions.pop("splats_pending", None)
+        if pending is not None:
+            merged = [self.finish_prune(out, count) for out, count in pending]
+            predictions["splats"] = {k: [m[k] for m in merged] for k in ("means", "sh", "opacities", "scales", "quats")}
+        return predictions
+
     # ------------------------------------------------------------------ reference entry point
     @torch.no_grad()
-    def render(self, gs_feats, images, predictions, views=None, context_predictions=None, rasterize: bool = False):
+    def render(self, gs_feats, images, predictions, views=None, context_predictions=None, rasterize: bool = False,
+               defer: bool = False):
         """gs_feats [B, S, 128, H, W] (as B200DPTHead(is_gsdpt=True) returns it), images [B, S, 3, H, W], predictions with
         `camera_params` [B, S, 9] and `gs_depth` [B, S, H, W, 1].  Adds predictions["splats"]: with pruning a dict of
         per-scene lists (means [K,3], sh [K,1,3], opacities [K], scales [K,3], quats [K,4]), as rasterization.py:381-386;
         without, the prepare_splats dict batched over B.  rasterize=True additionally renders every view from its predicted
         camera in chunks of four, as the reference does before it drops the images (rasterization.py:221-241), and keeps
-        them as predictions["rendered_colors" | "rendered_depths" | "rendered_alphas"] [B, S, H, W, 3 | 1 | 1]."""
+        them as predictions["rendered_colors" | "rendered_depths" | "rendered_alphas"] [B, S, H, W, 3 | 1 | 1].
+        defer=True (pruning only): no host read here; predictions["splats_pending"] holds the N-row buffers and device
+        counts until `finish(predictions)` turns them into predictions["splats"]."""
         if not self._loaded:
             raise RuntimeError("B200GaussianSplatRenderer: load_state_dict() has not been called")
         if context_predictions is not None:
@@ -511,7 +528,9 @@ class B200GaussianSplatRenderer(torch.nn.Module):
                     sp[k] = torch.cat(parts, dim=0)
             sp["gs_feats"] = raw.reshape(-1, 12)
             scenes.append(sp)
-        if self.enable_prune:
+        if self.enable_prune and defer and not rasterize:
+            predictions["splats_pending"] = [self.prune_gs(sp, defer=True) for sp in scenes]
+        elif self.enable_prune:
             merged = [self.prune_gs(sp) for sp in scenes]
             predictions["splats"] = {k: [m[k] for m in merged] for k in ("means", "sh", "opacities", "scales", "quats")}
             if rasterize:
@@ -596,7 +615,11 @@ class B200WorldMirror(torch.nn.Module):
         return cls(agg, cam, heads["depth_head"], heads["pts_head"], heads["norm_head"], gs_head, gs_renderer)
 
     @torch.no_grad()
-    def forward(self, views, cond_flags=(0, 0, 0), priors=None):
+    def forward(self, views, cond_flags=(0, 0, 0), priors=None, host_out=None):
+        """host_out: optional dict of PINNED host tensors keyed by prediction name (and "splats.means" | "splats.sh" |
+        "splats.opacities" | "splats.scales" | "splats.quats", sized for views * H * W rows of one scene): every prediction is
+        copied to its buffer on a copy stream as soon as the head that produces it has finished, underneath the heads
+        that are still running; the call returns after enqueueing, the caller synchronises the current stream."""
         imgs = views["img"]
         if sum(cond_flags) > 0:
             if priors is None:  # worldmirror.py:136-138: priors come from the views dictionary
@@ -608,6 +631,21 @@ class B200WorldMirror(torch.nn.Module):
             token_list, psi = self.visual_geometry_transformer(imgs)
         preds = {}
         main = torch.cuda.current_stream(imgs.device)
+        copy = None
+        if host_out is not None:
+            if getattr(self, "_copy", None) is None or self._copy.device != imgs.device:
+                self._copy = torch.cuda.Stream(device=imgs.device)
+            copy = self._copy
+
+        def emit(name, t):
+            if copy is None or name not in host_out:
+                return
+            copy.wait_stream(main)
+            with torch.cuda.stream(copy):
+                dst = host_out[name]
+                dst.view(-1)[:t.numel()].copy_(t.reshape(-1), non_blocking=True)
+            t.record_stream(copy)
+
         side = None
         if self.cam_head is not None:
             # The camera head is a chain of ~137 tiny kernels (latency-bound), the DPT heads are throughput-bound: run the
@@ -618,17 +656,33 @@ class B200WorldMirror(torch.nn.Module):
             side.wait_stream(main)
             with torch.cuda.stream(side):
                 preds["camera_params"] = self._camera(token_list)
+        if self.enable_gs:
+            # the Gaussian branch goes first: its splats are the largest result, so their read-back (and the host read of
+            # the voxel count) overlaps the three remaining DPT heads
+            if self.cam_head is None:
+                raise RuntimeError("the Gaussian branch positions its splats with the predicted cameras: cam_head is required")
+            gs_feat, preds["gs_depth"], preds["gs_depth_conf"] = self.gs_head(token_list, images=imgs, patch_start_idx=psi)
+            emit("gs_depth", preds["gs_depth"])
+            emit("gs_depth_conf", preds["gs_depth_conf"])
+            main.wait_stream(side)
+            preds["camera_params"].record_stream(main)
+            emit("camera_params", preds["camera_params"])
+            preds = self.gs_renderer.render(gs_feats=gs_feat, images=imgs, predictions=preds, views=views, defer=True)
+            del gs_feat
+            if "splats_pending" in preds and len(preds["splats_pending"]) == 1:
+                for k, t in preds["splats_pending"][0][0].items():
+                    emit("splats." + k, t)
         for name, head in (("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head)):
             if head is not None:
                 preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
-        gs_feat = None
-        if self.enable_gs:
-            gs_feat, preds["gs_depth"], preds["gs_depth_conf"] = self.gs_head(token_list, images=imgs, patch_start_idx=psi)
-        if side is not None:
+                emit(name, preds[name])
+                emit(name + "_conf", preds[name + "_conf"])
+        if side is not None and not self.enable_gs:
             main.wait_stream(side)
             preds["camera_params"].record_stream(main)
+            emit("camera_params", preds["camera_params"])
         if self.enable_gs:
-            if self.cam_head is None:
-                raise RuntimeError("the Gaussian branch positions its splats with the predicted cameras: cam_head is required")
-            preds = self.gs_renderer.render(gs_feats=gs_feat, images=imgs, predictions=preds, views=views)
+            preds = self.gs_renderer.finish(preds)
+        if copy is not None:
+            main.wait_stream(copy)
         return preds

@@ -357,3 +357,31 @@ def test_worldmirror_batch_of_scenes(state_dict_full):
         for b in range(2):
             assert torch.equal(both["splats"][k][b], singles[b]["splats"][k][0]), (k, b)
     assert not torch.equal(both["depth"][0], both["depth"][1])
+
+
+def test_forward_streams_predictions_to_pinned_host_buffers(state_dict_full):
+    """forward(..., host_out=...): every prediction lands in its pinned buffer (copied on a side stream underneath the
+    remaining heads) and equals the returned device tensors; the splat buffers carry K valid rows."""
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    model = heads.B200WorldMirror.from_state_dicts(state_dict_full, hsd)
+    S, h, w = 2, 56, 70
+    imgs = torch.rand(1, S, 3, h, w, generator=torch.Generator().manual_seed(13)).cuda()
+    N = S * h * w
+    shapes = {"camera_params": (1, S, 9), "depth": (1, S, h, w, 1), "depth_conf": (1, S, h, w), "pts3d": (1, S, h, w, 3),
+              "pts3d_conf": (1, S, h, w), "normals": (1, S, h, w, 3), "normals_conf": (1, S, h, w), "gs_depth": (1, S, h, w, 1),
+              "gs_depth_conf": (1, S, h, w), "splats.means": (N, 3), "splats.sh": (N, 1, 3), "splats.opacities": (N,),
+              "splats.scales": (N, 3), "splats.quats": (N, 4)}
+    host = {k: torch.full(v, float("nan")).pin_memory() for k, v in shapes.items()}
+    for _ in range(2):  # twice: the copy stream and the buffers are reused
+        preds = model({"img": imgs}, host_out=host)
+        torch.cuda.current_stream().synchronize()
+    for k in shapes:
+        if k.startswith("splats."):
+            ref = preds["splats"][k[7:]][0].cpu()
+            K = ref.shape[0]
+            assert 0 < K <= N and torch.equal(host[k][:K], ref), k
+        else:
+            assert torch.equal(host[k], preds[k].cpu()), k
+    plain = model({"img": imgs})
+    torch.cuda.synchronize()
+    assert torch.equal(plain["depth"], preds["depth"]) and torch.equal(plain["splats"]["means"][0], preds["splats"]["means"][0])
