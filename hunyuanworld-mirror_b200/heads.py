@@ -511,12 +511,26 @@ class B200GaussianSplatRenderer(torch.nn.Module):
             raise RuntimeError("B200GaussianSplatRenderer: load_state_dict() has not been called")
         if context_predictions is not None:
             raise NotImplementedError("context_predictions (training-time scale alignment) is not part of the inference path")
+        raws = self.parameters_of(gs_feats, images, views)
+        return self.assemble(raws, images, predictions, views, rasterize=rasterize, defer=defer)
+
+    def parameters_of(self, gs_feats, images, views=None):
+        """First half of render: the parameter head on every scene's context views -> list of raw [S, H, W, 12] (needs
+        neither the cameras nor gs_depth, so `B200WorldMirror` can launch it before the camera head has finished)."""
+        if not self._loaded:
+            raise RuntimeError("B200GaussianSplatRenderer: load_state_dict() has not been called")
         B, S_all = images.shape[:2]
         S = int(views["context_nums"]) if views is not None and "context_nums" in views else S_all
         feat = gs_feats.permute(0, 1, 3, 4, 2)  # back to channels-last: a view when it came from B200DPTHead
+        return [self.gs_head(feat[b, :S]) for b in range(B)]
+
+    def assemble(self, raws, images, predictions, views=None, rasterize: bool = False, defer: bool = False):
+        """Second half of render: prepare_splats, the gather across ranks when views are sharded, the voxel merge."""
+        B = images.shape[0]
+        S = raws[0].shape[0]
         scenes = []
         for b in range(B):
-            raw = self.gs_head(feat[b, :S])
+            raw = raws[b]
             sp = self.prepare_splats(raw, images[b, :S], predictions["gs_depth"][b, :S], predictions["camera_params"][b, :S])
             if self.sharded:  # views are sharded over ranks: every rank needs all splats of the scene
                 import torch.distributed as dist
@@ -637,10 +651,10 @@ class B200WorldMirror(torch.nn.Module):
                 self._copy = torch.cuda.Stream(device=imgs.device)
             copy = self._copy
 
-        def emit(name, t):
+        def emit(name, t, src=None):
             if copy is None or name not in host_out:
                 return
-            copy.wait_stream(main)
+            copy.wait_stream(main if src is None else src)
             with torch.cuda.stream(copy):
                 dst = host_out[name]
                 dst.view(-1)[:t.numel()].copy_(t.reshape(-1), non_blocking=True)
@@ -657,31 +671,41 @@ class B200WorldMirror(torch.nn.Module):
             with torch.cuda.stream(side):
                 preds["camera_params"] = self._camera(token_list)
         if self.enable_gs:
-            # the Gaussian branch goes first: its splats are the largest result, so their read-back (and the host read of
-            # the voxel count) overlaps the three remaining DPT heads
+            # The Gaussian branch goes first.  Its DPT head and the parameter head need no camera: they run on the main
+            # stream.  Everything that does (prepare_splats, the gather across ranks, the voxel merge) continues on the side
+            # stream behind the camera head, so the main stream never waits for the camera, and the splats - the largest
+            # result - are merged and read back underneath the three remaining DPT heads.
             if self.cam_head is None:
                 raise RuntimeError("the Gaussian branch positions its splats with the predicted cameras: cam_head is required")
             gs_feat, preds["gs_depth"], preds["gs_depth_conf"] = self.gs_head(token_list, images=imgs, patch_start_idx=psi)
             emit("gs_depth", preds["gs_depth"])
             emit("gs_depth_conf", preds["gs_depth_conf"])
-            main.wait_stream(side)
-            preds["camera_params"].record_stream(main)
-            emit("camera_params", preds["camera_params"])
-            preds = self.gs_renderer.render(gs_feats=gs_feat, images=imgs, predictions=preds, views=views, defer=True)
+            raws = self.gs_renderer.parameters_of(gs_feat, imgs, views)
             del gs_feat
-            if "splats_pending" in preds and len(preds["splats_pending"]) == 1:
-                for k, t in preds["splats_pending"][0][0].items():
-                    emit("splats." + k, t)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                for t in raws + [preds["gs_depth"], imgs]:
+                    t.record_stream(side)
+                emit("camera_params", preds["camera_params"], src=side)
+                preds = self.gs_renderer.assemble(raws, imgs, preds, views, defer=True)
+                if "splats_pending" in preds and len(preds["splats_pending"]) == 1:
+                    for k, t in preds["splats_pending"][0][0].items():
+                        emit("splats." + k, t, src=side)
+            del raws
         for name, head in (("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head)):
             if head is not None:
                 preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
                 emit(name, preds[name])
                 emit(name + "_conf", preds[name + "_conf"])
-        if side is not None and not self.enable_gs:
+        if side is not None:
             main.wait_stream(side)
             preds["camera_params"].record_stream(main)
-            emit("camera_params", preds["camera_params"])
+            if not self.enable_gs:
+                emit("camera_params", preds["camera_params"])
         if self.enable_gs:
+            for out, count in preds.get("splats_pending", []):
+                for t in list(out.values()) + [count]:
+                    t.record_stream(main)
             preds = self.gs_renderer.finish(preds)
         if copy is not None:
             main.wait_stream(copy)
