@@ -18,7 +18,7 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIBDIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIBDIR, "libwm_b200.so")
-SOURCES = ["gemm.cu", "attn.cu", "attn_split.cu", "rowops.cu", "conv.cu", "headops.cu", "camhead.cu", "priors.cu", "splat.cu", "raster.cu", "capi.cu"]
+SOURCES = ["gemm.cu", "attn.cu", "attn_split.cu", "rowops.cu", "conv.cu", "headops.cu", "camhead.cu", "priors.cu", "splat.cu", "raster.cu", "loader.cu", "capi.cu"]
 HEADERS = ["common.cuh", "ptx.cuh", "ops.cuh", "attn_common.cuh", os.path.join(ROOT, "include", "wm_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--shared",
               "-Xcompiler", "-fPIC"]

@@ -91,6 +91,8 @@ SIGNATURES = {
     "wm_raster_workspace_bytes": (C.c_int, [C.c_longlong, C.c_longlong, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "wm_raster_render": (C.c_int, [_vp, _fp, _fp, _fp, _vp, _vp, _fp, _fp, _i, C.c_longlong, _i, _i, C.c_longlong, _vp, C.c_size_t,
                                    _vp, _fp, _fp, _fp]),
+    "wm_load_image_workspace_bytes": (C.c_int, [_i, _i, _i, _i, C.POINTER(C.c_size_t)]),
+    "wm_load_image": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _fp, _vp, C.c_size_t]),
     "wm_pack_bf16": (C.c_int, [_vp, _fp, C.c_longlong, _i, _i, _vp]),
 }
 

@@ -1074,6 +1074,18 @@ wm_status wm_raster_render(wm_stream stream, const float* means2d, const float* 
                        workspace, workspace_bytes, offsets, out_rgb, out_depth, out_alpha);
 }
 
+wm_status wm_load_image_workspace_bytes(int H, int W, int new_w, int new_h, size_t* bytes) {
+  return load_image_workspace_bytes(H, W, new_w, new_h, bytes);
+}
+
+wm_status wm_load_image(wm_stream stream, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top, int crop_h,
+                        int out_H, int out_W, int pad_top, int pad_left, float* out, void* workspace, size_t workspace_bytes) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return load_image(static_cast<cudaStream_t>(stream), rgb, H, W, new_w, new_h, crop_top, crop_h, out_H, out_W, pad_top, pad_left, out,
+                    workspace, workspace_bytes);
+}
+
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
   int sms;
   WM_TRY(require_sm100(&sms));

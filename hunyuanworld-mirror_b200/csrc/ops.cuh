@@ -76,6 +76,10 @@ wm_status raster_render(cudaStream_t st, const float* means2d, const float* coni
                         const unsigned* cum, const float* opacities, const float* sh, int C, long long N, int W, int H,
                         long long n_isects, void* workspace, size_t workspace_bytes, unsigned* offsets, float* out_rgb,
                         float* out_depth, float* out_alpha);
+// image loader (loader.cu)
+wm_status load_image_workspace_bytes(int H, int W, int new_w, int new_h, size_t* bytes);
+wm_status load_image(cudaStream_t st, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top, int crop_h, int out_H,
+                     int out_W, int pad_top, int pad_left, float* out, void* workspace, size_t workspace_bytes);
 wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);
 
 }  // namespace wm

@@ -307,6 +307,15 @@ wm_status wm_raster_render(wm_stream stream, const float* means2d, const float* 
                            long long n_isects, void* workspace, size_t workspace_bytes, unsigned* offsets, float* out_rgb,
                            float* out_depth, float* out_alpha);
 
+/* ---- image loader: prepare_images_to_tensor (src/utils/inference_utils.py:187-248) ---- */
+/* from the decoded image on: Pillow's Image.resize((new_w, new_h), BICUBIC) (bit-exact: two separable passes, 22-bit
+ * fixed-point coefficients, uint8 intermediate), torchvision's ToTensor (/ 255), the centre crop (rows [crop_top,
+ * crop_top + crop_h) of the resized image) and the constant-1.0 padding: the result is placed at (pad_top, pad_left) of
+ * out [3, out_H, out_W] fp32.  rgb: device uint8 [H, W, 3].  workspace: wm_load_image_workspace_bytes. */
+wm_status wm_load_image_workspace_bytes(int H, int W, int new_w, int new_h, size_t* bytes);
+wm_status wm_load_image(wm_stream stream, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top, int crop_h,
+                        int out_H, int out_W, int pad_top, int pad_left, float* out, void* workspace, size_t workspace_bytes);
+
 #ifdef __cplusplus
 }
 #endif
