@@ -21,7 +21,9 @@
 //                    border tile that fall outside the image are clipped by the store);
 //   NT = 32 (final): relu(acc + bias) -> 1x1 conv (32 -> od) -> activate_head -> fp32 prediction + confidence;
 //   NT = 256 (project): relu(acc + bias) -> 1x1 conv (256 -> od <= 16) + bias, raw fp32 [pixels, od]: the Gaussian
-//                    parameter head `gs_renderer.gs_head` (models/rasterization.py:149-153), hidden map never stored.
+//                    parameter head `gs_renderer.gs_head` (models/rasterization.py:149-153).  The hidden map never leaves
+//                    tensor memory: the epilogue rewrites it as fp16 in place and a second MMA (A from TMEM, W2 from
+//                    shared memory) projects it.
 #include <cuda_fp16.h>
 
 #include "common.cuh"
@@ -79,7 +81,8 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   constexpr bool FINAL = EPI == EPI_FINAL;
   constexpr bool STORE = EPI == EPI_STORE;
   static_assert(!FINAL || NT == 32, "final epilogue: 32 hidden channels");
-  static_assert(EPI != EPI_PROJECT || CV_PROJ_MAX * NT * 4 <= CV_STG_BYTES, "projection weights must fit the staging tile");
+  static_assert(EPI != EPI_PROJECT || CV_PROJ_MAX * NT * 2 <= CV_STG_BYTES, "projection weights must fit the staging tile");
+  static_assert(EPI != EPI_PROJECT || (NT % 64 == 0 && NT / 2 + CV_PROJ_MAX <= NT), "projecting epilogue reuses the accumulator columns");
   constexpr uint32_t TMEM_COLS = 2 * NT < 32 ? 32 : 2 * NT;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -93,7 +96,9 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* empty = full + CV_STAGES;
   uint64_t* tfull = empty + CV_STAGES;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* hfull = tempty + 2;   // projecting epilogue: the fp16 hidden map of accumulator i is in TMEM
+  uint64_t* d2full = hfull + 2;   // projecting epilogue: the projected columns of accumulator i are in TMEM
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(d2full + 2);
 
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
@@ -110,6 +115,8 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
       mbar_init(&tempty[i], 4);  // one arrival per epilogue warp
+      mbar_init(&hfull[i], 4);
+      mbar_init(&d2full[i], 1);
     }
     fence_barrier_init();
   }
@@ -163,12 +170,30 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_f16(128, NT);
       uint32_t it = 0, tcount = 0;
+      // projecting epilogue: out[128 x 16] = relu(hidden)[128 x NT, fp16 in TMEM] x W2^T[NT x 16, fp16 in smem], issued for
+      // the PREVIOUS tile in the middle of the current tile's main loop (its hidden map has been converted by then)
+      auto project = [&](uint32_t pc) {
+        const uint32_t pacc = pc & 1, pph = (pc >> 1) & 1;
+        mbar_wait(&hfull[pacc], pph);
+        tcgen05_fence_after();
+        constexpr uint32_t idesc2 = umma_idesc_f16(128, CV_PROJ_MAX);
+        const uint32_t base = tmem_base + pacc * NT;
+#pragma unroll
+        for (int k = 0; k < NT / 16; ++k) {  // 16 hidden channels = 8 TMEM columns of packed fp16 per step
+          const uint64_t wdesc = umma_desc_sw128(smem_u32(sC) + (k >> 2) * (CV_PROJ_MAX * 128), 16, 1024) + 2 * (k & 3);
+          umma_ts(base + NT / 2, base + k * 8, wdesc, idesc2, k != 0);
+        }
+        umma_commit(&d2full[pacc]);
+      };
       for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++tcount) {
         const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
         mbar_wait(&tempty[acc], aph ^ 1);
         tcgen05_fence_after();
         const uint32_t d_tmem = tmem_base + acc * NT;
         for (int kb = 0; kb < g.kblocks; ++kb, ++it) {
+          if constexpr (EPI == EPI_PROJECT) {
+            if (kb == g.kblocks / 2 && tcount > 0) project(tcount - 1);
+          }
           const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
           mbar_wait(&full[s], ph);
           tcgen05_fence_after();
@@ -185,6 +210,9 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         umma_commit(&tfull[acc]);
       }
+      if constexpr (EPI == EPI_PROJECT) {
+        if (tcount > 0) project(tcount - 1);
+      }
     }
     __syncwarp();
   } else if (warp >= 4) {
@@ -193,12 +221,19 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t stg = smem_u32(sC);
     uint32_t tcount = 0;
     if constexpr (EPI == EPI_PROJECT) {
-      // w2 [od, NT] -> smem [(c / 4), j, (c % 4)]: one broadcast 16-byte load feeds four FMAs of output j
-      float* ws = reinterpret_cast<float*>(sC);
-      for (int i = et; i < g.od * NT; i += 128) {
-        const int j = i / NT, c = i - j * NT;
-        ws[((c >> 2) * g.od + j) * 4 + (c & 3)] = __ldg(g.w2 + i);
+      // w2 [od, NT] fp32 -> fp16 B operand of the projecting MMA: NT / 64 k-blocks of 16 rows (outputs, zero beyond od)
+      // x 128 B in the SWIZZLE_128B K-major layout (the layout TMA would have written)
+      for (int i = et; i < (NT / 64) * CV_PROJ_MAX * 8; i += 128) {
+        const int ch = i & 7, n = (i >> 3) % CV_PROJ_MAX, kb = i / (8 * CV_PROJ_MAX);
+        uint32_t w[4] = {0u, 0u, 0u, 0u};
+        if (n < g.od) {
+          const float* src = g.w2 + (size_t)n * NT + kb * 64 + ch * 8;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) w[q] = pack_half2_sat(__ldg(src + 2 * q), __ldg(src + 2 * q + 1));
+        }
+        st_shared_v4(stg + kb * (CV_PROJ_MAX * 128) + sw128_offset(n, ch), w[0], w[1], w[2], w[3]);
       }
+      fence_proxy_async_smem();
       named_bar_sync(1, 128);
     }
     for (int tile = blockIdx.x; tile < g.total_tiles; tile += gridDim.x, ++tcount) {
@@ -255,47 +290,42 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
         }
       } else if constexpr (EPI == EPI_PROJECT) {
-        // two partial sums per output (packed fma.rn.f32x2: the 256 x od multiply-adds of a pixel would otherwise take longer
-        // to issue than the tile's MMAs; measured before: tensor pipe 50 % active, issue slots 61 %)
-        float2 o[CV_PROJ_MAX];
-#pragma unroll
-        for (int j = 0; j < CV_PROJ_MAX; ++j) o[j] = make_float2(j < g.od ? __ldg(g.b2 + j) : 0.f, 0.f);
+        // relu(acc [+ b1]) -> fp16, written back IN PLACE into the first NT / 2 columns of this accumulator (the columns a
+        // group is written to have already been read); the MMA warp multiplies it with W2 into columns [NT/2, NT/2 + 16).
+        // (The first version did the 256 x od multiply-adds per pixel on the CUDA cores with the weights broadcast from
+        // shared memory: 16 useful bytes per shared-memory wavefront, in competition with the MMA's own operand reads -
+        // tensor pipe 50 % active.)
 #pragma unroll 1
         for (int grp = 0; grp < NT / 32; ++grp) {
           uint32_t v[32];
           tmem_ld_x32(taddr + grp * 32, v);
           tmem_wait_ld();
-          if (grp == NT / 32 - 1) {
-            tcgen05_fence_before();
-            __syncwarp();
-            if ((threadIdx.x & 31) == 0) mbar_arrive(&tempty[acc]);
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
+            if (g.bias != nullptr) a += __ldg(g.bias + grp * 32 + 2 * i), b += __ldg(g.bias + grp * 32 + 2 * i + 1);
+            pk[i] = pack_half2_sat(fmaxf(a, 0.f), fmaxf(b, 0.f));
           }
-#pragma unroll
-          for (int c4 = 0; c4 < 8; ++c4) {
-            float h[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              float a = __uint_as_float(v[4 * c4 + i]);
-              if (g.bias != nullptr) a += __ldg(g.bias + grp * 32 + 4 * c4 + i);
-              h[i] = fmaxf(a, 0.f);
-            }
-            const uint32_t wrow = stg + static_cast<uint32_t>(((grp * 8 + c4) * g.od) * 16);
-#pragma unroll
-            for (int j = 0; j < CV_PROJ_MAX; ++j) {
-              if (j < g.od) {
-                uint32_t w0, w1, w2, w3;
-                ld_shared_v4(wrow + j * 16, w0, w1, w2, w3);
-                o[j] = ffma2(make_float2(__uint_as_float(w0), __uint_as_float(w1)), make_float2(h[0], h[1]), o[j]);
-                o[j] = ffma2(make_float2(__uint_as_float(w2), __uint_as_float(w3)), make_float2(h[2], h[3]), o[j]);
-              }
-            }
-          }
+          tmem_st_x16(taddr + grp * 16, pk);
         }
+        tmem_wait_st();
+        tcgen05_fence_before();
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(&hfull[acc]);
+        mbar_wait(&d2full[acc], aph);
+        tcgen05_fence_after();
+        uint32_t d2[16];
+        tmem_ld_x16(taddr + NT / 2, d2);
+        tmem_wait_ld();
+        tcgen05_fence_before();
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) mbar_arrive(&tempty[acc]);
         if (valid) {
           float* pr = g.pred + pix * g.od;
 #pragma unroll
           for (int j = 0; j < CV_PROJ_MAX; ++j)
-            if (j < g.od) pr[j] = o[j].x + o[j].y;
+            if (j < g.od) pr[j] = __uint_as_float(d2[j]) + __ldg(g.b2 + j);
         }
       } else {
 #pragma unroll 1

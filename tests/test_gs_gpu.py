@@ -85,7 +85,7 @@ def test_conv2d_project(n, H, Wd):
     capi.check(lib.wm_conv2d_project(_st(), d["x"].data_ptr(), n, H, Wd, 128, d["w1"].data_ptr(), None, d["w2"].data_ptr(),
                                      d["b2"].data_ptr(), 12, out.data_ptr()))
     torch.cuda.synchronize()
-    _close(out.cpu(), ref, f"conv2d_project {n}x{H}x{Wd}", rel=2.0 ** -11)
+    _close(out.cpu(), ref, f"conv2d_project {n}x{H}x{Wd}")  # hidden map and W2 as fp16 operands of the second MMA
 
 
 def test_prepare_splats_matches_oracle():
