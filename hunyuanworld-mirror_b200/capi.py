@@ -86,6 +86,9 @@ SIGNATURES = {
     "wm_prune_workspace_bytes": (C.c_int, [C.c_longlong, C.POINTER(C.c_size_t)]),
     "wm_prune_splats": (C.c_int, [_vp, C.c_longlong, _fp, _fp, _fp, _fp, _fp, _fp, C.c_double, _vp, C.c_size_t, _fp, _fp, _fp,
                                   _fp, _fp, _vp]),
+    "wm_conf_filter_workspace_bytes": (C.c_int, [C.c_longlong, C.POINTER(C.c_size_t)]),
+    "wm_conf_filter_splats": (C.c_int, [_vp, C.c_longlong, C.c_longlong, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _vp, C.c_size_t, _fp, _fp,
+                                        _fp, _fp, _fp, _fp]),
     "wm_raster_project": (C.c_int, [_vp, _fp, _fp, _fp, _fp, _fp, _fp, _i, C.c_longlong, _i, _i, _f, _f, _f, _fp, _fp, _fp, _vp, _vp,
                                     _vp, _vp, C.c_size_t]),
     "wm_raster_workspace_bytes": (C.c_int, [C.c_longlong, C.c_longlong, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),

@@ -1050,6 +1050,18 @@ wm_status wm_prune_splats(wm_stream stream, long long N, const float* means, con
                       workspace_bytes, out_means, out_quats, out_scales, out_opacities, out_sh, count);
 }
 
+wm_status wm_conf_filter_workspace_bytes(long long N, size_t* bytes) { return conf_filter_workspace_bytes(N, bytes); }
+
+wm_status wm_conf_filter_splats(wm_stream stream, long long N, long long K, const float* conf, const float* means, const float* quats,
+                                const float* scales, const float* opacities, const float* sh, const float* weights, void* workspace,
+                                size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
+                                float* out_sh, float* out_weights) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return conf_filter_splats(static_cast<cudaStream_t>(stream), N, K, conf, means, quats, scales, opacities, sh, weights, workspace,
+                            workspace_bytes, out_means, out_quats, out_scales, out_opacities, out_sh, out_weights);
+}
+
 wm_status wm_raster_project(wm_stream stream, const float* means, const float* quats, const float* scales, const float* opacities,
                             const float* viewmats, const float* Ks, int C, long long N, int W, int H, float near_plane,
                             float far_plane, float eps2d, float* means2d, float* conics, float* depths, int* radii, unsigned* tiles,

@@ -66,6 +66,11 @@ wm_status prune_splats(cudaStream_t st, long long N, const float* means, const f
                        const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
                        size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities, float* out_sh,
                        unsigned* count);
+wm_status conf_filter_workspace_bytes(long long N, size_t* bytes);
+wm_status conf_filter_splats(cudaStream_t st, long long N, long long K, const float* conf, const float* means, const float* quats,
+                             const float* scales, const float* opacities, const float* sh, const float* weights, void* workspace,
+                             size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
+                             float* out_sh, float* out_weights);
 // splat rasterisation (raster.cu)
 wm_status raster_project(cudaStream_t st, const float* means, const float* quats, const float* scales, const float* opacities,
                          const float* viewmats, const float* Ks, int C, long long N, int W, int H, float near_plane, float far_plane,

@@ -345,4 +345,154 @@ wm_status prune_splats(cudaStream_t st, long long N, const float* means, const f
   return WM_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ confidence filter
+// apply_confidence_filter (rasterization.py:248-299): confidences <= 1e-5 become -inf, the K most confident splats are
+// kept (torch.topk, sorted=False: its output order and its choice among equal values are unspecified).  Here the choice is
+// made deterministic: the K-th largest key is found with an exact 4-pass radix select (8 bits per pass, block-private
+// shared-memory histograms, 256 global atomics per block), equal keys are taken in ascending index, and the survivors are
+// written in ascending original index, so that the voxel merge behind it keeps accumulating in index order.
+// HBM-bound integer work: 4 x 4 B per splat for the select, 16 B for the scan, 64 B read + 64 B written per kept splat.
+struct ConfWs {
+  unsigned* state;  // [0] key prefix found so far, [1] how many are still to take among the keys matching the prefix
+  unsigned* hist;   // [4][256]
+  unsigned long long *packed, *scanned;  // low word: keys above the threshold before i; high word: keys equal to it
+  void* cub_tmp;
+  size_t cub_bytes;
+};
+
+// order-preserving key of a masked confidence: NaN (positive) sorts above +inf, as torch.topk treats it
+__device__ __forceinline__ unsigned conf_key(float c) {
+  if (c <= 1e-5f) c = -INFINITY;
+  const unsigned u = __float_as_uint(c);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__global__ void conf_init_kernel(unsigned* state, unsigned* hist, unsigned K) {
+  for (int i = threadIdx.x; i < 4 * 256; i += blockDim.x) hist[i] = 0u;
+  if (threadIdx.x == 0) state[0] = 0u, state[1] = K;
+}
+
+__global__ void __launch_bounds__(SP_THREADS)
+conf_hist_kernel(const float* __restrict__ conf, unsigned N, int pass, const unsigned* __restrict__ state, unsigned* __restrict__ hist) {
+  __shared__ unsigned s_h[256];
+  s_h[threadIdx.x] = 0u;  // SP_THREADS == 256
+  __syncthreads();
+  const int shift = 24 - 8 * pass;
+  const unsigned mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + 8)), prefix = state[0];
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const unsigned k = conf_key(__ldg(conf + i));
+    if ((k & mask) == prefix) atomicAdd(&s_h[(k >> shift) & 255u], 1u);
+  }
+  __syncthreads();
+  if (s_h[threadIdx.x]) atomicAdd(hist + pass * 256 + threadIdx.x, s_h[threadIdx.x]);
+}
+
+// the digit of this pass: the largest d with |{digit > d}| < remaining <= |{digit >= d}|
+__global__ void conf_pick_kernel(int pass, unsigned* state, const unsigned* __restrict__ hist) {
+  if (threadIdx.x != 0) return;
+  const unsigned rem = state[1];
+  unsigned acc = 0u;
+  for (int d = 255; d >= 0; --d) {
+    const unsigned h = hist[pass * 256 + d];
+    if (acc + h >= rem) {
+      state[0] |= (unsigned)d << (24 - 8 * pass);
+      state[1] = rem - acc;
+      return;
+    }
+    acc += h;
+  }
+}
+
+__global__ void __launch_bounds__(SP_THREADS)
+conf_mark_kernel(const float* __restrict__ conf, unsigned N, const unsigned* __restrict__ state, unsigned long long* __restrict__ packed) {
+  const unsigned T = state[0];
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const unsigned k = conf_key(__ldg(conf + i));
+    packed[i] = k > T ? 1ull : (k == T ? (1ull << 32) : 0ull);
+  }
+}
+
+__global__ void __launch_bounds__(SP_THREADS)
+conf_gather_kernel(const float* __restrict__ conf, unsigned N, const unsigned* __restrict__ state,
+                   const unsigned long long* __restrict__ scanned, SplatOut in, SplatOut out) {
+  const unsigned T = state[0], need = state[1];
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const unsigned k = conf_key(__ldg(conf + i));
+    if (k < T) continue;
+    const unsigned long long s = scanned[i];
+    const unsigned above = (unsigned)s, ties = (unsigned)(s >> 32);
+    if (k == T && ties >= need) continue;
+    const size_t o = (size_t)above + (ties < need ? ties : need), src = i;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      out.means[o * 3 + d] = __ldg(in.means + src * 3 + d);
+      out.scales[o * 3 + d] = __ldg(in.scales + src * 3 + d);
+      out.sh[o * 3 + d] = __ldg(in.sh + src * 3 + d);
+    }
+#pragma unroll
+    for (int d = 0; d < 4; ++d) out.quats[o * 4 + d] = __ldg(in.quats + src * 4 + d);
+    out.opacities[o] = __ldg(in.opacities + src);
+    out.weights[o] = __ldg(in.weights + src);
+  }
+}
+
+static wm_status conf_layout(unsigned N, void* base, size_t* total, ConfWs* ws) {
+  size_t scan_bytes = 0;
+  WM_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)N,
+                                        (cudaStream_t)0));
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? static_cast<char*>(base) + off : nullptr;
+    off += sp_align(bytes);
+    return p;
+  };
+  ConfWs w{};
+  w.state = static_cast<unsigned*>(take(2 * sizeof(unsigned)));
+  w.hist = static_cast<unsigned*>(take(4 * 256 * sizeof(unsigned)));
+  w.packed = static_cast<unsigned long long*>(take((size_t)N * 8));
+  w.scanned = static_cast<unsigned long long*>(take((size_t)N * 8));
+  w.cub_bytes = scan_bytes;
+  w.cub_tmp = take(scan_bytes);
+  *total = off;
+  if (ws) *ws = w;
+  return WM_OK;
+}
+
+wm_status conf_filter_workspace_bytes(long long N, size_t* bytes) {
+  WM_CHECK(N > 0 && N < (1ll << 31) && bytes, "conf_filter_workspace_bytes: bad argument");
+  return conf_layout((unsigned)N, nullptr, bytes, nullptr);
+}
+
+// N splats -> the K most confident, in ascending original index; outputs sized for K rows.
+wm_status conf_filter_splats(cudaStream_t st, long long N, long long K, const float* conf, const float* means, const float* quats,
+                             const float* scales, const float* opacities, const float* sh, const float* weights, void* workspace,
+                             size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
+                             float* out_sh, float* out_weights) {
+  WM_CHECK(N > 0 && N < (1ll << 31) && K > 0 && K <= N && conf && means && quats && scales && opacities && sh && weights && workspace &&
+               out_means && out_quats && out_scales && out_opacities && out_sh && out_weights,
+           "conf_filter_splats: bad argument");
+  ConfWs w{};
+  size_t need = 0;
+  WM_TRY(conf_layout((unsigned)N, workspace, &need, &w));
+  WM_CHECK(workspace_bytes >= need, "conf_filter_splats: workspace of %zu bytes, %zu needed", workspace_bytes, need);
+  const unsigned n = (unsigned)N;
+  const int grid = (int)std::min<size_t>(((size_t)n + SP_THREADS - 1) / SP_THREADS, 148 * 8);
+  conf_init_kernel<<<1, 256, 0, st>>>(w.state, w.hist, (unsigned)K);
+  for (int pass = 0; pass < 4; ++pass) {
+    conf_hist_kernel<<<grid, SP_THREADS, 0, st>>>(conf, n, pass, w.state, w.hist);
+    conf_pick_kernel<<<1, 32, 0, st>>>(pass, w.state, w.hist);
+  }
+  conf_mark_kernel<<<grid, SP_THREADS, 0, st>>>(conf, n, w.state, w.packed);
+  WM_LAUNCH_CHECK();
+  size_t tmp = w.cub_bytes;
+  WM_CUDA(cub::DeviceScan::ExclusiveSum(w.cub_tmp, tmp, (const unsigned long long*)w.packed, w.scanned, (int)n, st));
+  SplatOut in{const_cast<float*>(means), const_cast<float*>(quats), const_cast<float*>(scales), const_cast<float*>(opacities),
+              const_cast<float*>(sh), const_cast<float*>(weights)};
+  SplatOut out{out_means, out_quats, out_scales, out_opacities, out_sh, out_weights};
+  conf_gather_kernel<<<grid, SP_THREADS, 0, st>>>(conf, n, w.state, w.scanned, in, out);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+
 }  // namespace wm

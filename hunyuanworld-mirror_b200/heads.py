@@ -383,7 +383,8 @@ class B200GaussianSplatRenderer(torch.nn.Module):
     `render` fills `predictions["splats"]`.  The reference also rasterises every view with gsplat and then drops the
     images (rasterization.py:221-246); that dead compute is not reproduced.  Built for the configuration WorldMirror
     constructs (worldmirror.py:110-118): sh_degree 0, no offsets, residual SH, position from gs_depth + predicted camera.
-    `enable_conf_filter` (off in that configuration) is not implemented."""
+    `enable_conf_filter` (off in that configuration) drops the least confident splats before the merge
+    (`apply_confidence_filter`, rasterization.py:211-213, 248-299)."""
 
     SPLAT_KEYS = ("means", "quats", "scales", "opacities", "sh", "weights")
 
@@ -392,11 +393,13 @@ class B200GaussianSplatRenderer(torch.nn.Module):
                  render_novel_views: bool = False, enable_conf_filter: bool = False, conf_threshold_percent: float = 30.0,
                  max_gaussians: int = 5000000, debug=False, sharded: bool = False, group=None):
         super().__init__()
-        if feature_dim != 256 or sh_degree != 0 or predict_offset or not predict_residual_sh or enable_conf_filter:
+        if feature_dim != 256 or sh_degree != 0 or predict_offset or not predict_residual_sh:
             raise NotImplementedError("B200GaussianSplatRenderer covers WorldMirror's configuration: feature_dim 256, "
-                                      "sh_degree 0, no offsets, residual SH, no confidence filter")
+                                      "sh_degree 0, no offsets, residual SH")
         self.feature_dim, self.sh_degree, self.nums_sh = feature_dim, sh_degree, 1
         self.enable_prune, self.voxel_size = enable_prune, voxel_size
+        self.enable_conf_filter, self.conf_threshold_percent, self.max_gaussians = enable_conf_filter, conf_threshold_percent, max_gaussians
+        self._fws = None
         self.sharded, self.group = sharded, group  # views sharded over the ranks of `group` (None: the default group)
         self.w: Dict[str, torch.Tensor] = {}
         self._loaded = False
@@ -456,6 +459,37 @@ class B200GaussianSplatRenderer(torch.nn.Module):
                                 out["means"].data_ptr(), out["quats"].data_ptr(), out["scales"].data_ptr(),
                                 out["opacities"].data_ptr(), out["sh"].data_ptr(), out["weights"].data_ptr()))
         return out
+
+    def apply_confidence_filter(self, splats, conf):
+        """rasterization.py:248-299 for one scene: splats over N rows, conf with N elements (view-major, the splat order) ->
+        the K = max(1, min(max_gaussians, ceil(N (100 - p) / 100))) most confident, confidences <= 1e-5 counting as -inf.
+        The reference's torch.topk(sorted=False) leaves order and tie choice open; here ties go to the lower index and the
+        survivors keep their original order (exact radix select, no host read: K follows from N).  Keys outside
+        `mask_keys` pass through untouched, as in the reference."""
+        if not self.enable_conf_filter or conf is None:
+            return splats
+        lib = capi.lib()
+        m = splats["means"]
+        N, dev = m.shape[0], m.device
+        conf = conf.to(dev, torch.float32).reshape(-1).contiguous()
+        if conf.numel() != N:
+            raise RuntimeError(f"apply_confidence_filter: {conf.numel()} confidences for {N} splats")
+        p = self.conf_threshold_percent
+        keep = int(math.ceil(N * (100.0 - p) / 100.0)) if p > 0 else N
+        K = max(1, min(self.max_gaussians, keep))
+        need = C.c_size_t(0)
+        capi.check(lib.wm_conf_filter_workspace_bytes(N, C.byref(need)))
+        if self._fws is None or self._fws.numel() < need.value or self._fws.device != dev:
+            self._fws = torch.empty(need.value, dtype=torch.uint8, device=dev)
+        src = {k: splats[k].contiguous() for k in self.SPLAT_KEYS}
+        out = {k: torch.empty((K,) + tuple(src[k].shape[1:]), dtype=torch.float32, device=dev) for k in self.SPLAT_KEYS}
+        LAUNCHES[0] += 12  # init, 4 x (histogram, pick), mark, scan (CUB, counted once), gather
+        capi.check(lib.wm_conf_filter_splats(_st(), N, K, conf.data_ptr(), src["means"].data_ptr(), src["quats"].data_ptr(),
+                                             src["scales"].data_ptr(), src["opacities"].data_ptr(), src["sh"].data_ptr(),
+                                             src["weights"].data_ptr(), self._fws.data_ptr(), self._fws.numel(),
+                                             out["means"].data_ptr(), out["quats"].data_ptr(), out["scales"].data_ptr(),
+                                             out["opacities"].data_ptr(), out["sh"].data_ptr(), out["weights"].data_ptr()))
+        return {k: out.get(k, v) for k, v in splats.items()}
 
     def prune_gs(self, splats, voxel_size=None, defer: bool = False):
         """rasterization.py:301-387 for one scene (tensors over N splats) -> tensors over the K occupied voxels, ascending
@@ -541,6 +575,13 @@ class B200GaussianSplatRenderer(torch.nn.Module):
                     dist.all_gather(parts, sp[k], group=self.group)
                     sp[k] = torch.cat(parts, dim=0)
             sp["gs_feats"] = raw.reshape(-1, 12)
+            if self.enable_conf_filter and "depth_conf" in predictions:  # rasterization.py:211-213 (the depth head's confidence)
+                conf = predictions["depth_conf"][b, :S].to(torch.float32).contiguous()
+                if self.sharded:
+                    parts = [torch.empty_like(conf) for _ in range(world)]
+                    dist.all_gather(parts, conf, group=self.group)
+                    conf = torch.cat(parts, dim=0)
+                sp = self.apply_confidence_filter(sp, conf)
             scenes.append(sp)
         if self.enable_prune and defer and not rasterize:
             predictions["splats_pending"] = [self.prune_gs(sp, defer=True) for sp in scenes]
@@ -682,9 +723,14 @@ class B200WorldMirror(torch.nn.Module):
             emit("gs_depth_conf", preds["gs_depth_conf"])
             raws = self.gs_renderer.parameters_of(gs_feat, imgs, views)
             del gs_feat
+            if self.gs_renderer.enable_conf_filter and self.depth_head is not None:
+                # the confidence filter reads the depth head's confidence (rasterization.py:211-213): that head goes first
+                preds["depth"], preds["depth_conf"] = self.depth_head(token_list, images=imgs, patch_start_idx=psi)
+                emit("depth", preds["depth"])
+                emit("depth_conf", preds["depth_conf"])
             side.wait_stream(main)
             with torch.cuda.stream(side):
-                for t in raws + [preds["gs_depth"], imgs]:
+                for t in raws + [preds["gs_depth"], imgs] + ([preds["depth_conf"]] if "depth_conf" in preds else []):
                     t.record_stream(side)
                 emit("camera_params", preds["camera_params"], src=side)
                 preds = self.gs_renderer.assemble(raws, imgs, preds, views, defer=True)
@@ -693,7 +739,7 @@ class B200WorldMirror(torch.nn.Module):
                         emit("splats." + k, t, src=side)
             del raws
         for name, head in (("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head)):
-            if head is not None:
+            if head is not None and name not in preds:
                 preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
                 emit(name, preds[name])
                 emit(name + "_conf", preds[name + "_conf"])

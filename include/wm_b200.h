@@ -286,6 +286,17 @@ wm_status wm_prune_splats(wm_stream stream, long long N, const float* means, con
                           size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
                           float* out_sh, unsigned* count);
 
+/* apply_confidence_filter (rasterization.py:248-299) for one scene: conf [N] (confidences <= 1e-5 count as -inf), keep the K
+ * most confident splats, K = max(1, min(max_gaussians, ceil(N * (100 - percent) / 100))) computed by the caller.  The
+ * reference takes torch.topk(sorted=False), whose order and tie choice are unspecified; here equal confidences are taken in
+ * ascending index and the K survivors come out in ascending original index (exact radix select + scan + gather).  Outputs
+ * are sized for K rows.  workspace: wm_conf_filter_workspace_bytes(N). */
+wm_status wm_conf_filter_workspace_bytes(long long N, size_t* bytes);
+wm_status wm_conf_filter_splats(wm_stream stream, long long N, long long K, const float* conf, const float* means, const float* quats,
+                                const float* scales, const float* opacities, const float* sh, const float* weights, void* workspace,
+                                size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
+                                float* out_sh, float* out_weights);
+
 /* ---- forward splat rasterisation: gsplat 1.5.3's rasterization() as the reference ---- */
 /* calls it (src/models/models/rasterization.py:29-66: pinhole, classic mode, tile 16, eps2d 0.3, SH degree 0,
  * render_mode "RGB+ED"), restated from submodules/gsplat/gsplat/cuda/csrc/{ProjectionEWA3DGSPacked,IntersectTile,

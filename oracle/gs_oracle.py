@@ -131,6 +131,33 @@ def prune_gs(splats: Dict[str, np.ndarray], voxel_size: float = 0.002) -> Dict[s
     return out
 
 
+FILTER_KEYS = ("means", "quats", "scales", "opacities", "sh", "weights")
+
+
+def conf_filter_count(n: int, percent: float = 30.0, max_gaussians: int = 5000000) -> int:
+    """K of apply_confidence_filter (rasterization.py:272-276)."""
+    keep = int(np.ceil(n * (100.0 - percent) / 100.0)) if percent > 0 else n
+    return max(1, min(max_gaussians, keep))
+
+
+def conf_filter_indices(conf: np.ndarray, percent: float = 30.0, max_gaussians: int = 5000000) -> np.ndarray:
+    """Which splats apply_confidence_filter keeps (rasterization.py:266-279), one scene: confidences <= 1e-5 become -inf,
+    the K largest survive.  torch.topk(sorted=False) leaves both the order of its result and the choice among equal values
+    unspecified; stated here deterministically: equal values in ascending index, result in ascending index."""
+    c = conf.reshape(-1).astype(np.float32).copy()
+    c[c <= np.float32(1e-5)] = -np.inf
+    K = conf_filter_count(c.shape[0], percent, max_gaussians)
+    order = np.argsort(-c, kind="stable")  # NaN last in numpy; confidences are 1 + exp(.) and never NaN
+    return np.sort(order[:K])
+
+
+def apply_confidence_filter(splats: Dict[str, np.ndarray], conf: np.ndarray, percent: float = 30.0,
+                            max_gaussians: int = 5000000) -> Dict[str, np.ndarray]:
+    """rasterization.py:248-299 for one scene: the keys of `mask_keys` gathered at the kept indices, the rest untouched."""
+    idx = conf_filter_indices(conf, percent, max_gaussians)
+    return {k: (v[idx] if k in FILTER_KEYS else v) for k, v in splats.items()}
+
+
 def synthetic_splats(n: int = 20000, seed: int = 5) -> Dict[str, np.ndarray]:
     """Seeded splats whose means cluster (many voxel collisions at voxel sizes 0.002 .. 0.05), negative coordinates
     included, a few exactly repeated points, a few zero weights."""

@@ -385,3 +385,88 @@ def test_forward_streams_predictions_to_pinned_host_buffers(state_dict_full):
     plain = model({"img": imgs})
     torch.cuda.synchronize()
     assert torch.equal(plain["depth"], preds["depth"]) and torch.equal(plain["splats"]["means"][0], preds["splats"]["means"][0])
+
+
+# ---------------------------------------------------------------------------------------------- confidence filter
+def _filter_renderer(percent, max_gaussians=5000000):
+    return heads.B200GaussianSplatRenderer(sh_degree=0, predict_offset=False, predict_residual_sh=True, enable_prune=True, voxel_size=0.01,
+                                           enable_conf_filter=True, conf_threshold_percent=percent, max_gaussians=max_gaussians)
+
+
+def test_conf_filter_matches_reference_and_oracle():
+    """`apply_confidence_filter` on the GPU: the kept rows are exactly the reference's kept set (fixture from the real
+    reference, tests/golden/make_golden_conf.py) in ascending index, bit-equal to the oracle's gather; filter -> prune is
+    bit-equal to the oracle and equal to the reference's result to fp32 rounding (its accumulation order is unspecified)."""
+    cfx = np.load(os.path.join(GOLDEN, "conf_filter.npz"))
+    syn = G.synthetic_splats(int(cfx["n_syn"]))
+    dev = {k: torch.from_numpy(v).cuda() for k, v in syn.items()}
+    conf = torch.from_numpy(cfx["conf"]).cuda()
+    for i, (p, mg) in enumerate(cfx["cases"]):
+        r = _filter_renderer(float(p), int(mg))
+        out = r.apply_confidence_filter(dict(dev), conf.reshape(2, 60, 100))
+        torch.cuda.synchronize()
+        kept = cfx[f"kept{i}"]
+        for k in KEYS + ("weights",):
+            assert np.array_equal(out[k].cpu().numpy(), syn[k][kept]), (p, mg, k)
+    r = _filter_renderer(30.0)
+    merged = r.prune_gs(r.apply_confidence_filter(dict(dev), conf))
+    torch.cuda.synchronize()
+    ref = G.prune_gs(G.apply_confidence_filter(syn, cfx["conf"], 30.0), voxel_size=0.01)
+    for k in KEYS:
+        g = merged[k].cpu().numpy().reshape(ref["means"].shape[0], -1)
+        if k == "quats":
+            np.testing.assert_allclose(g, ref[k], rtol=3e-7, atol=1e-9)
+        else:
+            assert np.array_equal(g, ref[k].reshape(g.shape)), k
+        np.testing.assert_allclose(g, cfx["pruned_" + k], rtol=2e-5, atol=1e-6)
+
+
+def test_conf_filter_ties_large_and_errors():
+    """Heavy ties (confidences from 37 distinct values, a third masked) at 518-scale N: the stated rule (ties to the lower
+    index, ascending output) against the oracle, bit for bit; K = N keeps everything; wrong sizes raise."""
+    g = np.random.default_rng(21)
+    N = 2 * 518 * 518 + 13
+    conf = (1.0 + g.integers(0, 37, size=N) * 0.25).astype(np.float32)
+    conf[g.random(N) < 0.33] = 0.0
+    sp = {"means": g.normal(size=(N, 3)), "quats": g.normal(size=(N, 4)), "scales": g.random((N, 3)), "opacities": g.random(N),
+          "sh": g.normal(size=(N, 3)), "weights": g.random(N)}
+    sp = {k: v.astype(np.float32) for k, v in sp.items()}
+    dev = {k: torch.from_numpy(v).cuda() for k, v in sp.items()}
+    dev["gs_feats"] = torch.zeros(N, 12, device="cuda")
+    for p in (30.0, 50.0, 90.0, 0.0):
+        out = _filter_renderer(p).apply_confidence_filter(dict(dev), torch.from_numpy(conf).cuda())
+        torch.cuda.synchronize()
+        idx = G.conf_filter_indices(conf, p)
+        assert out["gs_feats"].shape[0] == N  # not in mask_keys: passed through (rasterization.py:282-297)
+        for k in KEYS + ("weights",):
+            assert np.array_equal(out[k].cpu().numpy(), sp[k][idx]), (p, k)
+    with pytest.raises(RuntimeError):
+        _filter_renderer(30.0).apply_confidence_filter(dict(dev), torch.ones(N - 1, device="cuda"))
+    off = _renderer()
+    assert off.apply_confidence_filter(dev, torch.from_numpy(conf).cuda()) is dev  # filter off: untouched (rasterization.py:260-261)
+
+
+def test_worldmirror_forward_with_confidence_filter(state_dict_full):
+    """`B200WorldMirror.forward` with enable_conf_filter: the depth head runs before the splat assembly, the splats are
+    the oracle's filter -> prune of the un-filtered, un-pruned splats of the same forward (bit for bit)."""
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    model = heads.B200WorldMirror.from_state_dicts(state_dict_full, hsd)
+    imgs = W.synthetic_images(2, 252, 252, seed=1).cuda()
+    r = model.gs_renderer
+    r.enable_prune = False
+    raw = model({"img": imgs})
+    torch.cuda.synchronize()
+    r.enable_prune, r.enable_conf_filter, r.conf_threshold_percent = True, True, 40.0
+    preds = model({"img": imgs})
+    torch.cuda.synchronize()
+    assert torch.equal(preds["depth_conf"], raw["depth_conf"]) and torch.equal(preds["depth"], raw["depth"])
+    sp = {k: raw["splats"][k][0].reshape(raw["splats"][k].shape[1], -1).squeeze(-1).cpu().numpy() for k in KEYS + ("weights",)}
+    ref = G.prune_gs(G.apply_confidence_filter(sp, raw["depth_conf"][0].cpu().numpy(), 40.0), 0.002)
+    K = ref["means"].shape[0]
+    assert preds["splats"]["means"][0].shape[0] == K
+    for k in KEYS:
+        g = preds["splats"][k][0].reshape(K, -1).cpu().numpy()
+        if k == "quats":
+            np.testing.assert_allclose(g, ref[k], rtol=3e-7, atol=1e-9)
+        else:
+            assert np.array_equal(g, ref[k].reshape(K, -1)), k

@@ -77,3 +77,41 @@ def test_prune_of_reference_scale_scene(fx, gs_sd, c1_tokens):
         ref = fx["pruned_" + k + "_sum"]
         got = out[k].reshape(K, -1).astype(np.float64).sum(axis=0)
         np.testing.assert_allclose(got, ref, rtol=5e-3, atol=5e-3 * float(np.abs(fx["pruned_" + k]).mean()) * K)
+
+
+# ---------------------------------------------------------------------------------------------- confidence filter
+@pytest.fixture(scope="module")
+def cfx():
+    return np.load(os.path.join(GOLDEN, "conf_filter.npz"))
+
+
+def test_conf_filter_keeps_the_reference_set(cfx):
+    """oracle `conf_filter_indices` vs the reference's apply_confidence_filter (rasterization.py:248-299) on seeded distinct
+    confidences with masked (<= 1e-5) entries: the same kept set for every (percent, max_gaussians) case."""
+    conf = cfx["conf"]
+    for i, (p, mg) in enumerate(cfx["cases"]):
+        kept = G.conf_filter_indices(conf, float(p), int(mg))
+        assert kept.shape[0] == G.conf_filter_count(conf.shape[0], float(p), int(mg))
+        assert np.array_equal(kept, cfx[f"kept{i}"]), (p, mg)
+
+
+def test_conf_filter_then_prune_matches_reference(cfx):
+    """filter -> prune_gs against the reference's result: same voxels; values to fp32 rounding (the reference accumulates a
+    voxel in torch.topk's unspecified output order, the oracle in ascending index)."""
+    syn = G.synthetic_splats(int(cfx["n_syn"]))
+    out = G.prune_gs(G.apply_confidence_filter(syn, cfx["conf"], 30.0), voxel_size=0.01)
+    for k in KEYS:
+        ref = cfx["pruned_" + k]
+        got = out[k].reshape(ref.shape[0], -1)
+        assert got.shape == ref.shape, (k, got.shape, ref.shape)
+        np.testing.assert_allclose(got, ref, rtol=2e-5, atol=1e-6)
+
+
+def test_conf_filter_ties_and_masking():
+    """Stated tie rule: equal confidences are taken in ascending index; everything <= 1e-5 ranks below every live value."""
+    conf = np.array([2.0, 3.0, 2.0, 0.0, 2.0, 1e-6, 5.0, 2.0], dtype=np.float32)
+    assert G.conf_filter_indices(conf, 50.0).tolist() == [0, 1, 2, 6]  # K = 4: 5, 3 and the first two 2.0
+    assert G.conf_filter_indices(conf, 25.0).tolist() == [0, 1, 2, 4, 6, 7]  # K = 6: all live values
+    assert G.conf_filter_indices(conf, 12.5).tolist() == [0, 1, 2, 3, 4, 6, 7]  # K = 7: the first masked one joins
+    assert G.conf_filter_indices(conf, 0.0).tolist() == list(range(8))
+    assert G.conf_filter_indices(conf, 30.0, max_gaussians=2).tolist() == [1, 6]
