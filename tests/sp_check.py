@@ -74,6 +74,20 @@ def main():
     same = all(torch.equal(outs[0][k][0], outs[1][k][0]) for k in ("means", "sh", "opacities", "scales", "quats"))
     print(f"rank {rank}: sharded voxel merge == single-GPU merge: {same} ({S * h * w} splats -> {K} voxels)", flush=True)
     ok &= same and 0 < K < S * h * w
+    # the same with the confidence filter: the depth head's confidence is gathered with the splats
+    preds["depth_conf"] = (1.0 + torch.randint(0, 50, (1, S, h, w), generator=g).float() * 0.125).to(dev)  # ties on purpose
+    outs = []
+    for sharded in (True, False):
+        r = H2.B200GaussianSplatRenderer(voxel_size=0.01, sharded=sharded, enable_conf_filter=True, conf_threshold_percent=35.0)
+        r.load_state_dict({k[len("gs_renderer."):]: v for k, v in gsd.items() if k.startswith("gs_renderer.")})
+        v = sl if sharded else slice(0, S)
+        p = {k: t[:, v].contiguous() for k, t in preds.items()}
+        outs.append(r.render(feat[:, v].permute(0, 1, 4, 2, 3), im[:, v].contiguous(), p)["splats"])
+    torch.cuda.synchronize()
+    Kf = outs[1]["means"][0].shape[0]
+    same = all(torch.equal(outs[0][k][0], outs[1][k][0]) for k in ("means", "sh", "opacities", "scales", "quats"))
+    print(f"rank {rank}: sharded filter + merge == single-GPU: {same} ({K} -> {Kf} voxels with the 35 % filter)", flush=True)
+    ok &= same and 0 < Kf < K
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()

@@ -46,3 +46,16 @@ for it in range(2):
           f"({rend.rasterizer.last['n_isects']} tile intersections in the last chunk)", flush=True)
     print(f"pass {it}: gs DPT head {ev[0].elapsed_time(ev[1]):.3f} ms, parameter head + prepare + merge {ev[1].elapsed_time(ev[2]):.3f} ms, "
           f"{n * size * size} splats -> {out['means'][0].shape[0]} voxels", flush=True)
+    # the confidence filter alone (off in WorldMirror's configuration): 30 % dropped, the depth-like confidence of this head
+    frend = H.B200GaussianSplatRenderer(enable_conf_filter=True, conf_threshold_percent=30.0)
+    N = n * size * size
+    raw = {k: torch.rand((N, d) if d > 1 else (N,), generator=g).cuda() for k, d in (("means", 3), ("quats", 4), ("scales", 3), ("opacities", 1), ("sh", 3), ("weights", 1))}
+    frend.apply_confidence_filter(raw, conf)
+    ev3 = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev3[0].record()
+    kept = frend.apply_confidence_filter(raw, conf)
+    ev3[1].record()
+    torch.cuda.synchronize()
+    ms = ev3[0].elapsed_time(ev3[1])
+    K = kept["means"].shape[0]
+    print(f"pass {it}: confidence filter {N} -> {K} splats: {ms:.3f} ms ({(N * 40 + K * 128) / ms / 1e6:.0f} GB/s of algorithmic traffic)", flush=True)
