@@ -588,9 +588,7 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         elif self.enable_prune:
             merged = [self.prune_gs(sp) for sp in scenes]
             predictions["splats"] = {k: [m[k] for m in merged] for k in ("means", "sh", "opacities", "scales", "quats")}
-            if rasterize:
-                if self.sharded:
-                    raise NotImplementedError("rasterize=True with views sharded over ranks")
+            if rasterize:  # views sharded over ranks: every rank holds the whole merged scene and renders its own views
                 H, W = images.shape[-2:]
                 outs = [[], [], []]
                 for b, m in enumerate(merged):

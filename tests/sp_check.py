@@ -88,6 +88,20 @@ def main():
     same = all(torch.equal(outs[0][k][0], outs[1][k][0]) for k in ("means", "sh", "opacities", "scales", "quats"))
     print(f"rank {rank}: sharded filter + merge == single-GPU: {same} ({K} -> {Kf} voxels with the 35 % filter)", flush=True)
     ok &= same and 0 < Kf < K
+    # rasterize=True with sharded views: every rank renders ITS views from the whole merged scene
+    outs = []
+    for sharded in (True, False):
+        r = H2.B200GaussianSplatRenderer(voxel_size=0.01, sharded=sharded)
+        r.load_state_dict({k[len("gs_renderer."):]: v for k, v in gsd.items() if k.startswith("gs_renderer.")})
+        v = sl if sharded else slice(0, S)
+        p = {k: t[:, v].contiguous() for k, t in preds.items()}
+        outs.append(r.render(feat[:, v].permute(0, 1, 4, 2, 3), im[:, v].contiguous(), p, rasterize=True))
+    torch.cuda.synchronize()
+    for name in ("rendered_colors", "rendered_depths", "rendered_alphas"):
+        a, f = outs[0][name], outs[1][name][:, sl]
+        e = (a - f).abs().max().item()
+        print(f"rank {rank}: sharded {name} {tuple(a.shape)} vs single GPU max abs {e:.2e}, mean alpha {outs[1]['rendered_alphas'].mean().item():.3f}", flush=True)
+        ok &= a.shape == f.shape and e <= 1e-6
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
