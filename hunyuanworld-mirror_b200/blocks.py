@@ -31,8 +31,9 @@ def _p(t: Optional[torch.Tensor]) -> Optional[int]:
 
 
 class B200RotaryPositionEmbedding2D:
-    """Marker for `rope=`: stands where the reference passes `RotaryPositionEmbedding2D(frequency=100)` (rope.py:80-181).
-    The rotation itself happens inside the QKV kernel's epilogue; the tables come from `wm_rope_tables`."""
+    """Stands where the reference passes `RotaryPositionEmbedding2D(frequency=100)` (rope.py:80-181).  Inside a block the
+    rotation happens in the QKV kernel's epilogue; called on its own (`rope(tokens, positions)`, rope.py:148) it runs the
+    stand-alone operator `wm_rope2d`, which takes arbitrary positions.  The tables come from `wm_rope_tables`."""
 
     def __init__(self, frequency: float = 100.0, scaling_factor: float = 1.0):
         if frequency != 100.0 or scaling_factor != 1.0:
@@ -46,6 +47,29 @@ class B200RotaryPositionEmbedding2D:
             capi.lib().wm_rope_tables(max_pos, cos, sin)
             self._tables[key] = (torch.tensor(list(cos), device=dev), torch.tensor(list(sin), device=dev))
         return self._tables[key]
+
+
+    @torch.no_grad()
+    def forward(self, tokens: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+        """tokens [B', heads, L, 64], positions [B', L, 2] (y, x) -> rotated tokens, fp32 (rope.py:148-181; same assertions)."""
+        assert tokens.size(-1) % 2 == 0, "Feature dimension must be even"
+        assert positions.ndim == 3 and positions.shape[-1] == 2, "Positions must have shape (batch_size, n_tokens, 2)"
+        if tokens.ndim != 4 or tokens.size(-1) != HEAD_DIM or not tokens.is_cuda:
+            raise ValueError(f"B200RotaryPositionEmbedding2D: tokens must be a CUDA tensor [B, heads, L, {HEAD_DIM}], got "
+                             f"{tuple(tokens.shape)} on {tokens.device}")
+        Bn, Hh, L, _ = tokens.shape
+        if positions.shape[0] != Bn or positions.shape[1] != L:
+            raise ValueError(f"positions {tuple(positions.shape)} do not match tokens {tuple(tokens.shape)}")
+        t = tokens.to(torch.float32).contiguous()
+        pos = positions.to(tokens.device, torch.int64).contiguous()
+        max_pos = max(int(pos.max().item()), 0)  # the reference sizes its tables the same way (rope.py:171)
+        cs, sn = self.tables(max(512, max_pos), tokens.device)
+        out = torch.empty_like(t)
+        capi.check(capi.lib().wm_rope2d(_st(), t.data_ptr(), pos.data_ptr(), Bn, Hh, L, max(512, max_pos), cs.data_ptr(), sn.data_ptr(),
+                                        out.data_ptr()))
+        return out
+
+    __call__ = forward
 
 
 def grid_of_positions(pos: torch.Tensor) -> Tuple[int, int]:

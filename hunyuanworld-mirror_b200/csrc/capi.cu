@@ -1098,6 +1098,13 @@ wm_status wm_load_image(wm_stream stream, const unsigned char* rgb, int H, int W
                     workspace, workspace_bytes);
 }
 
+wm_status wm_rope2d(wm_stream stream, const float* tokens, const long long* positions, int batch, int heads, int L, int max_pos,
+                    const float* rope_cos, const float* rope_sin, float* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return rope2d(static_cast<cudaStream_t>(stream), tokens, positions, batch, heads, L, max_pos, rope_cos, rope_sin, out);
+}
+
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst) {
   int sms;
   WM_TRY(require_sm100(&sms));

@@ -244,4 +244,45 @@ wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int 
   return WM_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// RotaryPositionEmbedding2D.forward (rope.py:148-181) as a stand-alone operator (secondary seam of SURVEY.md section 8b;
+// inside wm_forward the rotation lives in the QKV epilogue).  tokens [B, Hh, L, 64] fp32, positions [B, L, 2] int64
+// (y, x), ANY values in [0, max_pos]: dims [0, 32) rotate with y, [32, 64) with x; within an axis dim j pairs with
+// j +- 16 (rotate-half) at frequency j % 16: out[j] = t[j] cos + (j < 16 ? -t[j + 16] : t[j - 16]) sin.
+// HBM-bound: 256 B read + 256 B written per row; 16 threads per row, one float4 each (+ the partner float4 from L1).
+__global__ void __launch_bounds__(256)
+rope2d_kernel(const float* __restrict__ t, const long long* __restrict__ pos, long long rows, int heads, int L, int max_pos,
+              const float* __restrict__ cos_t, const float* __restrict__ sin_t, float* __restrict__ out) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < rows * 16; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i >> 4;  // (b * heads + h) * L + l
+    const int c = (int)(i & 15), axis = c >> 3, j0 = (c & 7) * 4;  // this thread: dims axis * 32 + j0 .. + 3
+    const long long b = row / ((long long)heads * L);
+    const int l = (int)(row % L);
+    long long p = pos[(b * L + l) * 2 + axis];
+    p = p < 0 ? 0 : (p > max_pos ? max_pos : p);
+    const float4 x = *reinterpret_cast<const float4*>(t + row * 64 + axis * 32 + j0);
+    const float4 y = *reinterpret_cast<const float4*>(t + row * 64 + axis * 32 + (j0 ^ 16));
+    const float4 cs = *reinterpret_cast<const float4*>(cos_t + p * 16 + (j0 & 15));
+    const float4 sn = *reinterpret_cast<const float4*>(sin_t + p * 16 + (j0 & 15));
+    const float sg = j0 < 16 ? -1.f : 1.f;
+    float4 o;  // products rounded separately, then added: x * cos + rot * sin as torch evaluates it (rope.py:146)
+    o.x = __fadd_rn(__fmul_rn(x.x, cs.x), __fmul_rn(sg * y.x, sn.x));
+    o.y = __fadd_rn(__fmul_rn(x.y, cs.y), __fmul_rn(sg * y.y, sn.y));
+    o.z = __fadd_rn(__fmul_rn(x.z, cs.z), __fmul_rn(sg * y.z, sn.z));
+    o.w = __fadd_rn(__fmul_rn(x.w, cs.w), __fmul_rn(sg * y.w, sn.w));
+    *reinterpret_cast<float4*>(out + row * 64 + axis * 32 + j0) = o;
+  }
+}
+
+wm_status rope2d(cudaStream_t st, const float* tokens, const long long* pos, int batch, int heads, int L, int max_pos,
+                 const float* cos_t, const float* sin_t, float* out) {
+  WM_CHECK(tokens && pos && cos_t && sin_t && out && batch > 0 && heads > 0 && L > 0 && max_pos >= 0, "rope2d: bad argument");
+  WM_CHECK(tokens != out, "rope2d: in place is not supported (a thread reads its partner's input)");
+  const long long rows = (long long)batch * heads * L;
+  const int grid = (int)std::min<long long>((rows * 16 + 255) / 256, 148 * 16);
+  rope2d_kernel<<<grid, 256, 0, st>>>(tokens, pos, rows, heads, L, max_pos, cos_t, sin_t, out);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
 }  // namespace wm

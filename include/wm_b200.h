@@ -185,6 +185,11 @@ wm_status wm_patch_gather(wm_stream stream, const float* img, int n_views, int c
                           int rows_per_view, int row_offset, int ld, int normalize, void* out);
 /* cos / sin of pos * 100^(-2i/32), i < 16 (rope.py:80-111): host arrays [(max_pos+1)*16]. */
 void wm_rope_tables(int max_pos, float* cos_host, float* sin_host);
+/* RotaryPositionEmbedding2D.forward (rope.py:148-181) as an operator of its own: tokens [batch, heads, L, 64] fp32,
+ * positions [batch, L, 2] int64 (y, x) with arbitrary values in [0, max_pos], rope_cos/sin [max_pos+1, 16] from
+ * wm_rope_tables -> out (same shape, fp32, not in place).  Inside wm_forward the rotation is fused into wm_gemm_qkv. */
+wm_status wm_rope2d(wm_stream stream, const float* tokens, const long long* positions, int batch, int heads, int L, int max_pos,
+                    const float* rope_cos, const float* rope_sin, float* out);
 /* fp32 [rows, cols] -> bf16 [rows, ld] with zero tail columns. */
 wm_status wm_pack_bf16(wm_stream stream, const float* src, long long rows, int cols, int ld, void* dst);
 

@@ -103,3 +103,34 @@ def test_b200_block_error_behaviour():
     e = ((got - ref).norm() / (ref - x2).norm()).item()
     print(f"rectangular 5 x 9 grid, one view: rel fro on the branch {e:.3e}")
     assert e <= 1e-2
+
+
+@pytest.mark.gpu
+def test_b200_rope2d_matches_oracle_and_defect_d9_vectors():
+    """`RotaryPositionEmbedding2D.forward(tokens, positions)` on its own (rope.py:148-181) with ARBITRARY positions against
+    the oracle's rope_2d (pinned against the live reference module, tests/test_oracle.py): <= 1e-6 (the tables are correctly
+    rounded, torch's cosf / sinf are within an ulp); the hand-checked vectors of SURVEY.md section 9-D9; identity at (0, 0)."""
+    pkg = importlib.import_module("hunyuanworld-mirror_b200")
+    rope = pkg.B200RotaryPositionEmbedding2D(frequency=100)
+    g = torch.Generator().manual_seed(6)
+    t = torch.randn(3, 16, 77, 64, generator=g)
+    pos = torch.randint(0, 40, (3, 77, 2), generator=g)
+    pos[0, :5] = 0
+    pos[2, 3] = torch.tensor([600, 0])  # beyond the default table: it is rebuilt for the largest position
+    got = rope(t.cuda(), pos.cuda()).cpu()
+    ref = O.rope_2d(t, pos)
+    err = (got - ref).abs().max().item()
+    print(f"rope2d vs oracle: max abs err {err:.2e}")
+    assert got.shape == t.shape and err <= 1e-6
+    assert torch.equal(got[0, :, :5], t[0, :, :5])  # (0, 0): exactly the identity
+    # D9: one-hot inputs at (y, x) = (3, 5): d = 1 -> cos at 1, sin at 17; d = 33 -> cos/sin(5 * 100^(-2/32)) = -0.8209 / -0.5711
+    e = torch.zeros(1, 1, 2, 64)
+    e[0, 0, 0, 1], e[0, 0, 1, 33] = 1.0, 1.0
+    r = rope(e.cuda(), torch.tensor([[[3, 5], [3, 5]]]).cuda()).cpu()
+    th = 3 * 100.0 ** (-2.0 / 32.0)
+    assert abs(r[0, 0, 0, 1].item() - np.cos(th)) < 1e-6 and abs(r[0, 0, 0, 17].item() - np.sin(th)) < 1e-6
+    assert abs(r[0, 0, 1, 33].item() - (-0.8209)) < 1e-4 and abs(r[0, 0, 1, 49].item() - (-0.5711)) < 1e-4
+    with pytest.raises(ValueError):
+        rope(t, pos)  # no CPU path
+    with pytest.raises(AssertionError):
+        rope(t.cuda(), pos[..., :1].cuda())
