@@ -115,6 +115,28 @@ def test_truncated_stack_matches_oracle():
         assert e32 <= 5e-3 and e16 <= 4e-3
 
 
+@pytest.mark.parametrize("n,h,w,flags", [(1, 70, 98, [1, 1, 1]), (1, 14, 14, [0, 0, 0]), (2, 14, 42, [0, 1, 0]), (5, 28, 14, [1, 0, 1])])
+def test_edge_shapes_match_oracle(n, h, w, flags):
+    """Edge cases of the token geometry: a single view (global attention == frame attention, only the view-0 special
+    tokens, visual_transformer.py:411-412), the smallest image (one patch: 8 tokens per view), one-row / one-column grids,
+    partial prior flags, an odd number of views."""
+    sd = W.synthetic_state_dict(seed=0, depth=2, dino_depth=2)
+    m = pkg.B200VisualGeometryTransformer(depth=2, dino_depth=2, intermediate_idxs=(0, 1))
+    m.load_state_dict(sd)
+    imgs = W.synthetic_images(n, h, w, seed=7)
+    pri = W.synthetic_priors(n, h, w, seed=8)
+    outs, psi = m(imgs.cuda(), tuple(p.cuda() for p in pri), cond_flags=flags)
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        ref32, _ = O.aggregator_forward(imgs, sd, pri, flags, depth=2, dino_depth=2, intermediate=(0, 1))
+    assert psi == 7 and len(outs) == 2
+    for o, a in zip(outs, ref32):
+        assert tuple(o.shape) == (1, n, 7 + (h // 14) * (w // 14), 2048) and torch.isfinite(o).all()
+        e32 = rel_fro(o.cpu().numpy(), a.numpy())
+        print(f"{n} views {h}x{w} flags {flags}: vs fp32 oracle {e32:.3e}")
+        assert e32 <= 5e-3
+
+
 def test_large_layerscale_exposes_block_branches():
     """The reference initialises the aggregator's LayerScale to 0.01, which hides attention / MLP errors in the
     residual stream.  With gamma ~ 0.5 the branches dominate: two frame+global pairs still match the oracle."""
