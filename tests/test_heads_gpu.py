@@ -257,3 +257,41 @@ def test_dpt_head_518_matches_oracle():
     border = (pred.cpu() - ref_p)[0, 0, [0, -1]].abs().max().item() / ref_p.abs().max().item()
     print(f"DPT 518: rel fro {e:.3e}, conf {ec:.3e}, border rows max err / max {border:.3e}")
     assert torch.isfinite(pred).all() and e <= 2e-3 and ec <= 2e-3 and border <= 5e-3
+
+
+def test_single_view_forward_matches_oracle_heads(state_dict_full):
+    """Edge case S = 1 (one view, rectangular 42 x 70): the whole `B200WorldMirror.forward` including the Gaussian branch.
+    The heads are checked against the fp32 oracle heads run on the B200 aggregator's OWN tokens (the forward is
+    deterministic), so the gates are the heads' own: dense outputs 2e-3 rel. Frobenius, camera 3e-4; the splats are the
+    oracle's voxel merge of this forward's un-pruned splats, bit for bit (quaternions 2 ulp)."""
+    from oracle import gs_oracle as G
+
+    hsd = W.synthetic_heads_state_dict(seed=0, gs=True)
+    model = heads.B200WorldMirror.from_state_dicts(state_dict_full, hsd)
+    imgs = W.synthetic_images(1, 42, 70, seed=3).cuda()
+    preds = model({"img": imgs})
+    token_list, psi = model.visual_geometry_transformer(imgs)
+    torch.cuda.synchronize()
+    assert psi == 7 and token_list[0].shape == (1, 1, 7 + 3 * 5, 2048)
+    with torch.no_grad():
+        ref = HO.all_heads([t.cpu() for t in token_list], 42, 70, hsd)
+    for name in ("depth", "pts3d", "normals", "depth_conf", "pts3d_conf", "normals_conf"):
+        got, r = preds[name].cpu().numpy(), ref[name].numpy()
+        assert got.shape == r.shape, (name, got.shape, r.shape)
+        e = np.linalg.norm(got - r) / np.linalg.norm(r)
+        print(f"single view {name}: rel fro {e:.3e}")
+        assert np.isfinite(got).all() and e <= 2e-3
+    np.testing.assert_allclose(preds["camera_params"].cpu().numpy(), ref["camera_params"].numpy(), atol=3e-4, rtol=2e-4)
+    K = preds["splats"]["means"][0].shape[0]
+    model.gs_renderer.enable_prune = False
+    raw = model({"img": imgs})["splats"]
+    torch.cuda.synchronize()
+    keys = ("means", "quats", "scales", "opacities", "sh")
+    mref = G.prune_gs({k: raw[k][0].reshape(raw[k].shape[1], -1).squeeze(-1).cpu().numpy() for k in keys + ("weights",)}, 0.002)
+    assert mref["means"].shape[0] == K and 0 < K <= 42 * 70
+    for k in keys:
+        g = preds["splats"][k][0].reshape(K, -1).cpu().numpy()
+        if k == "quats":
+            np.testing.assert_allclose(g, mref[k], rtol=3e-7, atol=1e-9)
+        else:
+            assert np.array_equal(g, mref[k].reshape(K, -1)), k
