@@ -360,8 +360,9 @@ struct ConfWs {
   size_t cub_bytes;
 };
 
-// order-preserving key of a masked confidence: NaN (positive) sorts above +inf, as torch.topk treats it
+// order-preserving key of a masked confidence; NaN (either sign) sorts above +inf, as torch.topk treats it
 __device__ __forceinline__ unsigned conf_key(float c) {
+  if (c != c) return 0xFFFFFFFFu;
   if (c <= 1e-5f) c = -INFINITY;
   const unsigned u = __float_as_uint(c);
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);

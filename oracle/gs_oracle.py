@@ -147,7 +147,8 @@ def conf_filter_indices(conf: np.ndarray, percent: float = 30.0, max_gaussians: 
     c = conf.reshape(-1).astype(np.float32).copy()
     c[c <= np.float32(1e-5)] = -np.inf
     K = conf_filter_count(c.shape[0], percent, max_gaussians)
-    order = np.argsort(-c, kind="stable")  # NaN last in numpy; confidences are 1 + exp(.) and never NaN
+    nan = np.isnan(c)  # torch.topk ranks NaN above everything (confidences are 1 + exp(.): NaN only from broken inputs)
+    order = np.lexsort((np.arange(c.shape[0]), -np.where(nan, np.float32(np.inf), c), ~nan))  # NaN first, then descending, then index
     return np.sort(order[:K])
 
 

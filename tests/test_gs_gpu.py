@@ -428,6 +428,9 @@ def test_conf_filter_ties_large_and_errors():
     N = 2 * 518 * 518 + 13
     conf = (1.0 + g.integers(0, 37, size=N) * 0.25).astype(np.float32)
     conf[g.random(N) < 0.33] = 0.0
+    conf[[5, 77777, N - 2]] = np.nan  # NaN (either sign) ranks above everything, as torch.topk has it
+    conf[77777] = -conf[77777]
+    conf[123456] = np.inf
     sp = {"means": g.normal(size=(N, 3)), "quats": g.normal(size=(N, 4)), "scales": g.random((N, 3)), "opacities": g.random(N),
           "sh": g.normal(size=(N, 3)), "weights": g.random(N)}
     sp = {k: v.astype(np.float32) for k, v in sp.items()}

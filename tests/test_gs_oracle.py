@@ -115,3 +115,8 @@ def test_conf_filter_ties_and_masking():
     assert G.conf_filter_indices(conf, 12.5).tolist() == [0, 1, 2, 3, 4, 6, 7]  # K = 7: the first masked one joins
     assert G.conf_filter_indices(conf, 0.0).tolist() == list(range(8))
     assert G.conf_filter_indices(conf, 30.0, max_gaussians=2).tolist() == [1, 6]
+    # NaN ranks above everything, +inf included, as torch.topk has it
+    c2 = np.array([1.5, np.nan, np.inf, 2.0, -np.nan, 0.0], dtype=np.float32)
+    assert G.conf_filter_indices(c2, 50.0).tolist() == [1, 2, 4]
+    t = torch.topk(torch.from_numpy(np.where(c2 <= 1e-5, -np.inf, c2)), 3, sorted=False).indices.sort().values.tolist()
+    assert t == [1, 2, 4]
