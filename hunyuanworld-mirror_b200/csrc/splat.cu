@@ -390,11 +390,14 @@ conf_hist_kernel(const float* __restrict__ conf, unsigned N, int pass, const uns
 
 // the digit of this pass: the largest d with |{digit > d}| < remaining <= |{digit >= d}|
 __global__ void conf_pick_kernel(int pass, unsigned* state, const unsigned* __restrict__ hist) {
+  __shared__ unsigned s_h[256];
+  s_h[threadIdx.x] = hist[pass * 256 + threadIdx.x];  // 256 threads: one coalesced read instead of 256 dependent ones
+  __syncthreads();
   if (threadIdx.x != 0) return;
   const unsigned rem = state[1];
   unsigned acc = 0u;
   for (int d = 255; d >= 0; --d) {
-    const unsigned h = hist[pass * 256 + d];
+    const unsigned h = s_h[d];
     if (acc + h >= rem) {
       state[0] |= (unsigned)d << (24 - 8 * pass);
       state[1] = rem - acc;
@@ -481,7 +484,7 @@ wm_status conf_filter_splats(cudaStream_t st, long long N, long long K, const fl
   conf_init_kernel<<<1, 256, 0, st>>>(w.state, w.hist, (unsigned)K);
   for (int pass = 0; pass < 4; ++pass) {
     conf_hist_kernel<<<grid, SP_THREADS, 0, st>>>(conf, n, pass, w.state, w.hist);
-    conf_pick_kernel<<<1, 32, 0, st>>>(pass, w.state, w.hist);
+    conf_pick_kernel<<<1, 256, 0, st>>>(pass, w.state, w.hist);
   }
   conf_mark_kernel<<<grid, SP_THREADS, 0, st>>>(conf, n, w.state, w.packed);
   WM_LAUNCH_CHECK();
