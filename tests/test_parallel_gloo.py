@@ -48,6 +48,26 @@ def _worker(rank, world, port, q):
         t = torch.full((1, n // world, 2, 4), float(rank))
         cat = par.gather_outputs([t])[0]
         assert cat.shape == (1, n, 2, 4) and cat[0, :, 0, 0].tolist() == [0.0, 0.0, 1.0, 1.0]
+        # 4. Gaussian branch under view sharding: splats and the depth confidence gathered in rank order are the scene in
+        #    view order, so confidence filter + voxel merge of the gathered rows == the single-process result, bit for bit
+        import numpy as np
+
+        from oracle import gs_oracle as G
+
+        syn = G.synthetic_splats(4000)
+        conf = (1.0 + np.random.default_rng(3).integers(0, 9, size=4000) * 0.5).astype(np.float32)  # ties on purpose
+        full_sp = G.prune_gs(G.apply_confidence_filter(syn, conf, 40.0), voxel_size=0.01)
+        per = 4000 // world
+        mine = {k: torch.from_numpy(v[rank * per:(rank + 1) * per].copy()) for k, v in dict(syn, conf=conf).items()}
+        gathered = {}
+        for k, t in mine.items():
+            parts = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(parts, t)
+            gathered[k] = torch.cat(parts, dim=0).numpy()
+        gconf = gathered.pop("conf")
+        shard_sp = G.prune_gs(G.apply_confidence_filter(gathered, gconf, 40.0), voxel_size=0.01)
+        for k in full_sp:
+            assert np.array_equal(full_sp[k], shard_sp[k]), k
         q.put((rank, "ok"))
     except Exception as e:  # pragma: no cover
         q.put((rank, repr(e)))
