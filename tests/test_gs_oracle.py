@@ -120,3 +120,25 @@ def test_conf_filter_ties_and_masking():
     assert G.conf_filter_indices(c2, 50.0).tolist() == [1, 2, 4]
     t = torch.topk(torch.from_numpy(np.where(c2 <= 1e-5, -np.inf, c2)), 3, sorted=False).indices.sort().values.tolist()
     assert t == [1, 2, 4]
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_conf_filter_set_equals_torch_topk_on_distinct_values(seed):
+    """The third-party call the reference makes (`torch.topk(conf, K, largest=True, sorted=False)`, rasterization.py:279) on
+    random DISTINCT confidences with masked entries: the oracle keeps exactly that set, for random percentages."""
+    g = np.random.default_rng(seed)
+    n = int(g.integers(50, 3000))
+    conf = g.permutation(np.linspace(0.5, 40.0, n)).astype(np.float32)
+    conf[g.random(n) < 0.2] = 0.0
+    p = float(g.uniform(0.0, 99.0))
+    K = G.conf_filter_count(n, p)
+    masked = torch.from_numpy(conf).masked_fill(torch.from_numpy(conf) <= 1e-5, float("-inf"))
+    ref = torch.topk(masked, K, largest=True, sorted=False).indices.numpy()
+    got = G.conf_filter_indices(conf, p)
+    live = int((conf > 1e-5).sum())
+    if K <= live:  # no choice among the equal -inf entries involved
+        assert np.array_equal(np.sort(ref), got)
+    else:  # all live entries kept; the rest are masked ones (which ones is unspecified in torch, lowest indices here)
+        assert set(np.flatnonzero(conf > 1e-5)) <= set(got.tolist()) and got.shape[0] == K
+        rest = np.setdiff1d(got, np.flatnonzero(conf > 1e-5))
+        assert np.array_equal(rest, np.flatnonzero(conf <= 1e-5)[: K - live])
