@@ -182,10 +182,21 @@ class B200VisualGeometryTransformer(torch.nn.Module):
         self._p2p_rows = rows_per_rank
 
     def peer_gather_status(self):
-        """(enabled, timed_out) of the peer-memory exchange; timed_out means a forward ran on stale keys."""
+        """(enabled, timed_out) of the peer-memory exchange; timed_out means a forward ran on stale keys.  Synchronous
+        (one 4-byte device read) and clears the condition."""
         en, to = C.c_int(), C.c_int()
         capi.check(capi.lib().wm_p2p_status(self._handle, C.byref(en), C.byref(to)))
         return bool(en.value), bool(to.value)
+
+    def raise_on_peer_timeout(self):
+        """Call where the host synchronises anyway (B200WorldMirror.forward does): raises if a K|V shard of a peer did not
+        arrive in time during the forwards since the last check.  Without this call the library itself reports the
+        condition from the NEXT forward (wm_forward returns WM_ERR_STATE once), so it can never go unnoticed."""
+        if self.world > 1:
+            enabled, timed_out = self.peer_gather_status()
+            if enabled and timed_out:
+                raise RuntimeError("sequence-parallel K|V exchange timed out: a peer's shard did not arrive within 4 s and the "
+                                   "forward finished on stale keys (a rank is slow, desynchronised or has crashed)")
 
     # ------------------------------------------------------------------ forward
     def _workspace_for(self, n: int, H: int, W: int, device) -> torch.Tensor:

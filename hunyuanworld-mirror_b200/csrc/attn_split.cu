@@ -428,18 +428,24 @@ attn_merge_kernel(const AttnArgs a, __nv_bfloat16* __restrict__ out, int ldo) {
 template <int NPOLY, bool BOUNDED>
 static wm_status launch_split(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
                               const CUtensorMap& to, const AttnArgs& a) {
-  static bool cfg = false;
-  if (!cfg) {
+  static int cfg_dev[16] = {0};  // the shared-memory attribute is per device, not per process
+  int dev = 0;
+  WM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 16 || !cfg_dev[dev]) {
     WM_CUDA(cudaFuncSetAttribute(attn_split_kernel<NPOLY, BOUNDED>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATS_SMEM));
-    cfg = true;
+    if (dev >= 0 && dev < 16) cfg_dev[dev] = 1;
   }
   return launch_pdl(attn_split_kernel<NPOLY, BOUNDED>, dim3(grid), dim3(ATS_THREADS), ATS_SMEM, st, tq, tk, tv, to, a);
 }
 
+wm_status flash_attention_pipe(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
+                               const CUtensorMap& to, const AttnArgs& a, int variant);  // attn_pipe.cu
+
 size_t attn_partial_bytes(int sm_count) { return (size_t)2 * sm_count * kAttnSlotFloats * sizeof(float); }
 
 // variants 4..7 of flash_attention(): running-max softmax, polynomial share 0, 8, 10, 12 of every 32 exponentials;
-// variants 8..12: bounded-logit mode (q pre-scaled, |logit| bounded), polynomial share 0, 8, 12, 14, 16.
+// variants 8..12: bounded-logit mode (q pre-scaled, |logit| bounded), polynomial share 0, 8, 12, 14, 16;
+// variants 13..19: bounded-logit mode, half-tile pipelined (attn_pipe.cu).
 // With a partial workspace (attn_partial_bytes) the (item, kv tile) steps are dealt out evenly and split items are
 // merged by attn_merge_kernel; without one every CTA gets whole items.
 wm_status flash_attention_split(cudaStream_t st, int sm_count, const CUtensorMap& tq, const CUtensorMap& tk,
@@ -483,7 +489,12 @@ wm_status flash_attention_split(cudaStream_t st, int sm_count, const CUtensorMap
     case 10: r = launch_split<12, true>(st, grid, tq, tk, tv, to, a); break;
     case 11: r = launch_split<14, true>(st, grid, tq, tk, tv, to, a); break;
     case 12: r = launch_split<16, true>(st, grid, tq, tk, tv, to, a); break;
-    default: return fail(WM_ERR_INVALID, "flash_attention: unknown split variant %d", variant);
+    default:
+      if (variant >= 13 && variant <= 23) {  // second-generation kernels (attn_pipe.cu): 13-19 bounded, 20-23 general
+        r = flash_attention_pipe(st, grid, tq, tk, tv, to, a, variant);
+        break;
+      }
+      return fail(WM_ERR_INVALID, "flash_attention: unknown split variant %d", variant);
   }
   WM_TRY(r);
   if (a.part_o != nullptr && a.per_cta % a.n_kv != 0)

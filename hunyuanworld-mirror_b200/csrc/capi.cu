@@ -4,6 +4,7 @@
 // inside wm_forward / wm_forward_tokens / wm_embed.
 #include <dlfcn.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include <string>
 #include <unordered_map>
@@ -128,6 +129,12 @@ struct PeerGather {
   cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
   unsigned epoch = 0;
   bool used = false;  // pushes were enqueued since the last join with the forward's stream
+  // the error word of the gather header is copied to pinned host memory at the end of every forward that used the
+  // exchange and looked at (without blocking) when the next one starts: a forward that ran on stale keys because a
+  // shard never arrived cannot go unnoticed (wm_p2p_status reads it synchronously)
+  unsigned* err_host = nullptr;
+  cudaEvent_t ev_err = nullptr;
+  bool err_pending = false;
 };
 
 __global__ void p2p_flag_kernel(unsigned* flag, unsigned epoch) {
@@ -160,6 +167,8 @@ struct wm_handle {
   long long launches = 0;
   // tuning knobs (wm_set_int): attention kernel variants and the bounded-logit switch
   int attn_general_variant = 4, attn_bounded_variant = 10, attn_allow_bounded = 1, attn_balance = 1;
+  int gemm_split = 1;             // K-split of the residual GEMMs' tail tiles (gemm.cu); 0: whole tiles only
+  unsigned* gemm_flags = nullptr;  // kGemmFlagBytes of arrival counters, zero between launches
 };
 
 namespace wm {
@@ -207,6 +216,7 @@ struct Workspace {
   float *xd, *x;
   __nv_bfloat16 *ln, *q, *kv, *att, *hid;
   float* attn_part;  // partials of attention work items split between CTAs (attn_split.cu)
+  float* gemm_part;  // K slices of the residual GEMMs' tail tiles (gemm.cu)
   size_t bytes;
 };
 
@@ -230,6 +240,7 @@ static Workspace carve(void* base, int n, int gh, int gw, int world) {
   ws.att = reinterpret_cast<__nv_bfloat16*>(take(T * kEmbed * 2));
   ws.hid = reinterpret_cast<__nv_bfloat16*>(take(T * kMlp * 2));
   ws.attn_part = reinterpret_cast<float*>(take(attn_partial_bytes(kNumSms)));
+  ws.gemm_part = reinterpret_cast<float*>(take(gemm_partial_bytes(kNumSms)));
   ws.bytes = off + 1024;  // slack so the caller's base may be aligned up to 1024
   return ws;
 }
@@ -328,11 +339,13 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
         flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
                         0.125f, bounded ? h->attn_bounded_variant : h->attn_general_variant,
                         h->attn_balance ? ws.attn_part : nullptr, attn_partial_bytes(kNumSms), p2p ? &ag : nullptr));
+  float* gpart = h->gemm_split ? ws.gemm_part : nullptr;
   WM_OP(WM_PROF_PROJ, gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x,
-                                       kEmbed));
+                                       kEmbed, gpart, gemm_partial_bytes(kNumSms), h->gemm_flags));
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
   WM_OP(WM_PROF_FC1, gemm_bias_act(st, ws.ln, kEmbed, w.fc1_w, kEmbed, w.fc1_b, s.T, kMlp, kEmbed, ws.hid, kMlp, 1));
-  WM_OP(WM_PROF_FC2, gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed));
+  WM_OP(WM_PROF_FC2, gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed, gpart,
+                                      gemm_partial_bytes(kNumSms), h->gemm_flags));
   if (out2) WM_OP(WM_PROF_EMBED, copy_cols(st, x, s.T, out2, 2 * kEmbed, out2_col));
   return WM_OK;
 }
@@ -349,8 +362,30 @@ static wm_status check_ready(const wm_handle* h, const void* workspace, size_t w
   return WM_OK;
 }
 
+// A shard that did not arrive within the time limit lets the attention kernel finish on stale keys and sets the error
+// word; surface it at the latest when the next forward starts (clearing it, so that a recovered job can go on).
+static wm_status p2p_check_previous(wm_handle* h, cudaStream_t st, bool block) {
+  PeerGather& g = h->p2p;
+  if (!g.err_pending) return WM_OK;
+  if (block)
+    WM_CUDA(cudaEventSynchronize(g.ev_err));
+  else if (cudaEventQuery(g.ev_err) != cudaSuccess) {
+    cudaGetLastError();
+    return WM_OK;  // still in flight: looked at again by the next call
+  }
+  g.err_pending = false;
+  if (*g.err_host != 0) {
+    *g.err_host = 0;
+    WM_CUDA(cudaMemsetAsync(g.base + 64 * sizeof(unsigned), 0, sizeof(unsigned), st));
+    return fail(WM_ERR_STATE, "peer-memory K|V exchange: a shard did not arrive within 4 s in an earlier forward; its "
+                              "outputs were computed on stale keys (a peer is slow, desynchronised or gone)");
+  }
+  return WM_OK;
+}
+
 static wm_status run_stack(wm_handle* h, cudaStream_t st, const Workspace& ws, int n, int gh, int gw, float* const* out) {
   const int P = kPatchStart + gh * gw, T = n * P;
+  WM_TRY(p2p_check_previous(h, st, false));
   BlockShape fs{T, n, P, P, 0, P, kPatchStart, gw, true, 1e-5f, false};
   BlockShape gs{T, 1, T, T * h->world, h->rank * T, P, kPatchStart, gw, true, 1e-5f, true};
   int next_out = 0;
@@ -364,6 +399,11 @@ static wm_status run_stack(wm_handle* h, cudaStream_t st, const Workspace& ws, i
     WM_CUDA(cudaEventRecord(h->p2p.ev_done, h->p2p.comm));
     WM_CUDA(cudaStreamWaitEvent(st, h->p2p.ev_done, 0));
     h->p2p.used = false;
+    if (h->p2p.err_host) {
+      WM_CUDA(cudaMemcpyAsync(h->p2p.err_host, h->p2p.base + 64 * sizeof(unsigned), sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+      WM_CUDA(cudaEventRecord(h->p2p.ev_err, st));
+      h->p2p.err_pending = true;
+    }
   }
   return WM_OK;
 }
@@ -424,6 +464,8 @@ static void p2p_release(wm_handle* h) {
   if (g.base) cudaFree(g.base);
   if (g.ev_ready) cudaEventDestroy(g.ev_ready);
   if (g.ev_done) cudaEventDestroy(g.ev_done);
+  if (g.ev_err) cudaEventDestroy(g.ev_err);
+  if (g.err_host) cudaFreeHost(g.err_host);
   if (g.comm) cudaStreamDestroy(g.comm);
   g = PeerGather{};
 }
@@ -451,6 +493,16 @@ wm_status wm_create(const wm_config* cfg, wm_handle** out) {
   wm_handle* h = new (std::nothrow) wm_handle();
   WM_CHECK(h, "wm_create: out of host memory");
   h->cfg = *cfg;
+  // experiment switches (the defaults are what the forward was measured with): WM_ATTN_BOUNDED_VARIANT, WM_ATTN_GENERAL_VARIANT
+  if (const char* e = getenv("WM_ATTN_BOUNDED_VARIANT")) {
+    const int v = atoi(e);
+    if (v >= 8 && v <= 19) h->attn_bounded_variant = v;
+  }
+  if (const char* e = getenv("WM_GEMM_SPLIT")) h->gemm_split = atoi(e) != 0;
+  if (const char* e = getenv("WM_ATTN_GENERAL_VARIANT")) {
+    const int v = atoi(e);
+    if ((v >= 0 && v <= 7) || (v >= 20 && v <= 23)) h->attn_general_variant = v;
+  }
   h->rope_max_pos = 512;
   std::vector<float> c((h->rope_max_pos + 1) * 16), s((h->rope_max_pos + 1) * 16);
   wm_rope_tables(h->rope_max_pos, c.data(), s.data());
@@ -458,6 +510,8 @@ wm_status wm_create(const wm_config* cfg, wm_handle** out) {
   if (e == cudaSuccess) e = cudaMalloc(&h->rope_sin, s.size() * 4);
   if (e == cudaSuccess) e = cudaMemcpy(h->rope_cos, c.data(), c.size() * 4, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(h->rope_sin, s.data(), s.size() * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc(&h->gemm_flags, kGemmFlagBytes);
+  if (e == cudaSuccess) e = cudaMemset(h->gemm_flags, 0, kGemmFlagBytes);
   if (e != cudaSuccess) {
     wm_destroy(h);
     return fail(WM_ERR_CUDA, "wm_create: %s", cudaGetErrorString(e));
@@ -475,6 +529,7 @@ void wm_destroy(wm_handle* h) {
   if (h->rope_cos) cudaFree(h->rope_cos);
   if (h->rope_sin) cudaFree(h->rope_sin);
   if (h->dino_table) cudaFree(h->dino_table);
+  if (h->gemm_flags) cudaFree(h->gemm_flags);
   if (h->comm && h->nccl.CommDestroy) h->nccl.CommDestroy(h->comm);
   p2p_release(h);
   for (auto& v : h->prof_ev)
@@ -788,6 +843,10 @@ wm_status wm_p2p_attach(wm_handle* h, const void* ipc_handles_all) {
   WM_CUDA(cudaStreamCreateWithPriority(&g.comm, cudaStreamNonBlocking, hi));
   WM_CUDA(cudaEventCreateWithFlags(&g.ev_ready, cudaEventDisableTiming));
   WM_CUDA(cudaEventCreateWithFlags(&g.ev_done, cudaEventDisableTiming));
+  WM_CUDA(cudaEventCreateWithFlags(&g.ev_err, cudaEventDisableTiming));
+  WM_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&g.err_host), sizeof(unsigned), cudaHostAllocDefault));
+  *g.err_host = 0;
+  g.err_pending = false;
   g.epoch = 0;
   g.on = true;
   return WM_OK;
@@ -801,6 +860,11 @@ wm_status wm_p2p_status(wm_handle* h, int* enabled, int* timed_out) {
     unsigned e = 0;
     WM_CUDA(cudaMemcpy(&e, h->p2p.base + 64 * sizeof(unsigned), sizeof(e), cudaMemcpyDeviceToHost));
     *timed_out = (int)e;
+    if (e != 0) {  // reported: clear it so that a job that recovers can go on
+      WM_CUDA(cudaMemset(h->p2p.base + 64 * sizeof(unsigned), 0, sizeof(unsigned)));
+      if (h->p2p.err_host) *h->p2p.err_host = 0;
+      h->p2p.err_pending = false;
+    }
   }
   return WM_OK;
 }
@@ -846,15 +910,17 @@ wm_status wm_set_int(wm_handle* h, const char* name, int value) {
   WM_CHECK(h && name, "wm_set_int: null argument");
   const std::string n(name);
   if (n == "attn_general_variant") {
-    WM_CHECK(value >= 0 && value <= 7, "attn_general_variant must be in [0,7]");
+    WM_CHECK((value >= 0 && value <= 7) || (value >= 20 && value <= 23), "attn_general_variant must be in [0,7] or [20,23]");
     h->attn_general_variant = value;
   } else if (n == "attn_bounded_variant") {
-    WM_CHECK(value >= 8 && value <= 14, "attn_bounded_variant must be in [8,14]");
+    WM_CHECK(value >= 8 && value <= 19, "attn_bounded_variant must be in [8,19]");
     h->attn_bounded_variant = value;
   } else if (n == "attn_allow_bounded") {
     h->attn_allow_bounded = value != 0;
   } else if (n == "attn_balance") {
     h->attn_balance = value != 0;
+  } else if (n == "gemm_split") {
+    h->gemm_split = value != 0;
   } else if (n == "sp_mode") {
     WM_CHECK(value == 0 || value == 1, "sp_mode must be 0 (ncclAllGather) or 1 (peer-memory push)");
     h->sp_mode = value;
@@ -862,6 +928,18 @@ wm_status wm_set_int(wm_handle* h, const char* name, int value) {
     return fail(WM_ERR_INVALID, "wm_set_int: unknown option %s", name);
   }
   return WM_OK;
+}
+
+int wm_get_int(const wm_handle* h, const char* name) {
+  if (!h || !name) return -1;
+  const std::string n(name);
+  if (n == "attn_general_variant") return h->attn_general_variant;
+  if (n == "attn_bounded_variant") return h->attn_bounded_variant;
+  if (n == "attn_allow_bounded") return h->attn_allow_bounded;
+  if (n == "attn_balance") return h->attn_balance;
+  if (n == "sp_mode") return h->sp_mode;
+  if (n == "gemm_split") return h->gemm_split;
+  return -1;
 }
 
 float wm_logit_bound(const wm_handle* h, int kind, int layer) {
@@ -874,6 +952,19 @@ wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const vo
                               const float* gamma, int M, int N, int K, float* x, int ldx) {
   return gemm_ls_residual(static_cast<cudaStream_t>(stream), A, lda, W, ldw, bias, gamma, M, N, K, x, ldx);
 }
+
+wm_status wm_gemm_ls_residual_ws(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
+                                 const float* gamma, int M, int N, int K, float* x, int ldx, void* workspace,
+                                 size_t workspace_bytes) {
+  // workspace = [kGemmFlagBytes of counters, zero at first use and left zero | partial accumulators]
+  WM_CHECK(workspace && workspace_bytes >= wm_gemm_workspace_bytes(), "wm_gemm_ls_residual_ws: workspace too small");
+  uint8_t* p = static_cast<uint8_t*>(workspace);
+  return gemm_ls_residual(static_cast<cudaStream_t>(stream), A, lda, W, ldw, bias, gamma, M, N, K, x, ldx,
+                          reinterpret_cast<float*>(p + kGemmFlagBytes), workspace_bytes - kGemmFlagBytes,
+                          reinterpret_cast<unsigned*>(p));
+}
+
+size_t wm_gemm_workspace_bytes(void) { return kGemmFlagBytes + gemm_partial_bytes(kNumSms); }
 
 wm_status wm_copy_cols(wm_stream stream, const float* x, long long rows, float* out, int ld_out, int col0) {
   int sms;

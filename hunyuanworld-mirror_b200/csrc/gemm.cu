@@ -20,6 +20,14 @@
 // 5-stage smem ring (SWIZZLE_128B, K-major for both operands), two 256-column TMEM accumulators so the epilogue
 // of tile i overlaps the main loop of tile i+1.  Outputs leave through one swizzled staging tile per team and
 // TMA stores / reduce-adds (row clipping for the M tail comes for free).
+//
+// Tail split (EPI_RESID, N = 1024: proj / fc2).  172 pair tiles on 74 CTA pairs are 2.32 waves and used to run as 3.
+// With a partial workspace the tiles beyond the last FULL wave are cut along K into `split` slices, one per CTA pair,
+// and run FIRST: every slice leaves its raw fp32 accumulator in the workspace and raises a per-(tile, rank, team)
+// counter; the pairs then run their whole tiles as before; at the very end the owner (slice 0) of each tail tile adds
+// the slices IN FIXED ORDER (0, 1, .. split-1), applies bias and LayerScale and issues the one TMA reduce-add per
+// element.  Every element of x still receives exactly one add, in an order that does not depend on timing: the
+// forward stays bit-deterministic.  2 + 1/3 waves instead of 3.
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -49,6 +57,43 @@ struct GemmArgs {
   // EPI_TABLE
   const float* table;
   int table_period;
+  // tail split (EPI_RESID only; split == 1: every pair walks whole tiles round-robin, as the other epilogues do)
+  int split, full_tiles, tail_tiles;  // tiles [0, full_tiles) whole; tiles [full_tiles, full_tiles + tail_tiles) in `split` K slices
+  float* part;      // [tail_tiles][split][2 ranks][128 rows][256 cols] fp32 partial accumulators
+  unsigned* flags;  // [tail_tiles][2 ranks][2 teams] arrival counters; zero before the launch, left zero by it
+};
+
+// The work units of one CTA pair, in the order every role of the pair walks them.
+struct GemmUnit {
+  int tile, kb0, kb1, slice;  // slice < 0: a whole tile with the normal epilogue
+};
+struct GemmSched {
+  int pair_id, num_pairs, i;
+  __device__ GemmSched(int pair, int pairs) : pair_id(pair), num_pairs(pairs), i(-1) {}
+  __device__ bool next(const GemmArgs& g, GemmUnit& u) {
+    if (g.split > 1) {
+      if (i < 0) {  // the K slice of a tail tile goes first: its partial is long in memory when the owner needs it
+        i = 0;
+        if (pair_id < g.tail_tiles * g.split) {
+          const int t = pair_id / g.split;
+          u.slice = pair_id - t * g.split;
+          u.tile = g.full_tiles + t;
+          u.kb0 = (int)((long long)g.num_k_blocks * u.slice / g.split);
+          u.kb1 = (int)((long long)g.num_k_blocks * (u.slice + 1) / g.split);
+          return true;
+        }
+      }
+      u.tile = pair_id + i * num_pairs;
+      if (u.tile >= g.full_tiles) return false;
+    } else {
+      if (i < 0) i = 0;
+      u.tile = pair_id + i * num_pairs;
+      if (u.tile >= g.num_m_tiles * g.num_n_tiles) return false;
+    }
+    ++i;
+    u.kb0 = 0, u.kb1 = g.num_k_blocks, u.slice = -1;
+    return true;
+  }
 };
 
 // Exact-erf GELU (nn.GELU() default, mlp.py:16,25) with erf from Abramowitz-Stegun 7.1.26 (|err| <= 1.5e-7,
@@ -140,7 +185,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
-  const int total_tiles = g.num_m_tiles * g.num_n_tiles;  // pair tiles (256 x 256)
   const uint32_t rank = cluster_ctarank();
   const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
 
@@ -176,10 +220,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
       uint32_t it = 0;
-      for (int tile = pair_id; tile < total_tiles; tile += num_pairs) {
-        const int m0 = (tile / g.num_n_tiles) * (2 * BM) + rank * BM;
-        const int n0 = (tile % g.num_n_tiles) * BN + rank * (BN / 2);
-        for (int kb = 0; kb < g.num_k_blocks; ++kb, ++it) {
+      GemmSched sched(pair_id, num_pairs);
+      for (GemmUnit u; sched.next(g, u);) {
+        const int m0 = (u.tile / g.num_n_tiles) * (2 * BM) + rank * BM;
+        const int n0 = (u.tile % g.num_n_tiles) * BN + rank * (BN / 2);
+        for (int kb = u.kb0; kb < u.kb1; ++kb, ++it) {
           const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
           mbar_wait(&empty[s], ph ^ 1);
           const uint32_t lead_full = mapa_shared(smem_u32(&full[s]), 0);
@@ -198,12 +243,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (rank == 0 && elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(2 * BM, BN, false, false);
       uint32_t it = 0, tcount = 0;
-      for (int tile = pair_id; tile < total_tiles; tile += num_pairs, ++tcount) {
+      GemmSched sched(pair_id, num_pairs);
+      for (GemmUnit u; sched.next(g, u); ++tcount) {
         const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
         mbar_wait(&tempty[acc], aph ^ 1);
         tcgen05_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int kb = 0; kb < g.num_k_blocks; ++kb, ++it) {
+        for (int kb = u.kb0; kb < u.kb1; ++kb, ++it) {
           const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
           mbar_wait(&full[s], ph);
           tcgen05_fence_after();
@@ -211,7 +257,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + s * B_BYTES), 16, 1024);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)  // +32 bytes (>>4 = 2) per 16-element K step inside the 128B swizzle row
-            umma_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            umma_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, ((kb - u.kb0) | k) != 0);
           umma_commit_pair(&empty[s], 3);
         }
         umma_commit_pair(&tfull[acc], 3);
@@ -230,7 +276,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint32_t tcount = 0;
     const uint32_t lead_tempty[2] = {mapa_shared(smem_u32(&tempty[0]), 0), mapa_shared(smem_u32(&tempty[1]), 0)};
 
-    for (int tile = pair_id; tile < total_tiles; tile += num_pairs, ++tcount) {
+    GemmSched sched(pair_id, num_pairs);
+    int own_tail = -1;  // tail tile whose slices this pair adds up at the end (it ran slice 0)
+    for (GemmUnit u; sched.next(g, u); ++tcount) {
+      const int tile = u.tile;
       const int m0 = (tile / g.num_n_tiles) * (2 * BM) + rank * BM;
       const int n0 = (tile % g.num_n_tiles) * BN + team * 128;
       const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
@@ -238,6 +287,37 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + team * 128 + lane_base;
       const int row = m0 + et;
+
+      if (EPI == EPI_RESID && u.slice >= 0) {
+        // ---- K slice of a tail tile: the raw accumulator goes to the workspace (plain stores, 128 B per thread and
+        // chunk), then one release-add per team tells the owner that this slice is in memory
+        const int t = tile - g.full_tiles;
+        float* dst = g.part + ((size_t)(t * g.split + u.slice) * 2 + rank) * (BM * BN) + (size_t)et * BN + team * 128;
+#pragma unroll 1
+        for (int ch = 0; ch < 4; ++ch) {
+          uint32_t v[32];
+          tmem_ld_x32(taddr + ch * 32, v);
+          tmem_wait_ld();
+          if (ch == 3) {
+            tcgen05_fence_before();
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(lead_tempty[acc]);
+          }
+          float4* d4 = reinterpret_cast<float4*>(dst + ch * 32);
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            d4[c] = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]), __uint_as_float(v[4 * c + 2]),
+                                __uint_as_float(v[4 * c + 3]));
+        }
+        __threadfence();
+        named_bar_sync(bar_id, 128);
+        if (et == 0) {
+          __threadfence();
+          atomicAdd(g.flags + (t * 2 + rank) * 2 + team, 1u);
+        }
+        if (u.slice == 0) own_tail = t;
+        continue;
+      }
 
       if (EPI == EPI_BIAS || EPI == EPI_GELU || EPI == EPI_QKV) {
         // ---- bf16 outputs: two 64-column groups per team (one attention head each for EPI_QKV)
@@ -356,6 +436,81 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       }
     }
+    if (EPI == EPI_RESID && own_tail >= 0) {
+      // ---- add up the K slices of the tail tile this pair owns, in slice order, and finish it like any other tile
+      const int t = own_tail, tile = g.full_tiles + t;
+      const int m0 = (tile / g.num_n_tiles) * (2 * BM) + rank * BM;
+      const int n0 = (tile % g.num_n_tiles) * BN + team * 128;
+      unsigned* flag = g.flags + (t * 2 + rank) * 2 + team;
+      if (et == 0) {
+        uint32_t spins = 0, t0 = 0;
+        for (;;) {
+          unsigned v;
+          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+          if (v >= (unsigned)g.split) break;
+          __nanosleep(64);
+          if ((++spins & 0xfffu) == 0) {  // bounded like every other wait of the library
+            uint32_t tt;
+            asm volatile("mov.u32 %0, %%globaltimer_hi;" : "=r"(tt));
+            if (t0 == 0)
+              t0 = tt | 0x80000000u;
+            else if (((tt | 0x80000000u) - t0) >= WM_MBAR_TIMEOUT_TICKS)
+              __trap();
+          }
+        }
+        *flag = 0;  // every slice has arrived and nobody else reads the counter: ready for the next launch
+        __threadfence();
+      }
+      named_bar_sync(bar_id, 128);
+      const float* src = g.part + ((size_t)(t * g.split) * 2 + rank) * (BM * BN) + (size_t)et * BN + team * 128;
+      const size_t slice_stride = (size_t)2 * BM * BN;
+#pragma unroll 1
+      for (int ch = 0; ch < 4; ++ch) {
+        const int col0 = n0 + ch * 32;
+        float o[32];
+        {
+          const float4* s4 = reinterpret_cast<const float4*>(src + ch * 32);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const float4 a = __ldcg(s4 + c);
+            o[4 * c] = a.x, o[4 * c + 1] = a.y, o[4 * c + 2] = a.z, o[4 * c + 3] = a.w;
+          }
+        }
+        for (int k = 1; k < g.split; ++k) {
+          const float4* s4 = reinterpret_cast<const float4*>(src + k * slice_stride + ch * 32);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const float4 a = __ldcg(s4 + c);
+            o[4 * c] += a.x, o[4 * c + 1] += a.y, o[4 * c + 2] += a.z, o[4 * c + 3] += a.w;
+          }
+        }
+        const float4* b4 = reinterpret_cast<const float4*>(g.bias + col0);
+        const float4* g4 = reinterpret_cast<const float4*>(g.gamma + col0);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const float4 b = __ldg(b4 + c);
+          float4 gm = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (g.gamma != nullptr) gm = __ldg(g4 + c);
+          o[4 * c] = gm.x * (o[4 * c] + b.x), o[4 * c + 1] = gm.y * (o[4 * c + 1] + b.y);
+          o[4 * c + 2] = gm.z * (o[4 * c + 2] + b.z), o[4 * c + 3] = gm.w * (o[4 * c + 3] + b.w);
+        }
+        if (et == 0) tma_store_wait_read<0>();
+        named_bar_sync(bar_id, 128);
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          st_shared_v4(stg + sw128_offset(et, c), __float_as_uint(o[4 * c]), __float_as_uint(o[4 * c + 1]),
+                       __float_as_uint(o[4 * c + 2]), __float_as_uint(o[4 * c + 3]));
+        fence_proxy_async_smem();
+        named_bar_sync(bar_id, 128);
+        if (et == 0) {
+          if (g.gamma != nullptr)
+            tma_reduce_add_2d(&tmC0, stg_ptr, col0, m0);
+          else
+            tma_store_2d(&tmC0, stg_ptr, col0, m0);
+          tma_store_commit();
+        }
+      }
+    }
     if (et == 0) tma_store_wait<0>();
   }
 
@@ -370,22 +525,39 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
 // ------------------------------------------------------------------------------------------------ host
 static int g_sm_count = 0;
+constexpr int kGemmMaxSplit = 4;  // more slices than this buy little (the tail is already < 1/4 wave) and cost fix-up reads
+
+size_t gemm_partial_bytes(int sm_count) { return (size_t)(sm_count / 2) * 2 * BM * BN * sizeof(float); }
 
 template <int EPI>
 static wm_status launch(cudaStream_t st, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c0,
                         const CUtensorMap& c1, GemmArgs g) {
   if (g_sm_count == 0) WM_TRY(require_sm100(&g_sm_count));
-  static bool configured = false;
-  if (!configured) {
+  static int cfg_dev[16] = {0};  // the shared-memory attribute is per device, not per process
+  int dev = 0;
+  WM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 16 || !cfg_dev[dev]) {
     WM_CUDA(cudaFuncSetAttribute(gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
-    configured = true;
+    if (dev >= 0 && dev < 16) cfg_dev[dev] = 1;
   }
   g.num_m_tiles = (g.M + 2 * BM - 1) / (2 * BM);  // pair tiles: 256 rows
   g.num_n_tiles = g.N / BN;
   g.num_k_blocks = (g.K + BK - 1) / BK;
   const int tiles = g.num_m_tiles * g.num_n_tiles;
   const int pairs = g_sm_count / 2;
-  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  int grid = 2 * (tiles < pairs ? tiles : pairs);
+  g.split = 1, g.full_tiles = tiles, g.tail_tiles = 0;
+  if (EPI == EPI_RESID && g.part != nullptr && g.flags != nullptr) {
+    // the tiles beyond the last full wave, cut along K so that they fill (most of) one more wave of pairs
+    const int full = (tiles / pairs) * pairs, tail = tiles - full;
+    int sp = tail > 0 ? pairs / tail : 1;
+    if (sp > kGemmMaxSplit) sp = kGemmMaxSplit;
+    if (sp > g.num_k_blocks) sp = g.num_k_blocks;
+    if (sp >= 2) {
+      g.split = sp, g.full_tiles = full, g.tail_tiles = tail;
+      grid = 2 * (full > 0 ? pairs : tail * sp);
+    }
+  }
   return launch_pdl(gemm_kernel<EPI>, dim3(grid), dim3(GEMM_THREADS), GEMM_SMEM, st, a, b, c0, c1, g);
 }
 
@@ -444,14 +616,17 @@ wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const
 }
 
 wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias,
-                           const float* gamma, int M, int N, int K, float* x, int ldx) {
+                           const float* gamma, int M, int N, int K, float* x, int ldx, float* part, size_t part_bytes,
+                           unsigned* flags) {
   WM_TRY(check_common(A, W, M, N, K, lda, ldw));
   WM_CHECK(x && bias && ldx % 4 == 0 && ldx >= N, "gemm_ls_residual: bad x");
+  if (g_sm_count == 0) WM_TRY(require_sm100(&g_sm_count));
   CUtensorMap ta, tb, tx;
   WM_TRY(operand_maps(&ta, &tb, A, lda, W, ldw, M, N, K));
   WM_TRY(tmap_2d(&tx, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, x, M, N, ldx, 32, 128));
   GemmArgs g{};
   g.M = M, g.N = N, g.K = K, g.bias = bias, g.gamma = gamma;
+  if (part != nullptr && flags != nullptr && part_bytes >= gemm_partial_bytes(g_sm_count)) g.part = part, g.flags = flags;
   return launch<EPI_RESID>(st, ta, tb, tx, tx, g);
 }
 

@@ -378,6 +378,22 @@ class B200CameraHead(torch.nn.Module):
         return outs
 
 
+def camera_matrices(camera_params: torch.Tensor, H: int, W: int):
+    """camera_params [S, 9] -> (camera-to-world [S, 4, 4], K [S, 3, 3]): `vector_to_camera_matrices` followed by the
+    inverse of the homogeneous world-to-camera matrix, as `WorldMirror._gen_all_preds` (worldmirror.py:161-175) and
+    `prepare_prediction_cameras` (rasterization.py:506-530) do.  One kernel (csrc/splat.cu: splat_camera_kernel); the
+    inverse is the closed form [R^T | -R^T t] instead of the reference's LU-based torch.linalg.inv."""
+    S, dev = camera_params.shape[0], camera_params.device
+    cam = torch.empty(S, 16, dtype=torch.float32, device=dev)
+    cp = camera_params.to(torch.float32).contiguous()
+    _k(capi.lib().wm_splat_cameras(_st(), cp.data_ptr(), S, H, W, cam.data_ptr()))
+    c2w = torch.zeros(S, 4, 4, dtype=torch.float32, device=dev)
+    c2w[:, :3, :3], c2w[:, :3, 3], c2w[:, 3, 3] = cam[:, :9].reshape(S, 3, 3), cam[:, 9:12], 1.0
+    K = torch.zeros(S, 3, 3, dtype=torch.float32, device=dev)
+    K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2], K[:, 2, 2] = cam[:, 12], cam[:, 13], cam[:, 14], cam[:, 15], 1.0
+    return c2w, K
+
+
 class B200GaussianSplatRenderer(torch.nn.Module):
     """`GaussianSplatRenderer` (src/models/models/rasterization.py:97-246) as far as `WorldMirror.forward` observes it:
     `render` fills `predictions["splats"]`.  The reference also rasterises every view with gsplat and then drops the
@@ -410,15 +426,7 @@ class B200GaussianSplatRenderer(torch.nn.Module):
 
     def prediction_cameras(self, camera_params, H: int, W: int):
         """prepare_prediction_cameras (rasterization.py:506-530): camera_params [S, 9] -> camera-to-world [S, 4, 4], K [S, 3, 3]."""
-        S, dev = camera_params.shape[0], camera_params.device
-        cam = torch.empty(S, 16, dtype=torch.float32, device=dev)
-        cp = camera_params.to(torch.float32).contiguous()
-        _k(capi.lib().wm_splat_cameras(_st(), cp.data_ptr(), S, H, W, cam.data_ptr()))
-        c2w = torch.zeros(S, 4, 4, dtype=torch.float32, device=dev)
-        c2w[:, :3, :3], c2w[:, :3, 3], c2w[:, 3, 3] = cam[:, :9].reshape(S, 3, 3), cam[:, 9:12], 1.0
-        K = torch.zeros(S, 3, 3, dtype=torch.float32, device=dev)
-        K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2], K[:, 2, 2] = cam[:, 12], cam[:, 13], cam[:, 14], cam[:, 15], 1.0
-        return c2w, K
+        return camera_matrices(camera_params, H, W)
 
     def load_state_dict(self, sd, strict: bool = True, device=None):
         """Reference keys: gs_head.0.weight [256, 128, 3, 3] (no bias), gs_head.2.weight [12, 256, 1, 1], gs_head.2.bias [12]."""
@@ -609,8 +617,9 @@ class B200GaussianSplatRenderer(torch.nn.Module):
 
 class B200WorldMirror(torch.nn.Module):
     """`WorldMirror.forward` (src/models/models/worldmirror.py:120-196) on the B200 path: aggregator, camera head and the
-    depth / points / normals DPT heads, same `views` dictionary in, same prediction keys out (`camera_params`, `depth`,
-    `depth_conf`, `pts3d`, `pts3d_conf`, `normals`, `normals_conf`).  With any cond_flag set the priors are extracted
+    depth / points / normals DPT heads, same `views` dictionary in, same prediction keys out (`camera_params`,
+    `camera_poses` [B,S,4,4] camera-to-world, `camera_intrs` [B,S,3,3], `depth`, `depth_conf`, `pts3d`, `pts3d_conf`,
+    `normals`, `normals_conf`; the key set is pinned against the reference's own forward, tests/golden/c1_preds.npz).  With any cond_flag set the priors are extracted
     from `views` (`camera_pose`, `depthmap`, `camera_intrinsics`) by `priors.extract_priors`, as `WorldMirror.forward`
     does (worldmirror.py:133-143); `priors` may instead pass the already normalised (depth, rays, poses).  With the
     Gaussian branch (`gs_head`, `gs_renderer`; worldmirror.py:202-217) the predictions also carry `gs_depth`,
@@ -678,7 +687,9 @@ class B200WorldMirror(torch.nn.Module):
             if priors is None:  # worldmirror.py:136-138: priors come from the views dictionary
                 from .priors import extract_priors
 
-                priors = extract_priors(views)
+                agg = self.visual_geometry_transformer
+                priors = extract_priors(views, group=getattr(agg, "_sp_group", None), world=getattr(agg, "world", 1),
+                                        rank=getattr(agg, "rank", 0))
             token_list, psi = self.visual_geometry_transformer(imgs, priors, cond_flags=list(cond_flags))
         else:
             token_list, psi = self.visual_geometry_transformer(imgs)
@@ -709,6 +720,10 @@ class B200WorldMirror(torch.nn.Module):
             side.wait_stream(main)
             with torch.cuda.stream(side):
                 preds["camera_params"] = self._camera(token_list)
+                # worldmirror.py:161-175: camera-to-world poses and intrinsics of the predicted cameras
+                mats = [camera_matrices(cp, imgs.shape[-2], imgs.shape[-1]) for cp in preds["camera_params"]]
+                preds["camera_poses"] = torch.stack([m[0] for m in mats], dim=0)
+                preds["camera_intrs"] = torch.stack([m[1] for m in mats], dim=0)
         if self.enable_gs:
             # The Gaussian branch goes first.  Its DPT head and the parameter head need no camera: they run on the main
             # stream.  Everything that does (prepare_splats, the gather across ranks, the voxel merge) continues on the side
@@ -743,14 +758,17 @@ class B200WorldMirror(torch.nn.Module):
                 emit(name + "_conf", preds[name + "_conf"])
         if side is not None:
             main.wait_stream(side)
-            preds["camera_params"].record_stream(main)
+            for k in ("camera_params", "camera_poses", "camera_intrs"):
+                preds[k].record_stream(main)
             if not self.enable_gs:
                 emit("camera_params", preds["camera_params"])
         if self.enable_gs:
             for out, count in preds.get("splats_pending", []):
                 for t in list(out.values()) + [count]:
                     t.record_stream(main)
-            preds = self.gs_renderer.finish(preds)
+            preds = self.gs_renderer.finish(preds)  # host read of the voxel count: the stream is drained here
+            if hasattr(self.visual_geometry_transformer, "raise_on_peer_timeout"):
+                self.visual_geometry_transformer.raise_on_peer_timeout()
         if copy is not None:
             main.wait_stream(copy)
         return preds

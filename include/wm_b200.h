@@ -105,9 +105,12 @@ wm_status wm_profile_read(wm_handle* h, int cls, float* total_ms, int* count);
 /* Kernel (and collective) launches issued by forwards since the last wm_profile() call. */
 long long wm_launch_count(const wm_handle* h);
 
-/* Tuning knobs: "attn_general_variant" (0-7), "attn_bounded_variant" (8-12), "attn_allow_bounded" (0/1),
- * "attn_balance" (0/1: even split of attention work with partial merge). */
+/* Tuning knobs: "attn_general_variant" (0-7, 20-23: attn_pipe.cu), "attn_bounded_variant" (8-12: attn_split.cu, 13-19: attn_pipe.cu),
+ * "attn_allow_bounded" (0/1), "attn_balance" (0/1: even split of attention work with partial merge), "sp_mode",
+ * "gemm_split" (0/1: K-split of the residual GEMMs' tail tiles).
+ * wm_get_int returns the current value, or -1 for an unknown name. */
 wm_status wm_set_int(wm_handle* h, const char* name, int value);
+int wm_get_int(const wm_handle* h, const char* name);
 /* Bound of |q . k| * scale * log2(e) implied by the QK-LayerNorm weights of block `layer` of kind 0 = DINOv2 (always 0),
  * 1 = frame, 2 = global; the forward uses the bounded-logit attention when 0 < bound <= 80.  -1: invalid argument. */
 float wm_logit_bound(const wm_handle* h, int kind, int layer);
@@ -124,8 +127,10 @@ wm_status wm_nccl_allgather(wm_handle* h, wm_stream stream, void* buf, size_t by
  * so the transfer overlaps the math.  Two buffers alternate per global block (no acknowledgement round trip).
  * wm_p2p_alloc: allocate this rank's block for up to max_rows_per_rank tokens per rank and return its
  * cudaIpcMemHandle_t (64 bytes); exchange the handles (rank order) and hand all of them to wm_p2p_attach.
- * Every rank must run the same sequence of forwards.  wm_p2p_status: *timed_out != 0 if a shard ever failed to
- * arrive within 4 s (the forward then finished on stale keys; treat as an error). */
+ * Every rank must run the same sequence of forwards.  A shard that fails to arrive within 4 s sets an error word and
+ * lets the launch finish on stale keys; the word is copied to pinned host memory behind every forward and the NEXT
+ * wm_forward / wm_forward_tokens returns WM_ERR_STATE once (and clears it) -- nothing blocks.  wm_p2p_status reads the
+ * word synchronously: *timed_out != 0 reports (and clears) it. */
 wm_status wm_p2p_alloc(wm_handle* h, int rank, int world, int max_rows_per_rank, void* ipc_handle_64);
 wm_status wm_p2p_attach(wm_handle* h, const void* ipc_handles_all /* world x 64 bytes */);
 wm_status wm_p2p_status(wm_handle* h, int* enabled, int* timed_out);
@@ -150,6 +155,13 @@ wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const floa
  * TMA reduce-add (each element is added exactly once: deterministic); gamma NULL: x = A W^T + bias. */
 wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
                               const float* gamma, int M, int N, int K, float* x, int ldx);
+/* The same with a workspace of wm_gemm_workspace_bytes() whose first 4096 bytes are ZERO at first use (the kernel leaves
+ * them zero): tiles beyond the last full wave of CTA pairs are cut along K, every slice leaves an fp32 partial in the
+ * workspace and the slices are added in fixed order before the one reduce-add per element (bit-deterministic). */
+wm_status wm_gemm_ls_residual_ws(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
+                                 const float* gamma, int M, int N, int K, float* x, int ldx, void* workspace,
+                                 size_t workspace_bytes);
+size_t wm_gemm_workspace_bytes(void);
 /* out[:, col0 : col0+1024] = x [rows,1024] fp32: one half of `cat([frame, global], -1)` (visual_transformer.py:337-339). */
 wm_status wm_copy_cols(wm_stream stream, const float* x, long long rows, float* out, int ld_out, int col0);
 /* out [M,N] fp32 = A W^T + table[row % period] (DINOv2 patch embed + pos_embed, vision_transformer.py:209-221). */

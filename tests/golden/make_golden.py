@@ -29,11 +29,17 @@ CASES = {
     "c1_priors": (2, 252, 252, [1, 1, 1], True),
     "rect_partial": (3, 168, 224, [1, 0, 1], True),
     "c2s_nopriors": (2, 518, 518, [0, 0, 0], False),
+    # the configuration bench.py times at N = 1 (BASELINE.json configs[1]): global attention over 11 008 tokens
+    "c2_nopriors": (8, 518, 518, [0, 0, 0], False),
+    # single-GPU stand-in for BASELINE.json configs[2] (pose + depth + intrinsics prior tokens at 518 x 518)
+    "c3s_priors": (4, 518, 518, [1, 1, 1], True),
 }
 
 
-def token_subset(P: int) -> np.ndarray:
-    idx = list(range(0, 9)) + list(np.linspace(9, P - 1, 15).astype(int))
+def token_subset(P: int, n_views: int = 2) -> np.ndarray:
+    """All seven special tokens, the first patches, and patches spread over the grid (fewer per view for many views,
+    so that a fixture stays a few MB; the per-token norms stored beside it cover EVERY token)."""
+    idx = list(range(0, 9)) + list(np.linspace(9, P - 1, 15 if n_views < 4 else 5).astype(int))
     return np.unique(np.array(idx, dtype=np.int64))
 
 
@@ -68,7 +74,7 @@ def main():
         dt = time.time() - t0
         assert psi == 7 and len(outs) == 4
         P = outs[0].shape[2]
-        sel = token_subset(P)
+        sel = token_subset(P, n)
         fx = {
             "n_views": n, "H": h, "W": w, "cond_flags": np.array(flags), "with_priors": with_priors,
             "token_idx": sel, "ref_seconds": dt, "torch": torch.__version__,

@@ -321,7 +321,7 @@ static int case_attn(int batch, int Lq, int Lkv, int heads, float qscale, int va
   const int ldq = heads * 64, ldkv = heads * 128;
   BF Q, KV;
   // variants >= 8 (bounded-logit mode): q arrives pre-multiplied by scale * log2(e) and P = 2^(q . k)
-  const bool bounded = variant >= 8;
+  const bool bounded = variant >= 8 && variant <= 19;  // 20..23: general softmax of the pipelined kernel
   Q.fill((size_t)batch * Lq * ldq, bounded ? qscale * 0.125f * 1.4426950408889634f : qscale);
   KV.fill((size_t)batch * Lkv * ldkv, 1.0f);
   uint16_t *dq = dev(Q.h), *dkv = dev(KV.h);
@@ -449,6 +449,84 @@ static int bench_ln(int rows) {
   return 0;
 }
 
+static int bench_copy(int rows) {  // a17: one half of cat([frame, global], -1): read 4096 B + write 4096 B per token
+  struct C {
+    float *x, *out;
+    int rows;
+  } c;
+  c.rows = rows;
+  c.x = dev(randf((size_t)rows * 1024, 1.0f));
+  c.out = dev_alloc<float>((size_t)rows * 2048);
+  const float ms = time_ms(20, [](void* p) { C* c = (C*)p; WM(wm_copy_cols(0, c->x, c->rows, c->out, 2048, 1024)); }, &c);
+  printf("BENCH copy_cols rows=%d  %.4f ms  %.0f GB/s\n", rows, ms, rows * 8192.0 / ms * 1e-6);
+  return 0;
+}
+
+static int bench_gather(int views, int H, int W) {  // a1 + a2: normalise + im2col(14 x 14): read 4 B, write 2 B per pixel-channel
+  struct C {
+    float* img;
+    uint16_t* out;
+    int n, H, W, rows;
+  } c;
+  c.n = views, c.H = H, c.W = W, c.rows = 5 + (H / 14) * (W / 14);
+  c.img = dev(randf((size_t)views * 3 * H * W, 0.5f, 0.5f));
+  c.out = dev_alloc<uint16_t>((size_t)views * c.rows * 640, 0);
+  const float ms = time_ms(20, [](void* p) { C* c = (C*)p; WM(wm_patch_gather(0, c->img, c->n, 3, c->H, c->W, c->rows, 5, 640, 1, c->out)); }, &c);
+  printf("BENCH patch_gather views=%d %dx%d  %.4f ms  %.0f GB/s\n", views, H, W, ms, (double)views * 3 * H * W * 6.0 / ms * 1e-6);
+  return 0;
+}
+
+// MUFU.EX2 issue rate per data type: does the fp16 / bf16 form of ex2 run faster than the fp32 one on sm_100a?
+// (cuobjdump: ex2.approx.f16x2 / .bf16x2 each become TWO MUFU.EX2.F16 / .BF16 + PRMT, so only a higher unit rate could
+// make the packed forms pay.)  One CTA per SM, 16 warps, a long dependent-free stream of ex2 per thread.
+template <int MODE>
+__global__ void mufu_rate_kernel(float* out, int iters) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 0.1f, a2 = a0 + 0.2f, a3 = a0 + 0.3f;
+  unsigned h0 = 0x3c003800u + threadIdx.x, h1 = h0 + 7, h2 = h0 + 13, h3 = h0 + 29;
+  for (int i = 0; i < iters; ++i) {
+    if (MODE == 0) {
+      asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a0));
+      asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a1));
+      asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a2));
+      asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a3));
+    } else if (MODE == 1) {
+      asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(h0));
+      asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(h1));
+      asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(h2));
+      asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(h3));
+    } else {
+      asm volatile("ex2.approx.ftz.bf16x2 %0, %0;" : "+r"(h0));
+      asm volatile("ex2.approx.ftz.bf16x2 %0, %0;" : "+r"(h1));
+      asm volatile("ex2.approx.ftz.bf16x2 %0, %0;" : "+r"(h2));
+      asm volatile("ex2.approx.ftz.bf16x2 %0, %0;" : "+r"(h3));
+    }
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + __uint_as_float(h0 ^ h1 ^ h2 ^ h3);
+}
+static int bench_mufu() {
+  float* out = dev_alloc<float>(148 * 512);
+  const int iters = 20000;
+  for (int mode = 0; mode < 3; ++mode) {
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a));
+    CK(cudaEventCreate(&b));
+    for (int rep = 0; rep < 2; ++rep) {
+      CK(cudaEventRecord(a));
+      if (mode == 0) mufu_rate_kernel<0><<<148, 512>>>(out, iters);
+      if (mode == 1) mufu_rate_kernel<1><<<148, 512>>>(out, iters);
+      if (mode == 2) mufu_rate_kernel<2><<<148, 512>>>(out, iters);
+      CK(cudaEventRecord(b));
+      CK(cudaEventSynchronize(b));
+    }
+    float ms;
+    CK(cudaEventElapsedTime(&ms, a, b));
+    const double results = 148.0 * 512 * iters * 4 * (mode == 0 ? 1 : 2);
+    printf("BENCH mufu ex2 %-7s %.3f ms  %.1f G results/s  (%.2f results/clk/SM at 1.9 GHz)\n",
+           mode == 0 ? "f32" : mode == 1 ? "f16x2" : "bf16x2", ms, results / ms * 1e-6, results / ms * 1e-6 / 148 / 1.9);
+  }
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 2) {
     printf("usage: selftest <case> [args]\n");
@@ -466,6 +544,9 @@ int main(int argc, char** argv) {
   if (c == "bench_gemm") return bench_gemm(I(2, 0), I(3, 11008), I(4, 1024), I(5, 1024));
   if (c == "bench_attn") return bench_attn(I(2, 1), I(3, 11008), I(4, 11008), I(5, 16), I(6, 0), I(7, 0));
   if (c == "bench_ln") return bench_ln(I(2, 11008));
+  if (c == "bench_copy") return bench_copy(I(2, 11008));
+  if (c == "bench_gather") return bench_gather(I(2, 8), I(3, 518), I(4, 518));
+  if (c == "bench_mufu") return bench_mufu();
   printf("unknown case %s\n", c.c_str());
   return 64;
 }
