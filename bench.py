@@ -44,6 +44,21 @@ def flops_aggregator(n_local, n_total, P=1376):
                 total=dino + frame + glob_lin + glob_attn)
 
 
+def class_work(n_local, n_total, P=1376):
+    """Algorithmic work of one step per profiling class of the library (capi.PROF_CLASSES): FLOPs for the tensor-bound
+    classes (2 M N K per GEMM, 4 Lq Lkv 64 per head for attention), bytes for the HBM-bound LayerNorm (fp32 row in,
+    bf16 row out, two per block).  DINOv2 blocks see P-2 tokens per view, frame and global blocks P."""
+    T, Tall, Pd = n_local * P, n_total * P, P - 2
+    rows = 24 * (n_local * Pd + 2 * T)  # token rows through one linear layer of every block
+    return {
+        "gemm_qkv": ("tensor", rows * 2 * 1024 * 3072), "gemm_proj": ("tensor", rows * 2 * 1024 * 1024),
+        "gemm_fc1": ("tensor", rows * 2 * 1024 * 4096), "gemm_fc2": ("tensor", rows * 2 * 4096 * 1024),
+        "attn_local": ("tensor", 24 * n_local * 4 * 1024 * (Pd * Pd + P * P)),
+        "attn_global": ("tensor", 24 * T * 4 * 1024 * Tall),
+        "layernorm": ("hbm", 2 * rows * 1024 * (4 + 2)),
+    }
+
+
 class ClockSampler:
     """SM clock + throttle reasons sampled while the timed region runs (B200_PROFILING.md clocks line)."""
 
@@ -129,8 +144,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    # bounded sample of the 8-view workload so that warmup + steps stay within a few minutes (~7 s / view here)
-    sample_views = 2 if (args.steps + args.warmup) <= 14 else 1
+    # Bounded sample of the 8-view workload: the largest view count N in [2, 8] whose warmup + steps forwards stay within
+    # ~5 minutes of host time (~7.5 s / view / forward on the GPU box's cores, measured in round 1); N >= 2 keeps
+    # cross-view (global) attention in the CPU number.  All 8 views (the timed config itself) when steps + warmup <= 5.
+    sample_views = max(2, min(VIEWS_PER_RANK, int(300.0 / (7.5 * max(args.steps + args.warmup, 1)))))
     times, cores = cpu_reference_steps(sample_views, args.steps, args.warmup, not args.no_heads, not args.no_gs)
     total = sum(times)
     value = sample_views * len(times) / total
@@ -140,7 +157,7 @@ def run_reference(args):
             "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"WorldMirror fwd, {VIEWS_PER_RANK} views {SIZE}x{SIZE}, no priors (BASELINE configs[1])",
-                       "views_per_gpu": VIEWS_PER_RANK, "size": SIZE},
+                       "views_per_gpu": VIEWS_PER_RANK, "size": SIZE, "reference_sample_views": sample_views},
             "cpu_baseline": {"value": value, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -177,8 +194,12 @@ def run_b200(args):
         k, v = kv.split("=")
         capi.check(capi.lib().wm_set_int(model._handle, k.encode(), int(v)))
     n_local, n_total = args.views, args.views * world
-    imgs_host = W.synthetic_images(n_total, SIZE, SIZE, seed=1)[:, rank * n_local:(rank + 1) * n_local].contiguous().pin_memory()
+    sl_views = slice(rank * n_local, (rank + 1) * n_local)
+    imgs_all = W.synthetic_images(n_total, SIZE, SIZE, seed=1)
+    imgs_host = imgs_all[:, rank * n_local:(rank + 1) * n_local].contiguous().pin_memory()
     imgs_dev = imgs_host.to(dev)
+    if world == 1 or args.no_sp_parity:
+        del imgs_all
     prior_in = None
     if args.priors:  # BASELINE.json configs[2]: camera-pose + depth + intrinsics prior tokens (SURVEY.md section 8d inputs)
         pose_all, depth_all, intr_all = W.synthetic_scene(n_total, SIZE, SIZE, seed=2)
@@ -194,6 +215,36 @@ def run_b200(args):
 
     flags = [1, 1, 1] if args.priors else [0, 0, 0]
     lib = capi.lib()
+
+    # ---- N > 1: parity of the sharded forward BEFORE anything is timed.  The model that is about
+    # to be timed (full depth, this rank's views, peer-memory K|V exchange) against a single-GPU forward of ALL views by a
+    # second, non-parallel instance with the same weights on this rank's GPU.  No value is printed if it fails.
+    sp_parity = None
+    if world > 1 and not args.no_sp_parity:
+        with torch.no_grad():
+            pri = priors_now() if args.priors else None
+            outs, _ = model(imgs_dev, pri, cond_flags=flags)
+            outs = [o.clone() for o in outs]
+            ref = pkg.B200VisualGeometryTransformer()
+            ref.load_state_dict(W.synthetic_state_dict(seed=0))
+            pri_all = None
+            if args.priors:
+                depth_all = W.synthetic_scene(n_total, SIZE, SIZE, seed=2)[1].to(dev)
+                pri_all = pkg.priors.extract_priors({"img": imgs_all.to(dev), **prior_in, "depthmap": depth_all})
+                del depth_all
+            full_out, _ = ref(imgs_all.to(dev), pri_all, cond_flags=flags)
+            torch.cuda.synchronize()
+            errs = [((a - f[:, sl_views]).norm() / f[:, sl_views].norm()).item() for a, f in zip(outs, full_out)]
+        del ref, full_out, outs, imgs_all, pri_all
+        torch.cuda.empty_cache()
+        t = torch.tensor([max(errs)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        gate = 5e-3
+        sp_parity = {"rel_fro": t.item(), "gate": gate, "ok": bool(t.item() <= gate),
+                     "what": f"token_list of the sharded forward ({n_local} views on each of {world} GPUs, full depth, the timed model) vs a "
+                             f"single-GPU forward of all {n_total} views on every rank's own GPU; worst of 4 outputs, max over ranks"}
+        if not sp_parity["ok"]:
+            raise SystemExit(f"sp_parity failed: {json.dumps(sp_parity)} -- no value printed")
 
     def barrier():
         if world > 1:
@@ -316,6 +367,68 @@ def run_b200(args):
     e2e = {"value": n_total / (e2e_ms * 1e-3), "unit": "views/s", "h2d_bytes_per_step": imgs_host.numel() * 4,
            "d2h_bytes_per_step": d2h_bytes + splat_bytes[0], "ms_per_step": e2e_ms}
 
+    # ---- the same global attention through the GENERAL kernel (running max, no logit bound): what a checkpoint whose
+    # QK-norm weights exceed the bound would get.  Two extra forwards, outside every timed region.
+    roofline_general = None
+    if not args.no_extras:
+        capi.check(lib.wm_set_int(model._handle, b"attn_allow_bounded", 0))
+        g_total = timed(lambda: model(imgs_dev, priors_now() if args.priors else None, cond_flags=flags), 2, 1, prof_mask=1 << 3)
+        g_ms, g_n = capi.C.c_float(), capi.C.c_int()
+        capi.check(lib.wm_profile_read(model._handle, 3, capi.C.byref(g_ms), capi.C.byref(g_n)))
+        capi.check(lib.wm_profile(model._handle, 0))
+        capi.check(lib.wm_set_int(model._handle, b"attn_allow_bounded", 1))
+        g_avg = g_ms.value / max(g_n.value, 1)
+        roofline_general = {"kernel": "global attention, general softmax (attn_allow_bounded=0, variant %d), Lq=%d Lkv=%d" % (
+                                lib.wm_get_int(model._handle, b"attn_general_variant"), n_local * 1376, n_total * 1376),
+                            "bound": "tensor", "achieved": flops_aggregator(n_local, n_total)["global_attention"] / 24 / (g_avg * 1e-3) / 1e12,
+                            "unit": "TFLOP/s", "avg_launch_ms": g_avg, "launches_timed": g_n.value,
+                            "aggregator_ms_per_step": g_total / 2}
+
+    # ---- strong scaling: ONE fixed 64-view scene on N GPUs, aggregator + heads, images resident
+    strong = None
+    STRONG_VIEWS = 64
+    if not args.no_extras and not args.priors and STRONG_VIEWS % world == 0:
+        per = STRONG_VIEWS // world
+        if per == n_local:
+            strong = {"views_total": STRONG_VIEWS, "views_per_gpu": per, "ms_per_step": ms_per_step,
+                      "views_per_s": STRONG_VIEWS / (ms_per_step * 1e-3), "note": "identical to the weak line at this N"}
+        else:
+            s_imgs = W.synthetic_images(STRONG_VIEWS, SIZE, SIZE, seed=1)[:, rank * per:(rank + 1) * per].contiguous().to(dev)
+
+            def step_strong():
+                if heads_on:
+                    full({"img": s_imgs})
+                else:
+                    model(s_imgs)
+
+            s_ms = timed(step_strong, 2, 1) / 2
+            strong = {"views_total": STRONG_VIEWS, "views_per_gpu": per, "ms_per_step": s_ms, "views_per_s": STRONG_VIEWS / (s_ms * 1e-3),
+                      "steps": 2, "warmup": 1}
+            del s_imgs
+            torch.cuda.empty_cache()
+
+    # ---- same-box comparator: stock PyTorch (cuBLAS, its SDPA backends, autocast bf16) on the shapes of this path;
+    # rank 0 at N = 1 only, after every timed region of ours
+    torch_gpu = None
+    if world == 1 and not args.no_extras:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_torch_gpu as TG
+
+            torch_gpu = {"note": "stock PyTorch on this GPU, measured after (outside) every timed region of this bench; "
+                                 "tools/bench_torch_gpu.py"}
+            qkv = [torch.randn(1, 16, n_total * 1376, 64, device=dev, dtype=torch.bfloat16) for _ in range(3)]
+            ms = TG.time_ms(lambda: torch.nn.functional.scaled_dot_product_attention(*qkv), 10)
+            torch_gpu["sdpa_global"] = {"shape": [1, 16, n_total * 1376, 64], "ms": ms, "tflops": 4.0 * (n_total * 1376) ** 2 * 1024 / ms * 1e-9}
+            qkv = [torch.randn(n_local, 16, 1376, 64, device=dev, dtype=torch.bfloat16) for _ in range(3)]
+            ms = TG.time_ms(lambda: torch.nn.functional.scaled_dot_product_attention(*qkv), 10)
+            torch_gpu["sdpa_frame"] = {"shape": [n_local, 16, 1376, 64], "ms": ms, "tflops": 4.0 * n_local * 1376 ** 2 * 1024 / ms * 1e-9}
+            del qkv
+            torch_gpu["aggregator_autocast_bf16"] = TG.model_level(n_local, 3)
+            torch.cuda.empty_cache()
+        except Exception as e:  # a comparator must never take the bench down
+            torch_gpu = {"unavailable": f"{type(e).__name__}: {e}"}
+
     sp_exchange = None
     if world > 1:
         enabled, timed_out = model.peer_gather_status()
@@ -348,11 +461,25 @@ def run_b200(args):
                     "traffic": traffic, "peak_source": peak_src, "avg_launch_ms": attn_avg_ms, "launches_timed": attn_n.value,
                     "share_of_step": attn_ms.value / total_ms,
                     "whole_step_tflops": None if heads_on else fl["total"] / (ms_per_step * 1e-3) / 1e12}
+        peak_hbm = peaks.get("hbm_gbs") or 6500.0
+        kernels = []
+        for cls, (bound, work) in class_work(n_local, n_total).items():
+            if cls in breakdown and breakdown[cls]["ms"] > 0:
+                ms = breakdown[cls]["ms"]
+                ach = work / (ms * 1e-3) / (1e12 if bound == "tensor" else 1e9)
+                kernels.append({"class": cls, "bound": bound, "work": work, "work_unit": "FLOP" if bound == "tensor" else "bytes",
+                                "ms": ms, "launches": breakdown[cls]["launches"], "achieved": round(ach, 1),
+                                "unit": "TFLOP/s" if bound == "tensor" else "GB/s",
+                                "frac": round(ach / (peak_tf if bound == "tensor" else peak_hbm), 3)})
+        roofline["kernels"] = kernels
+        roofline["kernels_note"] = ("per class of one step from the event-per-launch breakdown pass (breakdown_ms); tensor classes against "
+                                    "bf16_tflops_sustained, layernorm against hbm_gbs of MEASURED_PEAKS.json")
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            t, cores = cpu_reference_steps(2, 1, 0, heads_on, gs_on)
-            cpu = {"value": 2 / t[0], "unit": "views/s", "cores": cores, "kind": "port",
-                   "sample": f"2 of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth{' + camera and 3 DPT heads' if heads_on else ''}{' + Gaussian branch' if gs_on else ''}, fp32, "
+            cpu_views = 4
+            t, cores = cpu_reference_steps(cpu_views, 1, 0, heads_on, gs_on)
+            cpu = {"value": cpu_views / t[0], "unit": "views/s", "cores": cores, "kind": "port",
+                   "sample": f"{cpu_views} of {VIEWS_PER_RANK} views at {SIZE}x{SIZE}, full depth{' + camera and 3 DPT heads' if heads_on else ''}{' + Gaussian branch' if gs_on else ''}, fp32, "
                              f"one forward ({t[0]:.1f} s); oracle/aggregator_oracle.py{' + oracle/heads_oracle.py' if heads_on else ''}{' + oracle/gs_oracle.py' if gs_on else ''}"}
         line = {"metric": METRIC, "value": value, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
@@ -372,6 +499,15 @@ def run_b200(args):
                 "breakdown_ms": breakdown}
         if cpu:
             line["cpu_baseline"] = cpu
+        if roofline_general is not None:
+            roofline_general.update(peak=peak_tf, frac=roofline_general["achieved"] / peak_tf)
+            line["roofline_general"] = roofline_general
+        if sp_parity is not None:
+            line["sp_parity"] = sp_parity
+        if strong is not None:
+            line["strong"] = strong
+        if torch_gpu is not None:
+            line["torch_gpu_baseline"] = torch_gpu
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -388,6 +524,8 @@ def main():
     ap.add_argument("--no-heads", action="store_true", help="time the aggregator alone (the round-1 workload before the heads existed)")
     ap.add_argument("--no-gs", action="store_true", help="leave the Gaussian branch (gs_depth, splats) out of the step")
     ap.add_argument("--priors", action="store_true", help="BASELINE configs[2]: pose + depth + intrinsics priors, cond_flags [1,1,1]")
+    ap.add_argument("--no-sp-parity", action="store_true", help="N > 1: skip the sharded-vs-single-GPU parity forward before timing")
+    ap.add_argument("--no-extras", action="store_true", help="skip roofline_general, strong and torch_gpu_baseline (all outside the timed regions)")
     ap.add_argument("--set", action="append", default=[], metavar="KNOB=INT", help="wm_set_int tuning knob (repeatable)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -216,7 +216,6 @@ struct Workspace {
   float *xd, *x;
   __nv_bfloat16 *ln, *q, *kv, *att, *hid;
   float* attn_part;  // partials of attention work items split between CTAs (attn_split.cu)
-  float* gemm_part;  // K slices of the residual GEMMs' tail tiles (gemm.cu)
   size_t bytes;
 };
 
@@ -240,7 +239,6 @@ static Workspace carve(void* base, int n, int gh, int gw, int world) {
   ws.att = reinterpret_cast<__nv_bfloat16*>(take(T * kEmbed * 2));
   ws.hid = reinterpret_cast<__nv_bfloat16*>(take(T * kMlp * 2));
   ws.attn_part = reinterpret_cast<float*>(take(attn_partial_bytes(kNumSms)));
-  ws.gemm_part = reinterpret_cast<float*>(take(gemm_partial_bytes(kNumSms)));
   ws.bytes = off + 1024;  // slack so the caller's base may be aligned up to 1024
   return ws;
 }
@@ -339,13 +337,12 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
         flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
                         0.125f, bounded ? h->attn_bounded_variant : h->attn_general_variant,
                         h->attn_balance ? ws.attn_part : nullptr, attn_partial_bytes(kNumSms), p2p ? &ag : nullptr));
-  float* gpart = h->gemm_split ? ws.gemm_part : nullptr;
+  unsigned* gflags = h->gemm_split ? h->gemm_flags : nullptr;
   WM_OP(WM_PROF_PROJ, gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x,
-                                       kEmbed, gpart, gemm_partial_bytes(kNumSms), h->gemm_flags));
+                                       kEmbed, gflags));
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n2w, w.n2b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
   WM_OP(WM_PROF_FC1, gemm_bias_act(st, ws.ln, kEmbed, w.fc1_w, kEmbed, w.fc1_b, s.T, kMlp, kEmbed, ws.hid, kMlp, 1));
-  WM_OP(WM_PROF_FC2, gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed, gpart,
-                                      gemm_partial_bytes(kNumSms), h->gemm_flags));
+  WM_OP(WM_PROF_FC2, gemm_ls_residual(st, ws.hid, kMlp, w.fc2_w, kMlp, w.fc2_b, w.ls2, s.T, kEmbed, kMlp, x, kEmbed, gflags));
   if (out2) WM_OP(WM_PROF_EMBED, copy_cols(st, x, s.T, out2, 2 * kEmbed, out2_col));
   return WM_OK;
 }
@@ -956,15 +953,14 @@ wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const vo
 wm_status wm_gemm_ls_residual_ws(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
                                  const float* gamma, int M, int N, int K, float* x, int ldx, void* workspace,
                                  size_t workspace_bytes) {
-  // workspace = [kGemmFlagBytes of counters, zero at first use and left zero | partial accumulators]
+  // workspace = kGemmFlagBytes of slice counters, zero at first use and left zero by every launch
   WM_CHECK(workspace && workspace_bytes >= wm_gemm_workspace_bytes(), "wm_gemm_ls_residual_ws: workspace too small");
-  uint8_t* p = static_cast<uint8_t*>(workspace);
+  WM_CHECK((reinterpret_cast<uintptr_t>(workspace) & 3) == 0, "wm_gemm_ls_residual_ws: workspace must be 4-byte aligned");
   return gemm_ls_residual(static_cast<cudaStream_t>(stream), A, lda, W, ldw, bias, gamma, M, N, K, x, ldx,
-                          reinterpret_cast<float*>(p + kGemmFlagBytes), workspace_bytes - kGemmFlagBytes,
-                          reinterpret_cast<unsigned*>(p));
+                          static_cast<unsigned*>(workspace));
 }
 
-size_t wm_gemm_workspace_bytes(void) { return kGemmFlagBytes + gemm_partial_bytes(kNumSms); }
+size_t wm_gemm_workspace_bytes(void) { return kGemmFlagBytes; }
 
 wm_status wm_copy_cols(wm_stream stream, const float* x, long long rows, float* out, int ld_out, int col0) {
   int sms;

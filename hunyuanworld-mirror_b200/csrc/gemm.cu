@@ -22,12 +22,16 @@
 // TMA stores / reduce-adds (row clipping for the M tail comes for free).
 //
 // Tail split (EPI_RESID, N = 1024: proj / fc2).  172 pair tiles on 74 CTA pairs are 2.32 waves and used to run as 3.
-// With a partial workspace the tiles beyond the last FULL wave are cut along K into `split` slices, one per CTA pair,
-// and run FIRST: every slice leaves its raw fp32 accumulator in the workspace and raises a per-(tile, rank, team)
-// counter; the pairs then run their whole tiles as before; at the very end the owner (slice 0) of each tail tile adds
-// the slices IN FIXED ORDER (0, 1, .. split-1), applies bias and LayerScale and issues the one TMA reduce-add per
-// element.  Every element of x still receives exactly one add, in an order that does not depend on timing: the
-// forward stays bit-deterministic.  2 + 1/3 waves instead of 3.
+// With a word of counters per (tail tile, rank, team) the tiles beyond the last FULL wave are cut along K into `split`
+// slices, one per CTA pair, and run FIRST.  Every slice adds its share gamma * (acc_s [+ b for s = 0]) to x with the
+// same TMA reduce-add as a whole tile, but IN SLICE ORDER: the epilogue team of slice s waits for the counter to reach
+// s (slice s-1 has seen its reduce-adds complete, cp.async.bulk.wait_group 0, then released the counter), the last
+// slice writes 0 back.  x = ((x + g (p0 + b)) + g p1) + g p2: one fixed order of fp32 additions, independent of
+// timing, so the forward stays bit-deterministic; no partial-sum workspace, no fix-up pass.  The slices are the first
+// unit of distinct pairs of one co-resident persistent grid (no deadlock), and while a team waits the MMA warp runs
+// on with the pair's next tile in the other TMEM accumulator.  2 + 1/3 waves instead of 3.
+// (A first version parked fp32 partials in a workspace and let the owner add them at the end: row-strided 16-byte
+// accesses and a serial fix-up made it SLOWER than 3 waves, 48 vs 25 us for proj; profiles/r02_s2_selftest.log.)
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -59,8 +63,7 @@ struct GemmArgs {
   int table_period;
   // tail split (EPI_RESID only; split == 1: every pair walks whole tiles round-robin, as the other epilogues do)
   int split, full_tiles, tail_tiles;  // tiles [0, full_tiles) whole; tiles [full_tiles, full_tiles + tail_tiles) in `split` K slices
-  float* part;      // [tail_tiles][split][2 ranks][128 rows][256 cols] fp32 partial accumulators
-  unsigned* flags;  // [tail_tiles][2 ranks][2 teams] arrival counters; zero before the launch, left zero by it
+  unsigned* flags;  // [tail_tiles][2 ranks][2 teams] slice counters; zero before the launch, left zero by it
 };
 
 // The work units of one CTA pair, in the order every role of the pair walks them.
@@ -72,7 +75,7 @@ struct GemmSched {
   __device__ GemmSched(int pair, int pairs) : pair_id(pair), num_pairs(pairs), i(-1) {}
   __device__ bool next(const GemmArgs& g, GemmUnit& u) {
     if (g.split > 1) {
-      if (i < 0) {  // the K slice of a tail tile goes first: its partial is long in memory when the owner needs it
+      if (i < 0) {  // the K slice of a tail tile goes first: the ordered adds finish under the whole tiles
         i = 0;
         if (pair_id < g.tail_tiles * g.split) {
           const int t = pair_id / g.split;
@@ -95,6 +98,25 @@ struct GemmSched {
     return true;
   }
 };
+
+// Spin until *flag >= want (acquire, gpu scope), bounded like every other wait of the library.
+__device__ __forceinline__ void wait_flag_ge(const unsigned* flag, unsigned want) {
+  uint32_t spins = 0, t0 = 0;
+  for (;;) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if (v >= want) return;
+    __nanosleep(32);
+    if ((++spins & 0xfffu) == 0) {
+      uint32_t tt;
+      asm volatile("mov.u32 %0, %%globaltimer_hi;" : "=r"(tt));
+      if (t0 == 0)
+        t0 = tt | 0x80000000u;
+      else if (((tt | 0x80000000u) - t0) >= WM_MBAR_TIMEOUT_TICKS)
+        __trap();
+    }
+  }
+}
 
 // Exact-erf GELU (nn.GELU() default, mlp.py:16,25) with erf from Abramowitz-Stegun 7.1.26 (|err| <= 1.5e-7,
 // far below the bf16 rounding of the output): Phi(x) = 1 - h for x >= 0, h for x < 0,
@@ -277,7 +299,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t lead_tempty[2] = {mapa_shared(smem_u32(&tempty[0]), 0), mapa_shared(smem_u32(&tempty[1]), 0)};
 
     GemmSched sched(pair_id, num_pairs);
-    int own_tail = -1;  // tail tile whose slices this pair adds up at the end (it ran slice 0)
     for (GemmUnit u; sched.next(g, u); ++tcount) {
       const int tile = u.tile;
       const int m0 = (tile / g.num_n_tiles) * (2 * BM) + rank * BM;
@@ -287,37 +308,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + team * 128 + lane_base;
       const int row = m0 + et;
-
-      if (EPI == EPI_RESID && u.slice >= 0) {
-        // ---- K slice of a tail tile: the raw accumulator goes to the workspace (plain stores, 128 B per thread and
-        // chunk), then one release-add per team tells the owner that this slice is in memory
-        const int t = tile - g.full_tiles;
-        float* dst = g.part + ((size_t)(t * g.split + u.slice) * 2 + rank) * (BM * BN) + (size_t)et * BN + team * 128;
-#pragma unroll 1
-        for (int ch = 0; ch < 4; ++ch) {
-          uint32_t v[32];
-          tmem_ld_x32(taddr + ch * 32, v);
-          tmem_wait_ld();
-          if (ch == 3) {
-            tcgen05_fence_before();
-            __syncwarp();
-            if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(lead_tempty[acc]);
-          }
-          float4* d4 = reinterpret_cast<float4*>(dst + ch * 32);
-#pragma unroll
-          for (int c = 0; c < 8; ++c)
-            d4[c] = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]), __uint_as_float(v[4 * c + 2]),
-                                __uint_as_float(v[4 * c + 3]));
-        }
-        __threadfence();
-        named_bar_sync(bar_id, 128);
-        if (et == 0) {
-          __threadfence();
-          atomicAdd(g.flags + (t * 2 + rank) * 2 + team, 1u);
-        }
-        if (u.slice == 0) own_tail = t;
-        continue;
-      }
 
       if (EPI == EPI_BIAS || EPI == EPI_GELU || EPI == EPI_QKV) {
         // ---- bf16 outputs: two 64-column groups per team (one attention head each for EPI_QKV)
@@ -385,7 +375,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
         }
       } else {
-        // ---- fp32 outputs: four 32-column chunks per team
+        // ---- fp32 outputs: four 32-column chunks per team.  A K slice of a tail tile (u.slice >= 0) adds its share of the
+        // product to x with the same TMA reduce-add, in SLICE ORDER: slice s waits until slice s-1 has published that its
+        // reduce-adds are complete (x = ((x + g (p0 + b)) + g p1) + g p2, one fixed order: bit-deterministic), and only
+        // slice 0 carries the bias.  The slices are the first unit of distinct, co-resident pairs, and the MMA warp runs
+        // on with the pair's next tile in the other accumulator while the epilogue team waits.
+        const bool sliced = EPI == EPI_RESID && u.slice >= 0;
+        const bool later = sliced && u.slice > 0;
+        unsigned* flag = sliced ? g.flags + ((tile - g.full_tiles) * 2 + rank) * 2 + team : nullptr;
 #pragma unroll 1
         for (int ch = 0; ch < 4; ++ch) {
           const int col0 = n0 + ch * 32;
@@ -411,7 +408,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const float4* g4 = reinterpret_cast<const float4*>(g.gamma + col0);
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
-              const float4 b = __ldg(b4 + c);
+              float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (!later) b = __ldg(b4 + c);
               float4 gm = make_float4(1.f, 1.f, 1.f, 1.f);
               if (g.gamma != nullptr) gm = __ldg(g4 + c);
               o[4 * c] = gm.x * (__uint_as_float(v[4 * c]) + b.x), o[4 * c + 1] = gm.y * (__uint_as_float(v[4 * c + 1]) + b.y);
@@ -427,87 +425,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           fence_proxy_async_smem();
           named_bar_sync(bar_id, 128);
           if (et == 0) {
-            if (EPI == EPI_RESID && g.gamma != nullptr)
+            if (later && ch == 0) wait_flag_ge(flag, (unsigned)u.slice);
+            if (EPI == EPI_RESID && (g.gamma != nullptr || later))
               tma_reduce_add_2d(&tmC0, stg_ptr, col0, m0);  // x += gamma * (acc + b), added at L2
             else
               tma_store_2d(&tmC0, stg_ptr, col0, m0);
             tma_store_commit();
           }
         }
-      }
-    }
-    if (EPI == EPI_RESID && own_tail >= 0) {
-      // ---- add up the K slices of the tail tile this pair owns, in slice order, and finish it like any other tile
-      const int t = own_tail, tile = g.full_tiles + t;
-      const int m0 = (tile / g.num_n_tiles) * (2 * BM) + rank * BM;
-      const int n0 = (tile % g.num_n_tiles) * BN + team * 128;
-      unsigned* flag = g.flags + (t * 2 + rank) * 2 + team;
-      if (et == 0) {
-        uint32_t spins = 0, t0 = 0;
-        for (;;) {
-          unsigned v;
-          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
-          if (v >= (unsigned)g.split) break;
-          __nanosleep(64);
-          if ((++spins & 0xfffu) == 0) {  // bounded like every other wait of the library
-            uint32_t tt;
-            asm volatile("mov.u32 %0, %%globaltimer_hi;" : "=r"(tt));
-            if (t0 == 0)
-              t0 = tt | 0x80000000u;
-            else if (((tt | 0x80000000u) - t0) >= WM_MBAR_TIMEOUT_TICKS)
-              __trap();
-          }
-        }
-        *flag = 0;  // every slice has arrived and nobody else reads the counter: ready for the next launch
-        __threadfence();
-      }
-      named_bar_sync(bar_id, 128);
-      const float* src = g.part + ((size_t)(t * g.split) * 2 + rank) * (BM * BN) + (size_t)et * BN + team * 128;
-      const size_t slice_stride = (size_t)2 * BM * BN;
-#pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
-        const int col0 = n0 + ch * 32;
-        float o[32];
-        {
-          const float4* s4 = reinterpret_cast<const float4*>(src + ch * 32);
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            const float4 a = __ldcg(s4 + c);
-            o[4 * c] = a.x, o[4 * c + 1] = a.y, o[4 * c + 2] = a.z, o[4 * c + 3] = a.w;
-          }
-        }
-        for (int k = 1; k < g.split; ++k) {
-          const float4* s4 = reinterpret_cast<const float4*>(src + k * slice_stride + ch * 32);
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            const float4 a = __ldcg(s4 + c);
-            o[4 * c] += a.x, o[4 * c + 1] += a.y, o[4 * c + 2] += a.z, o[4 * c + 3] += a.w;
-          }
-        }
-        const float4* b4 = reinterpret_cast<const float4*>(g.bias + col0);
-        const float4* g4 = reinterpret_cast<const float4*>(g.gamma + col0);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          const float4 b = __ldg(b4 + c);
-          float4 gm = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (g.gamma != nullptr) gm = __ldg(g4 + c);
-          o[4 * c] = gm.x * (o[4 * c] + b.x), o[4 * c + 1] = gm.y * (o[4 * c + 1] + b.y);
-          o[4 * c + 2] = gm.z * (o[4 * c + 2] + b.z), o[4 * c + 3] = gm.w * (o[4 * c + 3] + b.w);
-        }
-        if (et == 0) tma_store_wait_read<0>();
-        named_bar_sync(bar_id, 128);
-#pragma unroll
-        for (int c = 0; c < 8; ++c)
-          st_shared_v4(stg + sw128_offset(et, c), __float_as_uint(o[4 * c]), __float_as_uint(o[4 * c + 1]),
-                       __float_as_uint(o[4 * c + 2]), __float_as_uint(o[4 * c + 3]));
-        fence_proxy_async_smem();
-        named_bar_sync(bar_id, 128);
-        if (et == 0) {
-          if (g.gamma != nullptr)
-            tma_reduce_add_2d(&tmC0, stg_ptr, col0, m0);
-          else
-            tma_store_2d(&tmC0, stg_ptr, col0, m0);
-          tma_store_commit();
+        if (sliced && et == 0) {
+          tma_store_wait<0>();  // the reduce-adds of this slice are complete (not only read from the staging tile)
+          __threadfence();
+          const unsigned next = (u.slice + 1 == g.split) ? 0u : (unsigned)(u.slice + 1);  // the last slice re-arms the word
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flag), "r"(next) : "memory");
         }
       }
     }
@@ -525,9 +455,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
 // ------------------------------------------------------------------------------------------------ host
 static int g_sm_count = 0;
-constexpr int kGemmMaxSplit = 4;  // more slices than this buy little (the tail is already < 1/4 wave) and cost fix-up reads
+constexpr int kGemmMaxSplit = 4;  // more slices than this buy little (the tail is already < 1/4 wave) and lengthen the chain
 
-size_t gemm_partial_bytes(int sm_count) { return (size_t)(sm_count / 2) * 2 * BM * BN * sizeof(float); }
 
 template <int EPI>
 static wm_status launch(cudaStream_t st, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c0,
@@ -547,7 +476,7 @@ static wm_status launch(cudaStream_t st, const CUtensorMap& a, const CUtensorMap
   const int pairs = g_sm_count / 2;
   int grid = 2 * (tiles < pairs ? tiles : pairs);
   g.split = 1, g.full_tiles = tiles, g.tail_tiles = 0;
-  if (EPI == EPI_RESID && g.part != nullptr && g.flags != nullptr) {
+  if (EPI == EPI_RESID && g.flags != nullptr) {
     // the tiles beyond the last full wave, cut along K so that they fill (most of) one more wave of pairs
     const int full = (tiles / pairs) * pairs, tail = tiles - full;
     int sp = tail > 0 ? pairs / tail : 1;
@@ -616,8 +545,7 @@ wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const
 }
 
 wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias,
-                           const float* gamma, int M, int N, int K, float* x, int ldx, float* part, size_t part_bytes,
-                           unsigned* flags) {
+                           const float* gamma, int M, int N, int K, float* x, int ldx, unsigned* flags) {
   WM_TRY(check_common(A, W, M, N, K, lda, ldw));
   WM_CHECK(x && bias && ldx % 4 == 0 && ldx >= N, "gemm_ls_residual: bad x");
   if (g_sm_count == 0) WM_TRY(require_sm100(&g_sm_count));
@@ -626,7 +554,7 @@ wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* 
   WM_TRY(tmap_2d(&tx, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, x, M, N, ldx, 32, 128));
   GemmArgs g{};
   g.M = M, g.N = N, g.K = K, g.bias = bias, g.gamma = gamma;
-  if (part != nullptr && flags != nullptr && part_bytes >= gemm_partial_bytes(g_sm_count)) g.part = part, g.flags = flags;
+  g.flags = flags;
   return launch<EPI_RESID>(st, ta, tb, tx, tx, g);
 }
 

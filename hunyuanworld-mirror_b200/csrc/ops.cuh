@@ -10,12 +10,10 @@ wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const
                    const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
                    const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M,
                    void* q_out, void* kv_out);
-// part / flags (both or neither): workspace of gemm_partial_bytes() and kGemmFlagBytes of ZEROED counters that let the
-// kernel cut the tiles beyond the last full wave along K (deterministic fix-up, gemm.cu); null: whole tiles only.
+// flags: kGemmFlagBytes of ZEROED counters (left zero by every launch) that let the kernel cut the tiles beyond the
+// last full wave along K and add the slices in fixed order (gemm.cu); null: whole tiles only.
 wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias,
-                           const float* gamma, int M, int N, int K, float* x, int ldx, float* part = nullptr,
-                           size_t part_bytes = 0, unsigned* flags = nullptr);
-size_t gemm_partial_bytes(int sm_count);
+                           const float* gamma, int M, int N, int K, float* x, int ldx, unsigned* flags = nullptr);
 constexpr size_t kGemmFlagBytes = 4096;
 wm_status copy_cols(cudaStream_t st, const float* x, long long rows, float* out, int ld_out, int col0);
 wm_status gemm_table(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* table,

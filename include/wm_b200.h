@@ -155,9 +155,9 @@ wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const floa
  * TMA reduce-add (each element is added exactly once: deterministic); gamma NULL: x = A W^T + bias. */
 wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
                               const float* gamma, int M, int N, int K, float* x, int ldx);
-/* The same with a workspace of wm_gemm_workspace_bytes() whose first 4096 bytes are ZERO at first use (the kernel leaves
- * them zero): tiles beyond the last full wave of CTA pairs are cut along K, every slice leaves an fp32 partial in the
- * workspace and the slices are added in fixed order before the one reduce-add per element (bit-deterministic). */
+/* The same with wm_gemm_workspace_bytes() (4 KB) of slice counters, ZERO at first use (the kernel leaves them zero):
+ * tiles beyond the last full wave of CTA pairs are cut along K and the slices add their shares to x in slice order
+ * through the counters (one fixed order of fp32 additions: bit-deterministic; no partial-sum buffer). */
 wm_status wm_gemm_ls_residual_ws(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
                                  const float* gamma, int M, int N, int K, float* x, int ldx, void* workspace,
                                  size_t workspace_bytes);

@@ -195,7 +195,7 @@ static int case_gemm_bias(int M, int N, int K, int gelu, int row_step) {
   return e.report(name);
 }
 
-static int case_gemm_resid(int M, int N, int K, int with_gamma, int with_out2, int row_step) {
+static int case_gemm_resid(int M, int N, int K, int with_gamma, int with_out2, int row_step, int split = 0) {
   BF A, W;
   A.fill((size_t)M * K, 1.0f);
   W.fill((size_t)N * K, 1.0f / sqrtf((float)K) * 1.7f);
@@ -204,7 +204,18 @@ static int case_gemm_resid(int M, int N, int K, int with_gamma, int with_out2, i
   float *db = dev(bias), *dg = dev(gamma), *dx = dev(x0);
   const int ld2 = 2 * N, col2 = N;
   float* d2 = dev_alloc<float>((size_t)M * ld2, 0);
-  WM(wm_gemm_ls_residual(0, da, K, dw, K, db, with_gamma ? dg : nullptr, M, N, K, dx, N));
+  if (split) {  // tail tiles cut along K (gemm.cu): run twice on the zeroed workspace, the flags must come back to zero
+    const size_t wsb = wm_gemm_workspace_bytes();
+    uint8_t* ws = dev_alloc<uint8_t>(wsb, 0);
+    float* dx_b = dev(x0);
+    WM(wm_gemm_ls_residual_ws(0, da, K, dw, K, db, with_gamma ? dg : nullptr, M, N, K, dx, N, ws, wsb));
+    WM(wm_gemm_ls_residual_ws(0, da, K, dw, K, db, with_gamma ? dg : nullptr, M, N, K, dx_b, N, ws, wsb));
+    CK(cudaDeviceSynchronize());
+    auto xa = host(dx, (size_t)M * N), xb = host(dx_b, (size_t)M * N);
+    if (memcmp(xa.data(), xb.data(), xa.size() * 4) != 0) { printf("FAIL split GEMM: two runs differ bitwise\n"); return 1; }
+  } else {
+    WM(wm_gemm_ls_residual(0, da, K, dw, K, db, with_gamma ? dg : nullptr, M, N, K, dx, N));
+  }
   if (with_out2) {
     if (N != 1024) { printf("out2 copy needs N=1024\n"); return 1; }
     WM(wm_copy_cols(0, dx, M, d2, ld2, col2));
@@ -226,7 +237,7 @@ static int case_gemm_resid(int M, int N, int K, int with_gamma, int with_out2, i
     }
   }
   char name[96];
-  snprintf(name, sizeof name, "gemm_ls_residual M=%d N=%d K=%d gamma=%d", M, N, K, with_gamma);
+  snprintf(name, sizeof name, "gemm_ls_residual M=%d N=%d K=%d gamma=%d split=%d", M, N, K, with_gamma, split);
   int rc = e.report(name);
   if (with_out2) rc |= e2.report("  second (strided) output");
   return rc;
@@ -380,6 +391,7 @@ static float time_ms(int iters, void (*fn)(void*), void* ctx) {
 
 struct GemmCtx {
   int kind, M, N, K;
+  void* ws;
   uint16_t *a, *w, *out, *q, *kv;
   float *bias, *gamma, *x, *qw, *cs;
 };
@@ -390,6 +402,9 @@ static void gemm_run(void* p) {
   if (c->kind == 2)
     WM(wm_gemm_qkv(0, c->a, c->w, c->bias, c->qw, c->qw, c->qw, c->qw, 1e-5f, c->cs, c->cs, 1376, 7, 37, 1.0f, c->M, c->q, c->kv));
   if (c->kind == 3) WM(wm_gemm_ls_residual(0, c->a, c->K, c->w, c->K, c->bias, c->gamma, c->M, c->N, c->K, c->x, c->N));
+  if (c->kind == 4)
+    WM(wm_gemm_ls_residual_ws(0, c->a, c->K, c->w, c->K, c->bias, c->gamma, c->M, c->N, c->K, c->x, c->N, c->ws,
+                              wm_gemm_workspace_bytes()));
 }
 static int bench_gemm(int kind, int M, int N, int K) {
   GemmCtx c{};
@@ -405,8 +420,9 @@ static int bench_gemm(int kind, int M, int N, int K) {
   std::vector<float> cs(64 * 16), sn(64 * 16);
   wm_rope_tables(63, cs.data(), sn.data());
   c.cs = dev(cs);
+  if (kind == 4) c.ws = dev_alloc<uint8_t>(wm_gemm_workspace_bytes(), 0);
   const float ms = time_ms(20, gemm_run, &c);
-  const char* names[] = {"bias", "gelu", "qkv", "ls_residual"};
+  const char* names[] = {"bias", "gelu", "qkv", "ls_residual", "ls_resid_split"};
   printf("BENCH gemm_%-12s M=%d N=%d K=%d  %.3f ms  %.1f TFLOP/s\n", names[kind], M, N, K, ms, 2.0 * M * N * K / ms * 1e-9);
   return 0;
 }
@@ -537,7 +553,7 @@ int main(int argc, char** argv) {
   if (c == "probe") return case_probe(I(2, 0), I(3, 1024), I(4, 1024));
   if (c == "layernorm") return case_layernorm(I(2, 333));
   if (c == "gemm_bias") return case_gemm_bias(I(2, 300), I(3, 512), I(4, 192), I(5, 0), I(6, 1));
-  if (c == "gemm_resid") return case_gemm_resid(I(2, 300), I(3, 512), I(4, 192), I(5, 1), I(6, 1), I(7, 1));
+  if (c == "gemm_resid") return case_gemm_resid(I(2, 300), I(3, 512), I(4, 192), I(5, 1), I(6, 1), I(7, 1), I(8, 0));
   if (c == "gemm_table") return case_gemm_table(I(2, 300), I(3, 1024), I(4, 588), I(5, 640), I(6, 77));
   if (c == "gemm_qkv") return case_gemm_qkv(I(2, 300), I(3, 1), I(4, 1), I(5, 3));
   if (c == "attn") return case_attn(I(2, 2), I(3, 331), I(4, 331), I(5, 2), (float)I(6, 1), I(7, 0), I(8, 0), I(9, 0), I(10, 5));

@@ -295,3 +295,66 @@ def test_single_view_forward_matches_oracle_heads(state_dict_full):
             np.testing.assert_allclose(g, mref[k], rtol=3e-7, atol=1e-9)
         else:
             assert np.array_equal(g, mref[k].reshape(K, -1)), k
+
+
+@pytest.mark.parametrize("tag,flags", [("nopriors", (0, 0, 0)), ("priors", (1, 1, 1))])
+def test_worldmirror_predictions_match_reference_forward(tag, flags, state_dict_full):
+    """`B200WorldMirror.forward` against the dictionary the REFERENCE `WorldMirror.forward` (worldmirror.py:120-220,
+    enable_gs=False) returned on config C1 (tests/golden/make_golden_preds.py): the same key set, the same shapes, the
+    camera-to-world poses and intrinsics (worldmirror.py:161-175) and the dense predictions on a stride-6 lattice.
+    Gates: dense rel. Frobenius <= 1e-2 (north_star), camera parameters 2e-3 absolute, rotation <= 1e-3 rad,
+    intrinsics 0.5 % of the focal length."""
+    fx = np.load(os.path.join(GOLDEN, "c1_preds.npz"))
+    n, h, w, st = int(fx["n_views"]), int(fx["H"]), int(fx["W"]), int(fx["stride"])
+    model = heads.B200WorldMirror.from_state_dicts(state_dict_full, W.synthetic_heads_state_dict(seed=0))
+    views = {"img": W.synthetic_images(n, h, w, seed=1).cuda()}
+    if sum(flags):
+        pose, depth, intr = W.synthetic_scene(n, h, w, seed=2)
+        views.update(camera_pose=pose.cuda(), depthmap=depth.cuda(), camera_intrinsics=intr.cuda())
+    preds = model(views, cond_flags=flags)
+    torch.cuda.synchronize()
+    ref_keys = [str(k) for k in fx[tag + "_keys"]]
+    assert sorted(preds.keys()) == ref_keys, (sorted(preds.keys()), ref_keys)
+    for k, shp in zip(ref_keys, fx[tag + "_shapes"]):
+        assert str(tuple(preds[k].shape)) == str(shp), (k, tuple(preds[k].shape), shp)
+    for name in ("depth", "depth_conf", "pts3d", "pts3d_conf", "normals", "normals_conf"):
+        got, ref = preds[name][0, :, ::st, ::st].cpu().numpy(), fx[f"{tag}_{name}_sub"]
+        e = np.linalg.norm(got - ref) / np.linalg.norm(ref)
+        print(f"{tag} {name}: rel fro {e:.3e}")
+        assert np.isfinite(got).all() and e <= 1e-2, (name, e)
+    cp, cp_ref = preds["camera_params"].cpu(), torch.from_numpy(fx[tag + "_camera_params"])
+    assert (cp - cp_ref).abs().max().item() <= 2e-3
+    poses, poses_ref = preds["camera_poses"].cpu().numpy(), fx[tag + "_camera_poses"]
+    intrs, intrs_ref = preds["camera_intrs"].cpu().numpy(), fx[tag + "_camera_intrs"]
+    ang = HO.quat_angle(cp[..., 3:7], cp_ref[..., 3:7]).max().item()
+    print(f"{tag} cameras: |params| {(cp - cp_ref).abs().max().item():.3e}, rotation {ang:.3e} rad, "
+          f"|poses| {np.abs(poses - poses_ref).max():.3e}, |K| {np.abs(intrs - intrs_ref).max():.3e}")
+    assert ang <= 1e-3
+    np.testing.assert_allclose(poses, poses_ref, atol=3e-3)
+    np.testing.assert_allclose(intrs, intrs_ref, rtol=5e-3, atol=5e-3 * float(intrs_ref[..., 0, 0].max()))
+    np.testing.assert_array_equal(poses[..., 3, :], poses_ref[..., 3, :])
+
+
+def test_worldmirror_forward_c2_matches_reference_golden(state_dict_full):
+    """The configuration bench.py TIMES (BASELINE.json configs[1]: 8 views 518 x 518, no priors): the whole B200 forward
+    (bf16 aggregator with the default attention variants, fp32 camera head, fp16-operand DPT heads) against the REFERENCE
+    aggregator + REFERENCE heads run in fp32 on the same inputs (tests/golden/c2_heads.npz, stride-7 lattice + row sums
+    of every pixel).  Gates: north_star's 1e-2 rel. Frobenius on every dense map, 1e-3 rad on the camera rotation."""
+    fx = np.load(os.path.join(GOLDEN, "c2_heads.npz"))
+    n, h, w, st = int(fx["n_views"]), int(fx["H"]), int(fx["W"]), int(fx["stride"])
+    model = heads.B200WorldMirror.from_state_dicts(state_dict_full, W.synthetic_heads_state_dict(seed=0))
+    preds = model({"img": W.synthetic_images(n, h, w, seed=1).cuda()})
+    torch.cuda.synchronize()
+    for name in ("depth", "pts3d", "normals"):
+        got, ref = preds[name][0, :, ::st, ::st].cpu().numpy(), fx[name + "_sub"]
+        gc, rc = preds[name + "_conf"][0, :, ::st, ::st].cpu().numpy(), fx[name + "_conf_sub"]
+        e = np.linalg.norm(got - ref) / np.linalg.norm(ref)
+        ec = np.linalg.norm(gc - rc) / np.linalg.norm(rc)
+        rs = np.abs(preds[name][0].sum(dim=2).cpu().numpy() - fx[name + "_rowsum"]).max() / (w * float(fx[name + "_absmean"]))
+        print(f"C2 e2e {name}: rel fro {e:.3e}, conf {ec:.3e}, row-sum dev {rs:.3e}")
+        assert np.isfinite(got).all() and e <= 1e-2 and ec <= 1e-2 and rs <= 2e-2, (name, e, ec, rs)
+    cam_ref = torch.from_numpy(fx["camera_params_steps"][-1])
+    cp = preds["camera_params"].cpu()
+    ang = HO.quat_angle(cp[..., 3:7], cam_ref[..., 3:7]).max().item()
+    print(f"C2 e2e camera: |params| {(cp - cam_ref).abs().max().item():.3e}, rotation {ang:.3e} rad")
+    assert ang <= 1e-3 and (cp - cam_ref).abs().max().item() <= 5e-3

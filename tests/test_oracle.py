@@ -27,8 +27,14 @@ def _run_case(fx, sd):
         return O.aggregator_forward(imgs, sd, priors, list(fx["cond_flags"]), return_stages=True)
 
 
-@pytest.mark.parametrize("name", ["c1_nopriors", "c1_priors", "rect_partial"])
+SLOW = os.environ.get("WM_SLOW_TESTS", "0") == "1"  # the 8-view 518 x 518 oracle forward takes ~2 min of CPU
+
+
+@pytest.mark.parametrize("name", ["c1_nopriors", "c1_priors", "rect_partial", "c3s_priors",
+                                  pytest.param("c2_nopriors", marks=pytest.mark.skipif(not SLOW, reason="WM_SLOW_TESTS=1"))])
 def test_oracle_matches_reference_golden(name, state_dict_full):
+    """c3s_priors = 4 views 518 x 518 with all three priors (BASELINE.json configs[2] shapes at reduced view count),
+    c2_nopriors = the configuration bench.py times: the oracle is pinned to the reference at the timed image size."""
     fx = _load(name)
     outs, psi, stages = _run_case(fx, state_dict_full)
     assert psi == 7 and len(outs) == 4
