@@ -338,12 +338,15 @@ def run_b200(args):
         shapes.update({"gs_depth": (1, n_local, SIZE, SIZE, 1), "gs_depth_conf": (1, n_local, SIZE, SIZE)})
     host_out = {k: torch.empty(v, dtype=torch.float32).pin_memory() for k, v in shapes.items()}
     d2h_bytes = sum(t.numel() * 4 for t in host_out.values())
-    # the merged splats of the scene (one result, identical on every rank): rank 0 reads them back (N-row buffers of 14
-    # floats per row, the first K rows valid)
+    # the merged splats of the scene (one result, identical on every rank; N-row buffers of 14 floats per row, the first K
+    # rows valid): the read-back is shared, every rank copies rows [rank, rank + 1) * N / world over its own PCIe link
     splat_rows = n_total * SIZE * SIZE
-    splat_host = ({k: torch.empty((splat_rows,) + shp, dtype=torch.float32).pin_memory()
+    rows_mine = splat_rows // world
+    splat_host = ({k: torch.empty((rows_mine,) + shp, dtype=torch.float32).pin_memory()
                    for k, shp in (("means", (3,)), ("sh", (1, 3)), ("opacities", ()), ("scales", (3,)), ("quats", (4,)))}
-                  if gs_on and rank == 0 else None)
+                  if gs_on else None)
+    if gs_on and world > 1:
+        full.splat_readback = (rank * rows_mine, rows_mine)
     splat_bytes = [0]
     all_host = dict(host_out)
     if splat_host is not None:
@@ -365,7 +368,8 @@ def run_b200(args):
 
     e2e_ms = timed(step_e2e, args.steps, 3) / args.steps
     e2e = {"value": n_total / (e2e_ms * 1e-3), "unit": "views/s", "h2d_bytes_per_step": imgs_host.numel() * 4,
-           "d2h_bytes_per_step": d2h_bytes + splat_bytes[0], "ms_per_step": e2e_ms}
+           "d2h_bytes_per_step": d2h_bytes + splat_bytes[0], "ms_per_step": e2e_ms,
+           "d2h_note": "per rank: its views' dense predictions + its 1/N share of the merged splat rows" if world > 1 else None}
 
     # ---- the same global attention through the GENERAL kernel (running max, no logit bound): what a checkpoint whose
     # QK-norm weights exceed the bound would get.  Two extra forwards, outside every timed region.

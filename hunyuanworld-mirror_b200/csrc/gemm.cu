@@ -32,6 +32,8 @@
 // on with the pair's next tile in the other TMEM accumulator.  2 + 1/3 waves instead of 3.
 // (A first version parked fp32 partials in a workspace and let the owner add them at the end: row-strided 16-byte
 // accesses and a serial fix-up made it SLOWER than 3 waves, 48 vs 25 us for proj; profiles/r02_s2_selftest.log.)
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -456,7 +458,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 // ------------------------------------------------------------------------------------------------ host
 static int g_sm_count = 0;
 constexpr int kGemmMaxSplit = 4;  // more slices than this buy little (the tail is already < 1/4 wave) and lengthen the chain
-
+// The ordered chain costs one reduce-add round trip per slice; it hides under the pair's next whole tile only when
+// that tile is long enough.  Measured on B200 (profiles/r02_s3_selftest.log): K = 4096 (fc2) 76 -> 70 us, K = 1024
+// (proj) 25 -> 38 us.  Tiles shorter than this many 64-wide K blocks are not split.
+constexpr int kGemmSplitMinKBlocks = 32;
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
 
 template <int EPI>
 static wm_status launch(cudaStream_t st, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c0,
@@ -479,9 +488,13 @@ static wm_status launch(cudaStream_t st, const CUtensorMap& a, const CUtensorMap
   if (EPI == EPI_RESID && g.flags != nullptr) {
     // the tiles beyond the last full wave, cut along K so that they fill (most of) one more wave of pairs
     const int full = (tiles / pairs) * pairs, tail = tiles - full;
+    static const int max_split = env_int("WM_GEMM_MAX_SPLIT", kGemmMaxSplit);        // experiment switches
+    static const int min_kb = env_int("WM_GEMM_SPLIT_MIN_KB", kGemmSplitMinKBlocks);
     int sp = tail > 0 ? pairs / tail : 1;
+    if (sp > max_split) sp = max_split;
     if (sp > kGemmMaxSplit) sp = kGemmMaxSplit;
     if (sp > g.num_k_blocks) sp = g.num_k_blocks;
+    if (g.num_k_blocks < min_kb) sp = 1;
     if (sp >= 2) {
       g.split = sp, g.full_tiles = full, g.tail_tiles = tail;
       grid = 2 * (full > 0 ? pairs : tail * sp);

@@ -300,9 +300,20 @@ class B200CameraHead(torch.nn.Module):
         _k(capi.lib().wm_cam_layernorm(_st(), x.data_ptr(), stride, _p(w), _p(b), eps, M, _p(mod), y.data_ptr()))
         return y
 
-    def _run(self, feat, stride, S, steps, outs):
-        """One sample: `feat` holds the camera tokens, rows `stride` floats apart; outs[step] is a [S, 9] tensor."""
+    def _run(self, feat, stride, S, steps, outs, shard=None):
+        """One sample: `feat` holds the camera tokens, rows `stride` floats apart; outs[step] is a [S, 9] tensor.
+        shard = (group, world, rank): the S tokens are THIS RANK'S views of a scene of S * world views.  Every layer of
+        the head is per token except the trunk attention (camera_head.py:73,92 attends across the views), so only the
+        [S, 6144] q|k|v rows of each block are all-gathered; attention runs over all S * world tokens (a few
+        microseconds) and the rank keeps its own rows.  The weights (0.8 GB per refinement step) are streamed once per
+        rank for S rows instead of S * world."""
         lib, w, dev, Cd = capi.lib(), self.w, feat.device, self.dim
+        if shard is not None:
+            import torch.distributed as dist
+
+            group, world, rank = shard
+            qkv_all = torch.empty(S * world, 3 * Cd, dtype=torch.float32, device=dev)
+            att_all = torch.empty(S * world, Cd, dtype=torch.float32, device=dev)
         tok = self._ln(feat, stride, "token_norm", 1e-5, S)
         pred = torch.empty(S, 9, dtype=torch.float32, device=dev)
         emb = torch.empty(S, Cd, dtype=torch.float32, device=dev)
@@ -316,8 +327,13 @@ class B200CameraHead(torch.nn.Module):
                 p = f"refine_net.{i}."
                 n1 = self._ln(x, Cd, p + "norm1", 1e-5, S)
                 qkv = self._linear(n1, p + "attn.qkv", S)
-                att = torch.empty(S, Cd, dtype=torch.float32, device=dev)
-                _k(lib.wm_cam_attention(_st(), qkv.data_ptr(), S, att.data_ptr()))
+                if shard is None:
+                    att = torch.empty(S, Cd, dtype=torch.float32, device=dev)
+                    _k(lib.wm_cam_attention(_st(), qkv.data_ptr(), S, att.data_ptr()))
+                else:
+                    dist.all_gather_into_tensor(qkv_all, qkv, group=group)
+                    _k(lib.wm_cam_attention(_st(), qkv_all.data_ptr(), S * world, att_all.data_ptr()))
+                    att = att_all[rank * S:(rank + 1) * S]
                 self._linear(att, p + "attn.proj", S, resid=x, gamma=w[p + "ls1.gamma"], out=x)
                 n2 = self._ln(x, Cd, p + "norm2", 1e-5, S)
                 hid = self._linear(n2, p + "mlp.fc1", S, act=1)
@@ -327,30 +343,35 @@ class B200CameraHead(torch.nn.Module):
             _k(lib.wm_cam_predict(_st(), hid.data_ptr(), hid.shape[1], w["param_predictor.fc2.weight"].data_ptr(),
                                   w["param_predictor.fc2.bias"].data_ptr(), S, int(step == 0), pred.data_ptr(), outs[step].data_ptr()))
 
-    def _graph_for(self, S, steps, dev):
+    def _graph_for(self, S, steps, dev, shard=None):
         """The head is ~137 launches of a few microseconds each: captured once per (views, steps) into a CUDA graph so
         that the launch latency of issuing them from Python does not bound it.  WM_CAM_GRAPH=0 keeps eager launches."""
         import os
 
-        key = (S, steps, dev.index)
+        key = (S, steps, dev.index, None if shard is None else (shard[1], shard[2]))
         if key in self._graphs:
             return self._graphs[key]
         entry = None
-        if os.environ.get("WM_CAM_GRAPH", "1") != "0":
+        # sharded: the all-gathers would have to be captured too; WM_CAM_GRAPH=2 opts in (NCCL supports capture), the
+        # default keeps the sharded head eager (16 small collectives issued from Python, same stream order on all ranks)
+        mode = os.environ.get("WM_CAM_GRAPH", "1")
+        if mode != "0" and (shard is None or mode == "2"):
             tok_in = torch.zeros(S, self.dim, dtype=torch.float32, device=dev)
             outs = [torch.zeros(S, 9, dtype=torch.float32, device=dev) for _ in range(steps)]
-            self._run(tok_in, self.dim, S, steps, outs)  # warm-up outside capture
+            self._run(tok_in, self.dim, S, steps, outs, shard)  # warm-up outside capture
             torch.cuda.synchronize(dev)
             before = LAUNCHES[0]
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                self._run(tok_in, self.dim, S, steps, outs)
+                self._run(tok_in, self.dim, S, steps, outs, shard)
             entry = (graph, tok_in, outs, LAUNCHES[0] - before)
         self._graphs[key] = entry
         return entry
 
     @torch.no_grad()
-    def forward(self, feat_seq: list, steps: int = 4) -> list:
+    def forward(self, feat_seq: list, steps: int = 4, shard=None) -> list:
+        """shard = (group, world, rank): `feat_seq[-1]` holds this rank's views only and the result is this rank's rows
+        (see `_run`); every rank must call with the same number of views."""
         if not self._loaded:
             raise RuntimeError("B200CameraHead: load_state_dict() has not been called")
         latest = feat_seq[-1]
@@ -361,7 +382,7 @@ class B200CameraHead(torch.nn.Module):
         dev = latest.device
         outs = [torch.empty(B, S, 9, dtype=torch.float32, device=dev) for _ in range(steps)]
         with torch.cuda.device(dev):
-            g = self._graph_for(S, steps, dev)
+            g = self._graph_for(S, steps, dev, shard)
             for bi in range(B):
                 feat = latest[bi].to(torch.float32)
                 if g is not None:
@@ -374,7 +395,7 @@ class B200CameraHead(torch.nn.Module):
                 else:
                     if not feat.is_contiguous():
                         feat = feat.contiguous()
-                    self._run(feat, P * Cd, S, steps, [o[bi] for o in outs])
+                    self._run(feat, P * Cd, S, steps, [o[bi] for o in outs], shard)
         return outs
 
 
@@ -632,11 +653,17 @@ class B200WorldMirror(torch.nn.Module):
         self.gs_head, self.gs_renderer = gs_head, gs_renderer
         self.enable_gs = gs_head is not None and gs_renderer is not None
         self._side = None
+        self.camera_sharded = True  # views sharded over ranks: camera head on the local views (False: all views on every rank)
+        self.splat_readback = None  # (first row, rows): the slice of the merged splat buffers this rank copies to host_out
 
     def _camera(self, token_list):
         agg = self.visual_geometry_transformer
         if getattr(agg, "world", 1) > 1:
-            # the trunk attends across views (camera_head.py:73,92): gather every rank's camera tokens [S_local, 2048]
+            if self.camera_sharded:
+                # every layer but the trunk attention is per view: each rank runs its own views and the q|k|v rows of
+                # the trunk blocks are all-gathered (B200CameraHead._run)
+                return self.cam_head(token_list, shard=(agg._sp_group, agg.world, agg.rank))[-1]
+            # replicated: gather every rank's camera tokens [S_local, 2048] and run all views on every rank
             import torch.distributed as dist
 
             mine = token_list[-1][:, :, :1].contiguous()
@@ -704,6 +731,10 @@ class B200WorldMirror(torch.nn.Module):
         def emit(name, t, src=None):
             if copy is None or name not in host_out:
                 return
+            if name.startswith("splats.") and self.splat_readback is not None:
+                # the merged scene is identical on every rank: each one reads back its share of the rows
+                r0, nr = self.splat_readback
+                t = t[r0:r0 + nr]
             copy.wait_stream(main if src is None else src)
             with torch.cuda.stream(copy):
                 dst = host_out[name]

@@ -51,9 +51,40 @@ def main():
         e = ((a - f[:, sl]).norm() / f[:, sl].norm()).item()
         ok &= e < 2e-3
         print(f"rank {rank}: p2p (world {world}) vs single GPU rel fro {e:.3e}", flush=True)
+    # prior extraction with the views sharded (priors.extract_priors(group, world, rank)): the pose box is normalised over
+    # ALL views of the scene, so the sharded call must return exactly the rows of the whole-scene call
+    pose, depth, intr = W.synthetic_scene(per * world, H, Wd, seed=2)
+    allv = {"img": imgs.to(dev), "camera_pose": pose.to(dev), "depthmap": depth.to(dev), "camera_intrinsics": intr.to(dev)}
+    locv = {k: v[:, sl].contiguous() for k, v in allv.items()}
+    pf = pkg.priors.extract_priors(allv)
+    pl = pkg.priors.extract_priors(locv, group=None, world=world, rank=rank)
+    torch.cuda.synchronize()
+    for name, a_, f_ in zip(("depth", "rays", "poses"), pl, pf):
+        same = torch.equal(a_, f_[:, sl])
+        print(f"rank {rank}: sharded extract_priors {name} == whole-scene rows: {same}", flush=True)
+        ok &= same
+    # camera head with the views sharded: per-view layers on the local views, q|k|v rows of the trunk all-gathered
+    # (B200CameraHead._run) against all views on one GPU; same arithmetic per row, so equal to fp32 rounding at most
+    H2 = pkg.heads
+    hsd = W.synthetic_heads_state_dict(seed=0)
+    cam = H2.B200CameraHead(dim_in=2048)
+    cam.load_state_dict({k[len("cam_head."):]: v for k, v in hsd.items() if k.startswith("cam_head.")})
+    g = torch.Generator().manual_seed(5)
+    ctok = torch.randn(1, per * world, 1, 2048, generator=g).to(dev)
+    whole = cam([ctok])
+    for mode in (("eager", "graph") if os.environ.get("WM_TEST_CAM_GRAPH") == "1" else ("eager",)):
+        os.environ["WM_CAM_GRAPH"] = "1" if mode == "eager" else "2"
+        cam._graphs = {}
+        for _ in range(2):
+            mine_c = cam([ctok[:, sl].contiguous()], shard=(None, world, rank))
+        torch.cuda.synchronize()
+        for a_, f_ in zip(mine_c, whole):
+            e = (a_ - f_[:, sl]).abs().max().item()
+            ok &= e <= 1e-5
+        print(f"rank {rank}: sharded camera head ({mode}) vs all views on one GPU max abs {e:.2e}", flush=True)
+    os.environ["WM_CAM_GRAPH"] = "1"
     # Gaussian branch with the views sharded: every rank gathers the other ranks' splats and merges the whole scene;
     # the result must equal, bit for bit, the merge of all views done on one GPU (same splats, same order)
-    H2 = pkg.heads
     gsd = W.synthetic_heads_state_dict(seed=0, gs=True)
     g = torch.Generator().manual_seed(3)
     S, h, w = per * world, 28, 42

@@ -465,3 +465,20 @@ def test_gathered_attention_scan_order_and_flags(variant, self_rank, late):
     err = (a - b).abs().max().item()
     print(f"gathered attention variant {variant} self {self_rank} late {late}: max abs diff {err:.3e}")
     assert err <= 2e-2 * b.abs().max().item() + 1e-3  # same math, different summation order (bf16 output)
+
+
+def test_batch_of_two_scenes(model_full):
+    """B = 2 through the primary seam (`VisualGeometryTransformer.forward(images [B, S, 3, H, W], priors, cond_flags)`,
+    visual_transformer.py:250-341): scenes never mix (frame attention per view, global attention per scene), so a batch of
+    two scenes with priors must equal, bit for bit, the two scenes run one at a time."""
+    n, h, w = 3, 126, 154
+    imgs = torch.cat([W.synthetic_images(n, h, w, seed=5), W.synthetic_images(n, h, w, seed=6)], dim=0).cuda()
+    pri = [torch.cat([a, b], dim=0).cuda() for a, b in zip(W.synthetic_priors(n, h, w, seed=7), W.synthetic_priors(n, h, w, seed=8))]
+    both, psi = model_full(imgs, tuple(pri), cond_flags=[1, 1, 1])
+    both = [t.clone() for t in both]
+    assert psi == 7 and both[0].shape == (2, n, 7 + (h // 14) * (w // 14), 2048)
+    for b in range(2):
+        one, _ = model_full(imgs[b:b + 1], tuple(p[b:b + 1] for p in pri), cond_flags=[1, 1, 1])
+        for x, y in zip(both, one):
+            assert torch.equal(x[b:b + 1], y)
+    assert not torch.equal(both[-1][0], both[-1][1])
