@@ -57,6 +57,7 @@ SIGNATURES = {
     "wm_gemm_qkv": (C.c_int, [_vp, _vp, _vp, _fp, _fp, _fp, _fp, _fp, _f, _fp, _fp, _i, _i, _i, _f, _i, _vp, _vp]),
     "wm_set_int": (C.c_int, [_vp, C.c_char_p, _i]),
     "wm_get_int": (C.c_int, [_vp, C.c_char_p]),
+    "wm_fp16_saturation": (C.c_int, [_vp, _vp, C.c_int]),
     "wm_logit_bound": (C.c_float, [_vp, _i, _i]),
     "wm_gemm_ls_residual": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _fp, _i, _i, _i, _fp, _i]),
     "wm_gemm_ls_residual_ws": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _fp, _i, _i, _i, _fp, _i, _vp, C.c_size_t]),

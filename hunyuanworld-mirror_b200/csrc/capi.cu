@@ -1026,6 +1026,10 @@ wm_status wm_conv2d_final(wm_stream stream, const void* in, int n, int H, int W,
   return conv2d_final(static_cast<cudaStream_t>(stream), in, n, H, W, Cin, w1, b1, w2, b2, od, act, pred, conf);
 }
 
+wm_status wm_fp16_saturation(wm_stream stream, unsigned* host_count, int reset) {
+  return fp16_saturation_read(static_cast<cudaStream_t>(stream), host_count, reset);
+}
+
 wm_status wm_layernorm_rows(wm_stream stream, const float* x, const float* w, const float* b, float eps, long long rows,
                             int rows_per_group, int in_group_rows, int in_offset, int C, void* y) {
   int sms;

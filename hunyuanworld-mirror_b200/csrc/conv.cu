@@ -31,6 +31,11 @@
 
 namespace wm {
 
+// Pixels x 32-channel groups of an fp16 output map whose fp32 value left the fp16 range (or was not finite) since the
+// last reset: the DPT heads keep their maps in fp16, and a checkpoint or input that overflows them must be reported.
+__device__ unsigned int g_fp16_saturated = 0;
+
+
 constexpr int CV_TW = 16, CV_TH = 8;   // tile = 8 rows x 16 columns of pixels
 constexpr int CV_STAGES = 4;
 constexpr int CV_KE = 64;              // fp16 elements per k-block (one 128-byte swizzle row)
@@ -301,12 +306,15 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tmem_ld_x32(taddr + grp * 32, v);
           tmem_wait_ld();
           uint32_t pk[16];
+          float mx = 0.f;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
             if (g.bias != nullptr) a += __ldg(g.bias + grp * 32 + 2 * i), b += __ldg(g.bias + grp * 32 + 2 * i + 1);
+            mx = fmaxf(mx, fmaxf(a, b));
             pk[i] = pack_half2_sat(fmaxf(a, 0.f), fmaxf(b, 0.f));
           }
+          if (valid && !(mx <= 65504.f)) atomicAdd(&g_fp16_saturated, 1u);
           tmem_st_x16(taddr + grp * 16, pk);
         }
         tmem_wait_st();
@@ -385,6 +393,12 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (g.relu == 1) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) xv[i] = fmaxf(xv[i], 0.f);
+          }
+          {  // fp16 maps: a value beyond the fp16 range is clamped by cvt.satfinite below -- never silently: count it
+            float mx = 0.f;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fabsf(xv[i]));
+            if (valid && !(mx <= 65504.f)) atomicAdd(&g_fp16_saturated, 1u);
           }
           // two 32-column groups fill one 128-byte staging row (64 fp16 channels) per pixel
           const int half = grp & 1;
@@ -498,6 +512,17 @@ wm_status conv2d_project(cudaStream_t st, const void* in, int n, int H, int W, i
   g.n = n, g.H = H, g.W = W, g.Cin = Cin, g.Cout = 256, g.taps = 9;
   g.bias = b1, g.w2 = w2, g.b2 = b2, g.od = od, g.pred = out;
   return launch_conv<256, EPI_PROJECT>(st, ta, tb, ta, g);
+}
+
+wm_status fp16_saturation_read(cudaStream_t st, unsigned* host_pinned, int reset) {
+  WM_CHECK(host_pinned != nullptr, "fp16_saturation_read: null destination");
+  WM_CUDA(cudaMemcpyFromSymbolAsync(host_pinned, g_fp16_saturated, sizeof(unsigned), 0, cudaMemcpyDeviceToHost, st));
+  if (reset) {
+    void* p = nullptr;
+    WM_CUDA(cudaGetSymbolAddress(&p, g_fp16_saturated));
+    WM_CUDA(cudaMemsetAsync(p, 0, sizeof(unsigned), st));
+  }
+  return WM_OK;
 }
 
 }  // namespace wm

@@ -35,6 +35,8 @@ wm_status special_tokens(cudaStream_t st, const float* cam, const float* reg, in
 // prediction heads (conv.cu, headops.cu)
 wm_status conv2d_nhwc(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* weight, int taps, int Cout,
                       const float* bias, const void* res1, int res1_bcast, const void* res2, int relu, void* out);
+// the count of fp16 saturations since the last reset (conv.cu: g_fp16_saturated), copied to pinned host memory on `st`
+wm_status fp16_saturation_read(cudaStream_t st, unsigned* host_pinned, int reset);
 wm_status conv2d_final(cudaStream_t st, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
                        const float* w2, const float* b2, int od, int act, float* pred, float* conf);
 wm_status ln_rows(cudaStream_t st, const float* x, const float* w, const float* b, float eps, long long rows,

@@ -19,6 +19,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from typing import Dict, List, Sequence, Tuple
 
 import torch
@@ -67,6 +68,32 @@ def uv_tables(w: int, h: int, channels: int, aspect: float, ratio: float = 0.1) 
     return pu.contiguous(), pv.contiguous()
 
 
+_SAT_HOST: Dict[int, torch.Tensor] = {}
+
+
+def fp16_saturation(device=None, reset: bool = True, sync: bool = True) -> int:
+    """Entries of the DPT heads' fp16 maps that left the fp16 range (and were clamped) since the last reset
+    (wm_fp16_saturation, csrc/conv.cu).  sync=False only enqueues the copy on the current stream and returns the value
+    of the PREVIOUS read (valid once the stream has been synchronised)."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    if idx not in _SAT_HOST:
+        _SAT_HOST[idx] = torch.zeros(1, dtype=torch.int32).pin_memory()
+    host = _SAT_HOST[idx]
+    prev = int(host.item())
+    with torch.cuda.device(idx):
+        st = torch.cuda.current_stream()
+        _k(capi.lib().wm_fp16_saturation(st.cuda_stream, host.data_ptr(), int(reset)))
+        if sync:
+            st.synchronize()
+            return int(host.item())
+    return prev
+
+
+class Fp16RangeError(FloatingPointError):
+    """Activations of a prediction head exceeded the fp16 range of its maps (they were clamped to +-65504)."""
+
+
 class B200DPTHead(torch.nn.Module):
     def __init__(self, dim_in: int = 2048, patch_size: int = 14, output_dim: int = 4, activation: str = "inv_log+expp1",
                  features: int = 256, out_channels: Sequence[int] = (256, 512, 1024, 1024), pos_embed: bool = True,
@@ -81,6 +108,7 @@ class B200DPTHead(torch.nn.Module):
             raise ValueError(f"Unknown attribute activation: {activation}")
         self.dim_in, self.output_dim, self.activation, self.act = dim_in, output_dim, activation, _ACT[act]
         self.is_gsdpt = bool(is_gsdpt)
+        self.tail_views = int(os.environ.get("WM_DPT_TAIL_VIEWS", "0")) or 1 << 30  # views per pass of the high-resolution tail (0: all)
         self.oc = tuple(out_channels)
         self.w: Dict[str, torch.Tensor] = {}
         self._pos: Dict[tuple, tuple] = {}
@@ -97,6 +125,8 @@ class B200DPTHead(torch.nn.Module):
         def conv(key):
             t = sd[key].detach().to(dev, torch.float32)
             co, ci, kh, kw = t.shape
+            if float(t.abs().max()) > 65504.0:
+                raise Fp16RangeError(f"{key}: |weight| exceeds the fp16 range of the convolution operands")
             return t.permute(0, 2, 3, 1).reshape(co, kh * kw * ci).to(ACT).contiguous()
 
         def vec(key):
@@ -221,9 +251,9 @@ class B200DPTHead(torch.nn.Module):
             # scratch.layer{i}_rn (no bias); only relu(rn) is ever read (in-place ReLU of the consuming RCU)
             rn.append(self._conv(f, n, h_, w_, c, f"rn{i}.w", 9, 256, relu=1))
             sizes.append((h_, w_))
-        # refinenet4 .. refinenet1 (dense_head.py:283-291)
+        # refinenet4 .. refinenet2 (dense_head.py:283-291) on all views of the chunk: small maps
         path = None
-        for r in (4, 3, 2, 1):
+        for r in (4, 3, 2):
             h_, w_ = sizes[r - 1]
             if r == 4:
                 x = rn[3]
@@ -231,22 +261,34 @@ class B200DPTHead(torch.nn.Module):
                 x = self._rcu(r, 1, rn[r - 1], n, h_, w_, extra=path, relu_out=1)
             u = self._rcu(r, 2, x, n, h_, w_)
             v = self._conv(u, n, h_, w_, 256, f"rf{r}.out.w", 1, 256, w[f"rf{r}.out.b"])
-            ho, wo = sizes[r - 2] if r > 1 else (2 * h_, 2 * w_)
+            ho, wo = sizes[r - 2]
             path = self._resize(v, n, h_, w_, 256, ho, wo)
-            hp, wp = ho, wo
-        o1 = self._conv(path, n, hp, wp, 256, "oc1.w", 9, 128, w["oc1.b"])
-        fused = self._resize(o1, n, hp, wp, 128, gh * PATCH, gw * PATCH, pu, pv)
-        _k(lib.wm_conv2d_final(_st(), fused.data_ptr(), n, H, W, 128, w["oc2.w"].data_ptr(), w["oc2.b"].data_ptr(),
-                                       w["oc3.w"].data_ptr(), w["oc3.b"].data_ptr(), self.output_dim, self.act, pred.data_ptr(),
-                                       conf.data_ptr()))
-        if self.is_gsdpt:
-            # fused + relu(input_merger(images)) (dense_head.py:239-242): the 7 horizontal taps of the 3-channel image become
-            # 21 (of 64) channels of an NHWC map, the 7 vertical taps run as an implicit GEMM with ReLU before the residual
-            assert H == gh * PATCH and W == gw * PATCH
-            rows = torch.empty(n, H, W, 64, dtype=ACT, device=dev)
-            _k(lib.wm_im2row7(_st(), images.data_ptr(), n, H, W, rows.data_ptr()))
-            _k(lib.wm_conv2d_nhwc(_st(), rows.data_ptr(), n, H, W, 64, w["im.w"].data_ptr(), 7, 128, w["im.b"].data_ptr(),
-                                  fused.data_ptr(), 0, None, 2, feat.data_ptr()))
+        # refinenet1, output_conv1, the resize to the image size and the final convolutions work on maps of 148^2 .. 518^2
+        # pixels: 90 .. 550 MB for 8 views, far beyond the 126 MB L2.  They run `tail_views` views at a time so that what
+        # one kernel writes is still in L2 when the next one reads it.
+        h_, w_ = sizes[0]
+        tv = max(1, min(n, int(self.tail_views)))
+        for v0 in range(0, n, tv):
+            m = min(tv, n - v0)
+            x = self._rcu(1, 1, rn[0][v0:v0 + m], m, h_, w_, extra=path[v0:v0 + m], relu_out=1)
+            u = self._rcu(1, 2, x, m, h_, w_)
+            v = self._conv(u, m, h_, w_, 256, "rf1.out.w", 1, 256, w["rf1.out.b"])
+            hp, wp = 2 * h_, 2 * w_
+            p1 = self._resize(v, m, h_, w_, 256, hp, wp)
+            o1 = self._conv(p1, m, hp, wp, 256, "oc1.w", 9, 128, w["oc1.b"])
+            fused = self._resize(o1, m, hp, wp, 128, gh * PATCH, gw * PATCH, pu, pv)
+            _k(lib.wm_conv2d_final(_st(), fused.data_ptr(), m, H, W, 128, w["oc2.w"].data_ptr(), w["oc2.b"].data_ptr(),
+                                   w["oc3.w"].data_ptr(), w["oc3.b"].data_ptr(), self.output_dim, self.act,
+                                   pred[v0:v0 + m].data_ptr(), conf[v0:v0 + m].data_ptr()))
+            if self.is_gsdpt:
+                # fused + relu(input_merger(images)) (dense_head.py:239-242): the 7 horizontal taps of the 3-channel image
+                # become 21 (of 64) channels of an NHWC map, the 7 vertical taps run as an implicit GEMM with ReLU before
+                # the residual
+                assert H == gh * PATCH and W == gw * PATCH
+                rows = torch.empty(m, H, W, 64, dtype=ACT, device=dev)
+                _k(lib.wm_im2row7(_st(), images[v0:v0 + m].data_ptr(), m, H, W, rows.data_ptr()))
+                _k(lib.wm_conv2d_nhwc(_st(), rows.data_ptr(), m, H, W, 64, w["im.w"].data_ptr(), 7, 128, w["im.b"].data_ptr(),
+                                      fused.data_ptr(), 0, None, 2, feat[v0:v0 + m].data_ptr()))
 
 
 class B200CameraHead(torch.nn.Module):
@@ -653,7 +695,9 @@ class B200WorldMirror(torch.nn.Module):
         self.gs_head, self.gs_renderer = gs_head, gs_renderer
         self.enable_gs = gs_head is not None and gs_renderer is not None
         self._side = None
-        self.camera_sharded = True  # views sharded over ranks: camera head on the local views (False: all views on every rank)
+        self.check_fp16_range = True  # raise Fp16RangeError when a DPT head's fp16 map saturates
+        # views sharded over ranks: camera head on the local views (WM_CAMERA_SHARDED=0: all views on every rank)
+        self.camera_sharded = os.environ.get("WM_CAMERA_SHARDED", "1") != "0"
         self.splat_readback = None  # (first row, rows): the slice of the merged splat buffers this rank copies to host_out
 
     def _camera(self, token_list):
@@ -721,6 +765,7 @@ class B200WorldMirror(torch.nn.Module):
         else:
             token_list, psi = self.visual_geometry_transformer(imgs)
         preds = {}
+        sat_now = False
         main = torch.cuda.current_stream(imgs.device)
         copy = None
         if host_out is not None:
@@ -798,8 +843,18 @@ class B200WorldMirror(torch.nn.Module):
                 for t in list(out.values()) + [count]:
                     t.record_stream(main)
             preds = self.gs_renderer.finish(preds)  # host read of the voxel count: the stream is drained here
+            sat_now = True  # ... so the saturation count copied below is valid right away
             if hasattr(self.visual_geometry_transformer, "raise_on_peer_timeout"):
                 self.visual_geometry_transformer.raise_on_peer_timeout()
         if copy is not None:
             main.wait_stream(copy)
+        if self.check_fp16_range and any(h is not None for h in (self.depth_head, self.pts_head, self.norm_head, self.gs_head)):
+            # fp16 maps in the DPT heads: a forward whose activations left the fp16 range must not pass silently.  With the
+            # Gaussian branch the stream has just been drained, so this forward's count is read now; otherwise the copy
+            # is only enqueued and the PREVIOUS forward's count is checked (no extra synchronisation on the hot path;
+            # `fp16_saturation()` checks explicitly).
+            n_sat = fp16_saturation(imgs.device, reset=True, sync=sat_now)
+            if n_sat:
+                raise Fp16RangeError(f"{n_sat} (pixel, 32-channel) entries of the DPT heads' fp16 maps left the fp16 range "
+                                     f"in {'this' if sat_now else 'the previous'} forward: the predictions are not valid")
         return preds

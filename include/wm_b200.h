@@ -225,6 +225,11 @@ wm_status wm_conv2d_nhwc(wm_stream stream, const void* in, int n, int H, int W, 
  * in, w1 [32, 9*Cin] fp16; b1 [32], w2 [od, 32], b2 [od] fp32; pred [n, H, W, od-1], conf [n, H, W] fp32; od = 2 or 4. */
 wm_status wm_conv2d_final(wm_stream stream, const void* in, int n, int H, int W, int Cin, const void* w1, const float* b1,
                           const float* w2, const float* b2, int od, int act, float* pred, float* conf);
+/* The DPT heads keep their maps in fp16: every convolution epilogue counts the (pixel, 32-channel
+ * group) entries whose fp32 value left the fp16 range before it was clamped.  Copies the count since the last reset to
+ * `host_count` (pinned host memory) on `stream` and, with reset != 0, clears it behind the copy.  A non-zero count means
+ * the predictions of that forward are not trustworthy (reference: fp32 / bf16-autocast maps, dense_head.py:164-251). */
+wm_status wm_fp16_saturation(wm_stream stream, unsigned* host_count, int reset);
 /* nn.LayerNorm(C) of gathered rows (dense_head.py:203-211): output row g * rows_per_group + i = LN(input row
  * g * in_group_rows + in_offset + i), fp32 in, fp16 out; C = 1024 or 2048. */
 wm_status wm_layernorm_rows(wm_stream stream, const float* x, const float* w, const float* b, float eps, long long rows,

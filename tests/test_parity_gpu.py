@@ -482,3 +482,35 @@ def test_batch_of_two_scenes(model_full):
         for x, y in zip(both, one):
             assert torch.equal(x[b:b + 1], y)
     assert not torch.equal(both[-1][0], both[-1][1])
+
+
+def test_large_qk_norm_weights_select_general_attention():
+    """A checkpoint whose QK-LayerNorm weights push the logit bound past the limit of the bounded-logit kernel (80 in
+    log2 units, capi.cu kMaxLogitBound): the library must select the general (running-max) attention on its own, the
+    result must not depend on `attn_allow_bounded`, and it must stay within the token_list gate against the oracle.
+    4 views of 518 x 518 (global attention over 5504 keys, all tile / tail paths), depth 2 + dino_depth 1; the q/k
+    norm weights and biases of every block are scaled by 2.2 (bound 18-20 -> ~92, logits 4.8 x larger)."""
+    sd = W.synthetic_state_dict(seed=0, depth=2, dino_depth=1)
+    for k in list(sd):
+        if ".attn.q_norm." in k or ".attn.k_norm." in k:
+            sd[k] = sd[k] * 2.2
+    m = pkg.B200VisualGeometryTransformer(depth=2, dino_depth=1, intermediate_idxs=(0, 1))
+    m.load_state_dict(sd)
+    lib, h = capi.lib(), m._handle
+    for kind in (1, 2):
+        for layer in (0, 1):
+            assert lib.wm_logit_bound(h, kind, layer) > 80.0
+    imgs = W.synthetic_images(4, 518, 518, seed=9)
+    outs, _ = m(imgs.cuda())
+    outs = [o.clone() for o in outs]
+    capi.check(lib.wm_set_int(h, b"attn_allow_bounded", 0))
+    outs2, _ = m(imgs.cuda())
+    for a, b in zip(outs, outs2):
+        assert torch.equal(a, b)  # the switch changes nothing: the general kernel ran both times
+    with torch.no_grad():
+        ref32, _ = O.aggregator_forward(imgs, sd, depth=2, dino_depth=1, intermediate=(0, 1))
+        ref16, _ = O.aggregator_forward(imgs, sd, depth=2, dino_depth=1, intermediate=(0, 1), emulate_bf16=True)
+    for o, a, b in zip(outs, ref32, ref16):
+        e32, e16 = rel_fro(o.cpu().numpy(), a.numpy()), rel_fro(o.cpu().numpy(), b.numpy())
+        print(f"bound > 80 (general attention): vs fp32 {e32:.3e}, vs bf16-emulating oracle {e16:.3e}")
+        assert torch.isfinite(o).all() and e32 <= 5e-3 and e16 <= 4e-3
