@@ -9,14 +9,15 @@ CUDA extension cannot be built here (nested `glm` submodule absent, SURVEY.md 9-
   bin_tiles  csrc/IntersectTile.cu:24-110 (keys image | tile | depth bits, stable sort), :209 (offsets)
   composite  csrc/RasterizeToPixels3DGSFwd.cu:62-200; colours gsplat/rendering.py:509-525, expected depth :760-766
 
-Parity status: PARTLY PINNED.  gsplat ships a pure-torch statement of projection and tile binning
-(gsplat/cuda/_torch_impl.py: _quat_scale_to_covar_preci, _fully_fused_projection :286, _isect_tiles :378,
-_isect_offset_encode :477) that runs on the CPU: tests/golden/make_golden_raster.py runs it on the seeded scene of
-`synthetic_scene` below and tests/test_raster_oracle.py checks `project(opacity_aware=False)` and `bin_tiles` against
-it (the torch version uses the fixed 3.33-sigma extent; the opacity-aware extent exists only in the CUDA kernel).  The
-compositing loop has no CPU statement in the reference (gsplat's torch path needs its CUDA `rasterize_to_indices_in_range`
-and nerfacc): that part is UNPINNED, restated line by line from the kernel, and checked through properties (alpha in
-[0, 0.999..], front-to-back order invariance to gaussian permutation, a single opaque splat)."""
+Parity status: PINNED against gsplat's own pure-torch statements, with one restated index list.  gsplat ships a
+pure-torch statement of projection and tile binning (gsplat/cuda/_torch_impl.py: _quat_scale_to_covar_preci,
+_fully_fused_projection :286, _isect_tiles :378, _isect_offset_encode :477) and of alpha compositing (`accumulate`
+:506-598) that run on the CPU: tests/golden/make_golden_raster.py runs them on the seeded scene of `synthetic_scene`
+below and tests/test_raster_oracle.py checks `project(opacity_aware=False)`, `bin_tiles` and `composite` against them.
+Two things exist only in gsplat's CUDA kernels and are restated from their sources: the opacity-aware extent of the
+projection, and the (gaussian, pixel) index list `accumulate` consumes (`rasterize_to_indices_in_range`,
+csrc/RasterizeToIndices3DGS.cu:58-160: alpha-threshold skip and exclusive early stop), written out in the generating
+script; `accumulate`'s two nerfacc helpers (not installed) are stubbed from their definitions there."""
 from __future__ import annotations
 
 from typing import Dict, Tuple

@@ -358,3 +358,45 @@ def test_worldmirror_forward_c2_matches_reference_golden(state_dict_full):
     ang = HO.quat_angle(cp[..., 3:7], cam_ref[..., 3:7]).max().item()
     print(f"C2 e2e camera: |params| {(cp - cam_ref).abs().max().item():.3e}, rotation {ang:.3e} rad")
     assert ang <= 1e-3 and (cp - cam_ref).abs().max().item() <= 5e-3
+
+
+@pytest.mark.parametrize("scale", [1e3, 1e6])
+def test_fp16_range_guard(scale, c1_tokens):
+    """The DPT heads keep their maps in fp16 (the reference: fp32 / bf16-autocast, dense_head.py:164-251).  With the
+    normalised tokens scaled by `scale` (norm.weight and norm.bias of the head) the head must EITHER stay in parity with
+    the fp32 oracle on the same weights OR report the saturation (`fp16_saturation()` > 0, which `B200WorldMirror.forward`
+    turns into Fp16RangeError); 1e6 is far outside the range and must be reported."""
+    toks, psi = c1_tokens, 7
+    hsd = dict(W.synthetic_heads_state_dict(seed=0))
+    pre = "depth_head."
+    hsd[pre + "norm.weight"] = hsd[pre + "norm.weight"] * scale
+    hsd[pre + "norm.bias"] = hsd[pre + "norm.bias"] * scale
+    head = heads.B200DPTHead(dim_in=2048, output_dim=2, activation="exp+expp1")
+    head.load_state_dict({k[len(pre):]: v for k, v in hsd.items() if k.startswith(pre)})
+    imgs = W.synthetic_images(2, 252, 252, seed=1)
+    heads.fp16_saturation(reset=True)
+    pred, conf = head([t.cuda() for t in toks], imgs.cuda(), psi)
+    sat = heads.fp16_saturation(reset=True)
+    print(f"scale {scale:g}: {sat} saturated (pixel, 32-channel) entries")
+    if scale >= 1e6:
+        assert sat > 0
+    if sat == 0:
+        with torch.no_grad():
+            ref_p, ref_c = HO.dpt_head(toks, 252, 252, hsd, pre, "exp+expp1")
+        # the last layer is exp(): compare where the oracle itself is finite
+        ok = torch.isfinite(ref_p) & torch.isfinite(ref_c)[..., None]
+        e = ((pred.cpu() - ref_p)[ok].norm() / ref_p[ok].norm()).item()
+        print(f"  in range: rel fro {e:.3e} on {ok.float().mean().item():.3f} of the pixels")
+        assert e <= 5e-3
+    else:
+        class _Agg:  # a stand-in aggregator that returns the fixture's tokens: only the guard of the forward is under test
+            world = 1
+
+            def __call__(self, imgs, *a, **k):
+                return [t.cuda() for t in toks], psi
+        model = heads.B200WorldMirror(_Agg(), depth_head=head)
+        with pytest.raises(heads.Fp16RangeError):
+            model({"img": imgs.cuda()})  # no Gaussian branch: the count is checked by the NEXT forward
+            torch.cuda.synchronize()
+            model({"img": imgs.cuda()})
+        heads.fp16_saturation(reset=True)

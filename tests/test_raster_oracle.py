@@ -54,3 +54,21 @@ def test_compositing_properties():
     assert 0.85 < a <= 0.9 + 1e-6
     np.testing.assert_allclose(one[0][0, 18, 20], a * np.array([R.C0 + 0.5, 0.5, 0.0]), rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(one[1][0, 18, 20, 0], 2.0, rtol=1e-5)
+
+
+def test_compositing_matches_gsplat_accumulate(fx):
+    """`composite` against gsplat's own pure-torch alpha compositing (`accumulate`, _torch_impl.py:506-598) fed with the
+    index list of `rasterize_to_indices_in_range` (tests/golden/make_golden_raster.py): colours, depth numerator and
+    alpha of every pixel of the seeded scene, from the REFERENCE's projected values and tile lists.  fp32 vs fp32, same
+    front-to-back order: agreement to rounding."""
+    if "acc_renders" not in fx.files:
+        pytest.skip("raster_scene.npz predates the compositing fixture")
+    sc = R.synthetic_scene()
+    W, H = sc["W"], sc["H"]
+    proj = {"means2d": fx["means2d"], "conics": fx["conics"], "depths": fx["depths"]}
+    rgb, dep, alpha = R.composite(proj, sc["opacities"], sc["sh"], fx["flatten_ids"], fx["offsets"], W, H)
+    ref, ref_a = fx["acc_renders"], fx["acc_alphas"]
+    assert ref.shape == (2, H, W, 4) and int(fx["acc_pairs"]) > 10000 and ref_a.max() > 0.9
+    np.testing.assert_allclose(alpha, ref_a, atol=2e-6)
+    np.testing.assert_allclose(rgb, ref[..., :3], atol=5e-6, rtol=1e-5)
+    np.testing.assert_allclose(dep * np.maximum(alpha, 1e-10), ref[..., 3:], atol=2e-5, rtol=1e-5)  # "ED" = numerator / alpha
