@@ -394,10 +394,11 @@ class B200CameraHead(torch.nn.Module):
         if key in self._graphs:
             return self._graphs[key]
         entry = None
-        # sharded: the all-gathers would have to be captured too; WM_CAM_GRAPH=2 opts in (NCCL supports capture), the
-        # default keeps the sharded head eager (16 small collectives issued from Python, same stream order on all ranks)
+        # sharded: eager (16 small collectives issued from Python, same stream order on all ranks).  Capturing the
+        # all-gathers into the graph works and gives the same numbers, but processes that hold a captured NCCL collective
+        # did not exit cleanly on the 2-GPU box (torchrun had to kill them), so it is not offered.
         mode = os.environ.get("WM_CAM_GRAPH", "1")
-        if mode != "0" and (shard is None or mode == "2"):
+        if mode != "0" and shard is None:
             tok_in = torch.zeros(S, self.dim, dtype=torch.float32, device=dev)
             outs = [torch.zeros(S, 9, dtype=torch.float32, device=dev) for _ in range(steps)]
             self._run(tok_in, self.dim, S, steps, outs, shard)  # warm-up outside capture
