@@ -411,6 +411,22 @@ def run_b200(args):
             del s_imgs
             torch.cuda.empty_cache()
 
+    # ---- BASELINE.json configs[3] / north_star: 128 views on 8 GPUs (16 per GPU), aggregator only: the global attention
+    # of that scene (Lq = 22 016 per rank against 176 128 keys) is the kernel the 60 %-of-peak target is quoted on
+    c4 = None
+    if not args.no_extras and not args.priors and world == 8 and n_local == 8:
+        c_imgs = W.synthetic_images(128, SIZE, SIZE, seed=1)[:, rank * 16:(rank + 1) * 16].contiguous().to(dev)
+        c_ms = timed(lambda: model(c_imgs), 2, 1, prof_mask=1 << 3) / 2
+        a_ms, a_n = capi.C.c_float(), capi.C.c_int()
+        capi.check(lib.wm_profile_read(model._handle, 3, capi.C.byref(a_ms), capi.C.byref(a_n)))
+        capi.check(lib.wm_profile(model._handle, 0))
+        a_avg = a_ms.value / max(a_n.value, 1)
+        c4 = {"views_total": 128, "views_per_gpu": 16, "aggregator_ms_per_step": c_ms, "views_per_s": 128 / (c_ms * 1e-3),
+              "attn_global_tflops": flops_aggregator(16, 128)["global_attention"] / 24 / (a_avg * 1e-3) / 1e12,
+              "attn_global_avg_launch_ms": a_avg, "steps": 2, "warmup": 1}
+        del c_imgs
+        torch.cuda.empty_cache()
+
     # ---- same-box comparator: stock PyTorch (cuBLAS, its SDPA backends, autocast bf16) on the shapes of this path;
     # rank 0 at N = 1 only, after every timed region of ours
     torch_gpu = None
@@ -510,6 +526,9 @@ def run_b200(args):
             line["sp_parity"] = sp_parity
         if strong is not None:
             line["strong"] = strong
+        if c4 is not None:
+            c4["attn_global_frac_of_sustained_peak"] = c4["attn_global_tflops"] / peak_tf
+            line["c4_128_views"] = c4
         if torch_gpu is not None:
             line["torch_gpu_baseline"] = torch_gpu
         print(json.dumps(line), flush=True)

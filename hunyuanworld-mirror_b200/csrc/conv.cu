@@ -34,6 +34,13 @@ namespace wm {
 // Pixels x 32-channel groups of an fp16 output map whose fp32 value left the fp16 range (or was not finite) since the
 // last reset: the DPT heads keep their maps in fp16, and a checkpoint or input that overflows them must be reported.
 __device__ unsigned int g_fp16_saturated = 0;
+// max(m, |a|, |b|) per fp16 lane of packed pairs, and "a lane reached the clamp value 65504 (0x7bff) or is not finite"
+__device__ __forceinline__ uint32_t habs_max2(uint32_t m, uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("{\n.reg .b32 t;\nmax.NaN.f16x2 t, %1, %2;\nmax.NaN.f16x2 %0, t, %3;\n}" : "=r"(d) : "r"(a & 0x7fff7fffu), "r"(b & 0x7fff7fffu), "r"(m));
+  return d;
+}
+__device__ __forceinline__ bool fp16_pair_saturated(uint32_t m) { return (m & 0xffffu) >= 0x7bffu || (m >> 16) >= 0x7bffu; }
 
 
 constexpr int CV_TW = 16, CV_TH = 8;   // tile = 8 rows x 16 columns of pixels
@@ -306,15 +313,16 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tmem_ld_x32(taddr + grp * 32, v);
           tmem_wait_ld();
           uint32_t pk[16];
-          float mx = 0.f;
+          uint32_t mx2 = 0u;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             float a = __uint_as_float(v[2 * i]), b = __uint_as_float(v[2 * i + 1]);
             if (g.bias != nullptr) a += __ldg(g.bias + grp * 32 + 2 * i), b += __ldg(g.bias + grp * 32 + 2 * i + 1);
-            mx = fmaxf(mx, fmaxf(a, b));
             pk[i] = pack_half2_sat(fmaxf(a, 0.f), fmaxf(b, 0.f));
           }
-          if (valid && !(mx <= 65504.f)) atomicAdd(&g_fp16_saturated, 1u);
+#pragma unroll
+          for (int i = 0; i < 16; i += 2) mx2 = habs_max2(mx2, pk[i], pk[i + 1]);
+          if (valid && fp16_pair_saturated(mx2)) atomicAdd(&g_fp16_saturated, 1u);
           tmem_st_x16(taddr + grp * 16, pk);
         }
         tmem_wait_st();
@@ -394,23 +402,23 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
             for (int i = 0; i < 32; ++i) xv[i] = fmaxf(xv[i], 0.f);
           }
-          {  // fp16 maps: a value beyond the fp16 range is clamped by cvt.satfinite below -- never silently: count it
-            float mx = 0.f;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fabsf(xv[i]));
-            if (valid && !(mx <= 65504.f)) atomicAdd(&g_fp16_saturated, 1u);
-          }
           // two 32-column groups fill one 128-byte staging row (64 fp16 channels) per pixel
           const int half = grp & 1;
           if (half == 0) {
             if (et == 0) tma_store_wait_read<0>();  // the previous store has drained the staging tile
             named_bar_sync(1, 128);
           }
+          // fp16 maps: a value beyond the fp16 range is clamped to +-65504 by cvt.satfinite -- never silently: the packed
+          // results are max-reduced (one HMNMX2 per two outputs) and a group that reached the clamp value is counted
+          uint32_t mx2 = 0u;
 #pragma unroll
-          for (int c = 0; c < 4; ++c)
-            st_shared_v4(stg + sw128_offset(et, half * 4 + c), pack_half2_sat(xv[8 * c], xv[8 * c + 1]),
-                         pack_half2_sat(xv[8 * c + 2], xv[8 * c + 3]), pack_half2_sat(xv[8 * c + 4], xv[8 * c + 5]),
-                         pack_half2_sat(xv[8 * c + 6], xv[8 * c + 7]));
+          for (int c = 0; c < 4; ++c) {
+            const uint32_t p0 = pack_half2_sat(xv[8 * c], xv[8 * c + 1]), p1 = pack_half2_sat(xv[8 * c + 2], xv[8 * c + 3]);
+            const uint32_t p2 = pack_half2_sat(xv[8 * c + 4], xv[8 * c + 5]), p3 = pack_half2_sat(xv[8 * c + 6], xv[8 * c + 7]);
+            mx2 = habs_max2(habs_max2(mx2, p0, p1), p2, p3);
+            st_shared_v4(stg + sw128_offset(et, half * 4 + c), p0, p1, p2, p3);
+          }
+          if (valid && fp16_pair_saturated(mx2)) atomicAdd(&g_fp16_saturated, 1u);
           if (half == 1) {
             fence_proxy_async_smem();
             named_bar_sync(1, 128);

@@ -696,6 +696,8 @@ class B200WorldMirror(torch.nn.Module):
         self.gs_head, self.gs_renderer = gs_head, gs_renderer
         self.enable_gs = gs_head is not None and gs_renderer is not None
         self._side = None
+        self.head_streams = os.environ.get("WM_HEAD_STREAMS", "0") == "1"
+        self._hstreams = []
         self.check_fp16_range = True  # raise Fp16RangeError when a DPT head's fp16 map saturates
         # views sharded over ranks: camera head on the local views (WM_CAMERA_SHARDED=0: all views on every rank)
         self.camera_sharded = os.environ.get("WM_CAMERA_SHARDED", "1") != "0"
@@ -828,11 +830,29 @@ class B200WorldMirror(torch.nn.Module):
                     for k, t in preds["splats_pending"][0][0].items():
                         emit("splats." + k, t, src=side)
             del raws
-        for name, head in (("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head)):
+        used = []
+        for i, (name, head) in enumerate((("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head))):
             if head is not None and name not in preds:
-                preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
-                emit(name, preds[name])
-                emit(name + "_conf", preds[name + "_conf"])
+                if self.head_streams:
+                    # the three heads are independent and their low-resolution stages launch fewer CTAs than there are
+                    # SMs: one stream per head lets the GPU overlap them (WM_HEAD_STREAMS=1)
+                    if len(self._hstreams) <= i or self._hstreams[i].device != imgs.device:
+                        self._hstreams = [torch.cuda.Stream(device=imgs.device) for _ in range(3)]
+                    hs = self._hstreams[i]
+                    hs.wait_stream(main)
+                    with torch.cuda.stream(hs):
+                        preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
+                    used.append((hs, name))
+                    emit(name, preds[name], src=hs)
+                    emit(name + "_conf", preds[name + "_conf"], src=hs)
+                else:
+                    preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
+                    emit(name, preds[name])
+                    emit(name + "_conf", preds[name + "_conf"])
+        for hs, name in used:
+            main.wait_stream(hs)
+            preds[name].record_stream(main)
+            preds[name + "_conf"].record_stream(main)
         if side is not None:
             main.wait_stream(side)
             for k in ("camera_params", "camera_poses", "camera_intrs"):
