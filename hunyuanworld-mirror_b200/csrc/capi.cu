@@ -493,7 +493,7 @@ wm_status wm_create(const wm_config* cfg, wm_handle** out) {
   // experiment switches (the defaults are what the forward was measured with): WM_ATTN_BOUNDED_VARIANT, WM_ATTN_GENERAL_VARIANT
   if (const char* e = getenv("WM_ATTN_BOUNDED_VARIANT")) {
     const int v = atoi(e);
-    if (v >= 8 && v <= 19) h->attn_bounded_variant = v;
+    if ((v >= 8 && v <= 19) || (v >= 24 && v <= 27)) h->attn_bounded_variant = v;
   }
   if (const char* e = getenv("WM_GEMM_SPLIT")) h->gemm_split = atoi(e) != 0;
   if (const char* e = getenv("WM_ATTN_GENERAL_VARIANT")) {
@@ -910,7 +910,7 @@ wm_status wm_set_int(wm_handle* h, const char* name, int value) {
     WM_CHECK((value >= 0 && value <= 7) || (value >= 20 && value <= 23), "attn_general_variant must be in [0,7] or [20,23]");
     h->attn_general_variant = value;
   } else if (n == "attn_bounded_variant") {
-    WM_CHECK(value >= 8 && value <= 19, "attn_bounded_variant must be in [8,19]");
+    WM_CHECK((value >= 8 && value <= 19) || (value >= 24 && value <= 27), "attn_bounded_variant must be in [8,19] or [24,27]");
     h->attn_bounded_variant = value;
   } else if (n == "attn_allow_bounded") {
     h->attn_allow_bounded = value != 0;

@@ -332,7 +332,7 @@ static int case_attn(int batch, int Lq, int Lkv, int heads, float qscale, int va
   const int ldq = heads * 64, ldkv = heads * 128;
   BF Q, KV;
   // variants >= 8 (bounded-logit mode): q arrives pre-multiplied by scale * log2(e) and P = 2^(q . k)
-  const bool bounded = variant >= 8 && variant <= 19;  // 20..23: general softmax of the pipelined kernel
+  const bool bounded = (variant >= 8 && variant <= 19) || variant >= 24;  // 20..23: general softmax of the pipelined kernel
   Q.fill((size_t)batch * Lq * ldq, bounded ? qscale * 0.125f * 1.4426950408889634f : qscale);
   KV.fill((size_t)batch * Lkv * ldkv, 1.0f);
   uint16_t *dq = dev(Q.h), *dkv = dev(KV.h);
