@@ -23,7 +23,7 @@ constexpr int ATS_SMEM = (4 + 2 * KV_ST + 2) * ATT_TILE + 512 + ATS_XCH + 1024;
 // logits; the bound is computed from the norm weights at load time, capi.cu).  softmax is shift-invariant, so the
 // reference maximum is fixed at 0: P = 2^s needs no running max, no exchange between the halves, no rescale
 // and no clamp -- exact up to the same bf16 rounding of P, because bf16 keeps 8 exponent bits.
-template <int NPOLY, bool BOUNDED, bool STREAM>
+template <int NPOLY, bool BOUNDED, int STREAM>
 __global__ void __launch_bounds__(ATS_THREADS, 1)
 attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO, const AttnArgs a) {
@@ -219,28 +219,30 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         tcgen05_fence_after();
         uint32_t pk[32];
         bool pv_waited = false;
-        if constexpr (BOUNDED && STREAM) {
+        if constexpr (BOUNDED && STREAM != 0) {
+          // (Measured, profiles/r02_s10_attn_stream_v1.log, r02_s11_attn_stream_v2.log: with the PV(j-1) wait at the top
+          // of the step 764 TFLOP/s; before the first half-store 893; STREAM 2 = unrolled, prefetching 16-column loads and
+          // one store at the end 966; the plain form below 986-994.  Not selected by default.)
           // Streaming form: the 64 scores of this thread go through in four chunks of 16 inside a ROLLED loop, every
           // chunk's TMEM load issued one chunk ahead (the load latency hides under the previous chunk's exponentials)
           // and its 8 packed probabilities stored to P straight away.  ptxas cannot pull the MUFU.EX2 of a whole tile
           // into one burst any more (at most 16 * (1 - NPOLY/32) per chunk), and at most 32 scores + 8 packed values
-          // are live.  P_qt must be free before the first store: the PV(j-1) wait moves to the top.
-          if (j > kv0) {
-            mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
-            tcgen05_fence_after();
-          }
+          // are live.  P_qt must be free before the first store: the PV(j-1) wait sits before the first (16-column) store,
+          // after half of the tile's exponentials (at the top of the step it was the hottest PC: 764 TFLOP/s).
           pv_waited = true;
           float2 sum2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
           int valid = 64;
           if (ragged && attn_phys_tile(a, j) == a.n_kv - 1) valid = a.Lkv - (a.n_kv - 1) * 128 - hf * 64;
           uint32_t va[16], vb[16];
           tmem_ld_x16(s_addr, va);
-#pragma unroll 1
+#pragma unroll(STREAM == 2 ? 2 : 1)
           for (int i = 0; i < 2; ++i) {
             tmem_wait_ld();
             tmem_ld_x16(s_addr + 32 * i + 16, vb);
+            uint32_t pk16s[16];
+            uint32_t* pk16 = STREAM == 2 ? pk + 16 * i : pk16s;  // STREAM 2: all 32 packed values kept, one store at the end
             {
-              uint32_t pk8[8];
+              uint32_t* pk8 = pk16;
               const int lim = valid - 32 * i;
               if (lim < 16) {  // only in the last, ragged key tile: P = 2^-120 for the keys beyond Lkv
                 __syncwarp();  // (warp-uniform; keeps this a real branch instead of 30 predicated selects per chunk)
@@ -261,7 +263,6 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 sum2[(c >> 1) & 1] = fadd2(sum2[(c >> 1) & 1], p);
                 pk8[c >> 1] = pack_bf16(p.x, p.y);
               }
-              tmem_st_x8(p_addr + 16 * i, pk8);
             }
             tmem_wait_ld();
             if (i == 0) {
@@ -272,7 +273,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
               if (lane == 0) mbar_arrive(&s_free[qt]);  // all 64 scores of this thread have left S_qt
             }
             {
-              uint32_t pk8[8];
+              uint32_t* pk8 = pk16 + 8;
               const int lim = valid - 32 * i - 16;
               if (lim < 16) {
                 __syncwarp();
@@ -293,8 +294,21 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 sum2[(c >> 1) & 1] = fadd2(sum2[(c >> 1) & 1], p);
                 pk8[c >> 1] = pack_bf16(p.x, p.y);
               }
-              tmem_st_x8(p_addr + 16 * i + 8, pk8);
             }
+            if constexpr (STREAM == 1) {
+              if (i == 0 && j > kv0) {
+                mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
+                tcgen05_fence_after();
+              }
+              tmem_st_x16(p_addr + 16 * i, pk16s);
+            }
+          }
+          if constexpr (STREAM == 2) {
+            if (j > kv0) {
+              mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
+              tcgen05_fence_after();
+            }
+            tmem_st_x32(p_addr, pk);
           }
           l += (sum2[0].x + sum2[0].y) + (sum2[1].x + sum2[1].y);
           tmem_wait_st();
@@ -508,7 +522,7 @@ attn_merge_kernel(const AttnArgs a, __nv_bfloat16* __restrict__ out, int ldo) {
 }
 
 // ------------------------------------------------------------------------------------------------ host
-template <int NPOLY, bool BOUNDED, bool STREAM = false>
+template <int NPOLY, bool BOUNDED, int STREAM = 0>
 static wm_status launch_split(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
                               const CUtensorMap& to, const AttnArgs& a) {
   static int cfg_dev[16] = {0};  // the shared-memory attribute is per device, not per process
@@ -529,7 +543,7 @@ size_t attn_partial_bytes(int sm_count) { return (size_t)2 * sm_count * kAttnSlo
 // variants 4..7 of flash_attention(): running-max softmax, polynomial share 0, 8, 10, 12 of every 32 exponentials;
 // variants 8..12: bounded-logit mode (q pre-scaled, |logit| bounded), polynomial share 0, 8, 12, 14, 16;
 // variants 13..19: bounded-logit mode, half-tile pipelined (attn_pipe.cu);
-// variants 24..27: bounded-logit mode with the streaming (rolled, prefetching) softmax loop, polynomial share 12, 16, 8, 20.
+// variants 24..27: bounded-logit mode with the streaming (rolled, prefetching) softmax loop, polynomial share 12, 16 (P stored in halves) and 12, 16 (one P store at the end).
 // With a partial workspace (attn_partial_bytes) the (item, kv tile) steps are dealt out evenly and split items are
 // merged by attn_merge_kernel; without one every CTA gets whole items.
 wm_status flash_attention_split(cudaStream_t st, int sm_count, const CUtensorMap& tq, const CUtensorMap& tk,
@@ -573,10 +587,10 @@ wm_status flash_attention_split(cudaStream_t st, int sm_count, const CUtensorMap
     case 10: r = launch_split<12, true>(st, grid, tq, tk, tv, to, a); break;
     case 11: r = launch_split<14, true>(st, grid, tq, tk, tv, to, a); break;
     case 12: r = launch_split<16, true>(st, grid, tq, tk, tv, to, a); break;
-    case 24: r = launch_split<12, true, true>(st, grid, tq, tk, tv, to, a); break;  // streaming softmax loop
-    case 25: r = launch_split<16, true, true>(st, grid, tq, tk, tv, to, a); break;
-    case 26: r = launch_split<8, true, true>(st, grid, tq, tk, tv, to, a); break;
-    case 27: r = launch_split<20, true, true>(st, grid, tq, tk, tv, to, a); break;
+    case 24: r = launch_split<12, true, 1>(st, grid, tq, tk, tv, to, a); break;  // streaming softmax loop, P stored in halves
+    case 25: r = launch_split<16, true, 1>(st, grid, tq, tk, tv, to, a); break;
+    case 26: r = launch_split<12, true, 2>(st, grid, tq, tk, tv, to, a); break;  // streaming loop, one P store at the end
+    case 27: r = launch_split<16, true, 2>(st, grid, tq, tk, tv, to, a); break;
     default:
       if (variant >= 13 && variant <= 23) {  // second-generation kernels (attn_pipe.cu): 13-19 bounded, 20-23 general
         r = flash_attention_pipe(st, grid, tq, tk, tv, to, a, variant);
