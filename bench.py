@@ -342,10 +342,13 @@ def run_b200(args):
     # rows valid): the read-back is shared, every rank copies rows [rank, rank + 1) * N / world over its own PCIe link
     splat_rows = n_total * SIZE * SIZE
     rows_mine = splat_rows // world
+    partitioned = gs_on and world > 1 and full.gs_renderer.partitioned  # every rank merges (and reads back) one key range
+    if partitioned:
+        rows_mine = int(rows_mine * 1.25)  # the ranges are balanced by sampled quantiles: within a few per cent of N / world
     splat_host = ({k: torch.empty((rows_mine,) + shp, dtype=torch.float32).pin_memory()
                    for k, shp in (("means", (3,)), ("sh", (1, 3)), ("opacities", ()), ("scales", (3,)), ("quats", (4,)))}
                   if gs_on else None)
-    if gs_on and world > 1:
+    if gs_on and world > 1 and not partitioned:
         full.splat_readback = (rank * rows_mine, rows_mine)
     splat_bytes = [0]
     all_host = dict(host_out)
@@ -360,7 +363,8 @@ def run_b200(args):
             # splats are read back as N-row buffers (the voxel count K is known on the host only at the end)
             preds = full({"img": x}, cond_flags=flags, priors=pri, host_out=all_host)
             if splat_host is not None:
-                splat_bytes[0] = sum(t.numel() * 4 for t in splat_host.values())
+                rows_read = min(rows_mine, preds["splats_rows"][0]) if partitioned else rows_mine
+                splat_bytes[0] = sum(t[:rows_read].numel() * 4 for t in splat_host.values())
         else:
             outs, _ = model(x, pri, cond_flags=flags)
             host_out["cam_tokens"].copy_(outs[-1][:, :, 0], non_blocking=True)

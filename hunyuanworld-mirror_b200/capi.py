@@ -90,6 +90,10 @@ SIGNATURES = {
     "wm_prune_workspace_bytes": (C.c_int, [C.c_longlong, C.POINTER(C.c_size_t)]),
     "wm_prune_splats": (C.c_int, [_vp, C.c_longlong, _fp, _fp, _fp, _fp, _fp, _fp, C.c_double, _vp, C.c_size_t, _fp, _fp, _fp,
                                   _fp, _fp, _vp]),
+    "wm_prune_splats_bounds": (C.c_int, [_vp, C.c_longlong, _fp, _fp, _fp, _fp, _fp, _fp, C.c_double, _vp, C.c_size_t, _fp, _fp, _fp,
+                                         _fp, _fp, _vp, _vp]),
+    "wm_voxel_bounds": (C.c_int, [_vp, C.c_longlong, _fp, C.c_double, _vp]),
+    "wm_voxel_keys": (C.c_int, [_vp, C.c_longlong, _fp, C.c_double, _vp, _vp]),
     "wm_conf_filter_workspace_bytes": (C.c_int, [C.c_longlong, C.POINTER(C.c_size_t)]),
     "wm_conf_filter_splats": (C.c_int, [_vp, C.c_longlong, C.c_longlong, _fp, _fp, _fp, _fp, _fp, _fp, _fp, _vp, C.c_size_t, _fp, _fp,
                                         _fp, _fp, _fp, _fp]),

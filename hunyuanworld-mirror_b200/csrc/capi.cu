@@ -1141,6 +1141,29 @@ wm_status wm_prune_splats(wm_stream stream, long long N, const float* means, con
                       workspace_bytes, out_means, out_quats, out_scales, out_opacities, out_sh, count);
 }
 
+wm_status wm_prune_splats_bounds(wm_stream stream, long long N, const float* means, const float* quats, const float* scales,
+                                 const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
+                                 size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
+                                 float* out_sh, unsigned* count, const long long* bounds) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  WM_CHECK(bounds != nullptr, "wm_prune_splats_bounds: null bounds");
+  return prune_splats(static_cast<cudaStream_t>(stream), N, means, quats, scales, opacities, sh, weights, voxel_size, workspace,
+                      workspace_bytes, out_means, out_quats, out_scales, out_opacities, out_sh, count, bounds);
+}
+
+wm_status wm_voxel_bounds(wm_stream stream, long long N, const float* means, double voxel_size, long long* bounds) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return voxel_bounds(static_cast<cudaStream_t>(stream), N, means, voxel_size, bounds);
+}
+
+wm_status wm_voxel_keys(wm_stream stream, long long N, const float* means, double voxel_size, const long long* bounds, long long* keys) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return voxel_keys(static_cast<cudaStream_t>(stream), N, means, voxel_size, bounds, keys);
+}
+
 wm_status wm_conf_filter_workspace_bytes(long long N, size_t* bytes) { return conf_filter_workspace_bytes(N, bytes); }
 
 wm_status wm_conf_filter_splats(wm_stream stream, long long N, long long K, const float* conf, const float* means, const float* quats,

@@ -70,7 +70,9 @@ wm_status prune_workspace_bytes(long long N, size_t* bytes);
 wm_status prune_splats(cudaStream_t st, long long N, const float* means, const float* quats, const float* scales,
                        const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
                        size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities, float* out_sh,
-                       unsigned* count);
+                       unsigned* count, const long long* ext_bounds = nullptr);
+wm_status voxel_bounds(cudaStream_t st, long long N, const float* means, double voxel_size, long long* bounds);
+wm_status voxel_keys(cudaStream_t st, long long N, const float* means, double voxel_size, const long long* bounds, long long* keys);
 wm_status conf_filter_workspace_bytes(long long N, size_t* bytes);
 wm_status conf_filter_splats(cudaStream_t st, long long N, long long K, const float* conf, const float* means, const float* quats,
                              const float* scales, const float* opacities, const float* sh, const float* weights, void* workspace,

@@ -312,10 +312,46 @@ wm_status prune_workspace_bytes(long long N, size_t* bytes) {
 }
 
 // prune_gs (rasterization.py:301-387) for one scene: N splats -> *count voxels (device word), outputs sized for N rows.
+// Voxel-index bounds of a set of means ([6] int64 on the device: min xyz, max xyz) and the flat keys for GIVEN bounds:
+// the two halves of prune_splats' keying, exposed so that ranks holding different views of one scene can agree on the
+// bounds (all-reduce min / max) and route every splat to the rank that owns its key range (heads.py).
+wm_status voxel_bounds(cudaStream_t st, long long N, const float* means, double voxel_size, long long* bounds) {
+  WM_CHECK(N >= 0 && N < (1ll << 31) && bounds && (N == 0 || means) && voxel_size > 0, "voxel_bounds: bad argument");
+  prune_init_kernel<<<1, 32, 0, st>>>(bounds);
+  if (N > 0) {
+    const int grid = (int)std::min<size_t>(((size_t)N + SP_THREADS - 1) / SP_THREADS, 148 * 16);
+    prune_bounds_kernel<<<grid, SP_THREADS, 0, st>>>(means, (unsigned)N, (float)voxel_size, bounds);
+  }
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+__global__ void __launch_bounds__(SP_THREADS)
+voxel_keys_kernel(const float* __restrict__ means, unsigned N, float vs, const long long* __restrict__ bounds, long long* __restrict__ keys) {
+  const long long mx = bounds[0], my = bounds[1], mz = bounds[2];
+  const long long dy = bounds[4] - my + 1, dz = bounds[5] - mz + 1;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const long long vx = sp_voxel(__ldg(means + (size_t)i * 3), vs) - mx;
+    const long long vy = sp_voxel(__ldg(means + (size_t)i * 3 + 1), vs) - my;
+    const long long vz = sp_voxel(__ldg(means + (size_t)i * 3 + 2), vs) - mz;
+    keys[i] = vx * dy * dz + vy * dz + vz;
+  }
+}
+
+wm_status voxel_keys(cudaStream_t st, long long N, const float* means, double voxel_size, const long long* bounds, long long* keys) {
+  WM_CHECK(N > 0 && N < (1ll << 31) && means && bounds && keys && voxel_size > 0, "voxel_keys: bad argument");
+  const int grid = (int)std::min<size_t>(((size_t)N + SP_THREADS - 1) / SP_THREADS, 148 * 16);
+  voxel_keys_kernel<<<grid, SP_THREADS, 0, st>>>(means, (unsigned)N, (float)voxel_size, bounds, keys);
+  WM_LAUNCH_CHECK();
+  return WM_OK;
+}
+
+// ext_bounds (device, [6] int64, or null): voxel-index bounds to key with instead of the bounds of `means` -- the bounds of the
+// WHOLE scene when this call merges one key range of it.
 wm_status prune_splats(cudaStream_t st, long long N, const float* means, const float* quats, const float* scales,
                        const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
                        size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities, float* out_sh,
-                       unsigned* count) {
+                       unsigned* count, const long long* ext_bounds) {
   WM_CHECK(N > 0 && N < (1ll << 31) && means && quats && scales && opacities && sh && weights && workspace && out_means && out_quats &&
                out_scales && out_opacities && out_sh && count && voxel_size > 0,
            "prune_splats: bad argument");
@@ -326,8 +362,12 @@ wm_status prune_splats(cudaStream_t st, long long N, const float* means, const f
   const unsigned n = (unsigned)N;
   const float vs = (float)voxel_size;  // the Python float becomes an fp32 divisor
   const int grid = (int)std::min<size_t>(((size_t)n + SP_THREADS - 1) / SP_THREADS, 148 * 16);
-  prune_init_kernel<<<1, 32, 0, st>>>(w.bounds);
-  prune_bounds_kernel<<<grid, SP_THREADS, 0, st>>>(means, n, vs, w.bounds);
+  if (ext_bounds != nullptr) {
+    WM_CUDA(cudaMemcpyAsync(w.bounds, ext_bounds, 6 * sizeof(long long), cudaMemcpyDeviceToDevice, st));
+  } else {
+    prune_init_kernel<<<1, 32, 0, st>>>(w.bounds);
+    prune_bounds_kernel<<<grid, SP_THREADS, 0, st>>>(means, n, vs, w.bounds);
+  }
   prune_keys_kernel<<<grid, SP_THREADS, 0, st>>>(means, n, vs, w.bounds, w.keys_in, w.vals_in);
   WM_LAUNCH_CHECK();
   size_t tmp = w.cub_bytes;

@@ -481,6 +481,9 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         self.enable_conf_filter, self.conf_threshold_percent, self.max_gaussians = enable_conf_filter, conf_threshold_percent, max_gaussians
         self._fws = None
         self.sharded, self.group = sharded, group  # views sharded over the ranks of `group` (None: the default group)
+        # sharded: every rank merges one key range of the scene (partition_scene) instead of the whole scene W times over;
+        # predictions["splats"] then holds this rank's range (WM_SPLAT_PARTITION=0: every rank gathers and merges everything)
+        self.partitioned = os.environ.get("WM_SPLAT_PARTITION", "1") != "0"
         self.w: Dict[str, torch.Tensor] = {}
         self._loaded = False
         self._ws = None
@@ -563,7 +566,7 @@ class B200GaussianSplatRenderer(torch.nn.Module):
                                              out["opacities"].data_ptr(), out["sh"].data_ptr(), out["weights"].data_ptr()))
         return {k: out.get(k, v) for k, v in splats.items()}
 
-    def prune_gs(self, splats, voxel_size=None, defer: bool = False):
+    def prune_gs(self, splats, voxel_size=None, defer: bool = False, bounds=None):
         """rasterization.py:301-387 for one scene (tensors over N splats) -> tensors over the K occupied voxels, ascending
         flat voxel index.  One host read (K) at the end, as the reference's `len(unique_voxels)`; defer=True returns the
         N-row buffers and the device-side count instead, so that the caller can keep launching work and read K later
@@ -572,19 +575,103 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         vs = self.voxel_size if voxel_size is None else voxel_size
         m = splats["means"]
         N, dev = m.shape[0], m.device
+        out = {k: torch.empty_like(splats[k]) for k in ("means", "quats", "scales", "opacities", "sh")}
+        count = torch.zeros(1, dtype=torch.int32, device=dev)
+        if N == 0:  # a key range of a partitioned scene may be empty
+            return (out, count) if defer else self.finish_prune(out, count)
         need = C.c_size_t(0)
         capi.check(lib.wm_prune_workspace_bytes(N, C.byref(need)))
         if self._ws is None or self._ws.numel() < need.value or self._ws.device != dev:
             self._ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
-        out = {k: torch.empty_like(splats[k]) for k in ("means", "quats", "scales", "opacities", "sh")}
-        count = torch.zeros(1, dtype=torch.int32, device=dev)
         LAUNCHES[0] += 6  # bounds, keys, sort (several CUB kernels, counted once), flags, scan, merge
-        capi.check(lib.wm_prune_splats(_st(), N, m.data_ptr(), splats["quats"].data_ptr(), splats["scales"].data_ptr(),
-                                       splats["opacities"].data_ptr(), splats["sh"].reshape(N, 3).data_ptr(),
-                                       splats["weights"].data_ptr(), float(vs), self._ws.data_ptr(), self._ws.numel(),
-                                       out["means"].data_ptr(), out["quats"].data_ptr(), out["scales"].data_ptr(),
-                                       out["opacities"].data_ptr(), out["sh"].data_ptr(), count.data_ptr()))
+        args = (_st(), N, m.data_ptr(), splats["quats"].data_ptr(), splats["scales"].data_ptr(), splats["opacities"].data_ptr(),
+                splats["sh"].reshape(N, 3).data_ptr(), splats["weights"].data_ptr(), float(vs), self._ws.data_ptr(),
+                self._ws.numel(), out["means"].data_ptr(), out["quats"].data_ptr(), out["scales"].data_ptr(),
+                out["opacities"].data_ptr(), out["sh"].data_ptr(), count.data_ptr())
+        if bounds is None:
+            capi.check(lib.wm_prune_splats(*args))
+        else:  # the voxel-index bounds of the WHOLE scene: this call merges one key range of it
+            capi.check(lib.wm_prune_splats_bounds(*args, bounds.data_ptr()))
         return (out, count) if defer else self.finish_prune(out, count)
+
+    _PACK = (("means", 3), ("quats", 4), ("scales", 3), ("opacities", 1), ("sh", 3), ("weights", 1))
+
+    def partition_scene(self, sp):
+        """Views sharded over the ranks of `self.group`: instead of gathering all N_total splats on every rank and merging
+        them W times over, every rank ends up with ONE KEY RANGE of the scene and merges only that (N_total / W splats).
+          1. voxel-index bounds of the local splats, all-reduced (min / max) to the bounds of the scene;
+          2. flat voxel keys of the local splats with those bounds (the keys of the single-GPU merge);
+          3. W - 1 splitters = quantiles of a fixed-size sample of every rank's keys (all-gathered, so identical everywhere);
+             rank r owns the keys in [splitter[r-1], splitter[r]): equal keys always meet on one rank;
+          4. the local splats, stably ordered by owner, go out in ONE all-to-all of packed 15-float rows; the per-pair
+             row counts are all-gathered first and read by the host (the one synchronisation of this path);
+          5. what arrives is ordered by (source rank, original index) = the scene's global splat order, so the stable sort
+             inside the merge accumulates every voxel in the same order as the single-GPU merge: the ranks' results,
+             concatenated in rank order, equal it bit for bit (tests/sp_check.py).
+        Returns (splat dict of this rank's key range, bounds)."""
+        import torch.distributed as dist
+
+        lib, group = capi.lib(), self.group
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        m = sp["means"]
+        n, dev = m.shape[0], m.device
+        vs = float(self.voxel_size)
+        bounds = torch.empty(6, dtype=torch.int64, device=dev)
+        _k(lib.wm_voxel_bounds(_st(), n, m.data_ptr(), vs, bounds.data_ptr()))
+        lo, hi = bounds[:3].clone(), bounds[3:].clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+        bounds = torch.cat([lo, hi])
+        keys = torch.empty(n, dtype=torch.int64, device=dev)
+        _k(lib.wm_voxel_keys(_st(), n, m.data_ptr(), vs, bounds.data_ptr(), keys.data_ptr()))
+        S = 4096  # sample size per rank
+        samp = keys[(torch.arange(S, device=dev, dtype=torch.int64) * n) // S]
+        allsamp = torch.empty(world * S, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allsamp, samp, group=group)
+        allsamp = torch.sort(allsamp).values
+        splitters = allsamp[(torch.arange(1, world, device=dev, dtype=torch.int64) * (world * S)) // world].contiguous()
+        dest = torch.bucketize(keys, splitters, right=True)
+        order = torch.sort(dest, stable=True).indices
+        counts = torch.bincount(dest, minlength=world)
+        cm = torch.empty(world * world, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(cm, counts, group=group)
+        cm = cm.reshape(world, world).cpu()  # host read: cm[s, d] = rows rank s sends to rank d
+        send, recv = cm[rank].tolist(), cm[:, rank].tolist()
+        packed = torch.cat([sp[k].reshape(n, -1) for k, _ in self._PACK], dim=1).index_select(0, order)
+        got = torch.empty(sum(recv), packed.shape[1], dtype=torch.float32, device=dev)
+        dist.all_to_all_single(got, packed, recv, send, group=group)
+        part, c0 = {}, 0
+        for k, d in self._PACK:
+            t = got[:, c0:c0 + d].contiguous()
+            part[k] = t if d > 1 else t.reshape(-1)
+            c0 += d
+        LAUNCHES[0] += 3  # bounds, keys, (torch's sort / bucketize / gather kernels are library code)
+        return part, bounds
+
+    def gather_partitions(self, splats):
+        """predictions["splats"] of a partitioned merge (this rank's key range) -> the whole merged scene on every rank,
+        per-scene lists as the single-GPU renderer returns them.  One small all-gather of the row counts (host read) and
+        one padded all-gather per array."""
+        import torch.distributed as dist
+
+        group = self.group
+        world = dist.get_world_size(group)
+        out = {k: [] for k in splats}
+        for b in range(len(splats["means"])):
+            K = splats["means"][b].shape[0]
+            dev = splats["means"][b].device
+            ks = torch.empty(world, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(ks, torch.tensor([K], dtype=torch.int64, device=dev), group=group)
+            ks = ks.cpu().tolist()
+            cap = max(max(ks), 1)
+            for k, v in splats.items():
+                t = v[b]
+                pad = torch.zeros((cap,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+                pad[:K] = t
+                allp = torch.empty((world * cap,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+                dist.all_gather_into_tensor(allp, pad, group=group)
+                out[k].append(torch.cat([allp[r * cap:r * cap + ks[r]] for r in range(world)], dim=0))
+        return out
 
     @staticmethod
     def finish_prune(out, count):
@@ -597,6 +684,7 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         """Second half of render(..., defer=True): read the voxel counts (host sync) and slice the merged splats."""
         pending = predictions.pop("splats_pending", None)
         if pending is not None:
+            predictions["splats_rows"] = [out["means"].shape[0] for out, _ in pending]  # rows of the N-row merge buffers
             merged = [self.finish_prune(out, count) for out, count in pending]
             predictions["splats"] = {k: [m[k] for m in merged] for k in ("means", "sh", "opacities", "scales", "quats")}
         return predictions
@@ -638,6 +726,12 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         for b in range(B):
             raw = raws[b]
             sp = self.prepare_splats(raw, images[b, :S], predictions["gs_depth"][b, :S], predictions["camera_params"][b, :S])
+            conf_on = self.enable_conf_filter and "depth_conf" in predictions
+            if self.sharded and self.partitioned and self.enable_prune and not rasterize and not conf_on:
+                # every rank keeps and merges one key range of the scene (partition_scene)
+                part, bounds = self.partition_scene(sp)
+                scenes.append((part, bounds))
+                continue
             if self.sharded:  # views are sharded over ranks: every rank needs all splats of the scene
                 import torch.distributed as dist
 
@@ -655,7 +749,14 @@ class B200GaussianSplatRenderer(torch.nn.Module):
                     conf = torch.cat(parts, dim=0)
                 sp = self.apply_confidence_filter(sp, conf)
             scenes.append(sp)
-        if self.enable_prune and defer and not rasterize:
+        if scenes and isinstance(scenes[0], tuple):  # partitioned: (this rank's key range, the scene's bounds)
+            if defer:
+                predictions["splats_pending"] = [self.prune_gs(sp, defer=True, bounds=bd) for sp, bd in scenes]
+            else:
+                merged = [self.prune_gs(sp, bounds=bd) for sp, bd in scenes]
+                predictions["splats"] = {k: [m[k] for m in merged] for k in ("means", "sh", "opacities", "scales", "quats")}
+            predictions["splats_partitioned"] = True  # this rank's key range; gather_partitions() assembles the scene
+        elif self.enable_prune and defer and not rasterize:
             predictions["splats_pending"] = [self.prune_gs(sp, defer=True) for sp in scenes]
         elif self.enable_prune:
             merged = [self.prune_gs(sp) for sp in scenes]
@@ -786,7 +887,8 @@ class B200WorldMirror(torch.nn.Module):
             copy.wait_stream(main if src is None else src)
             with torch.cuda.stream(copy):
                 dst = host_out[name]
-                dst.view(-1)[:t.numel()].copy_(t.reshape(-1), non_blocking=True)
+                ne = min(t.numel(), dst.numel())  # (a key range of a partitioned scene may exceed the caller's estimate)
+                dst.view(-1)[:ne].copy_(t.reshape(-1)[:ne], non_blocking=True)
             t.record_stream(copy)
 
         side = None
@@ -820,16 +922,25 @@ class B200WorldMirror(torch.nn.Module):
                 preds["depth"], preds["depth_conf"] = self.depth_head(token_list, images=imgs, patch_start_idx=psi)
                 emit("depth", preds["depth"])
                 emit("depth_conf", preds["depth_conf"])
-            side.wait_stream(main)
-            with torch.cuda.stream(side):
-                for t in raws + [preds["gs_depth"], imgs] + ([preds["depth_conf"]] if "depth_conf" in preds else []):
-                    t.record_stream(side)
-                emit("camera_params", preds["camera_params"], src=side)
-                preds = self.gs_renderer.assemble(raws, imgs, preds, views, defer=True)
-                if "splats_pending" in preds and len(preds["splats_pending"]) == 1:
-                    for k, t in preds["splats_pending"][0][0].items():
-                        emit("splats." + k, t, src=side)
-            del raws
+            gs_ready = main.record_event()
+
+            def splat_chain(preds):
+                side.wait_event(gs_ready)
+                with torch.cuda.stream(side):
+                    for t in raws + [preds["gs_depth"], imgs] + ([preds["depth_conf"]] if "depth_conf" in preds else []):
+                        t.record_stream(side)
+                    emit("camera_params", preds["camera_params"], src=side)
+                    preds = self.gs_renderer.assemble(raws, imgs, preds, views, defer=True)
+                    if "splats_pending" in preds and len(preds["splats_pending"]) == 1:
+                        for k, t in preds["splats_pending"][0][0].items():
+                            emit("splats." + k, t, src=side)
+                return preds
+
+            # The partitioned merge of a sharded scene reads one small count matrix on the host in the middle of the chain:
+            # the remaining heads are enqueued first, so the main stream has work while the host waits for the side stream.
+            late_chain = self.gs_renderer.sharded and self.gs_renderer.partitioned
+            if not late_chain:
+                preds = splat_chain(preds)
         used = []
         for i, (name, head) in enumerate((("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head))):
             if head is not None and name not in preds:
@@ -853,6 +964,10 @@ class B200WorldMirror(torch.nn.Module):
             main.wait_stream(hs)
             preds[name].record_stream(main)
             preds[name + "_conf"].record_stream(main)
+        if self.enable_gs:
+            if late_chain:
+                preds = splat_chain(preds)
+            del raws
         if side is not None:
             main.wait_stream(side)
             for k in ("camera_params", "camera_poses", "camera_intrs"):

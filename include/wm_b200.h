@@ -308,6 +308,21 @@ wm_status wm_prune_splats(wm_stream stream, long long N, const float* means, con
                           size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales, float* out_opacities,
                           float* out_sh, unsigned* count);
 
+/* The same merge for ONE KEY RANGE of a scene whose views are spread over several GPUs (heads.py:
+ * B200GaussianSplatRenderer, partitioned merge): every rank computes the voxel-index bounds of its own splats
+ * (wm_voxel_bounds: [6] int64 on the device, min xyz then max xyz), the ranks all-reduce them (min / max), key their splats
+ * with the scene's bounds (wm_voxel_keys: the flat index of rasterization.py:322-331), exchange the splats so that every
+ * rank holds one contiguous key range in (rank, index) order, and merge it with wm_prune_splats_bounds (= wm_prune_splats
+ * keyed with the given bounds instead of those of its input).  The ranks' outputs, concatenated in rank order, are the
+ * single-GPU result bit for bit. */
+wm_status wm_voxel_bounds(wm_stream stream, long long N, const float* means, double voxel_size, long long* bounds);
+wm_status wm_voxel_keys(wm_stream stream, long long N, const float* means, double voxel_size, const long long* bounds,
+                        long long* keys);
+wm_status wm_prune_splats_bounds(wm_stream stream, long long N, const float* means, const float* quats, const float* scales,
+                                 const float* opacities, const float* sh, const float* weights, double voxel_size, void* workspace,
+                                 size_t workspace_bytes, float* out_means, float* out_quats, float* out_scales,
+                                 float* out_opacities, float* out_sh, unsigned* count, const long long* bounds);
+
 /* apply_confidence_filter (rasterization.py:248-299) for one scene: conf [N] (confidences <= 1e-5 count as -inf), keep the K
  * most confident splats, K = max(1, min(max_gaussians, ceil(N * (100 - percent) / 100))) computed by the caller.  The
  * reference takes torch.topk(sorted=False), whose order and tie choice are unspecified; here equal confidences are taken in

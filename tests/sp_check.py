@@ -90,17 +90,25 @@ def main():
     cp[..., 7:] = cp[..., 7:].abs() * 0.3 + 0.6
     preds = {"camera_params": cp.to(dev), "gs_depth": (torch.rand(1, S, h, w, 1, generator=g) * 0.05 + 0.2).to(dev)}
     outs = []
-    for sharded in (True, False):
+    for sharded, partitioned in ((True, True), (True, False), (False, False)):
         r = H2.B200GaussianSplatRenderer(voxel_size=0.01, sharded=sharded)
+        r.partitioned = partitioned
         r.load_state_dict({k[len("gs_renderer."):]: v for k, v in gsd.items() if k.startswith("gs_renderer.")})
         v = sl if sharded else slice(0, S)
         p = {k: t[:, v].contiguous() for k, t in preds.items()}
-        outs.append(r.render(feat[:, v].permute(0, 1, 4, 2, 3), im[:, v].contiguous(), p)["splats"])
+        res = r.render(feat[:, v].permute(0, 1, 4, 2, 3), im[:, v].contiguous(), p)
+        if partitioned:  # this rank merged one key range of the scene: the ranges in rank order are the scene
+            assert res.get("splats_partitioned")
+            mine_k = res["splats"]["means"][0].shape[0]
+            res["splats"] = r.gather_partitions(res["splats"])
+        outs.append(res["splats"])
     torch.cuda.synchronize()
-    K = outs[1]["means"][0].shape[0]
-    same = all(torch.equal(outs[0][k][0], outs[1][k][0]) for k in ("means", "sh", "opacities", "scales", "quats"))
-    print(f"rank {rank}: sharded voxel merge == single-GPU merge: {same} ({S * h * w} splats -> {K} voxels)", flush=True)
-    ok &= same and 0 < K < S * h * w
+    K = outs[2]["means"][0].shape[0]
+    same_p = all(torch.equal(outs[0][k][0], outs[2][k][0]) for k in ("means", "sh", "opacities", "scales", "quats"))
+    same = all(torch.equal(outs[1][k][0], outs[2][k][0]) for k in ("means", "sh", "opacities", "scales", "quats"))
+    print(f"rank {rank}: partitioned merge (this rank: {mine_k} of {K} voxels) == single-GPU merge: {same_p}; "
+          f"replicated sharded merge == single-GPU merge: {same} ({S * h * w} splats -> {K} voxels)", flush=True)
+    ok &= same and same_p and 0 < K < S * h * w and 0 < mine_k < K
     # the same with the confidence filter: the depth head's confidence is gathered with the splats
     preds["depth_conf"] = (1.0 + torch.randint(0, 50, (1, S, h, w), generator=g).float() * 0.125).to(dev)  # ties on purpose
     outs = []
