@@ -15,6 +15,7 @@ constexpr int ATT_SMEM = (4 + 2 * KV_ST + 2) * ATT_TILE + 512 + 1024;
 struct AttnArgs {
   int Lq, Lkv, batch;
   int n_qpairs, n_kv, total_items;
+  int n_cheap;  // > 0 (whole-item schedules only): items whose query pair holds ONE 128-row tile, dealt out last (attn_item)
   float scale_log2;
   // attn_split.cu only.  Work items are dealt out in `full_waves` strided waves (item = wave * grid + cta: CTAs that
   // run at the same time share a head's K|V in L2), then the remaining items' (item, kv tile) steps are split into
@@ -63,16 +64,34 @@ __device__ __forceinline__ void attn_wait_shards(const AttnArgs& a, int jp, unsi
   }
 }
 
+// Schedule position -> work item.  When the last query pair of every (head, batch entry) holds a single 128-row tile
+// (Lq mod 256 in 1..128: 1376 and 1374 rows per view are such lengths) that item costs about half of a full one.  Whole-item
+// schedules deal the full items out first and the cheap ones last, and the tail wave goes to the CTAs that drew cheap
+// items in the last full wave (AttnSched), so the longest CTA runs 4 full + 2 cheap items instead of 6 full ones at 8
+// views x 16 heads on 148 SMs.
+__device__ __forceinline__ int attn_item(const AttnArgs& a, int pos) {
+  if (a.n_cheap == 0) return pos;
+  const int n_full = a.total_items - a.n_cheap, qp_full = a.n_qpairs - 1;
+  if (pos < n_full) {
+    const int hb = pos / qp_full;
+    return hb * a.n_qpairs + (pos - hb * qp_full);
+  }
+  return (pos - n_full) * a.n_qpairs + qp_full;
+}
+
 // The segment sequence of one CTA; producer, MMA issuer and softmax warps walk it in lockstep.
 struct AttnSched {
   int w, tstep, tbegin, tend;
   __device__ explicit AttnSched(const AttnArgs& a) : w(0) {
-    tbegin = tstep = blockIdx.x * a.per_cta;
+    // whole-item schedules hand the tail items to the LAST CTAs (see attn_item); split schedules keep CTA order, which
+    // attn_merge_kernel relies on
+    const int c = a.part_o == nullptr ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+    tbegin = tstep = c * a.per_cta;
     tend = min(tbegin + a.per_cta, a.tail_steps);
   }
   __device__ bool next(const AttnArgs& a, int& item, int& kv0, int& kv1, int& slot) {
     if (w < a.full_waves) {
-      item = w * gridDim.x + blockIdx.x;
+      item = attn_item(a, w * gridDim.x + blockIdx.x);
       ++w;
       kv0 = 0, kv1 = a.n_kv, slot = -1;
       return true;
@@ -81,7 +100,7 @@ struct AttnSched {
     const int ti = tstep / a.n_kv;
     kv0 = tstep - ti * a.n_kv;
     kv1 = min(a.n_kv, kv0 + (tend - tstep));
-    item = a.full_waves * gridDim.x + ti;
+    item = attn_item(a, a.full_waves * gridDim.x + ti);
     slot = (kv0 == 0 && kv1 == a.n_kv) ? -1 : 2 * blockIdx.x + (tstep == tbegin ? 0 : 1);
     tstep += kv1 - kv0;
     return true;

@@ -573,9 +573,11 @@ wm_status flash_attention_split(cudaStream_t st, int sm_count, const CUtensorMap
     a.part_l = partial_ws + (size_t)2 * sm_count * 256 * 64;
     a.part_m = a.part_l + (size_t)2 * sm_count * 256;
   } else {
-    a.per_cta = a.n_kv;  // whole items only: CTA c takes tail item c, no partials
+    a.per_cta = a.n_kv;  // whole items only: no partials; the tail items go to the last CTAs (AttnSched)
     a.part_o = a.part_l = a.part_m = nullptr;
   }
+  const int last_rows = a.Lq - (a.n_qpairs - 1) * 256;
+  a.n_cheap = (a.part_o == nullptr && last_rows <= 128 && a.total_items > grid) ? a.total_items / a.n_qpairs : 0;
   wm_status r;
   switch (variant) {
     case 4: r = launch_split<0, false>(st, grid, tq, tk, tv, to, a); break;
