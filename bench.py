@@ -342,7 +342,7 @@ def run_b200(args):
     # rows valid): the read-back is shared, every rank copies rows [rank, rank + 1) * N / world over its own PCIe link
     splat_rows = n_total * SIZE * SIZE
     rows_mine = splat_rows // world
-    partitioned = gs_on and world > 1 and full.gs_renderer.partitioned  # every rank merges (and reads back) one key range
+    partitioned = gs_on and world > 1 and full.gs_renderer.use_partition()  # every rank merges (and reads back) one key range
     if partitioned:
         rows_mine = int(rows_mine * 1.25)  # the ranges are balanced by sampled quantiles: within a few per cent of N / world
     splat_host = ({k: torch.empty((rows_mine,) + shp, dtype=torch.float32).pin_memory()

@@ -482,8 +482,10 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         self._fws = None
         self.sharded, self.group = sharded, group  # views sharded over the ranks of `group` (None: the default group)
         # sharded: every rank merges one key range of the scene (partition_scene) instead of the whole scene W times over;
-        # predictions["splats"] then holds this rank's range (WM_SPLAT_PARTITION=0: every rank gathers and merges everything)
-        self.partitioned = os.environ.get("WM_SPLAT_PARTITION", "1") != "0"
+        # predictions["splats"] then holds this rank's range (WM_SPLAT_PARTITION=0 / 1 forces the replicated / partitioned merge)
+        # None: automatic (more than two ranks: at two the exchange costs what the second merge does), True / False: forced
+        env = os.environ.get("WM_SPLAT_PARTITION")
+        self.partitioned = None if env is None else env != "0"
         self.w: Dict[str, torch.Tensor] = {}
         self._loaded = False
         self._ws = None
@@ -595,6 +597,16 @@ class B200GaussianSplatRenderer(torch.nn.Module):
         return (out, count) if defer else self.finish_prune(out, count)
 
     _PACK = (("means", 3), ("quats", 4), ("scales", 3), ("opacities", 1), ("sh", 3), ("weights", 1))
+
+    def use_partition(self) -> bool:
+        """Whether a sharded scene is merged one key range per rank (partition_scene) or whole on every rank."""
+        if not self.sharded or not self.enable_prune:
+            return False
+        if self.partitioned is not None:
+            return bool(self.partitioned)
+        import torch.distributed as dist
+
+        return dist.get_world_size(self.group) > 2
 
     def partition_scene(self, sp):
         """Views sharded over the ranks of `self.group`: instead of gathering all N_total splats on every rank and merging
@@ -727,7 +739,7 @@ class B200GaussianSplatRenderer(torch.nn.Module):
             raw = raws[b]
             sp = self.prepare_splats(raw, images[b, :S], predictions["gs_depth"][b, :S], predictions["camera_params"][b, :S])
             conf_on = self.enable_conf_filter and "depth_conf" in predictions
-            if self.sharded and self.partitioned and self.enable_prune and not rasterize and not conf_on:
+            if self.use_partition() and not rasterize and not conf_on:
                 # every rank keeps and merges one key range of the scene (partition_scene)
                 part, bounds = self.partition_scene(sp)
                 scenes.append((part, bounds))
@@ -938,7 +950,7 @@ class B200WorldMirror(torch.nn.Module):
 
             # The partitioned merge of a sharded scene reads one small count matrix on the host in the middle of the chain:
             # the remaining heads are enqueued first, so the main stream has work while the host waits for the side stream.
-            late_chain = self.gs_renderer.sharded and self.gs_renderer.partitioned
+            late_chain = self.gs_renderer.use_partition()
             if not late_chain:
                 preds = splat_chain(preds)
         used = []
