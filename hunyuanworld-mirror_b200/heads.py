@@ -108,6 +108,7 @@ class B200DPTHead(torch.nn.Module):
             raise ValueError(f"Unknown attribute activation: {activation}")
         self.dim_in, self.output_dim, self.activation, self.act = dim_in, output_dim, activation, _ACT[act]
         self.is_gsdpt = bool(is_gsdpt)
+        self.ln_cache = None  # dict shared by the heads of one forward (B200WorldMirror sets and clears it): normalised token rows
         self.tail_views = int(os.environ.get("WM_DPT_TAIL_VIEWS", "0")) or 1 << 30  # views per pass of the high-resolution tail (0: all)
         self.oc = tuple(out_channels)
         self.w: Dict[str, torch.Tensor] = {}
@@ -132,9 +133,19 @@ class B200DPTHead(torch.nn.Module):
         def vec(key):
             return sd[key].detach().to(dev, torch.float32).contiguous()
 
-        w["norm.w"], w["norm.b"] = vec("norm.weight"), vec("norm.bias")
+        # LayerNorm's affine part is folded into the 1x1 projections that consume it,
+        #   W (x_hat * g + b) + c = (W diag(g)) x_hat + (W b + c),
+        # so that the normalised rows x_hat do not depend on the head: the four heads of a forward share them
+        # (`ln_cache`, 4 instead of 16 LayerNorm(2048) launches over the same token rows)
+        gamma, beta = vec("norm.weight"), vec("norm.bias")
+        w["norm.w"], w["norm.b"] = torch.ones_like(gamma), torch.zeros_like(beta)
         for i in range(4):
-            w[f"proj{i}.w"], w[f"proj{i}.b"] = conv(f"projects.{i}.weight"), vec(f"projects.{i}.bias")
+            Wp = sd[f"projects.{i}.weight"].detach().to(dev, torch.float32)  # [co, 2048, 1, 1]
+            folded = Wp * gamma[None, :, None, None]
+            if float(folded.abs().max()) > 65504.0:
+                raise Fp16RangeError(f"projects.{i}.weight * norm.weight exceeds the fp16 range of the convolution operands")
+            w[f"proj{i}.w"] = folded.permute(0, 2, 3, 1).reshape(Wp.shape[0], -1).to(ACT).contiguous()
+            w[f"proj{i}.b"] = (vec(f"projects.{i}.bias") + Wp.reshape(Wp.shape[0], -1) @ beta).contiguous()
             w[f"rn{i}.w"] = conv(f"scratch.layer{i + 1}_rn.weight")
         for i, k in ((0, 4), (1, 2)):
             t = sd[f"resize_layers.{i}.weight"].detach().to(dev, torch.float32)  # [ci, co, k, k]
@@ -229,11 +240,17 @@ class B200DPTHead(torch.nn.Module):
         tabs, pu, pv = self._pos_tables(gh, gw, H, W)
         dev = toks[0].device
         rn, sizes = [], []
+        cache = self.ln_cache
         for i, t in enumerate(toks):
             t = t.to(torch.float32).contiguous()
-            ln = torch.empty(n, gh, gw, Cd, dtype=ACT, device=dev)
-            _k(lib.wm_layernorm_rows(_st(), t.data_ptr(), w["norm.w"].data_ptr(), w["norm.b"].data_ptr(), 1e-5, n * g, g, P,
-                                             psi, Cd, ln.data_ptr()))
+            key = (i, t.data_ptr(), n, P, int(_st()))
+            ln = cache.get(key) if cache is not None else None
+            if ln is None:
+                ln = torch.empty(n, gh, gw, Cd, dtype=ACT, device=dev)
+                _k(lib.wm_layernorm_rows(_st(), t.data_ptr(), w["norm.w"].data_ptr(), w["norm.b"].data_ptr(), 1e-5, n * g, g, P,
+                                                 psi, Cd, ln.data_ptr()))
+                if cache is not None:
+                    cache[key] = ln
             c = self.oc[i]
             f = self._conv(ln, n, gh, gw, Cd, f"proj{i}.w", 1, c, w[f"proj{i}.b"], res1=tabs[i], bcast=1)
             h_, w_ = gh, gw
@@ -809,6 +826,7 @@ class B200WorldMirror(torch.nn.Module):
         self.gs_head, self.gs_renderer = gs_head, gs_renderer
         self.enable_gs = gs_head is not None and gs_renderer is not None
         self._side = None
+        self.share_ln = os.environ.get("WM_SHARE_LN", "1") != "0"  # one LayerNorm(2048) of the token rows for all DPT heads
         self.head_streams = os.environ.get("WM_HEAD_STREAMS", "0") == "1"
         self._hstreams = []
         self.check_fp16_range = True  # raise Fp16RangeError when a DPT head's fp16 map saturates
@@ -883,6 +901,10 @@ class B200WorldMirror(torch.nn.Module):
         preds = {}
         sat_now = False
         main = torch.cuda.current_stream(imgs.device)
+        dpt = [h for h in (self.gs_head, self.depth_head, self.pts_head, self.norm_head) if h is not None]
+        ln_cache = {} if (self.share_ln and not self.head_streams and len({h.dim_in for h in dpt}) == 1) else None
+        for h in dpt:
+            h.ln_cache = ln_cache  # the normalised token rows are the same for every head (same stream: keyed by it)
         copy = None
         if host_out is not None:
             if getattr(self, "_copy", None) is None or self._copy.device != imgs.device:
@@ -994,6 +1016,8 @@ class B200WorldMirror(torch.nn.Module):
             sat_now = True  # ... so the saturation count copied below is valid right away
             if hasattr(self.visual_geometry_transformer, "raise_on_peer_timeout"):
                 self.visual_geometry_transformer.raise_on_peer_timeout()
+        for h in dpt:
+            h.ln_cache = None
         if copy is not None:
             main.wait_stream(copy)
         if self.check_fp16_range and any(h is not None for h in (self.depth_head, self.pts_head, self.norm_head, self.gs_head)):

@@ -373,7 +373,12 @@ def test_fp16_range_guard(scale, c1_tokens):
     hsd[pre + "norm.weight"] = hsd[pre + "norm.weight"] * scale
     hsd[pre + "norm.bias"] = hsd[pre + "norm.bias"] * scale
     head = heads.B200DPTHead(dim_in=2048, output_dim=4, activation="norm+expp1")
-    head.load_state_dict({k[len(pre):]: v for k, v in hsd.items() if k.startswith(pre)})
+    try:
+        head.load_state_dict({k[len(pre):]: v for k, v in hsd.items() if k.startswith(pre)})
+    except heads.Fp16RangeError as e:  # the folded projection weights themselves leave the fp16 range: reported at load time
+        print(f"scale {scale:g}: {e}")
+        assert scale >= 1e6
+        return
     imgs = W.synthetic_images(2, 252, 252, seed=1)
     heads.fp16_saturation(reset=True)
     pred, conf = head([t.cuda() for t in toks], imgs.cuda(), psi)
