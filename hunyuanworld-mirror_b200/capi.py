@@ -135,3 +135,25 @@ def last_error() -> str:
 def check(status: int) -> None:
     if status != WM_OK:
         raise WmError(status, last_error())
+
+
+class nvtx_range:
+    """`with nvtx_range("name"):` pushes an NVTX range when WM_NVTX=1 (for nsys / ncu --nvtx timelines); free otherwise."""
+    enabled = os.environ.get("WM_NVTX", "0") == "1"
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if self.enabled:
+            import torch
+
+            torch.cuda.nvtx.range_push(self.name)
+        return self
+
+    def __exit__(self, *a):
+        if self.enabled:
+            import torch
+
+            torch.cuda.nvtx.range_pop()
+        return False

@@ -895,9 +895,11 @@ class B200WorldMirror(torch.nn.Module):
                 agg = self.visual_geometry_transformer
                 priors = extract_priors(views, group=getattr(agg, "_sp_group", None), world=getattr(agg, "world", 1),
                                         rank=getattr(agg, "rank", 0))
-            token_list, psi = self.visual_geometry_transformer(imgs, priors, cond_flags=list(cond_flags))
+            with capi.nvtx_range("wm.aggregator"):
+                token_list, psi = self.visual_geometry_transformer(imgs, priors, cond_flags=list(cond_flags))
         else:
-            token_list, psi = self.visual_geometry_transformer(imgs)
+            with capi.nvtx_range("wm.aggregator"):
+                token_list, psi = self.visual_geometry_transformer(imgs)
         preds = {}
         sat_now = False
         main = torch.cuda.current_stream(imgs.device)
@@ -933,7 +935,7 @@ class B200WorldMirror(torch.nn.Module):
                 self._side = torch.cuda.Stream(device=imgs.device, priority=-1)
             side = self._side
             side.wait_stream(main)
-            with torch.cuda.stream(side):
+            with torch.cuda.stream(side), capi.nvtx_range("wm.camera_head"):
                 preds["camera_params"] = self._camera(token_list)
                 # worldmirror.py:161-175: camera-to-world poses and intrinsics of the predicted cameras
                 mats = [camera_matrices(cp, imgs.shape[-2], imgs.shape[-1]) for cp in preds["camera_params"]]
@@ -946,7 +948,8 @@ class B200WorldMirror(torch.nn.Module):
             # result - are merged and read back underneath the three remaining DPT heads.
             if self.cam_head is None:
                 raise RuntimeError("the Gaussian branch positions its splats with the predicted cameras: cam_head is required")
-            gs_feat, preds["gs_depth"], preds["gs_depth_conf"] = self.gs_head(token_list, images=imgs, patch_start_idx=psi)
+            with capi.nvtx_range("wm.gs_head"):
+                gs_feat, preds["gs_depth"], preds["gs_depth_conf"] = self.gs_head(token_list, images=imgs, patch_start_idx=psi)
             emit("gs_depth", preds["gs_depth"])
             emit("gs_depth_conf", preds["gs_depth_conf"])
             raws = self.gs_renderer.parameters_of(gs_feat, imgs, views)
@@ -964,7 +967,8 @@ class B200WorldMirror(torch.nn.Module):
                     for t in raws + [preds["gs_depth"], imgs] + ([preds["depth_conf"]] if "depth_conf" in preds else []):
                         t.record_stream(side)
                     emit("camera_params", preds["camera_params"], src=side)
-                    preds = self.gs_renderer.assemble(raws, imgs, preds, views, defer=True)
+                    with capi.nvtx_range("wm.splats"):
+                        preds = self.gs_renderer.assemble(raws, imgs, preds, views, defer=True)
                     if "splats_pending" in preds and len(preds["splats_pending"]) == 1:
                         for k, t in preds["splats_pending"][0][0].items():
                             emit("splats." + k, t, src=side)
@@ -991,7 +995,8 @@ class B200WorldMirror(torch.nn.Module):
                     emit(name, preds[name], src=hs)
                     emit(name + "_conf", preds[name + "_conf"], src=hs)
                 else:
-                    preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
+                    with capi.nvtx_range("wm.dpt_" + name):
+                        preds[name], preds[name + "_conf"] = head(token_list, images=imgs, patch_start_idx=psi)
                     emit(name, preds[name])
                     emit(name + "_conf", preds[name + "_conf"])
         for hs, name in used:
