@@ -3,6 +3,7 @@
 //     selftest <case> [args...]
 // CPU references here are plain loops over the same bf16-rounded inputs (fp32/double accumulate); they are
 // test infrastructure only.  tests/native/run_selftest.sh drives the whole matrix on the GPU box.
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -543,6 +544,114 @@ static int bench_mufu() {
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ softmax inner-loop model
+// How much of the attention kernel's exponential throughput is lost to too few warps?  A stand-in for the softmax warps'
+// inner loop without the tensor core: every thread reads CHUNK * 2 "scores" per step from shared memory (standing in for the
+// TMEM load), turns them into P = 2^s with NPOLY of every 32 on the FMA pipe (the kernel's packed polynomial) and the rest on
+// MUFU, adds them up, packs bf16 pairs and writes them back.  16 warps x 64 scores per step at <= 128 registers (the kernel's
+// shape) against 32 warps x 32 scores per step at <= 64 registers (4 threads per query row): same elements per SM.
+__device__ __forceinline__ float2 st_ffma2(float2 a, float2 b, float2 c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long*>(&a)),
+      "l"(*reinterpret_cast<unsigned long long*>(&b)), "l"(*reinterpret_cast<unsigned long long*>(&c)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 st_fadd2(float2 a, float2 b) {
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 st_exp2_poly2(float2 x) {
+  const float2 magic = make_float2(12582912.0f, 12582912.0f);
+  const float2 xr = st_fadd2(x, magic);
+  const float2 n = st_fadd2(xr, make_float2(-12582912.0f, -12582912.0f));
+  const float2 f = st_ffma2(n, make_float2(-1.0f, -1.0f), x);
+  float2 p = st_ffma2(make_float2(0.05520551f, 0.05520551f), f, make_float2(0.24261397f, 0.24261397f));
+  p = st_ffma2(p, f, make_float2(0.69325477f, 0.69325477f));
+  p = st_ffma2(p, f, make_float2(0.9999277f, 0.9999277f));
+  float2 r;
+  r.x = __uint_as_float(__float_as_uint(p.x) + (__float_as_uint(xr.x) << 23));
+  r.y = __uint_as_float(__float_as_uint(p.y) + (__float_as_uint(xr.y) << 23));
+  return r;
+}
+template <int THREADS, int CHUNK, int NPOLY>
+__global__ void __launch_bounds__(THREADS, 1) softmax_rate_kernel(float* out, int steps) {
+  extern __shared__ float4 st_smem[];
+  // CHUNK scores per half-step and thread, laid out [CHUNK / 4][THREADS] float4 so that a warp reads 512 contiguous bytes
+  float4* src = st_smem;
+  uint4* dst = reinterpret_cast<uint4*>(st_smem + (CHUNK / 4) * THREADS);
+  for (int i = threadIdx.x; i < (CHUNK / 4) * THREADS; i += THREADS)
+    src[i] = make_float4(-0.1f * (i & 7), -0.3f, -1.7f + 0.01f * (i & 3), -2.2f);
+  __syncthreads();
+  float2 sum2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+  for (int s = 0; s < steps; ++s) {
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      float v[CHUNK];
+#pragma unroll
+      for (int q = 0; q < CHUNK / 4; ++q) {
+        const float4 t = src[q * THREADS + (threadIdx.x + 32 * s + 64 * half) % THREADS];  // (moves with s and half: nothing is invariant or shared)
+        v[4 * q] = t.x, v[4 * q + 1] = t.y, v[4 * q + 2] = t.z, v[4 * q + 3] = t.w;
+      }
+      uint32_t pk[CHUNK / 2];
+#pragma unroll
+      for (int c = 0; c < CHUNK; c += 2) {
+        const float2 xs = make_float2(v[c], v[c + 1]);
+        float2 p;
+        if (c >= CHUNK - NPOLY * CHUNK / 32) {
+          p = st_exp2_poly2(xs);
+        } else {
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p.x) : "f"(xs.x));
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p.y) : "f"(xs.y));
+        }
+        sum2[(c >> 1) & 1] = st_fadd2(sum2[(c >> 1) & 1], p);
+        __nv_bfloat162 b2 = __floats2bfloat162_rn(p.x, p.y);
+        pk[c >> 1] = *reinterpret_cast<uint32_t*>(&b2);
+      }
+#pragma unroll
+      for (int q = 0; q < CHUNK / 8; ++q)
+        dst[(q + half * (CHUNK / 8)) * THREADS + threadIdx.x] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+    }
+  }
+  out[blockIdx.x * THREADS + threadIdx.x] = sum2[0].x + sum2[0].y + sum2[1].x + sum2[1].y;
+}
+template <int THREADS, int CHUNK, int NPOLY>
+static void bench_softmax_one(float* out, const char* what) {
+  const size_t smem = (size_t)(CHUNK / 4) * THREADS * 16 + (size_t)2 * (CHUNK / 8) * THREADS * 16;
+  CK(cudaFuncSetAttribute(softmax_rate_kernel<THREADS, CHUNK, NPOLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaFuncAttributes fa;
+  CK(cudaFuncGetAttributes(&fa, softmax_rate_kernel<THREADS, CHUNK, NPOLY>));
+  // same number of elements per SM for every configuration: THREADS * 2 * CHUNK per step
+  const int steps = (int)(512ll * 64 * 2 * 4000 / ((long long)THREADS * 2 * CHUNK));
+  cudaEvent_t a, b;
+  CK(cudaEventCreate(&a));
+  CK(cudaEventCreate(&b));
+  float ms = 0;
+  for (int rep = 0; rep < 2; ++rep) {
+    CK(cudaEventRecord(a));
+    softmax_rate_kernel<THREADS, CHUNK, NPOLY><<<148, THREADS, smem>>>(out, steps);
+    CK(cudaEventRecord(b));
+    CK(cudaEventSynchronize(b));
+    CK(cudaEventElapsedTime(&ms, a, b));
+  }
+  const double elems = 148.0 * THREADS * 2.0 * CHUNK * steps;
+  printf("BENCH softmax-loop %-44s regs %3d  %.3f ms  %.2f elements/clk/SM at 1.9 GHz\n", what, fa.numRegs, ms,
+         elems / ms * 1e-6 / 148 / 1.9);
+}
+static int bench_softmax() {
+  float* out = dev_alloc<float>(148 * 1024);
+  bench_softmax_one<512, 32, 12>(out, "16 warps x 64 scores/step, 12/32 polynomial");
+  bench_softmax_one<1024, 16, 12>(out, "32 warps x 32 scores/step, 12/32 polynomial");
+  bench_softmax_one<512, 32, 16>(out, "16 warps x 64 scores/step, 16/32 polynomial");
+  bench_softmax_one<1024, 16, 16>(out, "32 warps x 32 scores/step, 16/32 polynomial");
+  bench_softmax_one<512, 32, 0>(out, "16 warps x 64 scores/step, MUFU only");
+  bench_softmax_one<1024, 16, 0>(out, "32 warps x 32 scores/step, MUFU only");
+  bench_softmax_one<768, 16, 12>(out, "24 warps x 32 scores/step, 12/32 polynomial");
+  bench_softmax_one<256, 32, 12>(out, " 8 warps x 64 scores/step, 12/32 polynomial");
+  printf("(the attention kernel: 256 x 128 scores per 2170 clk = 15.1 elements/clk/SM; MUFU bound at 12/32: 25.6)\n");
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 2) {
     printf("usage: selftest <case> [args]\n");
@@ -563,6 +672,7 @@ int main(int argc, char** argv) {
   if (c == "bench_copy") return bench_copy(I(2, 11008));
   if (c == "bench_gather") return bench_gather(I(2, 8), I(3, 518), I(4, 518));
   if (c == "bench_mufu") return bench_mufu();
+  if (c == "bench_softmax") return bench_softmax();
   printf("unknown case %s\n", c.c_str());
   return 64;
 }
