@@ -205,6 +205,13 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     float* my_max = xmax + (qt * 4 + hf) * 128 + row;          // + parity * 256
     const float* peer_max = xmax + (qt * 4 + (hf ^ 1)) * 128 + row;
     uint32_t scount = 0, pvbase = 0;  // s_full[qt] phases consumed / pv_done[qt] phases of finished items
+    // this warp's five barriers as ONE shared-window address + constant offsets, and the logical index of the ragged key
+    // tile, both computed once: the softmax loop spent ~30 of its ~300 instructions per tile rebuilding them
+    uint32_t bq = smem_u32(bars) + 8u * qt;
+    asm volatile("" : "+r"(bq));  // opaque: kept in a register, not rematerialised from the generic pointer
+    constexpr uint32_t B_SFULL = (4 + 4 * ST) * 8, B_SFREE = B_SFULL + 16, B_PFULL = B_SFULL + 32, B_PVDONE = B_SFULL + 48,
+                       B_OFREE = B_SFULL + 64;
+    const int j_rag = ragged ? (2 * a.n_kv - 1 - a.kv_rot) % a.n_kv : -1;  // attn_phys_tile(a, j_rag) == n_kv - 1
 
     AttnSched sched(a);
     for (int item, kv0, kv1, slot; sched.next(a, item, kv0, kv1, slot);) {
@@ -215,7 +222,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
 
       float m = BOUNDED ? 0.f : -INFINITY, l = 0.f;
       for (int j = kv0; j < kv1; ++j, ++scount) {
-        mbar_wait(&s_full[qt], scount & 1);
+        mbar_wait(bq + B_SFULL, scount & 1);
         tcgen05_fence_after();
         uint32_t pk[32];
         bool pv_waited = false;
@@ -232,7 +239,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           pv_waited = true;
           float2 sum2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
           int valid = 64;
-          if (ragged && attn_phys_tile(a, j) == a.n_kv - 1) valid = a.Lkv - (a.n_kv - 1) * 128 - hf * 64;
+          if (j == j_rag) valid = a.Lkv - (a.n_kv - 1) * 128 - hf * 64;
           uint32_t va[16], vb[16];
           tmem_ld_x16(s_addr, va);
 #pragma unroll(STREAM == 2 ? 2 : 1)
@@ -270,7 +277,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             } else {
               tcgen05_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive(&s_free[qt]);  // all 64 scores of this thread have left S_qt
+              if (lane == 0) mbar_arrive(bq + B_SFREE);  // all 64 scores of this thread have left S_qt
             }
             {
               uint32_t* pk8 = pk16 + 8;
@@ -297,7 +304,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             }
             if constexpr (STREAM == 1) {
               if (i == 0 && j > kv0) {
-                mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
+                mbar_wait(bq + B_PVDONE, (pvbase + j - kv0 - 1) & 1);
                 tcgen05_fence_after();
               }
               tmem_st_x16(p_addr + 16 * i, pk16s);
@@ -305,7 +312,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           }
           if constexpr (STREAM == 2) {
             if (j > kv0) {
-              mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
+              mbar_wait(bq + B_PVDONE, (pvbase + j - kv0 - 1) & 1);
               tcgen05_fence_after();
             }
             tmem_st_x32(p_addr, pk);
@@ -314,7 +321,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           tmem_wait_st();
           tcgen05_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&p_full[qt]);
+          if (lane == 0) mbar_arrive(bq + B_PFULL);
           continue;
         } else if constexpr (BOUNDED) {
           // two 32-column chunks, one after the other: at most 32 scores + 16 packed probabilities are live
@@ -328,9 +335,9 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             if (i == 1) {
               tcgen05_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive(&s_free[qt]);  // the MMA warp may overwrite S_qt once both halves have arrived
+              if (lane == 0) mbar_arrive(bq + B_SFREE);  // the MMA warp may overwrite S_qt once both halves have arrived
             }
-            if (ragged && attn_phys_tile(a, j) == a.n_kv - 1) {
+            if (j == j_rag) {
               const int valid = a.Lkv - (a.n_kv - 1) * 128 - hf * 64 - i * 32;
 #pragma unroll
               for (int c = 0; c < 32; ++c)
@@ -358,8 +365,8 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           tmem_wait_ld();
           tcgen05_fence_before();
           __syncwarp();
-              if (lane == 0) mbar_arrive(&s_free[qt]);  // the MMA warp may overwrite S_qt once both halves have arrived
-          if (ragged && attn_phys_tile(a, j) == a.n_kv - 1) {
+              if (lane == 0) mbar_arrive(bq + B_SFREE);  // the MMA warp may overwrite S_qt once both halves have arrived
+          if (j == j_rag) {
             const int valid = a.Lkv - (a.n_kv - 1) * 128 - hf * 64;
 #pragma unroll
             for (int i = 0; i < 2; ++i)
@@ -382,7 +389,7 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             const bool need = (m_new - m) * a.scale_log2 > 8.0f;
             if (__any_sync(0xffffffffu, need)) {
               // O correction: wait for PV(j-1), then scale this thread's 32 columns of O and its partial l
-              mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
+              mbar_wait(bq + B_PVDONE, (pvbase + j - kv0 - 1) & 1);
               pv_waited = true;
               tcgen05_fence_after();
               const float alpha = need ? ex2_approx((m - m_new) * a.scale_log2) : 1.0f;
@@ -419,25 +426,25 @@ attn_split_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
           l += (sum2[0].x + sum2[0].y) + (sum2[1].x + sum2[1].y);
         }
         if (j > kv0 && !pv_waited) {  // P_qt is still being read by PV(j-1) until this completes (normally long done)
-          mbar_wait(&pv_done[qt], (pvbase + j - kv0 - 1) & 1);
+          mbar_wait(bq + B_PVDONE, (pvbase + j - kv0 - 1) & 1);
           tcgen05_fence_after();
         }
         tmem_st_x32(p_addr, pk);
         tmem_wait_st();
         tcgen05_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&p_full[qt]);
+        if (lane == 0) mbar_arrive(bq + B_PFULL);
       }
       // ---- epilogue: merge the partial row sums, O / l -> bf16 -> swizzled staging tile -> TMA store
       pvbase += kv1 - kv0;
-      mbar_wait(&pv_done[qt], (pvbase - 1) & 1);
+      mbar_wait(bq + B_PVDONE, (pvbase - 1) & 1);
       tcgen05_fence_after();
       uint32_t o[32];
       tmem_ld_x32(o_addr, o);
       tmem_wait_ld();
       tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&o_free[qt]);  // the next item's first PV may overwrite O_qt
+      if (lane == 0) mbar_arrive(bq + B_OFREE);  // the next item's first PV may overwrite O_qt
       xsum[(qt * 2 + hf) * 128 + row] = l;
       if (leader) tma_store_wait_read<0>();  // the previous store has drained the staging tile
       named_bar_sync(1 + qt, 256);

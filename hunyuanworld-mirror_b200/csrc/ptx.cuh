@@ -48,6 +48,12 @@ __device__ __forceinline__ void fence_barrier_init() {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// The same on 32-bit shared-window addresses: a hot loop that keeps ONE such address in a register (and adds constant
+// offsets) spares the generic -> shared conversion, which the compiler otherwise rematerialises per use (S2R CgaCtaId + 6
+// integer instructions, predicated or not they cost issue slots).
+__device__ __forceinline__ void mbar_arrive(uint32_t bar_saddr) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_saddr) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
@@ -63,6 +69,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "=r"(ok)
       : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)  // suspend-time hint: the warp sleeps instead of polling (measured:
       : "memory");                                         // without it attention loses 10-25 % to issue-slot theft)
+  return ok != 0;
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar_saddr, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t"
+      "}\n"
+      : "=r"(ok)
+      : "r"(bar_saddr), "r"(parity), "r"(0x989680u)
+      : "memory");
   return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
@@ -82,6 +101,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #endif
         __trap();  // surfaces as a launch failure on the host instead of a hung GPU
       }
+    }
+  }
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar_saddr, uint32_t parity) {
+  if (mbar_try_wait(bar_saddr, parity)) return;  // the common case in a pipelined loop: one probe, no loop state
+  uint32_t spins = 0, t0 = 0;
+  while (!mbar_try_wait(bar_saddr, parity)) {
+    if ((++spins & 0xfffu) == 0) {
+      uint32_t t;
+      asm volatile("mov.u32 %0, %%globaltimer_hi;" : "=r"(t));
+      if (t0 == 0)
+        t0 = t | 0x80000000u;
+      else if (((t | 0x80000000u) - t0) >= WM_MBAR_TIMEOUT_TICKS)
+        __trap();
     }
   }
 }
