@@ -104,6 +104,8 @@ SIGNATURES = {
                                    _vp, _fp, _fp, _fp]),
     "wm_load_image_workspace_bytes": (C.c_int, [_i, _i, _i, _i, C.POINTER(C.c_size_t)]),
     "wm_load_image": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _fp, _vp, C.c_size_t]),
+    "wm_load_image_static_bytes": (C.c_size_t, []),
+    "wm_load_image_static": (C.c_int, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _fp]),
     "wm_rope2d": (C.c_int, [_vp, _fp, _vp, _i, _i, _i, _i, _fp, _fp, _fp]),
     "wm_pack_bf16": (C.c_int, [_vp, _fp, C.c_longlong, _i, _i, _vp]),
 }

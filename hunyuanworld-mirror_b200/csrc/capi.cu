@@ -1212,6 +1212,16 @@ wm_status wm_load_image(wm_stream stream, const unsigned char* rgb, int H, int W
                     workspace, workspace_bytes);
 }
 
+size_t wm_load_image_static_bytes(void) { return load_image_static_capacity(); }
+
+wm_status wm_load_image_static(wm_stream stream, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top, int crop_h,
+                               int out_H, int out_W, int pad_top, int pad_left, float* out) {
+  int sms;
+  WM_TRY(require_sm100(&sms));
+  return load_image_static(static_cast<cudaStream_t>(stream), rgb, H, W, new_w, new_h, crop_top, crop_h, out_H, out_W, pad_top,
+                           pad_left, out);
+}
+
 wm_status wm_rope2d(wm_stream stream, const float* tokens, const long long* positions, int batch, int heads, int L, int max_pos,
                     const float* rope_cos, const float* rope_sin, float* out) {
   int sms;

@@ -143,4 +143,48 @@ wm_status load_image(cudaStream_t st, const unsigned char* rgb, int H, int W, in
   return WM_OK;
 }
 
+// ---- no-allocation variant (no counterpart in the reference) -------------
+// Callers that must not allocate (CUDA-graph capture around them, tight serving loops) get the same two passes with the
+// scratch (both coefficient tables + the uint8 intermediate image) in a file-scope device array instead of a caller
+// buffer.  Every GPU that loads the library holds kLoadStaticBytes until exit.  The array is shared by all calls and
+// keeps the last call's contents: every byte a call reads it has written itself first (tables by the two copies, the
+// intermediate image by the horizontal pass), so nothing has to start at zero; two calls that overlap on the GPU
+// (different streams, no ordering between them) race on it.
+constexpr size_t kLoadStaticBytes = (size_t)8 << 20;
+static __device__ __align__(256) unsigned char g_load_scratch[kLoadStaticBytes];
+
+// In host code `g_load_scratch` is a host-side stand-in, not a device address: ask the runtime once per device, with
+// that device current.
+static wm_status load_scratch_address(void** out) {
+  constexpr int kMaxDev = 64;
+  static void* addr[kMaxDev] = {nullptr};
+  int dev = -1;
+  WM_CUDA(cudaGetDevice(&dev));
+  WM_CHECK(dev >= 0 && dev < kMaxDev, "load_image_static: device ordinal %d out of range", dev);
+  void* p = __atomic_load_n(&addr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    WM_CUDA(cudaGetSymbolAddress(&p, g_load_scratch));
+    WM_CHECK(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0, "load_image_static: bad scratch address");
+    __atomic_store_n(&addr[dev], p, __ATOMIC_RELEASE);  // every thread would store the same value
+  }
+  *out = p;
+  return WM_OK;
+}
+
+size_t load_image_static_capacity() { return kLoadStaticBytes; }
+
+wm_status load_image_static(cudaStream_t st, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top, int crop_h,
+                            int out_H, int out_W, int pad_top, int pad_left, float* out) {
+  size_t need = 0;
+  WM_TRY(load_image_workspace_bytes(H, W, new_w, new_h, &need));
+  if (need > kLoadStaticBytes)
+    return fail(WM_ERR_INVALID,
+                "load_image_static: a %dx%d image resized to %dx%d needs %zu bytes of scratch, the static array holds %zu "
+                "(use wm_load_image with a caller workspace)",
+                W, H, new_w, new_h, need, kLoadStaticBytes);
+  void* scratch = nullptr;
+  WM_TRY(load_scratch_address(&scratch));
+  return load_image(st, rgb, H, W, new_w, new_h, crop_top, crop_h, out_H, out_W, pad_top, pad_left, out, scratch, kLoadStaticBytes);
+}
+
 }  // namespace wm

@@ -92,6 +92,9 @@ wm_status raster_render(cudaStream_t st, const float* means2d, const float* coni
 wm_status load_image_workspace_bytes(int H, int W, int new_w, int new_h, size_t* bytes);
 wm_status load_image(cudaStream_t st, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top, int crop_h, int out_H,
                      int out_W, int pad_top, int pad_left, float* out, void* workspace, size_t workspace_bytes);
+size_t load_image_static_capacity();
+wm_status load_image_static(cudaStream_t st, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top, int crop_h,
+                            int out_H, int out_W, int pad_top, int pad_left, float* out);
 wm_status rope2d(cudaStream_t st, const float* tokens, const long long* pos, int batch, int heads, int L, int max_pos,
                  const float* cos_t, const float* sin_t, float* out);
 wm_status pack_bf16_rows(cudaStream_t st, const float* src, long long rows, int cols, int ld, void* dst);

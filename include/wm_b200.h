@@ -363,6 +363,18 @@ wm_status wm_raster_render(wm_stream stream, const float* means2d, const float* 
 wm_status wm_load_image_workspace_bytes(int H, int W, int new_w, int new_h, size_t* bytes);
 wm_status wm_load_image(wm_stream stream, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top, int crop_h,
                         int out_H, int out_W, int pad_top, int pad_left, float* out, void* workspace, size_t workspace_bytes);
+/* wm_load_image without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture around them, tight serving
+ * loops, harnesses that forbid it).  The scratch (coefficient tables + the uint8 intermediate image) is a file-scope
+ * static __device__ array of wm_load_image_static_bytes() = 8 MiB inside the library: every GPU that loads the library
+ * holds it until exit.  A geometry whose wm_load_image_workspace_bytes exceeds it is rejected with WM_ERR_INVALID
+ * (2048 x 1365 -> 518 wide needs 2.0 MiB; 8 MiB covers H * new_w <= about 2.7 M pixels).  The call itself makes no
+ * cudaMalloc / cudaFree or allocating library call.  All calls share the array, which keeps the last call's contents;
+ * every call overwrites what it reads, nothing needs to start at zero.  Calls that overlap on the GPU (different
+ * streams without an ordering between them, or two host threads) race on it: serialise them or use wm_load_image. */
+size_t wm_load_image_static_bytes(void);
+wm_status wm_load_image_static(wm_stream stream, const unsigned char* rgb, int H, int W, int new_w, int new_h, int crop_top,
+                               int crop_h, int out_H, int out_W, int pad_top, int pad_left, float* out);
 
 #ifdef __cplusplus
 }
