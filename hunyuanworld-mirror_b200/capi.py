@@ -55,6 +55,9 @@ SIGNATURES = {
     "wm_layernorm": (C.c_int, [_vp, _fp, _fp, _fp, _f, _i, _vp, _i]),
     "wm_gemm_bias_act": (C.c_int, [_vp, _vp, _i, _vp, _i, _fp, _i, _i, _i, _vp, _i, _i]),
     "wm_gemm_qkv": (C.c_int, [_vp, _vp, _vp, _fp, _fp, _fp, _fp, _fp, _f, _fp, _fp, _i, _i, _i, _f, _i, _vp, _vp]),
+    "wm_gemm_qkv_guard": (C.c_int, [_vp, _vp, _vp, _fp, _fp, _fp, _fp, _fp, _f, _fp, _fp, _i, _i, _i, _f, _i, _vp, _vp, _vp]),
+    "wm_flash_attn_guarded": (C.c_int, [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, C.c_size_t, _vp, _f]),
+    "wm_guard_words": (C.c_int, [_vp, _i, C.POINTER(C.c_float)]),
     "wm_set_int": (C.c_int, [_vp, C.c_char_p, _i]),
     "wm_get_int": (C.c_int, [_vp, C.c_char_p]),
     "wm_fp16_saturation": (C.c_int, [_vp, _vp, C.c_int]),

@@ -410,7 +410,8 @@ umma_probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant
 // ------------------------------------------------------------------------------------------------ host
 wm_status flash_attention_split(cudaStream_t st, int sm_count, const CUtensorMap& tq, const CUtensorMap& tk,
                                 const CUtensorMap& tv, const CUtensorMap& to, AttnArgs a, int variant, void* out, int ldo,
-                                float* partial_ws, size_t partial_ws_bytes, const AttnGather* gather);  // attn_split.cu
+                                float* partial_ws, size_t partial_ws_bytes, const AttnGather* gather,
+                                const AttnGuard* guard);  // attn_split.cu
 
 template <int NPOLY>
 static wm_status launch_attn(cudaStream_t st, int grid, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
@@ -429,7 +430,7 @@ constexpr int kDefaultVariant = 2;
 
 wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
                           int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, float* partial_ws,
-                          size_t partial_ws_bytes, const AttnGather* gather) {
+                          size_t partial_ws_bytes, const AttnGather* gather, const AttnGuard* guard) {
   static int sm_count = 0;
   if (sm_count == 0) WM_TRY(require_sm100(&sm_count));
   WM_CHECK(q && k && v && o, "flash_attention: null pointer");
@@ -451,8 +452,8 @@ wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k
   const int grid = a.total_items < sm_count ? a.total_items : sm_count;
   if (variant < 0) variant = kDefaultVariant;
   if (variant >= 4)
-    return flash_attention_split(st, sm_count, tq, tk, tv, to, a, variant, o, ldo, partial_ws, partial_ws_bytes, gather);
-  WM_CHECK(gather == nullptr, "flash_attention: an in-flight gather needs a split-row variant (4..12)");
+    return flash_attention_split(st, sm_count, tq, tk, tv, to, a, variant, o, ldo, partial_ws, partial_ws_bytes, gather, guard);
+  WM_CHECK(gather == nullptr && guard == nullptr, "flash_attention: an in-flight gather or a guard needs a split-row variant (4..12)");
   switch (variant) {
     case 0: return launch_attn<0>(st, grid, tq, tk, tv, to, a);
     case 1: return launch_attn<8>(st, grid, tq, tk, tv, to, a);

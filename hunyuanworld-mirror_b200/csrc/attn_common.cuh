@@ -32,6 +32,10 @@ struct AttnArgs {
   unsigned epoch;
   const unsigned* flags;
   unsigned* err;  // set to 1 when a shard did not arrive within kGatherTimeoutNs (the launch then finishes on stale keys)
+  // device-side kernel choice (AttnGuard, common.cuh); guard_mode == 0: none
+  const unsigned* guard_norm2;
+  int guard_mode, guard_heads;
+  float guard_limit2;  // limit^2, compared with max_h |q|^2 |k|^2
 };
 constexpr unsigned long long kGatherTimeoutNs = 4000000000ull;
 
@@ -62,6 +66,27 @@ __device__ __forceinline__ void attn_wait_shards(const AttnArgs& a, int jp, unsi
     asm volatile("fence.proxy.async;" ::: "memory");  // the keys were written by a peer's copy engine; TMA reads them next
     have |= 1u << r;
   }
+}
+
+// True when this launch is the wrong one of the (bounded, running-max) pair for the data at hand: every thread of the
+// grid computes the same answer from 2 * heads words and returns before any barrier or TMEM allocation.  Call after
+// pdl_wait() (the words are written by the preceding QKV GEMM).  A NaN norm makes the bound fail.
+__device__ __forceinline__ bool attn_guard_fits(const AttnArgs& a) {
+  // lane h looks at head h: one round trip to L2 for the warp (a loop with an early-out costs one per head, ~12 us for 16
+  // heads at the start of every CTA).  Call with all 32 lanes of the warp active; guard_heads <= 32.
+  const int lane = threadIdx.x & 31;
+  bool ok = true;
+  if (lane < a.guard_heads) {
+    const float q2 = __uint_as_float(__ldcg(a.guard_norm2 + lane));
+    const float k2 = __uint_as_float(__ldcg(a.guard_norm2 + a.guard_heads + lane));
+    ok = q2 * k2 <= a.guard_limit2;  // false for NaN
+  }
+  return __all_sync(0xffffffffu, ok);
+}
+__device__ __forceinline__ bool attn_guard_skip(const AttnArgs& a) {
+  if (a.guard_mode != 1 && a.guard_mode != 2) return false;
+  const bool fits = attn_guard_fits(a);
+  return a.guard_mode == 1 ? !fits : fits;
 }
 
 // Schedule position -> work item.  When the last query pair of every (head, batch entry) holds a single 128-row tile

@@ -169,6 +169,10 @@ struct wm_handle {
   int attn_general_variant = 4, attn_bounded_variant = 10, attn_allow_bounded = 1, attn_balance = 1;
   int gemm_split = 1;             // K-split of the residual GEMMs' tail tiles (gemm.cu); 0: whole tiles only
   unsigned* gemm_flags = nullptr;  // kGemmFlagBytes of arrival counters, zero between launches
+  // device-side choice of the attention kernel for blocks whose weights do not bound the logits (AttnGuard): 32 words
+  // per block (DINOv2 blocks first, then frame / global pairs), cleared at the start of run_embed / run_stack
+  int attn_guard = 1;
+  unsigned* guard_words = nullptr;
 };
 
 namespace wm {
@@ -287,8 +291,34 @@ struct ProfScope {
   } while (0)
 
 // Block.forward eval branch (block.py:91-92): x += ls1 * attn(norm1(x)); x += ls2 * mlp(norm2(x))
+constexpr int kGuardWords = 2 * kHeads;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// Attention whose kernel form is chosen on the device (AttnGuard): variants (10, 4) are one launch of a kernel that holds
+// both softmax roles; any other pair is two launches of which one returns at once.
+static wm_status guarded_attention(wm_handle* h, cudaStream_t st, int cls, const void* q, int ldq, const void* k, const void* v,
+                                   int ldkv, void* o, int ldo, int batch, int Lq, int Lkv, int bounded_variant, int general_variant,
+                                   float* part, size_t part_bytes, const unsigned* norm2, float limit) {
+  if (bounded_variant == 10 && general_variant == 4) {
+    const AttnGuard g3{norm2, 3, limit};
+    if (h) {
+      WM_OP(cls, flash_attention(st, q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, kHeads, kLn2, 10, part, part_bytes, nullptr, &g3));
+      return WM_OK;
+    }
+    return flash_attention(st, q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, kHeads, kLn2, 10, part, part_bytes, nullptr, &g3);
+  }
+  const AttnGuard g1{norm2, 1, limit}, g2{norm2, 2, limit};
+  if (h) {
+    WM_OP(cls, flash_attention(st, q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, kHeads, 1.0f, bounded_variant, part, part_bytes, nullptr, &g1));
+    WM_OP(cls, flash_attention(st, q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, kHeads, kLn2, general_variant, part, part_bytes, nullptr, &g2));
+    return WM_OK;
+  }
+  WM_TRY(flash_attention(st, q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, kHeads, 1.0f, bounded_variant, part, part_bytes, nullptr, &g1));
+  return flash_attention(st, q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, kHeads, kLn2, general_variant, part, part_bytes, nullptr, &g2);
+}
+
 static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const BlockShape& s, const Workspace& ws,
-                           float* x, float* out2, int out2_col, bool gather) {
+                           float* x, float* out2, int out2_col, bool gather, int guard_slot) {
   WM_OP(WM_PROF_LN, layernorm(st, x, w.n1w, w.n1b, s.eps, s.T, s.T, 0, 0, 0, 0, ws.ln, 0, 0));
   const bool p2p = gather && h->p2p.on && h->sp_mode == 1 && s.T <= h->p2p.max_rows;
   __nv_bfloat16* kv_all = ws.kv;
@@ -301,10 +331,15 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
   // QK-LayerNorm bounds the logits (|q . k| <= |q| |k|, both norms fixed by the norm weights): when the bound is
   // small the softmax needs no running maximum, so q is pre-multiplied by scale * log2(e) and P = 2^(q . k).
   const bool bounded = h->attn_allow_bounded && w.logit_bound > 0.f && w.logit_bound <= kMaxLogitBound;
-  const float q_scale = bounded ? 0.125f * 1.4426950408889634f : 1.0f;
+  // No bound from the weights (DINOv2: no QK-norm; or norm gains too large): the QKV epilogue measures the q / k row
+  // lengths of THIS input and the device picks the kernel (AttnGuard); keys gathered from peers keep the weight rule.
+  const bool guarded = !bounded && h->attn_allow_bounded && h->attn_guard && !gather && guard_slot >= 0 && h->guard_words &&
+                       h->attn_bounded_variant <= 12 && h->attn_general_variant >= 4 && h->attn_general_variant <= 7;
+  unsigned* norm2 = guarded ? h->guard_words + (size_t)guard_slot * kGuardWords : nullptr;
+  const float q_scale = (bounded || guarded) ? 0.125f * 1.4426950408889634f : 1.0f;
   WM_OP(WM_PROF_QKV, gemm_qkv(st, ws.ln, kEmbed, w.qkv_w, w.qkv_b, w.qn_w, w.qn_b, w.kn_w, w.kn_b, 1e-5f,
                               s.rope ? h->rope_cos : nullptr, s.rope ? h->rope_sin : nullptr, s.tokens_per_view,
-                              s.patch_start, s.grid_w, q_scale, s.T, ws.q, kv_local));
+                              s.patch_start, s.grid_w, q_scale, s.T, ws.q, kv_local, norm2));
   AttnGather ag{};
   if (p2p) {
     // push this rank's K|V rows into every peer's buffer (copy engines, side stream) while attention starts on them
@@ -333,10 +368,17 @@ static wm_status run_block(wm_handle* h, cudaStream_t st, const BlockW& w, const
     if (r != 0) return fail(WM_ERR_NCCL, "ncclAllGather: %s", h->nccl.GetErrorString(r));
   }
   const __nv_bfloat16* kbase = gather ? kv_all : kv_local;
-  WM_OP(s.global ? WM_PROF_ATTN_GLOBAL : WM_PROF_ATTN_LOCAL,
-        flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
-                        0.125f, bounded ? h->attn_bounded_variant : h->attn_general_variant,
-                        h->attn_balance ? ws.attn_part : nullptr, attn_partial_bytes(kNumSms), p2p ? &ag : nullptr));
+  if (guarded) {
+    // q carries scale * log2(e) already, so the running-max form gets scale = ln 2 (its scale * log2(e) is then 1)
+    WM_TRY(guarded_attention(h, st, s.global ? WM_PROF_ATTN_GLOBAL : WM_PROF_ATTN_LOCAL, ws.q, kEmbed, kbase, kbase + kEmbed,
+                             2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, h->attn_bounded_variant, h->attn_general_variant,
+                             h->attn_balance ? ws.attn_part : nullptr, attn_partial_bytes(kNumSms), norm2, kMaxLogitBound));
+  } else {
+    WM_OP(s.global ? WM_PROF_ATTN_GLOBAL : WM_PROF_ATTN_LOCAL,
+          flash_attention(st, ws.q, kEmbed, kbase, kbase + kEmbed, 2 * kEmbed, ws.att, kEmbed, s.batch, s.Lq, s.Lkv, kHeads,
+                          0.125f, bounded ? h->attn_bounded_variant : h->attn_general_variant,
+                          h->attn_balance ? ws.attn_part : nullptr, attn_partial_bytes(kNumSms), p2p ? &ag : nullptr));
+  }
   unsigned* gflags = h->gemm_split ? h->gemm_flags : nullptr;
   WM_OP(WM_PROF_PROJ, gemm_ls_residual(st, ws.att, kEmbed, w.proj_w, kEmbed, w.proj_b, w.ls1, s.T, kEmbed, kEmbed, x,
                                        kEmbed, gflags));
@@ -386,11 +428,14 @@ static wm_status run_stack(wm_handle* h, cudaStream_t st, const Workspace& ws, i
   BlockShape fs{T, n, P, P, 0, P, kPatchStart, gw, true, 1e-5f, false};
   BlockShape gs{T, 1, T, T * h->world, h->rank * T, P, kPatchStart, gw, true, 1e-5f, true};
   int next_out = 0;
+  const int slot0 = h->cfg.dino_depth;
+  if (h->guard_words && h->attn_guard)
+    WM_CUDA(cudaMemsetAsync(h->guard_words + (size_t)slot0 * kGuardWords, 0, (size_t)2 * h->cfg.depth * kGuardWords * 4, st));
   for (int i = 0; i < h->cfg.depth; ++i) {
     float* o = nullptr;
     if (next_out < h->cfg.n_intermediate && h->cfg.intermediate[next_out] == i) o = out[next_out++];
-    WM_TRY(run_block(h, st, h->frame[i], fs, ws, ws.x, o, 0, false));
-    WM_TRY(run_block(h, st, h->global[i], gs, ws, ws.x, o, kEmbed, h->world > 1));
+    WM_TRY(run_block(h, st, h->frame[i], fs, ws, ws.x, o, 0, false, slot0 + 2 * i));
+    WM_TRY(run_block(h, st, h->global[i], gs, ws, ws.x, o, kEmbed, h->world > 1, slot0 + 2 * i + 1));
   }
   if (h->p2p.used) {  // the caller's stream must also cover the pushes this rank still has in flight
     WM_CUDA(cudaEventRecord(h->p2p.ev_done, h->p2p.comm));
@@ -424,7 +469,9 @@ static wm_status run_embed(wm_handle* h, cudaStream_t st, const Workspace& ws, c
   WM_OP(WM_PROF_EMBED, gemm_table(st, a_pe, ld_pe, pew.b16, pew.ld, h->dino_table, Pd, Td, kEmbed, ld_pe, ws.xd, kEmbed));
   // a4: DINOv2 blocks (no rope, no qk-norm, eps 1e-6)
   BlockShape ds{Td, n, Pd, Pd, 0, Pd, 0, gw, false, 1e-6f, false};
-  for (int i = 0; i < h->cfg.dino_depth; ++i) WM_TRY(run_block(h, st, h->dino[i], ds, ws, ws.xd, nullptr, 0, false));
+  if (h->guard_words && h->attn_guard)
+    WM_CUDA(cudaMemsetAsync(h->guard_words, 0, (size_t)h->cfg.dino_depth * kGuardWords * 4, st));
+  for (int i = 0; i < h->cfg.dino_depth; ++i) WM_TRY(run_block(h, st, h->dino[i], ds, ws, ws.xd, nullptr, 0, false, i));
   // a6 (depth): pixel-unshuffle -> fc1+GELU -> fc2 written to the patch rows of x, then the final norm accumulates
   const bool pose_on = flags[0] == 1 && poses, depth_on = flags[1] == 1 && depth, ray_on = flags[2] == 1 && rays;
   if (depth_on) {
@@ -509,6 +556,9 @@ wm_status wm_create(const wm_config* cfg, wm_handle** out) {
   if (e == cudaSuccess) e = cudaMemcpy(h->rope_sin, s.data(), s.size() * 4, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMalloc(&h->gemm_flags, kGemmFlagBytes);
   if (e == cudaSuccess) e = cudaMemset(h->gemm_flags, 0, kGemmFlagBytes);
+  const size_t guard_bytes = (size_t)(h->cfg.dino_depth + 2 * h->cfg.depth) * kGuardWords * 4;
+  if (e == cudaSuccess) e = cudaMalloc(&h->guard_words, guard_bytes);
+  if (e == cudaSuccess) e = cudaMemset(h->guard_words, 0, guard_bytes);
   if (e != cudaSuccess) {
     wm_destroy(h);
     return fail(WM_ERR_CUDA, "wm_create: %s", cudaGetErrorString(e));
@@ -527,6 +577,7 @@ void wm_destroy(wm_handle* h) {
   if (h->rope_sin) cudaFree(h->rope_sin);
   if (h->dino_table) cudaFree(h->dino_table);
   if (h->gemm_flags) cudaFree(h->gemm_flags);
+  if (h->guard_words) cudaFree(h->guard_words);
   if (h->comm && h->nccl.CommDestroy) h->nccl.CommDestroy(h->comm);
   p2p_release(h);
   for (auto& v : h->prof_ev)
@@ -903,6 +954,32 @@ wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const floa
                   rope_sin, tokens_per_view, patch_start, grid_w, q_scale, M, q, kv);
 }
 
+wm_status wm_gemm_qkv_guard(wm_stream stream, const void* A, const void* W, const float* bias, const float* qn_w,
+                            const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
+                            const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M, void* q,
+                            void* kv, unsigned* norm2) {
+  WM_CHECK(norm2 && (reinterpret_cast<uintptr_t>(norm2) & 3) == 0, "wm_gemm_qkv_guard: norm2 must be a 4-byte aligned device pointer");
+  return gemm_qkv(static_cast<cudaStream_t>(stream), A, kEmbed, W, bias, qn_w, qn_b, kn_w, kn_b, qk_eps, rope_cos,
+                  rope_sin, tokens_per_view, patch_start, grid_w, q_scale, M, q, kv, norm2);
+}
+
+wm_status wm_flash_attn_guarded(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                                int ldo, int batch, int Lq, int Lkv, int heads, int bounded_variant, int general_variant,
+                                void* workspace, size_t workspace_bytes, const unsigned* norm2, float limit) {
+  WM_CHECK(heads == kHeads, "wm_flash_attn_guarded: the guard words are laid out for %d heads", kHeads);
+  WM_CHECK(norm2 && limit > 0.f && limit <= 96.f, "wm_flash_attn_guarded: norm2 must be set and 0 < limit <= 96");
+  return guarded_attention(nullptr, static_cast<cudaStream_t>(stream), 0, q, ldq, k, v, ldkv, o, ldo, batch, Lq, Lkv, bounded_variant,
+                           general_variant, static_cast<float*>(workspace), workspace_bytes, norm2, limit);
+}
+
+wm_status wm_guard_words(const wm_handle* h, int slot, float* host32) {
+  WM_CHECK(h && host32 && h->guard_words, "wm_guard_words: null argument");
+  WM_CHECK(slot >= 0 && slot < h->cfg.dino_depth + 2 * h->cfg.depth, "wm_guard_words: slot %d out of range", slot);
+  WM_CUDA(cudaDeviceSynchronize());
+  WM_CUDA(cudaMemcpy(host32, h->guard_words + (size_t)slot * kGuardWords, kGuardWords * 4, cudaMemcpyDeviceToHost));
+  return WM_OK;
+}
+
 wm_status wm_set_int(wm_handle* h, const char* name, int value) {
   WM_CHECK(h && name, "wm_set_int: null argument");
   const std::string n(name);
@@ -914,6 +991,8 @@ wm_status wm_set_int(wm_handle* h, const char* name, int value) {
     h->attn_bounded_variant = value;
   } else if (n == "attn_allow_bounded") {
     h->attn_allow_bounded = value != 0;
+  } else if (n == "attn_guard") {
+    h->attn_guard = value != 0;
   } else if (n == "attn_balance") {
     h->attn_balance = value != 0;
   } else if (n == "gemm_split") {
@@ -933,6 +1012,7 @@ int wm_get_int(const wm_handle* h, const char* name) {
   if (n == "attn_general_variant") return h->attn_general_variant;
   if (n == "attn_bounded_variant") return h->attn_bounded_variant;
   if (n == "attn_allow_bounded") return h->attn_allow_bounded;
+  if (n == "attn_guard") return h->attn_guard;
   if (n == "attn_balance") return h->attn_balance;
   if (n == "sp_mode") return h->sp_mode;
   if (n == "gemm_split") return h->gemm_split;

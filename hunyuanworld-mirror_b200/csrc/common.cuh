@@ -34,6 +34,19 @@ struct AttnGather {
   unsigned* err;
 };
 
+// Data-dependent choice between the bounded-logit and the running-max attention kernels, made ON THE DEVICE (no host
+// read): the QKV epilogue leaves max |q_row|^2 (q already multiplied by scale * log2 e) and max |k_row|^2 per head in
+// norm2 [2 * heads] (float bits, accumulated with atomicMax: zero them before the GEMM), so |log2-logit| <= |q| |k| is
+// known when the attention launches.  Mode 3 (variants 10 + 4): ONE launch of a kernel that holds both forms of the softmax
+// role and branches on the words.  Modes 1 / 2 (any other pair): both kernels are launched; mode 1 (bounded kernel) returns
+// at once unless every head's bound is <= limit, mode 2 (running-max kernel) unless some head's bound is above it or NaN
+// (measured: the launch that returns at once still costs ~46 us behind a 200 KB-shared-memory kernel, tools/bench_guard.py).
+struct AttnGuard {
+  const unsigned* norm2;
+  int mode;     // 1: run only if the bound holds; 2: run only if it does not; 3: one launch, the device branches
+  float limit;  // on |q| |k| in log2 units (kMaxLogitBound)
+};
+
 inline wm_status fail(wm_status code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);

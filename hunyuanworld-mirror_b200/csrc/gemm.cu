@@ -58,6 +58,7 @@ struct GemmArgs {
   int tokens_per_view, patch_start, grid_w;
   float qk_eps;
   float q_scale;  // q is multiplied by this after norm + rope (softmax scale * log2 e folded in for bounded-logit attention)
+  unsigned* norm2;  // AttnGuard words or null: [head] max |q row|^2 (after q_scale), [16 + head] max |k row|^2, float bits
   // EPI_RESID
   const float* gamma;  // null: out = acc + b (plain store); else out += gamma * (acc + b) (TMA reduce-add)
   // EPI_TABLE
@@ -357,6 +358,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
                 for (int i = 0; i < 64; ++i) x[i] *= g.q_scale;
               }
+              if (g.norm2 != nullptr) {
+                // the squared length of this thread's q / k head row; the largest of the launch decides on the device
+                // which attention kernel runs (AttnGuard).  Bit patterns of non-negative floats order like the floats,
+                // a NaN (either sign) sorts above +inf and survives the maximum.
+                float n2 = 0.f;
+#pragma unroll
+                for (int i = 0; i < 64; ++i) n2 = fmaf(x[i], x[i], n2);
+                unsigned nb = row < g.M ? __float_as_uint(n2) : 0u;
+                nb = __reduce_max_sync(0xffffffffu, nb);
+                unsigned* word = g.norm2 + which * 16 + ((col0 & (kEmbed - 1)) >> 6);
+                if ((threadIdx.x & 31) == 0 && nb > __ldcg(word)) atomicMax(word, nb);
+              }
             }
           }
           if (et == 0) tma_store_wait_read<0>();  // the team's previous store has drained the staging tile
@@ -535,7 +548,7 @@ wm_status gemm_bias_act(cudaStream_t st, const void* A, int lda, const void* W, 
 wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const float* bias, const float* qn_w,
                    const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
                    const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M,
-                   void* q_out, void* kv_out) {
+                   void* q_out, void* kv_out, unsigned* norm2) {
   const int N = 3 * kEmbed, K = kEmbed;
   WM_TRY(check_common(A, W, M, N, K, lda, K));
   WM_CHECK(q_out && kv_out && bias, "gemm_qkv: null output or bias");
@@ -552,6 +565,7 @@ wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const
   g.M = M, g.N = N, g.K = K, g.bias = bias;
   g.qn_w = qn_w, g.qn_b = qn_b, g.kn_w = kn_w, g.kn_b = kn_b, g.qk_eps = qk_eps, g.q_scale = q_scale;
   g.rope_cos = rope_cos, g.rope_sin = rope_sin;
+  g.norm2 = norm2;
   g.tokens_per_view = tokens_per_view > 0 ? tokens_per_view : 1, g.patch_start = patch_start,
   g.grid_w = grid_w > 0 ? grid_w : 1;
   return launch<EPI_QKV>(st, ta, tb, tq, tkv, g);

@@ -9,7 +9,7 @@ wm_status gemm_bias_act(cudaStream_t st, const void* A, int lda, const void* W, 
 wm_status gemm_qkv(cudaStream_t st, const void* A, int lda, const void* W, const float* bias, const float* qn_w,
                    const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
                    const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M,
-                   void* q_out, void* kv_out);
+                   void* q_out, void* kv_out, unsigned* norm2 = nullptr);  // norm2: AttnGuard words [2 * 16], or null
 // flags: kGemmFlagBytes of ZEROED counters (left zero by every launch) that let the kernel cut the tiles beyond the
 // last full wave along K and add the slices in fixed order (gemm.cu); null: whole tiles only.
 wm_status gemm_ls_residual(cudaStream_t st, const void* A, int lda, const void* W, int ldw, const float* bias,
@@ -20,7 +20,7 @@ wm_status gemm_table(cudaStream_t st, const void* A, int lda, const void* W, int
                      int table_period, int M, int N, int K, float* out, int ldo);
 wm_status flash_attention(cudaStream_t st, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
                           int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, float* partial_ws,
-                          size_t partial_ws_bytes, const AttnGather* gather = nullptr);
+                          size_t partial_ws_bytes, const AttnGather* gather = nullptr, const AttnGuard* guard = nullptr);
 size_t attn_partial_bytes(int sm_count);  // workspace that lets the split-row kernel balance (item, kv tile) steps
 wm_status umma_probe(cudaStream_t st, const void* p, const void* v, float* d, int mode, uint32_t v_lbo, uint32_t v_sbo);
 wm_status layernorm(cudaStream_t st, const float* x, const float* w, const float* b, float eps, int rows,

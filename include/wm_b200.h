@@ -107,13 +107,21 @@ long long wm_launch_count(const wm_handle* h);
 
 /* Tuning knobs: "attn_general_variant" (0-7, 20-23: attn_pipe.cu), "attn_bounded_variant" (8-12: attn_split.cu, 13-19: attn_pipe.cu),
  * "attn_allow_bounded" (0/1), "attn_balance" (0/1: even split of attention work with partial merge), "sp_mode",
- * "gemm_split" (0/1: K-split of the residual GEMMs' tail tiles).
+ * "gemm_split" (0/1: K-split of the residual GEMMs' tail tiles), "attn_guard" (0/1: blocks whose weights do not bound the
+ * logits -- DINOv2, or QK-norm gains past the bound -- let the device choose between the bounded-logit and the running-max
+ * attention kernel from the q / k row lengths of the input at hand, wm_gemm_qkv_guard / wm_flash_attn_guarded; 0: such
+ * blocks always take the running-max kernel).
  * wm_get_int returns the current value, or -1 for an unknown name. */
 wm_status wm_set_int(wm_handle* h, const char* name, int value);
 int wm_get_int(const wm_handle* h, const char* name);
 /* Bound of |q . k| * scale * log2(e) implied by the QK-LayerNorm weights of block `layer` of kind 0 = DINOv2 (always 0),
  * 1 = frame, 2 = global; the forward uses the bounded-logit attention when 0 < bound <= 80.  -1: invalid argument. */
 float wm_logit_bound(const wm_handle* h, int kind, int layer);
+/* What the device-side guard of the LAST forward saw for one block (synchronises the device): host32 [32] = per head
+ * max |q row|^2 (q scaled by scale * log2 e), then max |k row|^2; all zero for a block that did not use the guard (its
+ * weights bound the logits, "attn_guard" 0, or keys gathered from peers).  slot: DINOv2 block i -> i; frame block i ->
+ * dino_depth + 2 i; global block i -> dino_depth + 2 i + 1.  The bounded-logit kernel ran iff max_h sqrt(q2_h k2_h) <= 80. */
+wm_status wm_guard_words(const wm_handle* h, int slot, float* host32);
 
 /* ---- sequence parallelism: K|V all-gather of the global blocks through NCCL --------- */
 /* `nccl_lib` = path of libnccl.so.2 (the one torch loaded).  unique_id: 128 bytes. */
@@ -151,6 +159,13 @@ wm_status wm_gemm_qkv(wm_stream stream, const void* A, const void* W, const floa
                       const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
                       const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M, void* q,
                       void* kv);
+/* wm_gemm_qkv that also records, per head, the largest squared row length of q (after q_scale) and of k:
+ * norm2 [32] device words = float bit patterns, [h] for q, [16 + h] for k, accumulated with atomicMax -- ZERO them before
+ * the call.  |q . k| <= |q| |k| then bounds this input's logits without a host read (attention.py:50-59). */
+wm_status wm_gemm_qkv_guard(wm_stream stream, const void* A, const void* W, const float* bias, const float* qn_w,
+                            const float* qn_b, const float* kn_w, const float* kn_b, float qk_eps, const float* rope_cos,
+                            const float* rope_sin, int tokens_per_view, int patch_start, int grid_w, float q_scale, int M,
+                            void* q, void* kv, unsigned* norm2);
 /* Linear + LayerScale + residual (block.py:91-92): x [M,N] fp32 += gamma * (A W^T + bias), the addition done by a
  * TMA reduce-add (each element is added exactly once: deterministic); gamma NULL: x = A W^T + bias. */
 wm_status wm_gemm_ls_residual(wm_stream stream, const void* A, int lda, const void* W, int ldw, const float* bias,
@@ -181,6 +196,13 @@ wm_status wm_flash_attn_ws(wm_stream stream, const void* q, int ldq, const void*
                            int ldo, int batch, int Lq, int Lkv, int heads, float scale, int variant, void* workspace,
                            size_t workspace_bytes);
 size_t wm_attn_workspace_bytes(void);
+/* F.scaled_dot_product_attention (attention.py:59) with the kernel chosen ON THE DEVICE: q must carry scale * log2(e)
+ * (wm_gemm_qkv_guard with q_scale), norm2 are that call's words.  Two launches are enqueued: the bounded-logit kernel
+ * (bounded_variant 8-12) runs iff max_h |q|_h |k|_h <= limit (80 in the forward), otherwise it returns at once and the
+ * running-max kernel (general_variant 4-7) runs instead; a NaN length selects the running-max kernel.  16 heads. */
+wm_status wm_flash_attn_guarded(wm_stream stream, const void* q, int ldq, const void* k, const void* v, int ldkv, void* o,
+                                int ldo, int batch, int Lq, int Lkv, int heads, int bounded_variant, int general_variant,
+                                void* workspace, size_t workspace_bytes, const unsigned* norm2, float limit);
 /* wm_flash_attn_ws (batch 1, variants 4-12) over a key buffer of Lkv / shard_rows shards that may still be filling:
  * keys are scanned starting with shard `self_rank`; shard r is read only once (int)(flags[r] - epoch) >= 0
  * (flags: device words written by wm_p2p_raise_flag or a peer's push; *err is set to 1 on a 4 s time-out). */

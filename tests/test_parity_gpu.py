@@ -332,13 +332,24 @@ def test_logit_bound_and_bounded_switch(model_full, state_dict_full):
         assert 0 < b <= 80 and abs(b - 1.02 * nq * nk * 0.125 * 1.4426950408889634) <= 1e-3 * b
     imgs = W.synthetic_images(2, 70, 98, seed=5).cuda()
     a, _ = model_full(imgs)
+    # DINOv2 blocks have no weight bound: the device measured this input's q / k rows and took the bounded kernel; the
+    # frame / global blocks are bounded by their weights and leave their guard words untouched
+    words = (C.c_float * 32)()
+    for slot in (0, 23):
+        capi.check(lib.wm_guard_words(h, slot, words))
+        w = np.array(list(words))
+        assert (w > 0).all() and np.sqrt((w[:16] * w[16:]).max()) <= 80.0, w
+    capi.check(lib.wm_guard_words(h, 24, words))
+    assert not any(words)
     capi.check(lib.wm_set_int(h, b"attn_allow_bounded", 0))
     try:
         b2, _ = model_full(imgs)
     finally:
         capi.check(lib.wm_set_int(h, b"attn_allow_bounded", 1))
+    # two bf16 paths that round differently in all 26 blocks of this model that can switch (with the device-side guard the
+    # DINOv2 blocks take the bounded kernel too, 3.04e-3 measured; 2.3e-3 when only the frame / global blocks switched)
     for x, y in zip(a, b2):
-        assert rel_fro(x.cpu().numpy(), y.cpu().numpy()) <= 3e-3
+        assert rel_fro(x.cpu().numpy(), y.cpu().numpy()) <= 4e-3
 
 
 def model_sd_max(sd, prefix):
@@ -501,12 +512,18 @@ def test_large_qk_norm_weights_select_general_attention():
         for layer in (0, 1):
             assert lib.wm_logit_bound(h, kind, layer) > 80.0
     imgs = W.synthetic_images(4, 518, 518, seed=9)
+    assert lib.wm_get_int(h, b"attn_guard") == 1
+    guarded, _ = m(imgs.cuda())  # default: the device decides per block from the q / k row lengths of this input
+    guarded = [o.clone() for o in guarded]
+    capi.check(lib.wm_set_int(h, b"attn_guard", 0))  # weights alone decide: every frame / global block is general
     outs, _ = m(imgs.cuda())
     outs = [o.clone() for o in outs]
     capi.check(lib.wm_set_int(h, b"attn_allow_bounded", 0))
     outs2, _ = m(imgs.cuda())
     for a, b in zip(outs, outs2):
         assert torch.equal(a, b)  # the switch changes nothing: the general kernel ran both times
+    for a, b in zip(outs, guarded):
+        assert torch.isfinite(b).all() and rel_fro(a.cpu().numpy(), b.cpu().numpy()) <= 3e-3
     with torch.no_grad():
         ref32, _ = O.aggregator_forward(imgs, sd, depth=2, dino_depth=1, intermediate=(0, 1))
         ref16, _ = O.aggregator_forward(imgs, sd, depth=2, dino_depth=1, intermediate=(0, 1), emulate_bf16=True)
@@ -514,3 +531,72 @@ def test_large_qk_norm_weights_select_general_attention():
         e32, e16 = rel_fro(o.cpu().numpy(), a.numpy()), rel_fro(o.cpu().numpy(), b.numpy())
         print(f"bound > 80 (general attention): vs fp32 {e32:.3e}, vs bf16-emulating oracle {e16:.3e}")
         assert torch.isfinite(o).all() and e32 <= 5e-3 and e16 <= 4e-3
+
+
+@pytest.mark.parametrize("vb,vg", [(10, 4), (12, 7)])
+def test_device_side_attention_guard(vb, vg):
+    """(10, 4): one launch of the kernel that holds both forms of the softmax role; (12, 7): two launches, one returns at once.
+    AttnGuard (wm_gemm_qkv_guard + wm_flash_attn_guarded): the QKV epilogue records the largest q / k row lengths per
+    head, and of the two attention launches exactly the one that fits the data does the work -- small logits: bit-equal to
+    the bounded-logit kernel; logits past the limit or a NaN row: bit-equal to the running-max kernel (never inf / NaN
+    from an overflowing 2^s).  DINOv2-style block (no QK-norm, no RoPE), ragged length, 3 views."""
+    lib, st = capi.lib(), torch.cuda.current_stream().cuda_stream
+    n, P, H = 3, 300, 16
+    T = n * P
+    c = 0.125 * 1.4426950408889634
+    g = torch.Generator().manual_seed(11)
+    wq = (torch.randn(3072, 1024, generator=g) * 0.03).to(torch.bfloat16).cuda()
+    bq = (torch.randn(3072, generator=g) * 0.1).cuda()
+    need = lib.wm_attn_workspace_bytes()
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+
+    def run(x_scale, poison=False):
+        ln = (torch.randn(T, 1024, generator=g) * x_scale).to(torch.bfloat16).cuda()
+        if poison:
+            ln[5, 17] = float("nan")
+        q = torch.empty(T, 1024, dtype=torch.bfloat16, device="cuda")
+        kv = torch.empty(T, 2048, dtype=torch.bfloat16, device="cuda")
+        norm2 = torch.zeros(32, dtype=torch.int32, device="cuda")
+        capi.check(lib.wm_gemm_qkv_guard(st, ln.data_ptr(), wq.data_ptr(), bq.data_ptr(), None, None, None, None, 1e-5, None, None,
+                                         P, 0, 1, c, T, q.data_ptr(), kv.data_ptr(), norm2.data_ptr()))
+        q0, kv0 = torch.empty_like(q), torch.empty_like(kv)
+        capi.check(lib.wm_gemm_qkv(st, ln.data_ptr(), wq.data_ptr(), bq.data_ptr(), None, None, None, None, 1e-5, None, None,
+                                   P, 0, 1, c, T, q0.data_ptr(), kv0.data_ptr()))
+        assert torch.equal(q.view(torch.int16), q0.view(torch.int16)) and torch.equal(kv.view(torch.int16), kv0.view(torch.int16))
+        o = torch.full((T, 1024), 7.0, dtype=torch.bfloat16, device="cuda")
+        capi.check(lib.wm_flash_attn_guarded(st, q.data_ptr(), 1024, kv.data_ptr(), kv.data_ptr() + 2048, 2048, o.data_ptr(), 1024,
+                                             n, P, P, H, vb, vg, ws.data_ptr(), need, norm2.data_ptr(), 80.0))
+        ob, og = torch.empty_like(o), torch.empty_like(o)
+        capi.check(lib.wm_flash_attn_ws(st, q.data_ptr(), 1024, kv.data_ptr(), kv.data_ptr() + 2048, 2048, ob.data_ptr(), 1024,
+                                        n, P, P, H, 1.0, vb, ws.data_ptr(), need))
+        capi.check(lib.wm_flash_attn_ws(st, q.data_ptr(), 1024, kv.data_ptr(), kv.data_ptr() + 2048, 2048, og.data_ptr(), 1024,
+                                        n, P, P, H, 0.6931471805599453, vg, ws.data_ptr(), need))
+        torch.cuda.synchronize()
+        words = norm2.view(torch.float32).cpu()
+        return q, kv, o, ob, og, words
+
+    same = lambda a, b: torch.equal(a.view(torch.int16), b.view(torch.int16))  # noqa: E731
+    # 1. small logits: the recorded lengths match the stored rows, the bounded kernel did the work
+    q, kv, o, ob, og, words = run(1.0)
+    qn = q.float().reshape(T, H, 64).pow(2).sum(-1).amax(0).cpu()
+    kn = kv[:, :1024].float().reshape(T, H, 64).pow(2).sum(-1).amax(0).cpu()
+    assert torch.allclose(words[:16], qn, rtol=2e-2) and torch.allclose(words[16:], kn, rtol=2e-2)
+    bound = float((words[:16] * words[16:]).max().sqrt())
+    assert bound < 80.0, bound
+    assert same(o, ob)
+    heads = lambda t: t.float().cpu().reshape(n, P, H, 64).permute(0, 2, 1, 3)  # noqa: E731
+    ref = O.sdpa(heads(q) / c, heads(kv[:, :1024]), heads(kv[:, 1024:])).permute(0, 2, 1, 3).reshape(T, 1024)
+    assert (o.float().cpu() - ref).abs().max().item() <= 0.02
+    # 2. logits far past the limit: the running-max kernel did the work and the result is finite and right
+    q, kv, o, ob, og, words = run(12.0)
+    bound = float((words[:16] * words[16:]).max().sqrt())
+    assert bound > 200.0, bound
+    assert same(o, og) and torch.isfinite(o.float()).all()
+    ref = O.sdpa(heads(q) / c, heads(kv[:, :1024]), heads(kv[:, 1024:])).permute(0, 2, 1, 3).reshape(T, 1024)
+    assert (o.float().cpu() - ref).abs().max().item() <= 0.05 * float(ref.abs().max())
+    # 3. a NaN row: its length is NaN, which must select the running-max kernel as well
+    q, kv, o, ob, og, words = run(1.0, poison=True)
+    assert torch.isnan(words).any()
+    og_bits, o_bits = og.view(torch.int16), o.view(torch.int16)
+    ok_rows = ~torch.isnan(og.float()).any(dim=1)
+    assert torch.equal(o_bits[ok_rows], og_bits[ok_rows]) and int(ok_rows.sum()) >= T - 1 - P
