@@ -6,6 +6,7 @@
 #include <cuda_fp16.h>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "ptx.cuh"
@@ -124,6 +125,60 @@ __global__ void __launch_bounds__(256) bilinear_kernel(const __half* __restrict_
   }
 }
 
+// The same for C / 8 a power of two (every map of the DPT heads: C = 128 or 256), written for the instruction count: the
+// generic kernel above issues ~150 instructions per 16 output bytes (32 conversions, 50 scalar multiply-adds, an integer
+// division) and is bound by issue slots, not by memory (profiles/r02_heads_launches.csv: 3.1 TB/s of algorithmic bytes on
+// the 518 x 518 map).  Here the interpolation runs on packed fp32 pairs (FMUL2 / FFMA2, the same IEEE roundings per lane,
+// operation order fixed explicitly: fma(lx, b, hx0 * a), fma(ly, t2, hy0 * t1)) and the index split is a shift.
+template <int LC8>
+__global__ void __launch_bounds__(256) bilinear_p2_kernel(const __half* __restrict__ in, int n, int Hi, int Wi, int Ho, int Wo,
+                                                          float sy, float sx, const float* __restrict__ pos_u,
+                                                          const float* __restrict__ pos_v, __half* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
+  constexpr int c8 = 1 << LC8, C = c8 * 8, half = C / 2;
+  const int img = blockIdx.y / Ho, yo = blockIdx.y - img * Ho;
+  const float fy = yo * sy;
+  const int y0 = min((int)fy, Hi - 1), y1 = min(y0 + 1, Hi - 1);
+  const float ly = fy - y0, hy0 = 1.f - ly;
+  const uint4* row0 = reinterpret_cast<const uint4*>(in + ((size_t)img * Hi + y0) * Wi * C);
+  const uint4* row1 = reinterpret_cast<const uint4*>(in + ((size_t)img * Hi + y1) * Wi * C);
+  uint4* orow = reinterpret_cast<uint4*>(out + ((size_t)img * Ho + yo) * Wo * C);
+  const float2 hy2 = make_float2(hy0, hy0), ly2 = make_float2(ly, ly);
+  const int total = Wo << LC8;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+    const int xo = t >> LC8, c = t & (c8 - 1);
+    const float fx = xo * sx;
+    const int x0 = min((int)fx, Wi - 1), x1 = min(x0 + 1, Wi - 1);
+    const float lx = fx - x0, hx0 = 1.f - lx;
+    const float2 hx2 = make_float2(hx0, hx0), lx2 = make_float2(lx, lx);
+    const uint4 ua = __ldg(row0 + (x0 << LC8) + c), ub = __ldg(row0 + (x1 << LC8) + c);
+    const uint4 ud = __ldg(row1 + (x0 << LC8) + c), ue = __ldg(row1 + (x1 << LC8) + c);
+    const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wb[4] = {ub.x, ub.y, ub.z, ub.w};
+    const uint32_t wd[4] = {ud.x, ud.y, ud.z, ud.w}, we[4] = {ue.x, ue.y, ue.z, ue.w};
+    float2 r[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&wa[k]));
+      const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&wb[k]));
+      const float2 d = __half22float2(*reinterpret_cast<const __half2*>(&wd[k]));
+      const float2 e = __half22float2(*reinterpret_cast<const __half2*>(&we[k]));
+      const float2 t1 = ffma2(lx2, b, fmul2(hx2, a));
+      const float2 t2 = ffma2(lx2, e, fmul2(hx2, d));
+      r[k] = ffma2(ly2, t2, fmul2(hy2, t1));
+    }
+    if (pos_u != nullptr) {
+      const int ch = c * 8;
+      const float* pp = ch < half ? pos_u + xo * half + ch : pos_v + yo * half + (ch - half);
+      const float4 p0 = __ldg(reinterpret_cast<const float4*>(pp)), p1 = __ldg(reinterpret_cast<const float4*>(pp) + 1);
+      r[0] = fadd2(r[0], make_float2(p0.x, p0.y)), r[1] = fadd2(r[1], make_float2(p0.z, p0.w));
+      r[2] = fadd2(r[2], make_float2(p1.x, p1.y)), r[3] = fadd2(r[3], make_float2(p1.z, p1.w));
+    }
+    __stcs(orow + t, make_uint4(pack_half2_sat(r[0].x, r[0].y), pack_half2_sat(r[1].x, r[1].y), pack_half2_sat(r[2].x, r[2].y),
+                                pack_half2_sat(r[3].x, r[3].y)));
+  }
+}
+
 wm_status bilinear_nhwc(cudaStream_t st, const void* in, int n, int Hi, int Wi, int C, int Ho, int Wo, const float* pos_u,
                         const float* pos_v, void* out) {
   WM_CHECK(in && out && n > 0 && Hi > 0 && Wi > 0 && Ho > 0 && Wo > 0 && C > 0 && C % 16 == 0, "bilinear: bad geometry");
@@ -132,6 +187,13 @@ wm_status bilinear_nhwc(cudaStream_t st, const void* in, int n, int Hi, int Wi, 
   WM_CHECK((long long)n * Ho <= 65535 && (long long)Wo * C < (1LL << 31), "bilinear: n * Ho must fit a grid dimension");
   const int row_work = Wo * (C / 8);
   const unsigned gx = (unsigned)std::min((row_work + 255) / 256, 8);
+  static const bool generic_only = getenv("WM_BILINEAR_GENERIC") != nullptr;  // A/B switch for measurements
+  if (!generic_only && C == 128)
+    return launch_pdl(bilinear_p2_kernel<4>, dim3(gx, (unsigned)(n * Ho)), dim3(256), 0, st, static_cast<const __half*>(in), n, Hi, Wi,
+                      Ho, Wo, sy, sx, pos_u, pos_v, static_cast<__half*>(out));
+  if (!generic_only && C == 256)
+    return launch_pdl(bilinear_p2_kernel<5>, dim3(gx, (unsigned)(n * Ho)), dim3(256), 0, st, static_cast<const __half*>(in), n, Hi, Wi,
+                      Ho, Wo, sy, sx, pos_u, pos_v, static_cast<__half*>(out));
   return launch_pdl(bilinear_kernel, dim3(gx, (unsigned)(n * Ho)), dim3(256), 0, st, static_cast<const __half*>(in), n, Hi, Wi, C,
                     Ho, Wo, sy, sx, pos_u, pos_v, static_cast<__half*>(out));
 }
