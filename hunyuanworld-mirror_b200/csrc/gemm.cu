@@ -35,6 +35,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "ops.cuh"
 #include "ptx.cuh"
 
 namespace wm {
@@ -66,17 +67,50 @@ struct GemmArgs {
   int table_period;
   // tail split (EPI_RESID only; split == 1: every pair walks whole tiles round-robin, as the other epilogues do)
   int split, full_tiles, tail_tiles;  // tiles [0, full_tiles) whole; tiles [full_tiles, full_tiles + tail_tiles) in `split` K slices
+  // stream-K (EPI_RESID only): the (tile, k block) units of the whole problem are cut into one contiguous range per CTA
+  // pair, so every pair does the same amount of MMA work; a tile that straddles two ranges is added to x in two pieces, in a
+  // fixed order (see GemmSched).  split == 2 then only describes the flag protocol.
+  int streamk;
   unsigned* flags;  // [tail_tiles][2 ranks][2 teams] slice counters; zero before the launch, left zero by it
 };
 
 // The work units of one CTA pair, in the order every role of the pair walks them.
 struct GemmUnit {
   int tile, kb0, kb1, slice;  // slice < 0: a whole tile with the normal epilogue
+  int flag_idx;               // which group of slice counters orders the adds of a split tile
 };
 struct GemmSched {
   int pair_id, num_pairs, i;
-  __device__ GemmSched(int pair, int pairs) : pair_id(pair), num_pairs(pairs), i(-1) {}
+  int u0, u1;  // stream-K: the pair's range of (tile, k block) units, u = tile * num_k_blocks + kb
+  __device__ GemmSched(int pair, int pairs) : pair_id(pair), num_pairs(pairs), i(-1), u0(0), u1(0) {}
   __device__ bool next(const GemmArgs& g, GemmUnit& u) {
+    if (g.streamk) {
+      // Pair p owns units [total p / P, total (p + 1) / P): at least one whole tile's worth (the host takes this mode only
+      // for tiles >= pairs), so a tile is cut at most once.  The piece that ENDS a tile (kb0 > 0) is the first unit of its
+      // pair and adds first, with the bias (slice 0); the piece that BEGINS it (kb1 < num_k_blocks) is the LAST unit of the
+      // previous pair and adds second (slice 1).  The two are a whole kernel apart in time, so the second never waits,
+      // and the order of the fp32 additions is fixed: bit-deterministic.  The cut at the start of pair p uses counters p.
+      if (i < 0) {
+        const long long total = (long long)g.num_m_tiles * g.num_n_tiles * g.num_k_blocks;
+        u0 = (int)(total * pair_id / num_pairs);
+        u1 = (int)(total * (pair_id + 1) / num_pairs);
+        i = 0;
+      }
+      if (u0 >= u1) return false;
+      const int nkb = g.num_k_blocks;
+      u.tile = u0 / nkb;
+      u.kb0 = u0 - u.tile * nkb;
+      const int end = min(u1, (u.tile + 1) * nkb);
+      u.kb1 = end - u.tile * nkb;
+      if (u.kb0 > 0)
+        u.slice = 0, u.flag_idx = pair_id;
+      else if (u.kb1 < nkb)
+        u.slice = 1, u.flag_idx = pair_id + 1;
+      else
+        u.slice = -1, u.flag_idx = 0;
+      u0 = end;
+      return true;
+    }
     if (g.split > 1) {
       if (i < 0) {  // the K slice of a tail tile goes first: the ordered adds finish under the whole tiles
         i = 0;
@@ -84,6 +118,7 @@ struct GemmSched {
           const int t = pair_id / g.split;
           u.slice = pair_id - t * g.split;
           u.tile = g.full_tiles + t;
+          u.flag_idx = t;
           u.kb0 = (int)((long long)g.num_k_blocks * u.slice / g.split);
           u.kb1 = (int)((long long)g.num_k_blocks * (u.slice + 1) / g.split);
           return true;
@@ -97,7 +132,7 @@ struct GemmSched {
       if (u.tile >= g.num_m_tiles * g.num_n_tiles) return false;
     }
     ++i;
-    u.kb0 = 0, u.kb1 = g.num_k_blocks, u.slice = -1;
+    u.kb0 = 0, u.kb1 = g.num_k_blocks, u.slice = -1, u.flag_idx = 0;
     return true;
   }
 };
@@ -397,7 +432,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         // on with the pair's next tile in the other accumulator while the epilogue team waits.
         const bool sliced = EPI == EPI_RESID && u.slice >= 0;
         const bool later = sliced && u.slice > 0;
-        unsigned* flag = sliced ? g.flags + ((tile - g.full_tiles) * 2 + rank) * 2 + team : nullptr;
+        unsigned* flag = sliced ? g.flags + (u.flag_idx * 2 + rank) * 2 + team : nullptr;
 #pragma unroll 1
         for (int ch = 0; ch < 4; ++ch) {
           const int col0 = n0 + ch * 32;
@@ -497,20 +532,35 @@ static wm_status launch(cudaStream_t st, const CUtensorMap& a, const CUtensorMap
   const int tiles = g.num_m_tiles * g.num_n_tiles;
   const int pairs = g_sm_count / 2;
   int grid = 2 * (tiles < pairs ? tiles : pairs);
-  g.split = 1, g.full_tiles = tiles, g.tail_tiles = 0;
+  g.split = 1, g.full_tiles = tiles, g.tail_tiles = 0, g.streamk = 0;
   if (EPI == EPI_RESID && g.flags != nullptr) {
-    // the tiles beyond the last full wave, cut along K so that they fill (most of) one more wave of pairs
-    const int full = (tiles / pairs) * pairs, tail = tiles - full;
-    static const int max_split = env_int("WM_GEMM_MAX_SPLIT", kGemmMaxSplit);        // experiment switches
+    // Measured (profiles/r02_s30_streamk.log): correct and bit-deterministic, but SLOWER at the bench shape: proj 25 -> 30 us,
+    // fc2 67 (ordered tail split) -> 76 us; in the step 2.55 -> 3.0 and 5.24 -> 6.22 ms.  Every cut tile pays a second
+    // epilogue pass (TMEM -> registers -> staging -> reduce-add), and with 2.3 tiles per pair that is 4 epilogues per pair
+    // instead of 3 at most; only M = 5504, K = 4096 gains (43 -> 39 us).  Off by default.
+    static const int streamk_on = env_int("WM_GEMM_STREAMK", 0);                      // experiment switches
+    static const int max_split = env_int("WM_GEMM_MAX_SPLIT", kGemmMaxSplit);
     static const int min_kb = env_int("WM_GEMM_SPLIT_MIN_KB", kGemmSplitMinKBlocks);
-    int sp = tail > 0 ? pairs / tail : 1;
-    if (sp > max_split) sp = max_split;
-    if (sp > kGemmMaxSplit) sp = kGemmMaxSplit;
-    if (sp > g.num_k_blocks) sp = g.num_k_blocks;
-    if (g.num_k_blocks < min_kb) sp = 1;
-    if (sp >= 2) {
-      g.split = sp, g.full_tiles = full, g.tail_tiles = tail;
-      grid = 2 * (full > 0 ? pairs : tail * sp);
+    const int waves = (tiles + pairs - 1) / pairs;
+    // stream-K when the last wave of whole tiles would be less than ~85 % full: every pair gets tiles * k blocks / pairs
+    // units.  (172 tiles on 74 pairs: 2.32 tile times instead of 3.)  Needs tiles >= pairs (a tile is cut at most once)
+    // and (pairs + 1) * 4 slice counters.
+    if (streamk_on && tiles >= pairs && (long long)tiles * 100 < (long long)waves * pairs * 85 && g.num_k_blocks >= 4 &&
+        (size_t)(pairs + 2) * 4 * sizeof(unsigned) <= kGemmFlagBytes) {
+      g.streamk = 1, g.split = 2;
+      grid = 2 * pairs;
+    } else {
+      // the tiles beyond the last full wave, cut along K so that they fill (most of) one more wave of pairs
+      const int full = (tiles / pairs) * pairs, tail = tiles - full;
+      int sp = tail > 0 ? pairs / tail : 1;
+      if (sp > max_split) sp = max_split;
+      if (sp > kGemmMaxSplit) sp = kGemmMaxSplit;
+      if (sp > g.num_k_blocks) sp = g.num_k_blocks;
+      if (g.num_k_blocks < min_kb) sp = 1;
+      if (sp >= 2) {
+        g.split = sp, g.full_tiles = full, g.tail_tiles = tail;
+        grid = 2 * (full > 0 ? pairs : tail * sp);
+      }
     }
   }
   return launch_pdl(gemm_kernel<EPI>, dim3(grid), dim3(GEMM_THREADS), GEMM_SMEM, st, a, b, c0, c1, g);

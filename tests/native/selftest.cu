@@ -403,6 +403,7 @@ static void gemm_run(void* p) {
   if (c->kind == 2)
     WM(wm_gemm_qkv(0, c->a, c->w, c->bias, c->qw, c->qw, c->qw, c->qw, 1e-5f, c->cs, c->cs, 1376, 7, 37, 1.0f, c->M, c->q, c->kv));
   if (c->kind == 3) WM(wm_gemm_ls_residual(0, c->a, c->K, c->w, c->K, c->bias, c->gamma, c->M, c->N, c->K, c->x, c->N));
+  if (c->kind == 5) WM(wm_gemm_ls_residual(0, c->a, c->K, c->w, c->K, c->bias, nullptr, c->M, c->N, c->K, c->x, c->N));  // plain store
   if (c->kind == 4)
     WM(wm_gemm_ls_residual_ws(0, c->a, c->K, c->w, c->K, c->bias, c->gamma, c->M, c->N, c->K, c->x, c->N, c->ws,
                               wm_gemm_workspace_bytes()));
@@ -423,7 +424,7 @@ static int bench_gemm(int kind, int M, int N, int K) {
   c.cs = dev(cs);
   if (kind == 4) c.ws = dev_alloc<uint8_t>(wm_gemm_workspace_bytes(), 0);
   const float ms = time_ms(20, gemm_run, &c);
-  const char* names[] = {"bias", "gelu", "qkv", "ls_residual", "ls_resid_split"};
+  const char* names[] = {"bias", "gelu", "qkv", "ls_residual", "ls_resid_split", "ls_store"};
   printf("BENCH gemm_%-12s M=%d N=%d K=%d  %.3f ms  %.1f TFLOP/s\n", names[kind], M, N, K, ms, 2.0 * M * N * K / ms * 1e-9);
   return 0;
 }
