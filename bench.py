@@ -375,6 +375,23 @@ def run_b200(args):
            "d2h_bytes_per_step": d2h_bytes + splat_bytes[0], "ms_per_step": e2e_ms,
            "d2h_note": "per rank: its views' dense predictions + its 1/N share of the merged splat rows" if world > 1 else None}
 
+    # ---- which attention kernel the blocks of the timed forward took: frame / global blocks by their weight bound, DINOv2
+    # blocks (no QK-norm) by what the QKV epilogue measured on this input (AttnGuard, wm_guard_words); outside timed regions
+    attn_choice = None
+    if lib.wm_get_int(model._handle, b"attn_guard") == 1:
+        words = (capi.C.c_float * 32)()
+        dd = model.dino_depth if hasattr(model, "dino_depth") else 24
+        bounds = []
+        for slot in range(dd):
+            capi.check(lib.wm_guard_words(model._handle, slot, words))
+            w = [float(v) for v in words]
+            bounds.append(max(w[i] * w[16 + i] for i in range(16)) ** 0.5)
+        attn_choice = {"dino_blocks": dd, "dino_blocks_bounded_kernel": int(sum(0 < b <= 80.0 for b in bounds)),
+                       "dino_max_abs_log2_logit_bound": max(bounds) if bounds else None, "limit": 80.0,
+                       "frame_global_weight_bound_max": max(float(lib.wm_logit_bound(model._handle, k, i)) for k in (1, 2) for i in range(24)),
+                       "note": "synthetic random-init weights give small logits; a block whose measured |q||k| exceeds the limit "
+                               "runs the running-max form of the same launch (roofline_general times that form)"}
+
     # ---- the same global attention through the GENERAL kernel (running max, no logit bound): what a checkpoint whose
     # QK-norm weights exceed the bound would get.  Two extra forwards, outside every timed region.
     roofline_general = None
@@ -526,6 +543,8 @@ def run_b200(args):
         if roofline_general is not None:
             roofline_general.update(peak=peak_tf, frac=roofline_general["achieved"] / peak_tf)
             line["roofline_general"] = roofline_general
+        if attn_choice is not None:
+            line["attn_kernel_choice"] = attn_choice
         if sp_parity is not None:
             line["sp_parity"] = sp_parity
         if strong is not None:

@@ -7,9 +7,13 @@
 //                   opacity-aware extent min(3.33, sqrt(2 ln(255 o))), near / far and image culling;
 //   tile binning    csrc/IntersectTile.cu:24-110: key = image | tile | depth bits, value = flat (image, gaussian) index,
 //                   stable radix sort (CUB, library), per-tile offsets (:209);
-//   compositing     csrc/RasterizeToPixels3DGSFwd.cu:18-200: one 16 x 16 block per tile, gaussians staged through shared
-//                   memory in batches of 256, front to back, alpha = min(0.999, o exp(-sigma)), skipped below 1/255,
-//                   a pixel stops before the gaussian that would take its transmittance to <= 1e-4;
+//   compositing     csrc/RasterizeToPixels3DGSFwd.cu:18-200 defines the arithmetic (front to back, alpha = min(0.999,
+//                   o exp(-sigma)), skipped below 1/255, a pixel stops before the gaussian that would take its
+//                   transmittance to <= 1e-4); the kernel here is organised differently, see raster_stream_kernel:
+//                   after the sort every intersection becomes one packed 48-byte record in tile order, and a tile's
+//                   block streams its contiguous run of records through a ring of shared-memory stages with bulk
+//                   asynchronous copies (one producer thread, mbarrier full / empty pairs), so the compositing warps
+//                   never gather, never wait for a block-wide barrier, and the next records land while they work;
 //   colours         spherical harmonics of degree 0: max(C0 sh + 0.5, 0) (gsplat/rendering.py:509-525), expected depth =
 //                   sum w z / max(alpha, 1e-10) (:760-766).
 // HBM / latency-bound integer and fp32 SIMT work; no tensor cores.
@@ -165,52 +169,121 @@ __global__ void raster_fill_kernel(unsigned* p, unsigned n, unsigned v) {
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = v;
 }
 
-__global__ void __launch_bounds__(RS_BLOCK)
-raster_pixels_kernel(const float* __restrict__ means2d, const float* __restrict__ conics, const float* __restrict__ depths,
-                     const float* __restrict__ opacities, const float* __restrict__ sh, const unsigned* __restrict__ offsets,
-                     const unsigned* __restrict__ flat_ids, RasterGeom g, float* __restrict__ out_rgb, float* __restrict__ out_depth,
-                     float* __restrict__ out_alpha) {
-  __shared__ float s_xy[RS_BLOCK][2], s_conic[RS_BLOCK][3], s_col[RS_BLOCK][4], s_op[RS_BLOCK];
+// ------------------------------------------------------------------------------------------------ streamed compositing
+// One record per (tile, gaussian) intersection, written in sorted (image, tile, depth) order: everything a pixel needs.
+constexpr int RS_REC = 12;      // floats per record: x, y, conic a b c, opacity, r, g, b, depth, 2 pad (48 bytes, 16-byte aligned)
+constexpr int RS_CHUNK = 128;   // records per shared-memory stage (6 KB)
+constexpr int RS_STAGES = 4;
+constexpr int RS_STREAM_THREADS = RS_BLOCK + 32;  // 8 compositing warps (16 x 2 pixels each) + 1 producer warp
+
+__global__ void __launch_bounds__(256)
+raster_pack_kernel(const float* __restrict__ means2d, const float* __restrict__ conics, const float* __restrict__ depths,
+                   const float* __restrict__ opacities, const float* __restrict__ sh, const unsigned* __restrict__ flat_ids,
+                   unsigned n, unsigned N, float4* __restrict__ rec) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned f = flat_ids[i];
+    const size_t gi = f % N;
+    const float r = fmaxf(RS_C0 * sh[gi * 3] + 0.5f, 0.f), gg = fmaxf(RS_C0 * sh[gi * 3 + 1] + 0.5f, 0.f),
+                b = fmaxf(RS_C0 * sh[gi * 3 + 2] + 0.5f, 0.f);
+    rec[(size_t)i * 3] = make_float4(means2d[(size_t)f * 2], means2d[(size_t)f * 2 + 1], conics[(size_t)f * 3], conics[(size_t)f * 3 + 1]);
+    rec[(size_t)i * 3 + 1] = make_float4(conics[(size_t)f * 3 + 2], opacities[gi], r, gg);
+    rec[(size_t)i * 3 + 2] = make_float4(b, depths[f], 0.f, 0.f);
+  }
+}
+
+__device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// One block per 16 x 16 pixel tile.  Warp 8 lane 0 is the producer: chunk k of the tile's records goes to stage k % 4 with
+// ONE bulk copy that completes on full[stage]; it reuses a stage once all 8 compositing warps have arrived on empty[stage].
+// A compositing warp owns 16 x 2 pixels, reads every record of a stage as a shared-memory broadcast, and keeps arriving
+// (without computing) once all of its pixels are saturated or outside the image, counting itself in s_done once.  When the
+// producer finds all 8 warps counted it publishes the index of the first chunk it will NOT load and completes that
+// stage's barrier without data: the warps wake, see the index and leave (at most 3 chunks later than the last useful one).
+__global__ void __launch_bounds__(RS_STREAM_THREADS)
+raster_stream_kernel(const float* __restrict__ rec, const unsigned* __restrict__ offsets, RasterGeom g, float* __restrict__ out_rgb,
+                     float* __restrict__ out_depth, float* __restrict__ out_alpha) {
+  __shared__ __align__(128) float s_rec[RS_STAGES][RS_CHUNK * RS_REC];
+  __shared__ __align__(8) uint64_t s_full[RS_STAGES], s_empty[RS_STAGES];
+  __shared__ unsigned s_done;
+  __shared__ int s_stop_at;
   const int cam = blockIdx.z, ty = blockIdx.y, tx = blockIdx.x;
   const unsigned tile = (unsigned)((cam * g.th + ty) * g.tw + tx);
-  const int i = ty * RS_TILE + threadIdx.y, j = tx * RS_TILE + threadIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < RS_STAGES; ++s) {
+      mbar_init(&s_full[s], 1);
+      mbar_init(&s_empty[s], RS_BLOCK / 32);
+    }
+    s_done = 0;
+    s_stop_at = -1;
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const unsigned start = offsets[tile], end = offsets[tile + 1];
+  const unsigned n = end - start;
+  const int nchunks = (int)((n + RS_CHUNK - 1) / RS_CHUNK);
+
+  if (warp == RS_BLOCK / 32) {
+    // ---------------------------------------------------------------- producer
+    if (lane == 0) {
+      for (int k = 0; k < nchunks; ++k) {
+        const int s = k % RS_STAGES;
+        if (k >= RS_STAGES) {
+          mbar_wait(&s_empty[s], ((k / RS_STAGES) - 1) & 1);
+          if (*reinterpret_cast<volatile unsigned*>(&s_done) >= RS_BLOCK / 32) {
+            *reinterpret_cast<volatile int*>(&s_stop_at) = k;
+            mbar_arrive(&s_full[s]);  // release: the index is visible to whoever wakes on this phase
+            break;
+          }
+        }
+        const uint32_t cnt = min((unsigned)RS_CHUNK, n - (unsigned)k * RS_CHUNK);
+        const uint32_t bytes = cnt * RS_REC * 4;
+        mbar_arrive_expect_tx(&s_full[s], bytes);
+        bulk_copy_g2s(s_rec[s], rec + ((size_t)start + (size_t)k * RS_CHUNK) * RS_REC, bytes, &s_full[s]);
+      }
+    }
+    return;
+  }
+
+  // ------------------------------------------------------------------ compositing warps
+  const int i = ty * RS_TILE + warp * 2 + (lane >> 4), j = tx * RS_TILE + (lane & 15);
   const float px = (float)j + 0.5f, py = (float)i + 0.5f;
   const bool inside = i < g.H && j < g.W;
   bool done = !inside;
-  const unsigned start = offsets[tile], end = offsets[tile + 1];
-  const unsigned tr = threadIdx.y * RS_TILE + threadIdx.x;
+  bool warp_done = __all_sync(0xffffffffu, done);
+  if (warp_done && lane == 0) atomicAdd(&s_done, 1u);
   float T = 1.0f, acc[4] = {0.f, 0.f, 0.f, 0.f};
-  const unsigned nb = (end - start + RS_BLOCK - 1) / RS_BLOCK;
-  for (unsigned b = 0; b < nb; ++b) {
-    if (__syncthreads_count(done) >= RS_BLOCK) break;
-    const unsigned bs = start + RS_BLOCK * b, idx = bs + tr;
-    if (idx < end) {
-      const unsigned f = flat_ids[idx];
-      const size_t gi = f % (unsigned)g.N;
-      s_xy[tr][0] = means2d[(size_t)f * 2], s_xy[tr][1] = means2d[(size_t)f * 2 + 1];
-      s_conic[tr][0] = conics[(size_t)f * 3], s_conic[tr][1] = conics[(size_t)f * 3 + 1], s_conic[tr][2] = conics[(size_t)f * 3 + 2];
-      s_op[tr] = opacities[gi];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) s_col[tr][k] = fmaxf(RS_C0 * sh[gi * 3 + k] + 0.5f, 0.f);
-      s_col[tr][3] = depths[f];
-    }
-    __syncthreads();
-    const unsigned n = min((unsigned)RS_BLOCK, end - bs);
-    for (unsigned t = 0; t < n && !done; ++t) {
-      const float dx = s_xy[t][0] - px, dy = s_xy[t][1] - py;
-      const float sigma = 0.5f * (s_conic[t][0] * dx * dx + s_conic[t][2] * dy * dy) + s_conic[t][1] * dx * dy;
-      const float alpha = fminf(0.999f, s_op[t] * __expf(-sigma));
-      if (sigma < 0.f || alpha < RS_ALPHA_MIN) continue;
-      const float next_T = T * (1.0f - alpha);
-      if (next_T <= 1e-4f) {
-        done = true;
-        break;
+  for (int k = 0; k < nchunks; ++k) {
+    const int s = k % RS_STAGES;
+    mbar_wait(&s_full[s], (k / RS_STAGES) & 1);
+    if (*reinterpret_cast<volatile int*>(&s_stop_at) == k) break;
+    if (!warp_done) {
+      const unsigned cnt = min((unsigned)RS_CHUNK, n - (unsigned)k * RS_CHUNK);
+      const float4* r4 = reinterpret_cast<const float4*>(s_rec[s]);
+      for (unsigned t = 0; t < cnt && !done; ++t) {
+        const float4 a = r4[3 * t], b = r4[3 * t + 1], c = r4[3 * t + 2];  // x y ca cb | cc op r g | b z
+        const float dx = a.x - px, dy = a.y - py;
+        const float sigma = 0.5f * (a.z * dx * dx + b.x * dy * dy) + a.w * dx * dy;
+        const float alpha = fminf(0.999f, b.y * __expf(-sigma));
+        if (sigma < 0.f || alpha < RS_ALPHA_MIN) continue;
+        const float next_T = T * (1.0f - alpha);
+        if (next_T <= 1e-4f) {
+          done = true;
+          break;
+        }
+        const float vis = alpha * T;
+        acc[0] += b.z * vis, acc[1] += b.w * vis, acc[2] += c.x * vis, acc[3] += c.y * vis;
+        T = next_T;
       }
-      const float vis = alpha * T;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) acc[k] += s_col[t][k] * vis;
-      T = next_T;
+      warp_done = __all_sync(0xffffffffu, done);
+      if (warp_done && lane == 0) atomicAdd(&s_done, 1u);
     }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&s_empty[s]);  // release: orders this warp's reads of the stage (and its s_done count) before the refill
   }
   if (inside) {
     const size_t pix = ((size_t)cam * g.H + i) * g.W + j;
@@ -264,7 +337,8 @@ wm_status raster_workspace_bytes(long long elems, long long n_isects, size_t* sc
   WM_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort, (const long long*)nullptr, (long long*)nullptr, (const unsigned*)nullptr,
                                           (unsigned*)nullptr, n, 0, 64, (cudaStream_t)0));
   *scan_bytes = rs_align(scan);
-  *render_bytes = 2 * rs_align((size_t)n * 8) + 2 * rs_align((size_t)n * 4) + rs_align(sort);
+  // keys in / out, values in / out, CUB's sort storage, and the packed records of the streamed compositing pass
+  *render_bytes = 2 * rs_align((size_t)n * 8) + 2 * rs_align((size_t)n * 4) + rs_align(sort) + rs_align((size_t)n * RS_REC * 4);
   return WM_OK;
 }
 
@@ -292,7 +366,9 @@ wm_status raster_render(cudaStream_t st, const float* means2d, const float* coni
   unsigned* vals_in = reinterpret_cast<unsigned*>(p + 2 * rs_align(nn * 8));
   unsigned* vals_out = reinterpret_cast<unsigned*>(p + 2 * rs_align(nn * 8) + rs_align(nn * 4));
   void* sort_tmp = p + 2 * rs_align(nn * 8) + 2 * rs_align(nn * 4);
-  size_t sort_bytes = workspace_bytes - (2 * rs_align(nn * 8) + 2 * rs_align(nn * 4));
+  const size_t rec_bytes = rs_align(nn * RS_REC * 4);
+  size_t sort_bytes = need - (2 * rs_align(nn * 8) + 2 * rs_align(nn * 4)) - rec_bytes;
+  float* rec = reinterpret_cast<float*>(p + need - rec_bytes);
   if (n == 0) {
     raster_fill_kernel<<<(n_tiles + 256) / 256, 256, 0, st>>>(offsets, n_tiles + 1, 0u);
   } else {
@@ -306,8 +382,12 @@ wm_status raster_render(cudaStream_t st, const float* means2d, const float* coni
     raster_offsets_kernel<<<g2, 256, 0, st>>>(keys_out, n, tile_bits, g.tw * g.th, n_tiles, offsets);
   }
   WM_LAUNCH_CHECK();
-  raster_pixels_kernel<<<dim3(g.tw, g.th, C), dim3(RS_TILE, RS_TILE), 0, st>>>(means2d, conics, depths, opacities, sh, offsets, vals_out, g,
-                                                                               out_rgb, out_depth, out_alpha);
+  if (n > 0) {
+    const int g3 = (int)std::min<size_t>(((size_t)n + 255) / 256, 148 * 16);
+    raster_pack_kernel<<<g3, 256, 0, st>>>(means2d, conics, depths, opacities, sh, vals_out, n, (unsigned)N, reinterpret_cast<float4*>(rec));
+    WM_LAUNCH_CHECK();
+  }
+  raster_stream_kernel<<<dim3(g.tw, g.th, C), dim3(RS_STREAM_THREADS), 0, st>>>(rec, offsets, g, out_rgb, out_depth, out_alpha);
   WM_LAUNCH_CHECK();
   return WM_OK;
 }

@@ -4,7 +4,8 @@
 The reference hands its splats to gsplat 1.5.3 (`rasterization(..., packed=True, rasterize_mode="classic",
 render_mode="RGB+ED", sh_degree=0)`); inside `WorldMirror.forward` the images are then dropped
 (rasterization.py:221-246), so `B200GaussianSplatRenderer.render` does not call this; it serves the novel-view / video
-rendering callers (`infer.py:264`).  csrc/raster.cu restates gsplat's projection, tile binning and compositing kernels.
+rendering callers (`infer.py:264`).  csrc/raster.cu restates gsplat's projection and tile binning; compositing follows gsplat's
+arithmetic but streams packed per-intersection records through shared memory with bulk asynchronous copies.
 There is no CPU path."""
 from __future__ import annotations
 
