@@ -1,6 +1,6 @@
 """Cost of the device-side attention guard (AttnGuard) at the DINOv2 / frame shape: the bounded-logit kernel alone, the
 running-max kernel alone, and the guarded pair of launches when the data fits / does not fit the bound.
-    python tools/bench_guard.py [views] [L]"""
+    python tools/bench_guard.py [views] [L] [only cases whose name contains this]"""
 import importlib
 import os
 import sys
@@ -34,7 +34,10 @@ def main():
         "guarded (12, 7) two launches, does not fit": lambda: lib.wm_flash_attn_guarded(st, *a, 12, 7, ws.data_ptr(), need, big.data_ptr(), 80.0),
     }
     flops = 4.0 * n * H * L * L * 64
+    only = sys.argv[3] if len(sys.argv) > 3 else ""
     for name, fn in cases.items():
+        if only not in name:
+            continue
         for _ in range(5):
             capi.check(fn())
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
