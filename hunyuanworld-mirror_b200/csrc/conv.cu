@@ -255,6 +255,25 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const bool valid = y < g.H && x < g.W;
       const size_t pix = ((size_t)img * g.H + y) * g.W + x;
       const uint32_t acc = tcount & 1, aph = (tcount >> 1) & 1;
+      // Residual maps (the skip inputs of a ResidualConvUnit / fusion block) are read by this thread for its own pixel, 64 bytes
+      // per map and 32-channel group.  The loads of group g + 1 are issued before group g is processed, and those of group 0
+      // before the accumulator is even complete, so their DRAM / L2 latency hides under the main loop and the previous
+      // group's arithmetic instead of stalling every group (with two residual maps the 148 x 148 convolution took 228 us
+      // against 160 us without: profiles/r02_heads_launches.csv).
+      uint4 rbuf[2][2][4];
+      auto issue_residuals = [&](int grp, uint4 (&dst)[2][4]) {
+        if constexpr (STORE) {
+#pragma unroll
+          for (int rsel = 0; rsel < 2; ++rsel) {
+            const __half* rp = rsel == 0 ? (g.res1_bcast ? nullptr : static_cast<const __half*>(g.res1)) : g.res2;
+            if (rp == nullptr || !valid) continue;
+            const uint4* r4 = reinterpret_cast<const uint4*>(rp + pix * g.Cout + n0 + grp * 32);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[rsel][i] = __ldg(r4 + i);
+          }
+        }
+      };
+      issue_residuals(0, rbuf[0]);
       mbar_wait(&tfull[acc], aph);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + acc * NT + lane_base;
@@ -344,8 +363,9 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (j < g.od) pr[j] = __uint_as_float(d2[j]) + __ldg(g.b2 + j);
         }
       } else {
-#pragma unroll 1
+#pragma unroll 2
         for (int grp = 0; grp < NT / 32; ++grp) {
+          if (grp + 1 < NT / 32) issue_residuals(grp + 1, rbuf[(grp + 1) & 1]);
           float xv[32];
           {
             uint32_t v0[32];
@@ -385,10 +405,9 @@ conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             for (int rsel = 0; rsel < 2; ++rsel) {
               const __half* rp = rsel == 0 ? (g.res1_bcast ? nullptr : static_cast<const __half*>(g.res1)) : g.res2;
               if (rp == nullptr) continue;
-              const uint4* r4 = reinterpret_cast<const uint4*>(rp + pix * g.Cout + col0);
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                const uint4 r = __ldg(r4 + i);
+                const uint4 r = rbuf[grp & 1][rsel][i];  // loaded one group ahead (issue_residuals)
                 const uint32_t u[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
