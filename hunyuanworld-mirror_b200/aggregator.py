@@ -206,8 +206,13 @@ class B200VisualGeometryTransformer(torch.nn.Module):
             nbytes = capi.lib().wm_workspace_bytes(self._handle, n, H, W, self.world)
             if nbytes == 0:
                 raise ValueError(f"invalid geometry n_views={n} H={H} W={W}")
-            self._workspace.clear()  # one live shape at a time keeps peak memory bounded
-            ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            # one buffer, as large as the largest shape seen so far: a smaller shape carves its workspace out of it, so
+            # callers that alternate between shapes do not re-allocate, and peak memory stays bounded by the largest one
+            big = next((t for t in self._workspace.values() if t.device == device and t.numel() >= nbytes), None)
+            if big is None:
+                self._workspace.clear()
+                big = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            ws = big
             self._workspace[key] = ws
         return ws
 

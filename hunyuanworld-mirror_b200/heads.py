@@ -183,7 +183,9 @@ class B200DPTHead(torch.nn.Module):
                 full = torch.cat([pu[None].expand(gh, -1, -1), pv[:, None].expand(-1, gw, -1)], dim=-1)
                 tabs.append(full.to(self._dev).contiguous())
             pu, pv = uv_tables(W, H, 128, W / H)
-            self._pos = {key: (tabs, pu.to(self._dev), pv.to(self._dev))}  # one live geometry
+            if len(self._pos) >= 4:  # a few live geometries (tables of one geometry: ~14 MB at 518 x 518): callers that alternate
+                self._pos.pop(next(iter(self._pos)))  # between shapes do not rebuild them every call; the oldest one goes
+            self._pos[key] = (tabs, pu.to(self._dev), pv.to(self._dev))
         return self._pos[key]
 
     # ------------------------------------------------------------------ ops

@@ -600,3 +600,19 @@ def test_device_side_attention_guard(vb, vg):
     og_bits, o_bits = og.view(torch.int16), o.view(torch.int16)
     ok_rows = ~torch.isnan(og.float()).any(dim=1)
     assert torch.equal(o_bits[ok_rows], og_bits[ok_rows]) and int(ok_rows.sum()) >= T - 1 - P
+
+
+def test_alternating_shapes_share_one_workspace(model_full):
+    """A caller that alternates between shapes must not re-allocate (or disturb) the workspace: the smaller shape carves its
+    buffers out of the larger one's allocation, and going back and forth reproduces the first results bit for bit."""
+    big = W.synthetic_images(3, 98, 126, seed=21).cuda()
+    small = W.synthetic_images(2, 70, 98, seed=22).cuda()
+    a1 = [t.clone() for t in model_full(big)[0]]
+    b1 = [t.clone() for t in model_full(small)[0]]
+    ptrs = {t.data_ptr() for t in model_full._workspace.values()}
+    assert len(ptrs) == 1 and len(model_full._workspace) >= 2
+    a2 = [t.clone() for t in model_full(big)[0]]
+    b2 = [t.clone() for t in model_full(small)[0]]
+    assert {t.data_ptr() for t in model_full._workspace.values()} == ptrs
+    for x, y in zip(a1 + b1, a2 + b2):
+        assert torch.equal(x, y)
