@@ -982,7 +982,9 @@ class B200WorldMirror(torch.nn.Module):
             if not late_chain:
                 preds = splat_chain(preds)
         used = []
-        for i, (name, head) in enumerate((("depth", self.depth_head), ("pts3d", self.pts_head), ("normals", self.norm_head))):
+        # The depth head goes LAST: whatever the last head produces is copied to the host with nothing left to hide the copy
+        # behind, and depth + confidence are half the bytes of points or normals (17 against 34 MB for 8 views of 518 x 518).
+        for i, (name, head) in enumerate((("pts3d", self.pts_head), ("normals", self.norm_head), ("depth", self.depth_head))):
             if head is not None and name not in preds:
                 if self.head_streams:
                     # the three heads are independent and their low-resolution stages launch fewer CTAs than there are
@@ -1036,4 +1038,7 @@ class B200WorldMirror(torch.nn.Module):
             if n_sat:
                 raise Fp16RangeError(f"{n_sat} (pixel, 32-channel) entries of the DPT heads' fp16 maps left the fp16 range "
                                      f"in {'this' if sat_now else 'the previous'} forward: the predictions are not valid")
+        # the order in which the reference fills its dictionary (worldmirror.py:161-217), whatever order the heads ran in
+        first = ("camera_params", "camera_poses", "camera_intrs", "depth", "depth_conf", "pts3d", "pts3d_conf", "normals", "normals_conf")
+        preds = {**{k: preds[k] for k in first if k in preds}, **{k: v for k, v in preds.items() if k not in first}}
         return preds
