@@ -1,6 +1,6 @@
 """Static evidence from the built library, no GPU needed: per kernel the registers / stack / static shared memory
 (`cuobjdump -res-usage`) and the count of the SASS instructions that prove the Blackwell paths — UTCHMMA / UTCQMMA
-(tcgen05.mma), UTMALDG / UTMASTG / UTMAREDG (TMA load / store / reduce-add), UTCBAR (tcgen05.commit), LDTM / STTM (tcgen05.ld /
+(tcgen05.mma), UTMALDG / UTMASTG / UTMAREDG (TMA load / store / reduce-add), UBLKCP (cp.async.bulk, non-tensor), UTCBAR (tcgen05.commit), LDTM / STTM (tcgen05.ld /
 st), SYNCS (mbarrier) — from `cuobjdump -sass`.  Usage: python tools/sass_summary.py > profiles/rNN_sass_summary.txt"""
 import collections
 import os
@@ -10,7 +10,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "hunyuanworld-mirror_b200", "lib", "libwm_b200.so")
-MNEMONICS = ("UTCHMMA", "UTCQMMA", "UTMALDG", "UTMASTG", "UTMAREDG", "UTCBAR", "LDTM", "STTM", "SYNCS", "MUFU.EX2", "HMMA", "STL", "LDL")
+MNEMONICS = ("UTCHMMA", "UTCQMMA", "UTMALDG", "UTMASTG", "UTMAREDG", "UBLKCP", "UTCBAR", "LDTM", "STTM", "SYNCS", "MUFU.EX2", "HMMA", "STL", "LDL")
 
 
 def demangle(names):
