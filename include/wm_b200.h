@@ -363,8 +363,11 @@ wm_status wm_conf_filter_splats(wm_stream stream, long long N, long long K, cons
  *   wm_raster_project: per (camera, gaussian) 2D mean, conic, depth, integer radii (0 = culled), tile count, and the
  *     inclusive scan `cum` of the tile counts (cum[C*N - 1] = number of intersections); quats are (w, x, y, z);
  *     viewmats [C, 4, 4] world-to-camera row major, Ks [C, 3, 3];
- *   wm_raster_workspace_bytes: scratch sizes for the scan (first call) and for sort + binning (second call);
- *   wm_raster_render: emit (image | tile | depth) keys, stable radix sort, tile offsets, front-to-back compositing;
+ *   wm_raster_workspace_bytes: scratch sizes for the scan (first call) and for sort + binning + the packed 48-byte
+ *     per-intersection records of the compositing pass (second call);
+ *   wm_raster_render: emit (image | tile | depth) keys, stable radix sort, tile offsets, one packed record per sorted
+ *     intersection, then front-to-back compositing that streams each tile's contiguous run of records through shared
+ *     memory with bulk asynchronous copies (gsplat's arithmetic, csrc/RasterizeToPixels3DGSFwd.cu:104-185; its own layout);
  *     sh [N, 3] degree-0 coefficients (colour = max(C0 sh + 0.5, 0)); offsets: scratch of C * tiles + 1 words;
  *     out_rgb [C, H, W, 3], out_depth [C, H, W] = expected depth, out_alpha [C, H, W]. */
 wm_status wm_raster_project(wm_stream stream, const float* means, const float* quats, const float* scales, const float* opacities,
