@@ -61,6 +61,20 @@ def test_argument_validation_needs_no_gpu():
     assert n8 > T * 1024 * (4 + 4 + 2 + 2 + 4 + 2 + 8) * 0.99 and n8w - n8 == 7 * T * 2048 * 2
 
 
+@pytest.mark.skipif(torch.cuda.is_available(), reason="CPU-only behaviour")
+def test_round2_entry_points_refuse_without_a_gpu():
+    """The entry points added in round 2 (the no-allocation image loader, the device-side attention choice) load, report their
+    constants and refuse to compute on a machine without a B200 -- no silent fallback."""
+    lib = capi.lib()
+    assert lib.wm_load_image_static_bytes() == 8 << 20
+    buf = (C.c_float * 64)()
+    assert lib.wm_load_image_static(None, buf, 4, 4, 2, 2, 0, 2, 2, 2, 0, 0, buf) == capi.WM_ERR_ARCH
+    assert lib.wm_flash_attn_guarded(None, buf, 1024, buf, buf, 2048, buf, 1024, 1, 128, 128, 16, 10, 4, None, 0, buf, 80.0) == capi.WM_ERR_ARCH
+    assert lib.wm_flash_attn_guarded(None, buf, 1024, buf, buf, 2048, buf, 1024, 1, 128, 128, 8, 10, 4, None, 0, buf, 80.0) == capi.WM_ERR_INVALID
+    assert lib.wm_gemm_qkv_guard(None, buf, buf, buf, None, None, None, None, 1e-5, None, None, 1, 0, 1, 1.0, 128, buf, buf, None) == capi.WM_ERR_INVALID
+    assert lib.wm_guard_words(None, 0, buf) == capi.WM_ERR_INVALID
+
+
 def test_rope_tables_match_oracle():
     lib = capi.lib()
     n = 38
